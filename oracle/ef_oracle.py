@@ -1,0 +1,401 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU restatement of the reference EF_layers path.
+
+A functional, dependency-free (torch + numpy on CPU) restatement of the algorithm
+in the reference's model/EF_layers.py and its caller model/Embedding.py.  It
+travels with the repo (the reference itself does not exist on the GPU box) and is
+the checker for the CUDA path and the ``cpu_baseline`` leg of bench.py.  Only
+tests/, __graft_entry__.smoke() and bench.py may import it; the product package
+singa_b200/ never does.
+
+Pinning: tests/test_oracle_pinned.py checks every function here against the
+UNMODIFIED reference run through oracle/ref_loader.py in the build container
+(where /root/reference exists) and, everywhere, against the golden vectors in
+tests/golden/ that oracle/make_golden.py produced from that reference.  The S2
+grid normalisation constants inherit the "parity unpinned" status of the e3nn
+shim (see ref_loader.py header).
+
+Parameters are passed as a flat dict keyed by the reference's own state_dict
+names, so a reference state_dict drops in unchanged.  The op
+sequence deliberately keeps the reference's dense formulation (dense [E,L,L]
+Wigner bmm, one-hot permutation einsum, index_add_) so that timing this file is a
+fair stand-in for timing the reference on CPU.
+
+All constants come from oracle-local code (no import from singa_b200).
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+
+# ---------------------------------------------------------------------------
+# constant tables
+# ---------------------------------------------------------------------------
+class Tables:
+    """Index tables of CoefficientMappingModule (EF_layers.py:1421-1549) for one
+    resolution, plus the grid matrices of SO3_Grid (EF_layers.py:539-601)."""
+
+    def __init__(self, lmax: int, mmax: int, jd, to_grid=None, from_grid=None,
+                 to_grid_full=None, from_grid_full=None):
+        self.lmax, self.mmax = lmax, mmax
+        self.L = (lmax + 1) ** 2
+        l_h, m_c = [], []
+        for l in range(lmax + 1):
+            mm = min(mmax, l)
+            for m in range(-mm, mm + 1):
+                l_h.append(l)
+                m_c.append(m)
+        self.l_harmonic = torch.tensor(l_h)
+        self.m_complex = torch.tensor(m_c)
+        self.M = len(l_h)
+        # to_m one-hot (EF_layers.py:1457-1474)
+        rows = []
+        self.m_size = []
+        for m in range(mmax + 1):
+            r = [j for j in range(self.M) if m_c[j] == m]
+            rows += r
+            self.m_size.append(len(r))
+            if m:
+                rows += [j for j in range(self.M) if m_c[j] == -m]
+        self.to_m = torch.zeros(self.M, self.M)
+        for out_i, in_i in enumerate(rows):
+            self.to_m[out_i, in_i] = 1.0
+        # coefficient_idx(lmax, mmax) on the full-m mapping (EF_layers.py:1514-1526)
+        self.keep = torch.tensor([l * l + l + m for l, m in zip(l_h, m_c)])
+        # get_rotate_inv_rescale (EF_layers.py:1530-1549)
+        resc = torch.ones(1, self.L, self.L)
+        for l in range(lmax + 1):
+            if l > mmax:
+                resc[:, l * l:(l + 1) ** 2, l * l:(l + 1) ** 2] = math.sqrt((2 * l + 1) / (2 * mmax + 1))
+        self.rotate_inv_rescale = resc[:, :, self.keep]
+        self.expand_index = torch.tensor([l for l in range(lmax + 1) for _ in range(2 * l + 1)])
+        self.jd = [torch.as_tensor(j, dtype=torch.float64) for j in jd]
+        self.to_grid, self.from_grid = to_grid, from_grid                 # (lmax, mmax) grid, [b,a,M]
+        self.to_grid_full, self.from_grid_full = to_grid_full, from_grid_full  # (lmax, lmax) grid, [b,a,L]
+
+
+# ---------------------------------------------------------------------------
+# edge frame and Wigner-D
+# ---------------------------------------------------------------------------
+def edge_rot_mat(edge_vec: torch.Tensor, rand: torch.Tensor) -> torch.Tensor:
+    """init_edge_rot_mat (EF_layers.py:2286-2351) with the uniform [0,1) draw
+    ``rand`` (same shape as edge_vec) supplied by the caller."""
+    d = torch.sqrt(torch.sum(edge_vec ** 2, dim=1))
+    nx = edge_vec / d.view(-1, 1)
+    v2 = rand - 0.5
+    v2 = v2 / torch.sqrt(torch.sum(v2 ** 2, dim=1)).view(-1, 1)
+    v2b = v2.clone()
+    v2b[:, 0] = -v2[:, 1]
+    v2b[:, 1] = v2[:, 0]
+    v2c = v2.clone()
+    v2c[:, 1] = -v2[:, 2]
+    v2c[:, 2] = v2[:, 1]
+    dot_b = torch.abs(torch.sum(v2b * nx, dim=1)).view(-1, 1)
+    dot_c = torch.abs(torch.sum(v2c * nx, dim=1)).view(-1, 1)
+    dot = torch.abs(torch.sum(v2 * nx, dim=1)).view(-1, 1)
+    v2 = torch.where(dot > dot_b, v2b, v2)
+    dot = torch.abs(torch.sum(v2 * nx, dim=1)).view(-1, 1)
+    v2 = torch.where(dot > dot_c, v2c, v2)
+    dot = torch.abs(torch.sum(v2 * nx, dim=1))
+    assert torch.max(dot) < 0.99
+    nz = torch.cross(nx, v2, dim=1)
+    nz = nz / torch.sqrt(torch.sum(nz ** 2, dim=1, keepdim=True))
+    nz = nz / torch.sqrt(torch.sum(nz ** 2, dim=1)).view(-1, 1)
+    ny = torch.cross(nx, nz, dim=1)
+    ny = ny / torch.sqrt(torch.sum(ny ** 2, dim=1, keepdim=True))
+    inv = torch.cat([nz.view(-1, 3, 1), nx.view(-1, 3, 1), -ny.view(-1, 3, 1)], dim=2)
+    return inv.transpose(1, 2).contiguous()
+
+
+def euler_angles(rot: torch.Tensor):
+    """(alpha, beta, gamma) of RotationToWignerDMatrix (EF_layers.py:509-517)."""
+    x = rot @ rot.new_tensor([0.0, 1.0, 0.0])
+    xn = F.normalize(x, p=2, dim=-1).clamp(-1, 1)
+    beta = torch.acos(xn[..., 1])
+    alpha = torch.atan2(xn[..., 0], xn[..., 2])
+    ca, sa, cb, sb = alpha.cos(), alpha.sin(), beta.cos(), beta.sin()
+    o, z = torch.ones_like(alpha), torch.zeros_like(alpha)
+    Ry = torch.stack([torch.stack([ca, z, sa], -1), torch.stack([z, o, z], -1), torch.stack([-sa, z, ca], -1)], -2)
+    Rx = torch.stack([torch.stack([o, z, z], -1), torch.stack([z, cb, -sb], -1), torch.stack([z, sb, cb], -1)], -2)
+    R = (Ry @ Rx).transpose(-1, -2) @ rot  # angles_to_matrix(alpha, beta, 0)^T @ rot
+    gamma = torch.atan2(R[..., 0, 2], R[..., 0, 0])
+    return alpha, beta, gamma
+
+
+def _z_rot(angle: torch.Tensor, l: int) -> torch.Tensor:
+    """_z_rot_mat (EF_layers.py:2220-2229)."""
+    n = 2 * l + 1
+    M = angle.new_zeros(angle.shape + (n, n))
+    idx = torch.arange(n)
+    freq = torch.arange(l, -l - 1, -1, dtype=angle.dtype)
+    M[..., idx, n - 1 - idx] = torch.sin(freq * angle[..., None])
+    M[..., idx, idx] = torch.cos(freq * angle[..., None])
+    return M
+
+
+def wigner_dense(rot: torch.Tensor, t: Tables) -> torch.Tensor:
+    """Dense block-diagonal [E, L, L] Wigner matrix (EF_layers.py:508-528, 2207-2217)."""
+    a, b, c = euler_angles(rot)
+    W = torch.zeros(len(a), t.L, t.L, dtype=rot.dtype)
+    for l in range(t.lmax + 1):
+        J = t.jd[l].to(rot.dtype)
+        blk = _z_rot(a, l) @ J @ _z_rot(b, l) @ J @ _z_rot(c, l)
+        W[:, l * l:(l + 1) ** 2, l * l:(l + 1) ** 2] = blk
+    return W
+
+
+def rotate(W, x, t: Tables):
+    """SO3_Rotation.rotate (EF_layers.py:494-497): [E,L,C] -> [E,M,C]."""
+    return torch.bmm(W[:, t.keep, :], x)
+
+
+def rotate_inv(W, x, t: Tables):
+    """SO3_Rotation.rotate_inv (EF_layers.py:500-505): [E,M,C] -> [E,L,C]."""
+    Winv = W.transpose(1, 2).contiguous()[:, :, t.keep] * t.rotate_inv_rescale.to(W.dtype)
+    return torch.bmm(Winv, x)
+
+
+# ---------------------------------------------------------------------------
+# small modules
+# ---------------------------------------------------------------------------
+def gaussian_smearing(dist, start, stop, num, width_scalar):
+    """GaussianSmearing (EF_layers.py:1777-1794)."""
+    offset = torch.linspace(start, stop, num)
+    coeff = -0.5 / (width_scalar * (offset[1] - offset[0])).item() ** 2
+    return torch.exp(coeff * (dist.view(-1, 1) - offset.to(dist.dtype).view(1, -1)) ** 2)
+
+
+def radial_function(p, pre, x):
+    """RadialFunction (EF_layers.py:1634-1657): Linear,(LN,SiLU) x2, Linear; keys net.{0,1,3,4,6}."""
+    i = 0
+    while f"{pre}net.{i}.weight" in p:
+        w, b = p[f"{pre}net.{i}.weight"], p[f"{pre}net.{i}.bias"]
+        if w.dim() == 2:
+            x = F.linear(x, w, b)
+            i += 1
+        else:
+            x = F.silu(F.layer_norm(x, (w.shape[0],), w, b))
+            i += 2
+    return x
+
+
+def smooth_leaky_relu(x, slope=0.2):
+    """SmoothLeakyReLU (EF_layers.py:1669-1677)."""
+    return ((1 + slope) / 2) * x + ((1 - slope) / 2) * x * (2 * torch.sigmoid(x) - 1)
+
+
+def rms_norm_sh(p, pre, x, t: Tables, eps=1e-5):
+    """EquivariantRMSNormArraySphericalHarmonicsV2 as configured through
+    get_normalization_layer (EF_layers.py:2099-2192, 2273): centring on,
+    std_balance_degrees on, 'component', affine."""
+    C = x.shape[2]
+    x0 = x[:, 0:1, :]
+    feat = torch.cat((x0 - x0.mean(dim=2, keepdim=True), x[:, 1:, :]), dim=1)
+    bal = torch.tensor([1.0 / (2 * l + 1) / (t.lmax + 1) for l in t.expand_index.tolist()], dtype=x.dtype).view(-1, 1)
+    nrm = torch.einsum("nic,ia->nac", feat.pow(2), bal).mean(dim=2, keepdim=True)
+    nrm = (nrm + eps).pow(-0.5)
+    w = p[f"{pre}affine_weight"].view(1, t.lmax + 1, C)[:, t.expand_index, :]
+    out = feat * (nrm * w)
+    out = torch.cat((out[:, 0:1, :] + p[f"{pre}affine_bias"].view(1, 1, C), out[:, 1:, :]), dim=1)
+    return out
+
+
+def so3_linear(p, pre, x, t: Tables):
+    """SO3_LinearV2 (EF_layers.py:655-671)."""
+    w = p[f"{pre}weight"][t.expand_index]
+    out = torch.einsum("bmi,moi->bmo", x, w)
+    return torch.cat((out[:, 0:1, :] + p[f"{pre}bias"].view(1, 1, -1), out[:, 1:, :]), dim=1)
+
+
+def s2_activation(x, to_grid, from_grid):
+    """S2Activation (EF_layers.py:1746-1754)."""
+    g = torch.einsum("bai,zic->zbac", to_grid, x)
+    return torch.einsum("bai,zbac->zic", from_grid, F.silu(g))
+
+
+def separable_s2_activation(scalars, x, to_grid, from_grid):
+    """SeparableS2Activation (EF_layers.py:1765-1773)."""
+    out = s2_activation(x, to_grid, from_grid)
+    return torch.cat((F.silu(scalars).unsqueeze(1), out[:, 1:, :]), dim=1)
+
+
+def so2_convolution(p, pre, x, x_edge, t: Tables, m_out: int, extra: int):
+    """SO2_Convolution.forward + SO2_m_Convolution.forward (EF_layers.py:807-875, 721-729).
+    x: [E, M, Cin] l-primary; returns ([E, M, m_out] l-primary, extra [E, extra] or None)."""
+    E = x.shape[0]
+    x = torch.einsum("nac,ba->nbc", x, t.to_m.to(x.dtype))
+    rad = radial_function(p, f"{pre}rad_func.", x_edge) if f"{pre}rad_func.net.0.weight" in p else None
+    w0, b0 = p[f"{pre}fc_m0.weight"], p[f"{pre}fc_m0.bias"]
+    x0 = x[:, :t.m_size[0]].reshape(E, -1)
+    off_rad = 0
+    if rad is not None:
+        x0 = x0 * rad[:, :w0.shape[1]]
+    off_rad += w0.shape[1]
+    y0 = F.linear(x0, w0, b0)
+    x_extra = None
+    if extra:
+        x_extra, y0 = y0[:, :extra], y0[:, extra:]
+    outs = [y0.reshape(E, -1, m_out)]
+    off = t.m_size[0]
+    for m in range(1, t.mmax + 1):
+        w = p[f"{pre}so2_m_conv.{m - 1}.fc.weight"]
+        xm = x[:, off:off + 2 * t.m_size[m]].reshape(E, 2, -1)
+        if rad is not None:
+            xm = xm * rad[:, off_rad:off_rad + w.shape[1]].reshape(E, 1, -1)
+        ym = F.linear(xm, w)
+        half = w.shape[0] // 2
+        yr, yi = ym[:, :, :half], ym[:, :, half:]
+        re = yr[:, 0:1] - yi[:, 1:2]
+        im = yr[:, 1:2] + yi[:, 0:1]
+        outs.append(torch.cat((re, im), dim=1).reshape(E, -1, m_out))
+        off += 2 * t.m_size[m]
+        off_rad += w.shape[1]
+    out = torch.cat(outs, dim=1)
+    out = torch.einsum("nac,ab->nbc", out, t.to_m.to(x.dtype))
+    return out, x_extra
+
+
+def segment_softmax(src, index, num_nodes=None):
+    """torch_geometric.utils.softmax 2.3.1 (EF_layers.py:1180)."""
+    n = int(index.max()) + 1 if num_nodes is None else num_nodes
+    idx = index.view(-1, 1).expand_as(src)
+    mx = torch.full((n, src.shape[1]), float("-inf"), dtype=src.dtype).scatter_reduce(
+        0, idx, src.detach(), "amax", include_self=True)
+    e = (src - mx.gather(0, idx)).exp()
+    den = torch.zeros((n, src.shape[1]), dtype=src.dtype).scatter_add(0, idx, e) + 1e-16
+    return e / den.gather(0, idx)
+
+
+# ---------------------------------------------------------------------------
+# the message-passing core
+# ---------------------------------------------------------------------------
+def graph_attention(p, pre, x_src, x_dst, x_edge, edge_index, W, t: Tables, heads: int,
+                    alpha_ch: int, value_ch: int, hidden: int, return_parts: bool = False):
+    """SO2EquivariantGraphAttention.forward (EF_layers.py:1079-1204), config path:
+    use_atom_edge_embedding False inside blocks, sep S2 act, attn renorm, no dropout."""
+    E = edge_index.shape[1]
+    msg = torch.cat((x_src[edge_index[0]], x_dst[edge_index[1]]), dim=2)      # [E, L, 2C]
+    msg = rotate(W, msg, t)                                                  # [E, M, 2C]
+    extra = heads * alpha_ch + hidden
+    msg, x0_extra = so2_convolution(p, f"{pre}so2_conv_1.", msg, x_edge, t, hidden, extra)
+    x0_alpha, x0_gate = x0_extra[:, :heads * alpha_ch], x0_extra[:, heads * alpha_ch:]
+    msg = separable_s2_activation(x0_gate, msg, t.to_grid, t.from_grid)
+    msg, _ = so2_convolution(p, f"{pre}so2_conv_2.", msg, x_edge, t, heads * value_ch, 0)
+    a = x0_alpha.reshape(-1, heads, alpha_ch)
+    a = F.layer_norm(a, (alpha_ch,), p[f"{pre}alpha_norm.weight"], p[f"{pre}alpha_norm.bias"])
+    a = smooth_leaky_relu(a)
+    logits = torch.einsum("bik,ik->bi", a, p[f"{pre}alpha_dot"])
+    alpha = segment_softmax(logits, edge_index[1])
+    attn = msg.reshape(E, t.M, heads, value_ch) * alpha.reshape(E, 1, heads, 1)
+    attn = attn.reshape(E, t.M, heads * value_ch)
+    out_e = rotate_inv(W, attn, t)                                           # [E, L, heads*value]
+    agg = torch.zeros(x_dst.shape[0], t.L, heads * value_ch, dtype=x_dst.dtype).index_add_(0, edge_index[1], out_e)
+    out = so3_linear(p, f"{pre}proj.", agg, t)
+    if return_parts:
+        return out, dict(logits=logits, alpha=alpha, agg=agg)
+    return out
+
+
+def feed_forward(p, pre, x, t: Tables):
+    """FeedForwardNetwork.forward (EF_layers.py:234-270), sep-S2 path on the (lmax,lmax) grid."""
+    gate = F.linear(x[:, 0, :], p[f"{pre}gating_linear.weight"], p[f"{pre}gating_linear.bias"])
+    h = so3_linear(p, f"{pre}so3_linear_1.", x, t)
+    h = separable_s2_activation(gate, h, t.to_grid_full, t.from_grid_full)
+    return so3_linear(p, f"{pre}so3_linear_2.", h, t)
+
+
+def trans_block(p, pre, x_src, x_dst, x_edge, edge_index, W, t, hp):
+    """TransBlockV2.forward (EF_layers.py:1338-1410).  Takes source / target node
+    tensors; for the homogeneous case pass the same tensor twice.  Returns
+    (block output for the target nodes, norm_1(x_src), norm_1(x_dst)) -- the last
+    two are what the reference leaves behind in the mutated x dict (1356-1357)."""
+    same = x_src is x_dst
+    res = x_dst
+    n_dst = rms_norm_sh(p, f"{pre}norm_1.", x_dst, t)
+    n_src = n_dst if same else rms_norm_sh(p, f"{pre}norm_1.", x_src, t)
+    y = graph_attention(p, f"{pre}ga.", n_src, n_dst, x_edge, edge_index, W, t,
+                        hp["num_heads"], hp["attn_alpha_channels"], hp["attn_value_channels"],
+                        hp["attn_hidden_channels"])
+    y = y + res
+    res = y
+    y = feed_forward(p, f"{pre}ffn.", rms_norm_sh(p, f"{pre}norm_2.", y, t), t)
+    return y + res, n_src, n_dst
+
+
+def edge_degree_embedding(p, pre, x_edge, edge_index, W, t: Tables, channels: int, n_target: int,
+                          rescale_factor: float):
+    """EdgeDegreeEmbedding.forward (EF_layers.py:86-149), use_atom_edge_embedding False."""
+    E = x_edge.shape[0]
+    m0 = radial_function(p, f"{pre}rad_func.", x_edge).reshape(E, t.m_size[0], channels)
+    xm = torch.cat((m0, torch.zeros(E, t.M - t.m_size[0], channels, dtype=m0.dtype)), dim=1)
+    xl = torch.einsum("nac,ab->nbc", xm, t.to_m.to(m0.dtype))
+    out_e = rotate_inv(W, xl, t)
+    agg = torch.zeros(n_target, t.L, channels, dtype=m0.dtype).index_add_(0, edge_index[1], out_e)
+    return agg / rescale_factor
+
+
+# ---------------------------------------------------------------------------
+# the caller: EquivariantEmbedding.forward (Embedding.py:205-480)
+# ---------------------------------------------------------------------------
+_AVG_DEGREE = 23.395238876342773  # Embedding.py:36
+
+
+def node_bits(x_feat: torch.Tensor) -> torch.Tensor:
+    """Embedding.py:250-253: last 15 feature columns, cast to long, read as a bit string."""
+    bits = x_feat[:, -15:].to(torch.long)
+    weights = 2 ** torch.arange(14, -1, -1, dtype=torch.long)
+    return (bits * weights).sum(dim=1)
+
+
+def embedding_forward(p, graph: dict, frames: dict, t: Tables, hp: dict, compute_dead_blocks: bool = True):
+    """graph: dict(z_p, z_l, x_p, x_l, pos_p, pos_l, ei_pp, ei_ll, ei_lp, ei_pl) (CPU tensors);
+    frames: dict(pp, ll, lp) of [E,3,3] edge_rot_mat (pass 4 reuses lp, Embedding.py:437-471).
+    Returns dict(protein_atoms, ligand_atoms, lp_edge, pl_edge) of [N, L, C]."""
+    C, nl = hp["sphere_channels"], hp["num_layers"]
+
+    def edge_feats(pos_s, pos_d, ei, z_s, z_d):
+        vec = pos_s[ei[0]] - pos_d[ei[1]]
+        dist = torch.norm(vec, dim=-1, p=2)
+        g = gaussian_smearing(dist, 0.0, hp["cutoff"], hp["edge_channels"], 20)
+        return torch.cat((g, p["source_embedding.weight"][z_s[ei[0]]], p["target_embedding.weight"][z_d[ei[1]]]), dim=1)
+
+    def init_nodes(z, xf):
+        emb = p["sphere_embedding.weight"][z] + p["sphere_embedding_2.weight"][node_bits(xf)]
+        x = torch.zeros(len(z), t.L, C, dtype=torch.long)      # dtype=torch.long quirk, Embedding.py:241-247
+        x[:, 0, :] = emb                                        # truncation toward zero (Embedding.py:262)
+        return x
+
+    def homo_pass(z, xf, pos, ei, rot):
+        W = wigner_dense(rot, t)
+        xe = edge_feats(pos, pos, ei, z, z)
+        x = init_nodes(z, xf) + edge_degree_embedding(p, "edge_degree_embedding.", xe, ei, W, t, C, len(z), _AVG_DEGREE)
+        for i in range(nl):
+            x, _, _ = trans_block(p, f"blocks.{i}.", x, x, xe, ei, W, t, hp)
+        return rms_norm_sh(p, "norm.", x, t)
+
+    out = {}
+    xp = homo_pass(graph["z_p"], graph["x_p"], graph["pos_p"], graph["ei_pp"], frames["pp"])
+    xl = homo_pass(graph["z_l"], graph["x_l"], graph["pos_l"], graph["ei_ll"], frames["ll"])
+
+    def hetero_pass(x_s, x_t, pos_s, pos_t, z_s, z_t, ei, W):
+        xe = edge_feats(pos_s, pos_t, ei, z_s, z_t)
+        x_t = x_t + edge_degree_embedding(p, "edge_degree_embedding.", xe, ei, W, t, C, len(z_t), _AVG_DEGREE)
+        y = None
+        for i in range(nl):
+            if compute_dead_blocks or i == nl - 1:
+                y, x_s, x_t = trans_block(p, f"blocks.{i}.", x_s, x_t, xe, ei, W, t, hp)
+            else:  # outputs of blocks 0..nl-2 are discarded by the caller (Embedding.py:415-424)
+                x_s = rms_norm_sh(p, f"blocks.{i}.norm_1.", x_s, t)
+                x_t = rms_norm_sh(p, f"blocks.{i}.norm_1.", x_t, t)
+        return rms_norm_sh(p, "norm.", y, t), x_s, x_t
+
+    W_lp = wigner_dense(frames["lp"], t)
+    lp, xl, xp = hetero_pass(xl, xp, graph["pos_l"], graph["pos_p"], graph["z_l"], graph["z_p"], graph["ei_lp"], W_lp)
+    pl, xp, xl = hetero_pass(xp, xl, graph["pos_p"], graph["pos_l"], graph["z_p"], graph["z_l"], graph["ei_pl"], W_lp)
+    out["lp_edge"], out["pl_edge"] = lp, pl
+    out["protein_atoms"] = xp + lp
+    out["ligand_atoms"] = xl + pl
+    return out
