@@ -1,0 +1,127 @@
+/* efl.h -- C ABI of libefl.so: B200 (sm_100a) kernels for the EF_layers hot path of Isomorpfishm/SINGA.
+ *
+ * The reference has no FFI layer: its boundary for this path is the Python surface of model/EF_layers.py as
+ * consumed by model/Embedding.py:12-33.  singa_b200/EF_layers.py keeps that surface and calls the functions
+ * below (through ctypes, singa_b200/_lib.py).  Each entry cites the reference code it replaces
+ * (paths relative to the reference root, model/EF_layers.py unless stated).
+ *
+ * Conventions: C linkage, POD arguments only; every pointer is a DEVICE pointer borrowed for the call (the
+ * row-map arrays of the S2 entry points are HOST arrays); no hidden allocation -- workspaces are supplied by the
+ * caller; all work is enqueued on `stream` (a cudaStream_t passed as void*), no synchronisation inside;
+ * return 0 on success, otherwise a cudaError_t value or an EFL_ERR_* code, with a message available from
+ * efl_last_error_string() (thread-local).  Shapes use L=(lmax+1)^2 coefficients, M kept coefficients with
+ * |m|<=mmax, WSZ = sum_l min(2l+1, 2mmax+1)*(2l+1) Wigner floats per edge; built for (lmax,mmax) in
+ * {(6,2), (8,2), (4,2)}.
+ *
+ * Edge operand layout ("m-primary, split by order"): for order m a dense [rows_m*Ec, (lmax+1-m)*CH] matrix,
+ * rows_m = 1 for m=0, else 2 (row 2e = +m "real", row 2e+1 = -m "imag"), Ec = edges of the chunk, in
+ * destination-sorted order.  The l<->m permutation einsums of the reference (:354-359) are folded into these
+ * layouts.  "dup layout" for gradients w.r.t. SO2_m_Convolution outputs: [2Ec, 2*half] with interleaved
+ * columns, row 2e = (d re_q, d im_q), row 2e+1 = (d im_q, -d re_q), matching weights whose rows are
+ * interleaved (real_q, imag_q).
+ */
+#ifndef EFL_H_
+#define EFL_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EFL_ERR_UNSUPPORTED 10001
+#define EFL_ERR_ARG 10002
+
+int efl_version(void);
+const char* efl_last_error_string(void);
+int efl_device_cc(int device, int* major, int* minor);
+
+/* SO3_Rotation.set_wigner / RotationToWignerDMatrix / wigner_D / _z_rot_mat (:485-528, :2207-2229).
+ * rot [E,3,3] fp32 edge frames, jd = concatenated J_l (l=0..lmax, row-major) -> wig [E, WSZ] kept rows. */
+int efl_wigner_from_rotmat(int lmax, int mmax, const float* rot, const float* jd, float* wig, int E, void* stream);
+
+/* Gather + rotate-in: SO3_Embedding.clone/_expand_edge + cat (:1110-1119), SO3_Rotation.rotate (:494-497),
+ * _m_primary (:354-355) and the radial multiply of SO2_Convolution (:820-850).
+ * x_src [Ns,L,C], x_dst [Nt,L,C]; src/dst/perm int32 [E] (dst-sorted order; perm = original edge id);
+ * wig [E,WSZ] and rad [E,rad_ld] in ORIGINAL edge order (rad may be NULL); a0..a2 operand buffers (fp32 or
+ * bf16) for chunk edges [e0, e0+Ec). */
+int efl_rotate_in_fwd(int lmax, int mmax, int C, int bf16_out, const float* x_src, const float* x_dst,
+                      const int* src, const int* dst, const int* perm, const float* wig, const float* rad,
+                      int rad_ld, void* a0, void* a1, void* a2, int e0, int Ec, void* stream);
+/* Backward of the above: da0..da2 (dgrad of so2_conv_1) -> drad [E,rad_ld] (original order) and per-edge
+ * d x [E, L, 2C] (sorted order; columns [0,C) source half, [C,2C) destination half). */
+int efl_rotate_in_bwd(int lmax, int mmax, int C, int bf16_in, const float* x_src, const float* x_dst,
+                      const int* src, const int* dst, const int* perm, const float* wig, const float* rad,
+                      int rad_ld, const void* da0, const void* da1, const void* da2, float* drad, float* dxe,
+                      int e0, int Ec, void* stream);
+/* Deterministic backward of the gather (:326-328): out[n,i,c] = sum_{k in [ptr[n],ptr[n+1])}
+ * buf[idx?idx[k]:k, i, coff+c]; buf rows are L*ldc floats. */
+int efl_segment_sum_rows(const float* buf, int L, int ldc, int coff, int C, const int* ptr, const int* idx,
+                         float* out, int num_nodes, int accumulate, void* stream);
+
+/* alpha*value (:1186-1190) + SO3_Rotation.rotate_inv with get_rotate_inv_rescale (:500-505, :1530-1549) +
+ * SO3_Embedding._reduce_edge (:342-351) fused: out [Nt, L, heads*value] for destinations [n0,n1), one CTA per
+ * destination, fixed summation order, no atomics.  alpha [E,heads] sorted order (NULL = 1). */
+int efl_rotate_back_aggregate_fwd(int lmax, int mmax, int heads, int value_ch, int bf16_in, const void* v0,
+                                  const void* v1, const void* v2, const float* alpha, const int* rowptr,
+                                  const int* perm, const float* wig, float* out, int n0, int n1, int e0,
+                                  void* stream);
+/* Backward: dout [Nt,L,heads*value] -> dy0..dy2 (d value, dup layout for m>0) and dalpha [E,heads]. */
+int efl_rotate_back_aggregate_bwd(int lmax, int mmax, int heads, int value_ch, int bf16, const void* v0,
+                                  const void* v1, const void* v2, void* dy0, void* dy1, void* dy2,
+                                  const float* alpha, const int* rowptr, const int* perm, const float* wig,
+                                  const float* dout, float* dalpha, int n0, int n1, int e0, void* stream);
+
+/* EdgeDegreeEmbedding tail (:116-147): m0 [E,(lmax+1)*C] (rad_func output, original order) -> out [Nt,L,C]. */
+int efl_edge_degree_fwd(int lmax, int mmax, int C, const float* m0, const int* rowptr, const int* perm,
+                        const float* wig, float rescale_factor, float* out, int Nt, void* stream);
+int efl_edge_degree_bwd(int lmax, int mmax, int C, const float* dout, const int* dst_orig, const float* wig,
+                        float rescale_factor, float* dm0, int E, void* stream);
+
+/* Attention logits (:1175-1178): extra[:, :heads*32] -> LayerNorm(32) (:1024) -> SmoothLeakyReLU (:1669-1677)
+ * -> dot alpha_dot -> logits [Ec, heads]. */
+int efl_alpha_logits_fwd(const float* extra, int ld, int heads, int alpha_ch, const float* ln_w, const float* ln_b,
+                         const float* alpha_dot, float* logits, int Ec, void* stream);
+/* Backward; part [nblocks, heads*32+64] receives per-block partial sums of (d alpha_dot | d ln_w | d ln_b). */
+int efl_alpha_logits_bwd(const float* extra, int ld, int heads, int alpha_ch, const float* ln_w, const float* ln_b,
+                         const float* alpha_dot, const float* dlogits, void* dextra, int ldo, int bf16_out,
+                         float* part, int nblocks, int Ec, void* stream);
+
+/* torch_geometric.utils.softmax(alpha, edge_index[1]) (:1180; torch_geometric 2.3.1) over the dst-sorted CSR:
+ * exp(x - max_seg) / (sum_seg + 1e-16), one warp per destination in [n0,n1). */
+int efl_segment_softmax_fwd(const float* logits, int heads, const int* rowptr, float* alpha, int n0, int n1,
+                            void* stream);
+int efl_segment_softmax_bwd(const float* alpha, const float* dalpha, int heads, const int* rowptr, float* dlogits,
+                            int n0, int n1, void* stream);
+
+/* SeparableS2Activation / S2Activation (:1736-1773) with the SO3_Grid matrices (:531-621) given as
+ * to_grid, from_grid [G, M] (G = res_beta*res_alpha).  Row maps (HOST arrays): nseg segments, base[nseg]
+ * device pointers, stride[nseg] elements per item, first[nseg+1] row ranges.  gate [n_items, gate_ld]. */
+int efl_s2act_fwd(int M, int G, int CH, int bf16_in, int bf16_out, int in_nseg, void* const* in_base,
+                  const long long* in_stride, const int* in_first, int out_nseg, void* const* out_base,
+                  const long long* out_stride, const int* out_first, const float* gate, long long gate_ld,
+                  const float* to_grid, const float* from_grid, long long n_items, void* stream);
+int efl_s2act_bwd(int M, int G, int CH, int bf16_in, int bf16_d, int in_nseg, void* const* in_base,
+                  const long long* in_stride, const int* in_first, int din_nseg, void* const* din_base,
+                  const long long* din_stride, const int* din_first, int dout_nseg, void* const* dout_base,
+                  const long long* dout_stride, const int* dout_first, int dup, const float* gate,
+                  long long gate_ld, void* dgate, long long dgate_ld, const float* to_grid, const float* from_grid,
+                  long long n_items, void* stream);
+
+/* SO2_Convolution / SO2_m_Convolution linear maps (:807-875, :721-729), fp32 SIMT accuracy mode.
+ * NT: C[i,n] = sum_k A[i,k] B[n,k] (+bias).  epilogue 0 plain; 1 split (cols < nsplit -> C0 fp32, rest -> C);
+ * 2 complex combine on row pairs / interleaved column pairs -> C [M, N/2]. */
+int efl_gemm_nt_f32(int epilogue, const float* A, long long lda, const float* B, long long ldb, const float* bias,
+                    float* C, long long ldc, float* C0, long long ldc0, int nsplit, int M, int N, int K,
+                    void* stream);
+/* TN (weight gradients): C[n,k] (+)= sum_i A[i,n] B[i,k], deterministic split over i.
+ * workspace: efl_gemm_tn_splits(Mred) * N1 * N2 floats. */
+int efl_gemm_tn_splits(int Mred);
+int efl_gemm_tn_f32(const float* A, long long lda, const float* B, long long ldb, float* C, long long ldc,
+                    int accumulate, float* workspace, int Mred, int N1, int N2, void* stream);
+/* Bias gradients: out[c] (+)= sum_r X[r,c]; workspace (rows/4096 + 1) * cols floats. */
+int efl_colsum(int bf16, const void* X, long long ld, int rows, int cols, float* out, int accumulate,
+               float* workspace, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EFL_H_ */

@@ -1,0 +1,90 @@
+"""ctypes binding of the C-ABI CUDA library (include/efl.h).
+
+The library is built in-tree by ``__graft_entry__.build()`` as
+``singa_b200/libefl.so``.  There is no CPU fallback: importing this module without
+the library raises, and every op checks that its tensors live on a CUDA device.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libefl.so")
+
+_P, _I, _L, _F = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float
+_CODES = {"p": _P, "i": _I, "l": _L, "f": _F}
+
+# name -> argument type codes (p pointer, i int, l long long, f float); every entry point returns int
+SIGNATURES = {
+    "efl_wigner_from_rotmat": "iipppip",
+    "efl_rotate_in_fwd": "iiiipppppppipppiip",
+    "efl_rotate_in_bwd": "iiiipppppppippppp" "iip",
+    "efl_segment_sum_rows": "piiiipppiip",
+    "efl_rotate_back_aggregate_fwd": "iiiiipppppppp" "iiip",
+    "efl_rotate_back_aggregate_bwd": "iiiiipppppppppppp" "iiip",
+    "efl_edge_degree_fwd": "iiippppfpip",
+    "efl_edge_degree_bwd": "iiipppfpip",
+    "efl_alpha_logits_fwd": "piiippppip",
+    "efl_alpha_logits_bwd": "piiippppp" "iipiip",
+    "efl_segment_softmax_fwd": "pippiip",
+    "efl_segment_softmax_bwd": "ppippiip",
+    "efl_s2act_fwd": "iiiii" "ippp" "ippp" "plpplp",
+    "efl_s2act_bwd": "iiiii" "ippp" "ippp" "ippp" "i" "plplpplp",
+    "efl_gemm_nt_f32": "iplplpplpliiiip",
+    "efl_gemm_tn_f32": "plplplipiiip",
+    "efl_colsum": "ipliipipp",
+}
+
+
+class EflError(RuntimeError):
+    pass
+
+
+def _load():
+    if not os.path.isfile(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build the CUDA library first (python -c 'import __graft_entry__ as g; g.build()'). "
+            "singa_b200 has no CPU or PyTorch fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, sig in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.argtypes = [_CODES[c] for c in sig]
+        fn.restype = _I
+    lib.efl_last_error_string.restype = ctypes.c_char_p
+    lib.efl_version.restype = _I
+    lib.efl_gemm_tn_splits.argtypes = [_I]
+    lib.efl_gemm_tn_splits.restype = _I
+    return lib
+
+
+LIB = _load()
+
+
+def ptr(t):
+    """Device pointer of a tensor (or None -> NULL)."""
+    if t is None:
+        return None
+    if isinstance(t, int):
+        return t
+    assert t.is_cuda, "singa_b200 ops need CUDA tensors (no CPU fallback)"
+    return t.data_ptr()
+
+
+def stream_ptr():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def call(name: str, *args):
+    """Invoke an entry point; the trailing stream argument is appended here."""
+    rc = getattr(LIB, name)(*args, stream_ptr())
+    if rc != 0:
+        raise EflError(f"{name} failed (code {rc}): {LIB.efl_last_error_string().decode()}")
+
+
+def check_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise EflError("singa_b200 kernels only run on CUDA tensors; there is no CPU path")

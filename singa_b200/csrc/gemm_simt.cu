@@ -1,0 +1,235 @@
+// fp32 SIMT GEMMs for the SO(2) linear maps: the accuracy ("fp32") mode of the path.
+//
+//   NT : C[i, n] = sum_k A[i, k] * B[n, k]            forward and dgrad (with a transposed weight copy)
+//   TN : C[n, k] (+)= sum_i A[i, n] * B[i, k]          wgrad (reduction over edges)
+//
+// NT epilogues (reference EF_layers.py:825-834, 721-729):
+//   0 PLAIN   : C = acc + bias
+//   1 SPLIT   : columns [0, nsplit) -> C0 (fp32, "extra" m=0 outputs: alpha inputs and gate),
+//               columns [nsplit, N) -> C   (hidden m=0 rows)
+//   2 COMPLEX : SO2_m_Convolution combine.  Rows come in pairs (2e: +m "real", 2e+1: -m "imag") and
+//               weight rows are interleaved on the host (2q: real weight q, 2q+1: imag weight q):
+//                 out[2e,   q] = acc[2e, 2q]   - acc[2e+1, 2q+1]
+//                 out[2e+1, q] = acc[2e+1, 2q] + acc[2e,   2q+1]
+// 64x64 tile, 16-deep k step, 256 threads, 4x4 micro-tile with even-aligned rows/cols so the
+// complex combine is thread-local.
+#include "efl_common.cuh"
+
+namespace efl {
+
+constexpr int BM = 64, BN = 64, BK = 16;
+
+template <typename TA, typename TC, int EPI>
+__global__ void __launch_bounds__(256) gemm_nt_kernel(const TA* __restrict__ A, long long lda,
+                                                      const TA* __restrict__ B, long long ldb,
+                                                      const float* __restrict__ bias, TC* __restrict__ C,
+                                                      long long ldc, float* __restrict__ C0, long long ldc0,
+                                                      int nsplit, int M, int N, int K) {
+  __shared__ float sA[BK][BM + 4];
+  __shared__ float sB[BK][BN + 4];
+  const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  for (int k0 = 0; k0 < K; k0 += BK) {
+    // 64 rows x 16 k per operand: 1024 elements, 4 per thread
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int idx = threadIdx.x + t * 256;
+      const int r = idx / BK, kk = idx % BK;
+      const int gm = m0 + r, gn = n0 + r, gk = k0 + kk;
+      sA[kk][r] = (gm < M && gk < K) ? to_f<TA>(A[(long long)gm * lda + gk]) : 0.f;
+      sB[kk][r] = (gn < N && gk < K) ? to_f<TA>(B[(long long)gn * ldb + gk]) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = sA[kk][ty * 4 + i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = sB[kk][tx * 4 + j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  const int rm = m0 + ty * 4, cn = n0 + tx * 4;
+  if (EPI == 2) {
+    // N is the interleaved width (2 * half); rows/cols are even aligned
+#pragma unroll
+    for (int ip = 0; ip < 2; ++ip) {
+#pragma unroll
+      for (int jp = 0; jp < 2; ++jp) {
+        const int r = rm + 2 * ip, c = cn + 2 * jp;
+        if (r + 1 < M && c + 1 < N) {
+          const float re = acc[2 * ip][2 * jp] - acc[2 * ip + 1][2 * jp + 1];
+          const float im = acc[2 * ip + 1][2 * jp] + acc[2 * ip][2 * jp + 1];
+          C[(long long)r * ldc + c / 2] = from_f<TC>(re);
+          C[(long long)(r + 1) * ldc + c / 2] = from_f<TC>(im);
+        }
+      }
+    }
+    return;
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = rm + i;
+    if (r >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = cn + j;
+      if (c >= N) continue;
+      const float v = acc[i][j] + (bias ? bias[c] : 0.f);
+      if (EPI == 1 && c < nsplit) C0[(long long)r * ldc0 + c] = v;
+      else C[(long long)r * ldc + (c - (EPI == 1 ? nsplit : 0))] = from_f<TC>(v);
+    }
+  }
+}
+
+// C[n, k] (+)= sum_{i in slice} A[i, n] * B[i, k]; deterministic split over i via blockIdx.z partials
+template <typename TA>
+__global__ void __launch_bounds__(256) gemm_tn_kernel(const TA* __restrict__ A, long long lda,
+                                                      const TA* __restrict__ B, long long ldb,
+                                                      float* __restrict__ P /* [splits, N1, N2] */, int Mred,
+                                                      int N1, int N2, int rows_per_split) {
+  __shared__ float sA[BK][BM + 4];
+  __shared__ float sB[BK][BN + 4];
+  const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
+  const int a0 = blockIdx.y * BM, b0 = blockIdx.x * BN;
+  const int i_begin = blockIdx.z * rows_per_split;
+  const int i_end = min(Mred, i_begin + rows_per_split);
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  for (int i0 = i_begin; i0 < i_end; i0 += BK) {
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int idx = threadIdx.x + t * 256;
+      const int kk = idx / BM, r = idx % BM;  // consecutive threads -> consecutive columns (coalesced)
+      const int gi = i0 + kk;
+      sA[kk][r] = (gi < i_end && a0 + r < N1) ? to_f<TA>(A[(long long)gi * lda + a0 + r]) : 0.f;
+      sB[kk][r] = (gi < i_end && b0 + r < N2) ? to_f<TA>(B[(long long)gi * ldb + b0 + r]) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = sA[kk][ty * 4 + i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = sB[kk][tx * 4 + j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  float* Pz = P + (size_t)blockIdx.z * N1 * N2;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = a0 + ty * 4 + i;
+    if (r >= N1) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = b0 + tx * 4 + j;
+      if (c < N2) Pz[(size_t)r * N2 + c] = acc[i][j];
+    }
+  }
+}
+
+// C[idx] = (accumulate ? C[idx] : 0) + sum_z P[z, idx], fixed order
+__global__ void splitk_reduce_kernel(const float* __restrict__ P, int splits, long long n, float* __restrict__ C,
+                                     long long ldc, int N2, int accumulate) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float acc = 0.f;
+  for (int z = 0; z < splits; ++z) acc += P[(size_t)z * n + i];
+  const long long r = i / N2, c = i % N2;
+  float* o = C + r * ldc + c;
+  *o = accumulate ? (*o + acc) : acc;
+}
+
+// out[c] (+)= sum_i X[i, c], deterministic two-stage column sum (bias gradients)
+template <typename T>
+__global__ void colsum_partial_kernel(const T* __restrict__ X, long long ld, int rows, int cols, int rows_per_block,
+                                      float* __restrict__ P) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(rows, r0 + rows_per_block);
+  float acc = 0.f;
+  for (int r = r0; r < r1; ++r) acc += to_f<T>(X[(long long)r * ld + c]);
+  P[(size_t)blockIdx.y * cols + c] = acc;
+}
+
+}  // namespace efl
+
+using namespace efl;
+
+extern "C" int efl_gemm_nt_f32(int epilogue, const float* A, long long lda, const float* B, long long ldb,
+                               const float* bias, float* C, long long ldc, float* C0, long long ldc0, int nsplit,
+                               int M, int N, int K, void* stream) {
+  if (M <= 0 || N <= 0) return EFL_OK;
+  dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM), block(256);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (epilogue == 0) gemm_nt_kernel<float, float, 0><<<grid, block, 0, s>>>(A, lda, B, ldb, bias, C, ldc, C0, ldc0, nsplit, M, N, K);
+  else if (epilogue == 1) gemm_nt_kernel<float, float, 1><<<grid, block, 0, s>>>(A, lda, B, ldb, bias, C, ldc, C0, ldc0, nsplit, M, N, K);
+  else if (epilogue == 2) {
+    EFL_REQUIRE(M % 2 == 0 && N % 2 == 0, "efl_gemm_nt_f32: complex epilogue needs even M and N");
+    gemm_nt_kernel<float, float, 2><<<grid, block, 0, s>>>(A, lda, B, ldb, bias, C, ldc, C0, ldc0, nsplit, M, N, K);
+  } else {
+    efl_set_error("efl_gemm_nt_f32: unknown epilogue");
+    return EFL_ERR_ARG;
+  }
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+// workspace: splits * N1 * N2 floats, splits = efl_gemm_tn_splits(Mred)
+extern "C" int efl_gemm_tn_splits(int Mred) {
+  int s = (Mred + 8191) / 8192;
+  return s < 1 ? 1 : (s > 64 ? 64 : s);
+}
+
+extern "C" int efl_gemm_tn_f32(const float* A, long long lda, const float* B, long long ldb, float* C,
+                               long long ldc, int accumulate, float* workspace, int Mred, int N1, int N2,
+                               void* stream) {
+  if (N1 <= 0 || N2 <= 0) return EFL_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int splits = efl_gemm_tn_splits(Mred);
+  int rows = (Mred + splits - 1) / splits;
+  rows = ((rows + BK - 1) / BK) * BK;
+  if (rows < BK) rows = BK;
+  dim3 grid((N2 + BN - 1) / BN, (N1 + BM - 1) / BM, splits), block(256);
+  gemm_tn_kernel<float><<<grid, block, 0, s>>>(A, lda, B, ldb, workspace, Mred, N1, N2, rows);
+  EFL_CHECK_LAUNCH();
+  const long long n = (long long)N1 * N2;
+  splitk_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(workspace, splits, n, C, ldc, N2, accumulate);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+// workspace: ceil(rows / 4096) * cols floats
+extern "C" int efl_colsum(int bf16, const void* X, long long ld, int rows, int cols, float* out, int accumulate,
+                          float* workspace, void* stream) {
+  if (cols <= 0) return EFL_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int rpb = 4096;
+  const int nb = rows > 0 ? (rows + rpb - 1) / rpb : 1;
+  dim3 grid((cols + 127) / 128, nb), block(128);
+  if (bf16) colsum_partial_kernel<__nv_bfloat16><<<grid, block, 0, s>>>((const __nv_bfloat16*)X, ld, rows, cols, rpb, workspace);
+  else colsum_partial_kernel<float><<<grid, block, 0, s>>>((const float*)X, ld, rows, cols, rpb, workspace);
+  EFL_CHECK_LAUNCH();
+  splitk_reduce_kernel<<<(cols + 255) / 256, 256, 0, s>>>(workspace, nb, cols, out, cols, cols, accumulate);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}

@@ -1,0 +1,497 @@
+// Edge-frame rotations (HBM-bound kernels).
+//
+//  rotate_in        : gather x[src] || x[dst], rotate into the edge frame with the kept
+//                     Wigner rows, optional per-edge radial scale, emit m-primary GEMM operands.
+//                     Replaces SO3_Embedding.clone/_expand_edge, cat, SO3_Rotation.rotate,
+//                     _m_primary and the radial multiply of SO2_Convolution
+//                     (reference EF_layers.py:1110-1139, 494-497, 354-355, 820-850).
+//  rotate_back_agg  : alpha * value, rotate back (rescale folded in) and segment-sum per
+//                     destination over the dst-sorted CSR.  Replaces EF_layers.py:1186-1199,
+//                     500-505, 342-351.  Deterministic: one CTA owns a destination, fixed order,
+//                     no atomics; the [E, L, heads*value] tensor never exists.
+//  edge_degree      : EdgeDegreeEmbedding tail (EF_layers.py:116-147): only the m'=0 Wigner row.
+//
+// Per-edge operand layout ("m-primary, split by order"): for order m the buffer is dense
+// [rows_m * Ec, (LMAX+1-m) * CH] with rows_m = 1 (m=0) or 2 (row 2e = +m "real", 2e+1 = -m "imag").
+#include "efl_common.cuh"
+
+namespace efl {
+
+template <int LMAX>
+struct OpBufs {
+  void* p[3];
+};
+
+// element (l, m') of local edge e, channel c in the split m-primary buffers
+template <int LMAX, typename T>
+__device__ __forceinline__ T* op_ptr(void* const* bufs, int e, int l, int mp, int CH, int c) {
+  const int am = mp < 0 ? -mp : mp;
+  const int K = (LMAX + 1 - am) * CH;
+  T* base = reinterpret_cast<T*>(bufs[am]);
+  if (am == 0) return base + (size_t)e * K + l * CH + c;
+  return base + ((size_t)e * 2 + (mp > 0 ? 0 : 1)) * K + (l - am) * CH + c;
+}
+
+// ------------------------------------------------------------------------------------------
+// rotate-in forward: one warp per edge, lane = channel of the src||dst concat (2C = 32)
+// ------------------------------------------------------------------------------------------
+template <int LMAX, int MMAX, int C, typename TOut>
+__global__ void __launch_bounds__(128) rotate_in_fwd_kernel(
+    const float* __restrict__ x_src, const float* __restrict__ x_dst, const int* __restrict__ src,
+    const int* __restrict__ dst, const int* __restrict__ perm, const float* __restrict__ wig,
+    const float* __restrict__ rad, int rad_ld, OpBufs<LMAX> out, int e0, int Ec) {
+  using T = Tab<LMAX, MMAX>;
+  static_assert(2 * C == 32, "lane = channel mapping needs 2C == 32");
+  constexpr int CH = 2 * C;
+  __shared__ float sW[4][T::WSZ + 1];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int el = blockIdx.x * 4 + warp;
+  if (el >= Ec) return;
+  const int e = e0 + el;
+  const int eo = perm[e];
+  const float* w = wig + (size_t)eo * T::WSZ;
+  for (int i = lane; i < T::WSZ; i += 32) sW[warp][i] = w[i];
+  const int node = lane < C ? src[e] : dst[e];
+  const float* xp = (lane < C ? x_src : x_dst) + (size_t)node * T::L * C + (lane & (C - 1));
+  float x[T::L];
+#pragma unroll
+  for (int i = 0; i < T::L; ++i) x[i] = __ldg(xp + i * C);
+  __syncwarp();
+  const float* rd = rad ? rad + (size_t)eo * rad_ld : nullptr;
+#pragma unroll
+  for (int l = 0; l <= LMAX; ++l) {
+#pragma unroll
+    for (int mp = -T::mm(l); mp <= T::mm(l); ++mp) {
+      const float* wr = &sW[warp][T::wrow(l, mp)];
+      float acc = 0.f;
+#pragma unroll
+      for (int n = 0; n < 2 * l + 1; ++n) acc = fmaf(wr[n], x[l * l + n], acc);
+      if (rd) {
+        const int am = mp < 0 ? -mp : mp;
+        // radial layout: [m=0 | m=1 | m=2 ...], each (LMAX+1-m)*CH wide (EF_layers.py:823,848)
+        int roff = 0;
+#pragma unroll
+        for (int k = 0; k < am; ++k) roff += (LMAX + 1 - k) * CH;
+        acc *= __ldg(rd + roff + (l - am) * CH + lane);
+      }
+      *op_ptr<LMAX, TOut>(out.p, el, l, mp, CH, lane) = from_f<TOut>(acc);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// rotate-in backward: per edge, dA (GEMM dgrad output) -> d rad, per-edge d x (src | dst halves)
+// ------------------------------------------------------------------------------------------
+template <int LMAX, int MMAX, int C, typename TIn>
+__global__ void __launch_bounds__(128) rotate_in_bwd_kernel(
+    const float* __restrict__ x_src, const float* __restrict__ x_dst, const int* __restrict__ src,
+    const int* __restrict__ dst, const int* __restrict__ perm, const float* __restrict__ wig,
+    const float* __restrict__ rad, int rad_ld, OpBufs<LMAX> dA, float* __restrict__ drad,
+    float* __restrict__ dxe /* [E, L, 2C] sorted order */, int e0, int Ec) {
+  using T = Tab<LMAX, MMAX>;
+  constexpr int CH = 2 * C;
+  __shared__ float sW[4][T::WSZ + 1];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int el = blockIdx.x * 4 + warp;
+  if (el >= Ec) return;
+  const int e = e0 + el;
+  const int eo = perm[e];
+  const float* w = wig + (size_t)eo * T::WSZ;
+  for (int i = lane; i < T::WSZ; i += 32) sW[warp][i] = w[i];
+  const int node = lane < C ? src[e] : dst[e];
+  const float* xp = (lane < C ? x_src : x_dst) + (size_t)node * T::L * C + (lane & (C - 1));
+  float x[T::L], dx[T::L];
+#pragma unroll
+  for (int i = 0; i < T::L; ++i) {
+    x[i] = rad ? __ldg(xp + i * C) : 0.f;
+    dx[i] = 0.f;
+  }
+  __syncwarp();
+  const float* rd = rad ? rad + (size_t)eo * rad_ld : nullptr;
+  float* drd = rad ? drad + (size_t)eo * rad_ld : nullptr;
+#pragma unroll
+  for (int l = 0; l <= LMAX; ++l) {
+#pragma unroll
+    for (int am = 0; am <= T::mm(l); ++am) {
+      int roff = 0;
+#pragma unroll
+      for (int k = 0; k < am; ++k) roff += (LMAX + 1 - k) * CH;
+      const int rcol = roff + (l - am) * CH + lane;
+      const float rv = rd ? __ldg(rd + rcol) : 1.f;
+      float dr = 0.f;
+#pragma unroll
+      for (int sgn = 0; sgn < (am == 0 ? 1 : 2); ++sgn) {
+        const int mp = sgn == 0 ? am : -am;
+        const float* wr = &sW[warp][T::wrow(l, mp)];
+        const float da = to_f<TIn>(*op_ptr<LMAX, TIn>(dA.p, el, l, mp, CH, lane));
+        if (rd) {
+          float xr = 0.f;
+#pragma unroll
+          for (int n = 0; n < 2 * l + 1; ++n) xr = fmaf(wr[n], x[l * l + n], xr);
+          dr = fmaf(da, xr, dr);
+        }
+        const float dxr = da * rv;
+#pragma unroll
+        for (int n = 0; n < 2 * l + 1; ++n) dx[l * l + n] = fmaf(wr[n], dxr, dx[l * l + n]);
+      }
+      if (rd) drd[rcol] = dr;
+    }
+  }
+  float* o = dxe + (size_t)e * T::L * CH + lane;
+#pragma unroll
+  for (int i = 0; i < T::L; ++i) o[i * CH] = dx[i];
+}
+
+// out[n, i, c] = sum_{k in [ptr[n], ptr[n+1])} buf[idx ? idx[k] : k, i, coff + c]
+__global__ void segment_sum_rows_kernel(const float* __restrict__ buf, int row_elems /* L*ldc */, int ldc, int coff,
+                                        int C, int L, const int* __restrict__ ptr, const int* __restrict__ idx,
+                                        float* __restrict__ out, int accumulate) {
+  const int n = blockIdx.x;
+  const int b = ptr[n], e = ptr[n + 1];
+  for (int t = threadIdx.x; t < L * C; t += blockDim.x) {
+    const int i = t / C, c = t % C;
+    float acc = 0.f;
+    for (int k = b; k < e; ++k) {
+      const int r = idx ? idx[k] : k;
+      acc += buf[(size_t)r * row_elems + i * ldc + coff + c];
+    }
+    float* o = out + (size_t)n * L * C + t;
+    *o = accumulate ? (*o + acc) : acc;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// rotate-back + aggregate forward: one CTA per destination node, thread = value channel
+// ------------------------------------------------------------------------------------------
+template <int LMAX, int MMAX, int CH, int VC, typename TIn>
+__global__ void __launch_bounds__(128) rotate_back_agg_fwd_kernel(
+    OpBufs<LMAX> V, const float* __restrict__ alpha /* [E, heads] sorted */, int heads,
+    const int* __restrict__ rowptr, const int* __restrict__ perm, const float* __restrict__ wig,
+    float* __restrict__ out /* [Nt, L, CH] */, int n0, int e0) {
+  using T = Tab<LMAX, MMAX>;
+  __shared__ float sW[2][T::WSZ + 1];
+  const int n = n0 + blockIdx.x;
+  const int c = threadIdx.x;
+  const bool active = c < CH;
+  const int cc = active ? c : 0;
+  const int kb = rowptr[n], ke = rowptr[n + 1];
+  float acc[T::L];
+#pragma unroll
+  for (int i = 0; i < T::L; ++i) acc[i] = 0.f;
+  int buf = 0;
+  if (kb < ke) {
+    const float* w = wig + (size_t)perm[kb] * T::WSZ;
+    for (int i = threadIdx.x; i < T::WSZ; i += blockDim.x) sW[0][i] = w[i];
+  }
+  __syncthreads();
+  for (int k = kb; k < ke; ++k) {
+    if (k + 1 < ke) {
+      const float* w = wig + (size_t)perm[k + 1] * T::WSZ;
+      for (int i = threadIdx.x; i < T::WSZ; i += blockDim.x) sW[buf ^ 1][i] = w[i];
+    }
+    const int el = k - e0;
+    const float a = alpha ? alpha[(size_t)k * heads + cc / VC] : 1.f;
+#pragma unroll
+    for (int l = 0; l <= LMAX; ++l) {
+      const float sc = a * T::rescale(l);
+#pragma unroll
+      for (int mp = -T::mm(l); mp <= T::mm(l); ++mp) {
+        const float v = sc * to_f<TIn>(*op_ptr<LMAX, TIn>(V.p, el, l, mp, CH, cc));
+        const float* wr = &sW[buf][T::wrow(l, mp)];
+#pragma unroll
+        for (int nn = 0; nn < 2 * l + 1; ++nn) acc[l * l + nn] = fmaf(wr[nn], v, acc[l * l + nn]);
+      }
+    }
+    __syncthreads();
+    buf ^= 1;
+  }
+  if (active) {
+    float* o = out + (size_t)n * T::L * CH + c;
+#pragma unroll
+    for (int i = 0; i < T::L; ++i) o[i * CH] = acc[i];
+  }
+}
+
+// backward: d out[n] -> dV (written in the duplicated "dY" layout the SO(2) dgrad/wgrad GEMMs
+// consume: row 2e = [d re | d im], row 2e+1 = [d im | -d re], columns interleaved (re_q, im_q))
+// and d alpha[e, h] = sum_{j, c in h} dva[j, c] * V[e, j, c].
+template <int LMAX, int MMAX, int CH, int VC, typename TIn, typename TOut>
+__global__ void __launch_bounds__(128) rotate_back_agg_bwd_kernel(
+    OpBufs<LMAX> V, OpBufs<LMAX> dY, const float* __restrict__ alpha, int heads,
+    const int* __restrict__ rowptr, const int* __restrict__ perm, const float* __restrict__ wig,
+    const float* __restrict__ dout /* [Nt, L, CH] */, float* __restrict__ dalpha /* [E, heads] sorted */,
+    int n0, int e0) {
+  using T = Tab<LMAX, MMAX>;
+  __shared__ float sW[2][T::WSZ + 1];
+  const int n = n0 + blockIdx.x;
+  const int c = threadIdx.x;
+  const bool active = c < CH;
+  const int cc = active ? c : 0;
+  const int kb = rowptr[n], ke = rowptr[n + 1];
+  float dy[T::L];
+  {
+    const float* d = dout + (size_t)n * T::L * CH + cc;
+#pragma unroll
+    for (int i = 0; i < T::L; ++i) dy[i] = d[i * CH];
+  }
+  int buf = 0;
+  if (kb < ke) {
+    const float* w = wig + (size_t)perm[kb] * T::WSZ;
+    for (int i = threadIdx.x; i < T::WSZ; i += blockDim.x) sW[0][i] = w[i];
+  }
+  __syncthreads();
+  for (int k = kb; k < ke; ++k) {
+    if (k + 1 < ke) {
+      const float* w = wig + (size_t)perm[k + 1] * T::WSZ;
+      for (int i = threadIdx.x; i < T::WSZ; i += blockDim.x) sW[buf ^ 1][i] = w[i];
+    }
+    const int el = k - e0;
+    const float a = alpha[(size_t)k * heads + cc / VC];
+    float da = 0.f;
+#pragma unroll
+    for (int l = 0; l <= LMAX; ++l) {
+      const float rs = T::rescale(l);
+      float dre[2 * MMAX + 1];  // index mp + MMAX
+#pragma unroll
+      for (int mp = -T::mm(l); mp <= T::mm(l); ++mp) {
+        const float* wr = &sW[buf][T::wrow(l, mp)];
+        float g = 0.f;
+#pragma unroll
+        for (int nn = 0; nn < 2 * l + 1; ++nn) g = fmaf(wr[nn], dy[l * l + nn], g);
+        g *= rs;
+        const float v = to_f<TIn>(*op_ptr<LMAX, TIn>(V.p, el, l, mp, CH, cc));
+        da = fmaf(g, v, da);
+        dre[mp + MMAX] = g * a;
+      }
+      if (active) {
+        // m = 0 row: plain
+        reinterpret_cast<TOut*>(dY.p[0])[(size_t)el * (LMAX + 1) * CH + l * CH + c] = from_f<TOut>(dre[MMAX]);
+#pragma unroll
+        for (int am = 1; am <= T::mm(l); ++am) {
+          const int half = (LMAX + 1 - am) * CH;
+          TOut* base = reinterpret_cast<TOut*>(dY.p[am]);
+          const float gr = dre[MMAX + am], gi = dre[MMAX - am];
+          const int q = (l - am) * CH + c;
+          TOut* r0 = base + ((size_t)el * 2) * (2 * half) + 2 * q;
+          TOut* r1 = r0 + 2 * half;
+          r0[0] = from_f<TOut>(gr);
+          r0[1] = from_f<TOut>(gi);
+          r1[0] = from_f<TOut>(gi);
+          r1[1] = from_f<TOut>(-gr);
+        }
+      }
+    }
+    // reduce d alpha over the VC channels of a head (VC-aligned groups inside a warp)
+    if (!active) da = 0.f;
+#pragma unroll
+    for (int o = VC / 2; o > 0; o >>= 1) da += __shfl_xor_sync(0xffffffffu, da, o);
+    if (active && (c % VC) == 0) dalpha[(size_t)k * heads + c / VC] = da;
+    __syncthreads();
+    buf ^= 1;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// EdgeDegreeEmbedding tail.  out[n, l*l+l+nn, c] = (1/rf) sum_e D^l[0, nn] rescale_l m0[e, l, c]
+// one warp per destination; lanes = 2 edge slots x C channels
+// ------------------------------------------------------------------------------------------
+template <int LMAX, int MMAX, int C>
+__global__ void __launch_bounds__(128) edge_degree_fwd_kernel(
+    const float* __restrict__ m0 /* [E, (LMAX+1)*C] original order */, const int* __restrict__ rowptr,
+    const int* __restrict__ perm, const float* __restrict__ wig, float inv_rf, float* __restrict__ out, int Nt) {
+  using T = Tab<LMAX, MMAX>;
+  static_assert(C == 16, "two edge slots x 16 channels per warp");
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = blockIdx.x * 4 + warp;
+  if (n >= Nt) return;
+  const int slot = lane >> 4, c = lane & 15;
+  float acc[T::L];
+#pragma unroll
+  for (int i = 0; i < T::L; ++i) acc[i] = 0.f;
+  for (int k = rowptr[n] + slot; k < rowptr[n + 1]; k += 2) {
+    const int eo = perm[k];
+    const float* w = wig + (size_t)eo * T::WSZ;
+    const float* r = m0 + (size_t)eo * (LMAX + 1) * C + c;
+#pragma unroll
+    for (int l = 0; l <= LMAX; ++l) {
+      const float v = __ldg(r + l * C) * T::rescale(l);
+      const float* wr = w + T::wrow(l, 0);
+#pragma unroll
+      for (int nn = 0; nn < 2 * l + 1; ++nn) acc[l * l + nn] = fmaf(__ldg(wr + nn), v, acc[l * l + nn]);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < T::L; ++i) {
+    const float t = acc[i] + __shfl_xor_sync(0xffffffffu, acc[i], 16);
+    if (slot == 0) out[(size_t)n * T::L * C + i * C + c] = t * inv_rf;
+  }
+}
+
+// d m0[e, l, c] = (1/rf) rescale_l sum_nn D^l[0, nn] dout[dst(e), l*l+nn, c]; thread = (edge, c)
+template <int LMAX, int MMAX, int C>
+__global__ void edge_degree_bwd_kernel(const float* __restrict__ dout, const int* __restrict__ dst_orig,
+                                       const float* __restrict__ wig, float inv_rf, float* __restrict__ dm0, int E) {
+  using T = Tab<LMAX, MMAX>;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= E * C) return;
+  const int e = t / C, c = t % C;
+  const float* w = wig + (size_t)e * T::WSZ;
+  const float* d = dout + (size_t)dst_orig[e] * T::L * C + c;
+#pragma unroll
+  for (int l = 0; l <= LMAX; ++l) {
+    const float* wr = w + T::wrow(l, 0);
+    float g = 0.f;
+#pragma unroll
+    for (int nn = 0; nn < 2 * l + 1; ++nn) g = fmaf(__ldg(wr + nn), d[(l * l + nn) * C], g);
+    dm0[(size_t)e * (LMAX + 1) * C + l * C + c] = g * T::rescale(l) * inv_rf;
+  }
+}
+
+}  // namespace efl
+
+// ------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------
+using namespace efl;
+
+#define DISPATCH_LM(lmax, mmax, CALL)                                                    \
+  if (lmax == 6 && mmax == 2) { CALL(6, 2); }                                            \
+  else if (lmax == 8 && mmax == 2) { CALL(8, 2); }                                       \
+  else if (lmax == 4 && mmax == 2) { CALL(4, 2); }                                       \
+  else { efl_set_error("unsupported (lmax, mmax); built for (6,2), (8,2), (4,2)"); return EFL_ERR_UNSUPPORTED; }
+
+extern "C" int efl_rotate_in_fwd(int lmax, int mmax, int C, int bf16_out, const float* x_src, const float* x_dst,
+                                 const int* src, const int* dst, const int* perm, const float* wig,
+                                 const float* rad, int rad_ld, void* a0, void* a1, void* a2, int e0, int Ec,
+                                 void* stream) {
+  if (Ec <= 0) return EFL_OK;
+  EFL_REQUIRE(C == 16, "efl_rotate_in_fwd: sphere_channels must be 16");
+  cudaStream_t s = (cudaStream_t)stream;
+  dim3 grid((Ec + 3) / 4), block(128);
+#define CALL(LM, MM)                                                                                          \
+  {                                                                                                           \
+    OpBufs<LM> o{{a0, a1, a2}};                                                                               \
+    if (bf16_out)                                                                                             \
+      rotate_in_fwd_kernel<LM, MM, 16, __nv_bfloat16><<<grid, block, 0, s>>>(x_src, x_dst, src, dst, perm,    \
+                                                                             wig, rad, rad_ld, o, e0, Ec);    \
+    else                                                                                                      \
+      rotate_in_fwd_kernel<LM, MM, 16, float><<<grid, block, 0, s>>>(x_src, x_dst, src, dst, perm, wig, rad,  \
+                                                                     rad_ld, o, e0, Ec);                      \
+  }
+  DISPATCH_LM(lmax, mmax, CALL)
+#undef CALL
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+extern "C" int efl_rotate_in_bwd(int lmax, int mmax, int C, int bf16_in, const float* x_src, const float* x_dst,
+                                 const int* src, const int* dst, const int* perm, const float* wig,
+                                 const float* rad, int rad_ld, const void* da0, const void* da1, const void* da2,
+                                 float* drad, float* dxe, int e0, int Ec, void* stream) {
+  if (Ec <= 0) return EFL_OK;
+  EFL_REQUIRE(C == 16, "efl_rotate_in_bwd: sphere_channels must be 16");
+  cudaStream_t s = (cudaStream_t)stream;
+  dim3 grid((Ec + 3) / 4), block(128);
+#define CALL(LM, MM)                                                                                           \
+  {                                                                                                            \
+    OpBufs<LM> o{{(void*)da0, (void*)da1, (void*)da2}};                                                        \
+    if (bf16_in)                                                                                               \
+      rotate_in_bwd_kernel<LM, MM, 16, __nv_bfloat16><<<grid, block, 0, s>>>(x_src, x_dst, src, dst, perm,     \
+                                                                             wig, rad, rad_ld, o, drad, dxe,   \
+                                                                             e0, Ec);                          \
+    else                                                                                                       \
+      rotate_in_bwd_kernel<LM, MM, 16, float><<<grid, block, 0, s>>>(x_src, x_dst, src, dst, perm, wig, rad,   \
+                                                                     rad_ld, o, drad, dxe, e0, Ec);            \
+  }
+  DISPATCH_LM(lmax, mmax, CALL)
+#undef CALL
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+extern "C" int efl_segment_sum_rows(const float* buf, int L, int ldc, int coff, int C, const int* ptr,
+                                    const int* idx, float* out, int num_nodes, int accumulate, void* stream) {
+  if (num_nodes <= 0) return EFL_OK;
+  segment_sum_rows_kernel<<<num_nodes, 256, 0, (cudaStream_t)stream>>>(buf, L * ldc, ldc, coff, C, L, ptr, idx, out,
+                                                                        accumulate);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+extern "C" int efl_rotate_back_aggregate_fwd(int lmax, int mmax, int heads, int value_ch, int bf16_in,
+                                             const void* v0, const void* v1, const void* v2, const float* alpha,
+                                             const int* rowptr, const int* perm, const float* wig, float* out,
+                                             int n0, int n1, int e0, void* stream) {
+  if (n1 <= n0) return EFL_OK;
+  EFL_REQUIRE(heads * value_ch == 112 && value_ch == 16, "efl_rotate_back_aggregate_fwd: needs heads*value == 112, value == 16");
+  cudaStream_t s = (cudaStream_t)stream;
+  dim3 grid(n1 - n0), block(128);
+#define CALL(LM, MM)                                                                                           \
+  {                                                                                                            \
+    OpBufs<LM> o{{(void*)v0, (void*)v1, (void*)v2}};                                                           \
+    if (bf16_in)                                                                                               \
+      rotate_back_agg_fwd_kernel<LM, MM, 112, 16, __nv_bfloat16><<<grid, block, 0, s>>>(o, alpha, heads,       \
+                                                                                        rowptr, perm, wig,     \
+                                                                                        out, n0, e0);          \
+    else                                                                                                       \
+      rotate_back_agg_fwd_kernel<LM, MM, 112, 16, float><<<grid, block, 0, s>>>(o, alpha, heads, rowptr, perm, \
+                                                                                wig, out, n0, e0);             \
+  }
+  DISPATCH_LM(lmax, mmax, CALL)
+#undef CALL
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+extern "C" int efl_rotate_back_aggregate_bwd(int lmax, int mmax, int heads, int value_ch, int bf16,
+                                             const void* v0, const void* v1, const void* v2, void* dy0, void* dy1,
+                                             void* dy2, const float* alpha, const int* rowptr, const int* perm,
+                                             const float* wig, const float* dout, float* dalpha, int n0, int n1,
+                                             int e0, void* stream) {
+  if (n1 <= n0) return EFL_OK;
+  EFL_REQUIRE(heads * value_ch == 112 && value_ch == 16, "efl_rotate_back_aggregate_bwd: needs heads*value == 112, value == 16");
+  cudaStream_t s = (cudaStream_t)stream;
+  dim3 grid(n1 - n0), block(128);
+#define CALL(LM, MM)                                                                                           \
+  {                                                                                                            \
+    OpBufs<LM> vi{{(void*)v0, (void*)v1, (void*)v2}};                                                          \
+    OpBufs<LM> dyo{{dy0, dy1, dy2}};                                                                           \
+    if (bf16)                                                                                                  \
+      rotate_back_agg_bwd_kernel<LM, MM, 112, 16, __nv_bfloat16, __nv_bfloat16><<<grid, block, 0, s>>>(        \
+          vi, dyo, alpha, heads, rowptr, perm, wig, dout, dalpha, n0, e0);                                     \
+    else                                                                                                       \
+      rotate_back_agg_bwd_kernel<LM, MM, 112, 16, float, float><<<grid, block, 0, s>>>(                        \
+          vi, dyo, alpha, heads, rowptr, perm, wig, dout, dalpha, n0, e0);                                     \
+  }
+  DISPATCH_LM(lmax, mmax, CALL)
+#undef CALL
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+extern "C" int efl_edge_degree_fwd(int lmax, int mmax, int C, const float* m0, const int* rowptr, const int* perm,
+                                   const float* wig, float rescale_factor, float* out, int Nt, void* stream) {
+  if (Nt <= 0) return EFL_OK;
+  EFL_REQUIRE(C == 16, "efl_edge_degree_fwd: sphere_channels must be 16");
+  cudaStream_t s = (cudaStream_t)stream;
+  dim3 grid((Nt + 3) / 4), block(128);
+#define CALL(LM, MM) edge_degree_fwd_kernel<LM, MM, 16><<<grid, block, 0, s>>>(m0, rowptr, perm, wig, 1.0f / rescale_factor, out, Nt);
+  DISPATCH_LM(lmax, mmax, CALL)
+#undef CALL
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+extern "C" int efl_edge_degree_bwd(int lmax, int mmax, int C, const float* dout, const int* dst_orig,
+                                   const float* wig, float rescale_factor, float* dm0, int E, void* stream) {
+  if (E <= 0) return EFL_OK;
+  EFL_REQUIRE(C == 16, "efl_edge_degree_bwd: sphere_channels must be 16");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int total = E * 16;
+  dim3 grid((total + 255) / 256), block(256);
+#define CALL(LM, MM) edge_degree_bwd_kernel<LM, MM, 16><<<grid, block, 0, s>>>(dout, dst_orig, wig, 1.0f / rescale_factor, dm0, E);
+  DISPATCH_LM(lmax, mmax, CALL)
+#undef CALL
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}

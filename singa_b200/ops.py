@@ -1,0 +1,491 @@
+"""Host-side orchestration of the EF_layers CUDA kernels (autograd wrappers).
+
+Everything numerical happens in libefl.so through the C ABI (``_lib.call``); this
+file only owns buffers, the destination-sorted CSR, edge chunking and the
+recompute-in-backward policy (SURVEY.md 8a "saved-for-backward note"): the edge
+activations of one attention layer at config 2 (0.9 M edges) would be ~40 GB, so
+forward keeps nothing per edge except logits/alpha ([E, heads]) and backward
+re-runs the forward kernels chunk by chunk before the gradient kernels.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from . import so3_constants as sc
+from ._lib import LIB, call, check_cuda, ptr
+
+# GEMM operand precision of the SO(2) linear maps: "fp32" (SIMT, parity mode) or
+# "bf16" (tcgen05 tensor cores, fp32 accumulate).  Set through set_precision().
+_PRECISION = "fp32"
+MAX_CHUNK_EDGES = 65536
+
+
+def set_precision(mode: str) -> None:
+    global _PRECISION
+    if mode not in ("fp32", "bf16"):
+        raise ValueError("precision must be 'fp32' or 'bf16'")
+    _PRECISION = mode
+
+
+def get_precision() -> str:
+    return _PRECISION
+
+
+# ---------------------------------------------------------------------------
+# constants on device
+# ---------------------------------------------------------------------------
+_CONST_CACHE: dict = {}
+
+
+def jd_device(lmax: int, device) -> torch.Tensor:
+    """Concatenated J_l blocks (row-major, l = 0..lmax) as fp32 on ``device``."""
+    key = ("jd", lmax, str(device))
+    if key not in _CONST_CACHE:
+        flat = np.concatenate([sc.j_matrix(l).reshape(-1) for l in range(lmax + 1)])
+        _CONST_CACHE[key] = torch.tensor(flat, dtype=torch.float32, device=device)
+    return _CONST_CACHE[key]
+
+
+def wigner_size(lmax: int, mmax: int) -> int:
+    return sum(min(2 * l + 1, 2 * mmax + 1) * (2 * l + 1) for l in range(lmax + 1))
+
+
+def wigner_from_rotmat(rot: torch.Tensor, lmax: int, mmax: int) -> torch.Tensor:
+    """[E,3,3] edge frames -> kept Wigner rows [E, WSZ] (set_wigner, EF_layers.py:485-528)."""
+    check_cuda(rot)
+    rot = rot.detach().to(torch.float32).contiguous()
+    E = rot.shape[0]
+    wig = torch.empty(E, wigner_size(lmax, mmax), dtype=torch.float32, device=rot.device)
+    call("efl_wigner_from_rotmat", lmax, mmax, ptr(rot), ptr(jd_device(lmax, rot.device)), ptr(wig), E)
+    return wig
+
+
+# ---------------------------------------------------------------------------
+# destination-sorted CSR
+# ---------------------------------------------------------------------------
+@dataclass
+class EdgeCSR:
+    num_src: int
+    num_dst: int
+    num_edges: int
+    perm: torch.Tensor        # int32 [E]  sorted position -> original edge id (stable in edge id)
+    rowptr: torch.Tensor      # int32 [num_dst + 1]
+    src_sorted: torch.Tensor  # int32 [E]
+    dst_sorted: torch.Tensor  # int32 [E]
+    dst_orig: torch.Tensor    # int32 [E]  original order
+    src_ptr: torch.Tensor     # int32 [num_src + 1]
+    src_idx: torch.Tensor     # int32 [E]  sorted positions grouped by source (stable)
+    chunks: list = field(default_factory=list)  # (n0, n1, e0, e1), edges of whole destinations
+
+
+def build_csr(edge_index: torch.Tensor, num_src: int, num_dst: int, max_chunk_edges: int = None) -> EdgeCSR:
+    """Stable sort of the edge list by destination (edge_index[1]) plus the source-side
+    grouping used by the backward of the gather.  Row 0 = source, row 1 = target
+    (aggregation is over row 1: EF_layers.py:143-145, 1180, 1197-1199)."""
+    check_cuda(edge_index)
+    E = edge_index.shape[1]
+    src, dst = edge_index[0], edge_index[1]
+    dst_s, perm = torch.sort(dst, stable=True)
+    src_s = src[perm]
+    counts = torch.bincount(dst, minlength=num_dst)
+    rowptr = torch.zeros(num_dst + 1, dtype=torch.int64, device=dst.device)
+    rowptr[1:] = torch.cumsum(counts, 0)
+    _, src_idx = torch.sort(src_s, stable=True)
+    scount = torch.bincount(src, minlength=num_src)
+    src_ptr = torch.zeros(num_src + 1, dtype=torch.int64, device=dst.device)
+    src_ptr[1:] = torch.cumsum(scount, 0)
+    i32 = lambda t: t.to(torch.int32).contiguous()
+    csr = EdgeCSR(num_src, num_dst, E, i32(perm), i32(rowptr), i32(src_s), i32(dst_s), i32(dst), i32(src_ptr),
+                  i32(src_idx))
+    csr.chunks = plan_chunks(rowptr.cpu().numpy(), max_chunk_edges or MAX_CHUNK_EDGES)
+    return csr
+
+
+def plan_chunks(rowptr: np.ndarray, max_edges: int) -> list:
+    """Greedy split of the destination range into chunks of whole destinations with at most
+    ``max_edges`` edges (a single destination with more edges gets a chunk of its own)."""
+    n = len(rowptr) - 1
+    chunks = []
+    n0 = 0
+    while n0 < n:
+        limit = rowptr[n0] + max_edges
+        n1 = int(np.searchsorted(rowptr, limit, side="right")) - 1
+        n1 = max(n1, n0 + 1)
+        n1 = min(n1, n)
+        chunks.append((n0, n1, int(rowptr[n0]), int(rowptr[n1])))
+        n0 = n1
+    return chunks
+
+
+# ---------------------------------------------------------------------------
+# helpers
+# ---------------------------------------------------------------------------
+def _interleave_rows(w: torch.Tensor) -> torch.Tensor:
+    """SO2_m_Convolution weight [2*half, K] (rows: real block then imag block, EF_layers.py:723-724)
+    -> rows interleaved (real_q, imag_q) so the complex combine is local to a column pair."""
+    half = w.shape[0] // 2
+    return torch.stack((w[:half], w[half:]), dim=1).reshape(2 * half, w.shape[1]).contiguous()
+
+
+def _deinterleave_rows(w: torch.Tensor) -> torch.Tensor:
+    half = w.shape[0] // 2
+    v = w.view(half, 2, w.shape[1])
+    return torch.cat((v[:, 0], v[:, 1]), dim=0).contiguous()
+
+
+class _Ptrs:
+    """Keeps ctypes arrays alive for the row-map arguments of the S2 kernels."""
+
+    def __init__(self, bases, strides, first):
+        n = len(bases)
+        self.n = n
+        self.b = (ctypes.c_void_p * n)(*bases)
+        self.s = (ctypes.c_longlong * n)(*strides)
+        self.f = (ctypes.c_int * (n + 1))(*first)
+
+    def args(self):
+        return (self.n, ctypes.cast(self.b, ctypes.c_void_p), ctypes.cast(self.s, ctypes.c_void_p),
+                ctypes.cast(self.f, ctypes.c_void_p))
+
+
+def _gemm_nt(epi, A, B, bias, C, ldc, C0, ldc0, nsplit, M, N, K):
+    if A.dtype == torch.float32:
+        call("efl_gemm_nt_f32", epi, ptr(A), A.stride(0), ptr(B), B.stride(0), ptr(bias), ptr(C), ldc, ptr(C0), ldc0,
+             nsplit, M, N, K)
+    else:
+        from . import tc_gemm
+        tc_gemm.gemm_nt(epi, A, B, bias, C, ldc, C0, ldc0, nsplit, M, N, K)
+
+
+def _gemm_tn(A, B, C, accumulate, Mred, N1, N2):
+    if A.dtype == torch.float32:
+        splits = LIB.efl_gemm_tn_splits(Mred)
+        ws = torch.empty(splits * N1 * N2, dtype=torch.float32, device=A.device)
+        call("efl_gemm_tn_f32", ptr(A), A.stride(0), ptr(B), B.stride(0), ptr(C), C.stride(0), int(accumulate), ptr(ws),
+             Mred, N1, N2)
+    else:
+        from . import tc_gemm
+        tc_gemm.gemm_tn(A, B, C, accumulate, Mred, N1, N2)
+
+
+def _colsum(X, rows, cols, out, accumulate):
+    ws = torch.empty(((rows + 4095) // 4096 + 1) * cols, dtype=torch.float32, device=X.device)
+    call("efl_colsum", int(X.dtype == torch.bfloat16), ptr(X), X.stride(0), rows, cols, ptr(out), int(accumulate),
+         ptr(ws))
+
+
+# ---------------------------------------------------------------------------
+# the fused edge path of SO2EquivariantGraphAttention
+# ---------------------------------------------------------------------------
+@dataclass
+class AttnDims:
+    lmax: int
+    mmax: int
+    C: int          # sphere channels
+    H: int          # attn hidden channels
+    heads: int
+    alpha_ch: int
+    value_ch: int
+
+    @property
+    def ms(self):  # rows per order
+        return [self.lmax + 1 - m for m in range(self.mmax + 1)]
+
+    @property
+    def M(self):
+        return self.ms[0] + 2 * sum(self.ms[1:])
+
+    @property
+    def first(self):  # m-primary row ranges: m0 | +1 | -1 | +2 | -2
+        f = [0, self.ms[0]]
+        for m in range(1, self.mmax + 1):
+            f.append(f[-1] + self.ms[m])
+            f.append(f[-1] + self.ms[m])
+        return f
+
+
+class _Workspace:
+    """Chunk-sized edge buffers.  Operand layout per order m: dense [rows_m*Ec, ms[m]*CH]."""
+
+    def __init__(self, d: AttnDims, Ec: int, dtype, device, backward: bool):
+        C2, H, VH = 2 * d.C, d.H, d.heads * d.value_ch
+        self.extra_w = d.heads * d.alpha_ch + H
+        e = lambda r, c, dt=dtype: torch.empty(max(r, 1), c, dtype=dt, device=device)
+        rows = [Ec] + [2 * Ec] * d.mmax
+        self.A = [e(rows[m], d.ms[m] * C2) for m in range(d.mmax + 1)]
+        self.extra = e(Ec, self.extra_w, torch.float32)
+        self.Hb = [e(rows[m], d.ms[m] * H) for m in range(d.mmax + 1)]
+        self.B = [e(rows[m], d.ms[m] * H) for m in range(d.mmax + 1)]
+        self.V = [e(rows[m], d.ms[m] * VH) for m in range(d.mmax + 1)]
+        if backward:
+            self.dY2 = [e(Ec, d.ms[0] * VH)] + [e(2 * Ec, 2 * d.ms[m] * VH) for m in range(1, d.mmax + 1)]
+            self.dB = [e(rows[m], d.ms[m] * H) for m in range(d.mmax + 1)]
+            self.dY1 = [e(Ec, self.extra_w + d.ms[0] * H)] + [e(2 * Ec, 2 * d.ms[m] * H) for m in range(1, d.mmax + 1)]
+            self.dA = [e(rows[m], d.ms[m] * C2) for m in range(d.mmax + 1)]
+
+
+def _rowmap_plain(bufs, d: AttnDims, CH, esz_offset=0, col_offset0=0, ld0=None):
+    """Row map over plain split buffers: m0 | +1 | -1 | +2 | -2."""
+    bases, strides = [], []
+    es = bufs[0].element_size()
+    ld0 = ld0 if ld0 is not None else d.ms[0] * CH
+    bases.append(bufs[0].data_ptr() + col_offset0 * es)
+    strides.append(ld0)
+    for m in range(1, d.mmax + 1):
+        K = d.ms[m] * CH
+        bases += [bufs[m].data_ptr(), bufs[m].data_ptr() + K * es]
+        strides += [2 * K, 2 * K]
+    return _Ptrs(bases, strides, d.first)
+
+
+def _rowmap_dup(bufs, d: AttnDims, CH, col_offset0, ld0):
+    bases, strides = [], []
+    es = bufs[0].element_size()
+    bases.append(bufs[0].data_ptr() + col_offset0 * es)
+    strides.append(ld0)
+    for m in range(1, d.mmax + 1):
+        K2 = 2 * d.ms[m] * CH
+        bases += [bufs[m].data_ptr(), 0]
+        strides += [2 * K2, 0]
+    return _Ptrs(bases, strides, d.first)
+
+
+class _Weights:
+    """GEMM-ready derived copies of the SO(2) convolution weights (never the stored parameters)."""
+
+    def __init__(self, conv_w, dtype, need_t: bool):
+        # conv_w: [W_m0, b_m0, W_m1, W_m2, ...]
+        self.w0 = conv_w[0].detach().to(dtype).contiguous()
+        self.b0 = conv_w[1].detach().to(torch.float32).contiguous()
+        self.wm = [_interleave_rows(w.detach()).to(dtype) for w in conv_w[2:]]
+        if need_t:
+            self.w0t = self.w0.t().contiguous()
+            self.wmt = [w.t().contiguous() for w in self.wm]
+
+
+def _chunk_forward(d: AttnDims, ws: _Workspace, w1: _Weights, w2: _Weights, x_src, x_dst, rad, csr: EdgeCSR, wig,
+                   ln_w, ln_b, adot, logits, alpha, grids, chunk, out):
+    n0, n1, e0, e1 = chunk
+    Ec = e1 - e0
+    if Ec == 0:
+        if out is not None:
+            out[n0:n1].zero_()
+        return
+    C2, H, VH = 2 * d.C, d.H, d.heads * d.value_ch
+    bf16 = int(ws.A[0].dtype == torch.bfloat16)
+    call("efl_rotate_in_fwd", d.lmax, d.mmax, d.C, bf16, ptr(x_src), ptr(x_dst), ptr(csr.src_sorted),
+         ptr(csr.dst_sorted), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.A[0]), ptr(ws.A[1]),
+         ptr(ws.A[2]), e0, Ec)
+    # so2_conv_1 (EF_layers.py:807-875)
+    _gemm_nt(1, ws.A[0], w1.w0, w1.b0, ws.Hb[0], d.ms[0] * H, ws.extra, ws.extra_w, ws.extra_w, Ec,
+             ws.extra_w + d.ms[0] * H, d.ms[0] * C2)
+    for m in range(1, d.mmax + 1):
+        _gemm_nt(2, ws.A[m], w1.wm[m - 1], None, ws.Hb[m], d.ms[m] * H, None, 0, 0, 2 * Ec, 2 * d.ms[m] * H,
+                 d.ms[m] * C2)
+    call("efl_alpha_logits_fwd", ptr(ws.extra), ws.extra_w, d.heads, d.alpha_ch, ptr(ln_w), ptr(ln_b), ptr(adot),
+         logits.data_ptr() + e0 * d.heads * 4, Ec)
+    call("efl_segment_softmax_fwd", ptr(logits), d.heads, ptr(csr.rowptr), ptr(alpha), n0, n1)
+    to_g, from_g, G = grids
+    rin = _rowmap_plain(ws.Hb, d, H)
+    rout = _rowmap_plain(ws.B, d, H)
+    call("efl_s2act_fwd", d.M, G, H, bf16, bf16, *rin.args(), *rout.args(),
+         ws.extra.data_ptr() + d.heads * d.alpha_ch * 4, ws.extra_w, ptr(to_g), ptr(from_g), Ec)
+    # so2_conv_2
+    _gemm_nt(0, ws.B[0], w2.w0, w2.b0, ws.V[0], d.ms[0] * VH, None, 0, 0, Ec, d.ms[0] * VH, d.ms[0] * H)
+    for m in range(1, d.mmax + 1):
+        _gemm_nt(2, ws.B[m], w2.wm[m - 1], None, ws.V[m], d.ms[m] * VH, None, 0, 0, 2 * Ec, 2 * d.ms[m] * VH,
+                 d.ms[m] * H)
+    if out is not None:
+        call("efl_rotate_back_aggregate_fwd", d.lmax, d.mmax, d.heads, d.value_ch, bf16, ptr(ws.V[0]), ptr(ws.V[1]),
+             ptr(ws.V[2]), ptr(alpha), ptr(csr.rowptr), ptr(csr.perm), ptr(wig), ptr(out), n0, n1, e0)
+
+
+class EdgeAttentionFunction(torch.autograd.Function):
+    """x_src, x_dst, rad, conv1 (W0,b0,W1,W2), alpha LN (w,b), alpha_dot, conv2 (W0,b0,W1,W2)
+    -> aggregated messages [num_dst, L, heads*value] (input of ``proj``)."""
+
+    @staticmethod
+    def forward(ctx, x_src, x_dst, rad, c1w0, c1b0, c1w1, c1w2, ln_w, ln_b, adot, c2w0, c2b0, c2w1, c2w2, csr, wig,
+                grids, dims):
+        d: AttnDims = dims
+        check_cuda(x_src, x_dst, rad, wig)
+        assert d.mmax == 2, "the edge path is built for mmax == 2"
+        x_src = x_src.contiguous()
+        x_dst = x_dst.contiguous()
+        rad = rad.contiguous()
+        dev = x_dst.device
+        dtype = torch.float32 if _PRECISION == "fp32" else torch.bfloat16
+        E = csr.num_edges
+        L = (d.lmax + 1) ** 2
+        out = torch.empty(csr.num_dst, L, d.heads * d.value_ch, dtype=torch.float32, device=dev)
+        logits = torch.empty(max(E, 1), d.heads, dtype=torch.float32, device=dev)
+        alpha = torch.empty(max(E, 1), d.heads, dtype=torch.float32, device=dev)
+        maxE = max((c[3] - c[2] for c in csr.chunks), default=0)
+        ws = _Workspace(d, maxE, dtype, dev, backward=False)
+        w1 = _Weights([c1w0, c1b0, c1w1, c1w2], dtype, need_t=False)
+        w2 = _Weights([c2w0, c2b0, c2w1, c2w2], dtype, need_t=False)
+        lw, lb, ad = ln_w.detach().contiguous(), ln_b.detach().contiguous(), adot.detach().contiguous()
+        for chunk in csr.chunks:
+            _chunk_forward(d, ws, w1, w2, x_src, x_dst, rad, csr, wig, lw, lb, ad, logits, alpha, grids, chunk, out)
+        ctx.save_for_backward(x_src, x_dst, rad, c1w0, c1b0, c1w1, c1w2, ln_w, ln_b, adot, c2w0, c2b0, c2w1, c2w2,
+                              logits, alpha)
+        ctx.misc = (csr, wig, grids, d, dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (x_src, x_dst, rad, c1w0, c1b0, c1w1, c1w2, ln_w, ln_b, adot, c2w0, c2b0, c2w1, c2w2, logits,
+         alpha) = ctx.saved_tensors
+        csr, wig, grids, d, dtype = ctx.misc
+        dev = x_dst.device
+        dout = dout.contiguous().to(torch.float32)
+        E = csr.num_edges
+        L = (d.lmax + 1) ** 2
+        C2, H, VH = 2 * d.C, d.H, d.heads * d.value_ch
+        bf16 = int(dtype == torch.bfloat16)
+        maxE = max((c[3] - c[2] for c in csr.chunks), default=0)
+        ws = _Workspace(d, maxE, dtype, dev, backward=True)
+        w1 = _Weights([c1w0, c1b0, c1w1, c1w2], dtype, need_t=True)
+        w2 = _Weights([c2w0, c2b0, c2w1, c2w2], dtype, need_t=True)
+        lw, lb, ad = ln_w.detach().contiguous(), ln_b.detach().contiguous(), adot.detach().contiguous()
+        f32 = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
+        g_c1w0, g_c1b0 = f32(*c1w0.shape), f32(*c1b0.shape)
+        g_c1wm = [f32(*c1w1.shape), f32(*c1w2.shape)]       # interleaved row order until the end
+        g_c2w0, g_c2b0 = f32(*c2w0.shape), f32(*c2b0.shape)
+        g_c2wm = [f32(*c2w1.shape), f32(*c2w2.shape)]
+        drad = torch.zeros_like(rad)
+        dxe = torch.empty(max(E, 1), L, C2, dtype=torch.float32, device=dev)
+        dalpha = torch.empty(max(E, 1), d.heads, dtype=torch.float32, device=dev)
+        dlogits = torch.empty(max(E, 1), d.heads, dtype=torch.float32, device=dev)
+        nblk = 148
+        stride = d.heads * d.alpha_ch + 2 * d.alpha_ch
+        part_all = f32(stride)
+        part = torch.empty(nblk, stride, dtype=torch.float32, device=dev)
+        to_g, from_g, G = grids
+        first = True
+        for chunk in csr.chunks:
+            n0, n1, e0, e1 = chunk
+            Ec = e1 - e0
+            if Ec == 0:
+                continue
+            _chunk_forward(d, ws, w1, w2, x_src, x_dst, rad, csr, wig, lw, lb, ad, logits, alpha, grids, chunk, None)
+            # ---- rotate-back + aggregate backward -> dV (dup layout), d alpha
+            call("efl_rotate_back_aggregate_bwd", d.lmax, d.mmax, d.heads, d.value_ch, bf16, ptr(ws.V[0]),
+                 ptr(ws.V[1]), ptr(ws.V[2]), ptr(ws.dY2[0]), ptr(ws.dY2[1]), ptr(ws.dY2[2]), ptr(alpha),
+                 ptr(csr.rowptr), ptr(csr.perm), ptr(wig), ptr(dout), ptr(dalpha), n0, n1, e0)
+            # ---- so2_conv_2 backward
+            acc = not first
+            _gemm_tn(ws.dY2[0], ws.B[0], g_c2w0, acc, Ec, d.ms[0] * VH, d.ms[0] * H)
+            _colsum(ws.dY2[0], Ec, d.ms[0] * VH, g_c2b0, acc)
+            _gemm_nt(0, ws.dY2[0], w2.w0t, None, ws.dB[0], d.ms[0] * H, None, 0, 0, Ec, d.ms[0] * H, d.ms[0] * VH)
+            for m in range(1, d.mmax + 1):
+                _gemm_tn(ws.dY2[m], ws.B[m], g_c2wm[m - 1], acc, 2 * Ec, 2 * d.ms[m] * VH, d.ms[m] * H)
+                _gemm_nt(0, ws.dY2[m], w2.wmt[m - 1], None, ws.dB[m], d.ms[m] * H, None, 0, 0, 2 * Ec, d.ms[m] * H,
+                         2 * d.ms[m] * VH)
+            # ---- S2 activation backward -> dY1 (m0: [d alpha_in | d gate | d hidden rows]; m>0 dup layout)
+            rin = _rowmap_plain(ws.Hb, d, H)
+            rdin = _rowmap_plain(ws.dB, d, H)
+            ld1 = ws.extra_w + d.ms[0] * H
+            rdout = _rowmap_dup(ws.dY1, d, H, ws.extra_w, ld1)
+            es = ws.dY1[0].element_size()
+            call("efl_s2act_bwd", d.M, G, H, bf16, bf16, *rin.args(), *rdin.args(), *rdout.args(), 1,
+                 ws.extra.data_ptr() + d.heads * d.alpha_ch * 4, ws.extra_w,
+                 ws.dY1[0].data_ptr() + d.heads * d.alpha_ch * es, ld1, ptr(to_g), ptr(from_g), Ec)
+            # ---- softmax + alpha-logit backward -> first heads*alpha columns of dY1[0]
+            call("efl_segment_softmax_bwd", ptr(alpha), ptr(dalpha), d.heads, ptr(csr.rowptr), ptr(dlogits), n0, n1)
+            call("efl_alpha_logits_bwd", ptr(ws.extra), ws.extra_w, d.heads, d.alpha_ch, ptr(lw), ptr(lb), ptr(ad),
+                 dlogits.data_ptr() + e0 * d.heads * 4, ptr(ws.dY1[0]), ld1, bf16, ptr(part), nblk, Ec)
+            part_all += part.sum(dim=0)
+            # ---- so2_conv_1 backward
+            _gemm_tn(ws.dY1[0], ws.A[0], g_c1w0, acc, Ec, ld1, d.ms[0] * C2)
+            _colsum(ws.dY1[0], Ec, ld1, g_c1b0, acc)
+            _gemm_nt(0, ws.dY1[0], w1.w0t, None, ws.dA[0], d.ms[0] * C2, None, 0, 0, Ec, d.ms[0] * C2, ld1)
+            for m in range(1, d.mmax + 1):
+                _gemm_tn(ws.dY1[m], ws.A[m], g_c1wm[m - 1], acc, 2 * Ec, 2 * d.ms[m] * H, d.ms[m] * C2)
+                _gemm_nt(0, ws.dY1[m], w1.wmt[m - 1], None, ws.dA[m], d.ms[m] * C2, None, 0, 0, 2 * Ec,
+                         d.ms[m] * C2, 2 * d.ms[m] * H)
+            # ---- rotate-in backward -> d rad, per-edge d x
+            call("efl_rotate_in_bwd", d.lmax, d.mmax, d.C, bf16, ptr(x_src), ptr(x_dst), ptr(csr.src_sorted),
+                 ptr(csr.dst_sorted), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.dA[0]), ptr(ws.dA[1]),
+                 ptr(ws.dA[2]), ptr(drad), ptr(dxe), e0, Ec)
+            first = False
+        # ---- gather backward: deterministic segment sums over the dst CSR and the src grouping
+        dx_dst = torch.empty_like(x_dst)
+        dx_src = torch.empty_like(x_src)
+        call("efl_segment_sum_rows", ptr(dxe), L, C2, d.C, d.C, ptr(csr.rowptr), None, ptr(dx_dst), csr.num_dst, 0)
+        call("efl_segment_sum_rows", ptr(dxe), L, C2, 0, d.C, ptr(csr.src_ptr), ptr(csr.src_idx), ptr(dx_src),
+             csr.num_src, 0)
+        ha = d.heads * d.alpha_ch
+        g_adot = part_all[:ha].view(d.heads, d.alpha_ch)
+        g_lnw = part_all[ha:ha + d.alpha_ch]
+        g_lnb = part_all[ha + d.alpha_ch:]
+        return (dx_src, dx_dst, drad, g_c1w0, g_c1b0, _deinterleave_rows(g_c1wm[0]), _deinterleave_rows(g_c1wm[1]),
+                g_lnw, g_lnb, g_adot, g_c2w0, g_c2b0, _deinterleave_rows(g_c2wm[0]), _deinterleave_rows(g_c2wm[1]),
+                None, None, None, None)
+
+
+# ---------------------------------------------------------------------------
+# EdgeDegreeEmbedding tail
+# ---------------------------------------------------------------------------
+class EdgeDegreeFunction(torch.autograd.Function):
+    """m0 [E, (lmax+1)*C] (radial MLP output, original edge order) -> [num_dst, L, C]."""
+
+    @staticmethod
+    def forward(ctx, m0, csr, wig, lmax, mmax, C, rescale_factor):
+        check_cuda(m0, wig)
+        m0 = m0.contiguous()
+        L = (lmax + 1) ** 2
+        out = torch.empty(csr.num_dst, L, C, dtype=torch.float32, device=m0.device)
+        call("efl_edge_degree_fwd", lmax, mmax, C, ptr(m0), ptr(csr.rowptr), ptr(csr.perm), ptr(wig),
+             float(rescale_factor), ptr(out), csr.num_dst)
+        ctx.misc = (csr, wig, lmax, mmax, C, rescale_factor, m0.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        csr, wig, lmax, mmax, C, rf, shape = ctx.misc
+        dout = dout.contiguous()
+        dm0 = torch.empty(shape, dtype=torch.float32, device=dout.device)
+        call("efl_edge_degree_bwd", lmax, mmax, C, ptr(dout), ptr(csr.dst_orig), ptr(wig), float(rf), ptr(dm0),
+             csr.num_edges)
+        return dm0, None, None, None, None, None, None
+
+
+# ---------------------------------------------------------------------------
+# node-level separable S2 activation (FeedForwardNetwork)
+# ---------------------------------------------------------------------------
+class NodeS2ActFunction(torch.autograd.Function):
+    """(gate [N, CH], x [N, L, CH]) -> SeparableS2Activation output [N, L, CH] on the (lmax, lmax) grid."""
+
+    @staticmethod
+    def forward(ctx, gate, x, to_g, from_g):
+        check_cuda(gate, x)
+        gate = gate.contiguous()
+        x = x.contiguous()
+        N, Lc, CH = x.shape
+        G = to_g.shape[0]
+        y = torch.empty_like(x)
+        pin = _Ptrs([x.data_ptr()], [Lc * CH], [0, Lc])
+        pout = _Ptrs([y.data_ptr()], [Lc * CH], [0, Lc])
+        call("efl_s2act_fwd", Lc, G, CH, 0, 0, *pin.args(), *pout.args(), ptr(gate), CH, ptr(to_g), ptr(from_g), N)
+        ctx.save_for_backward(gate, x, to_g, from_g)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        gate, x, to_g, from_g = ctx.saved_tensors
+        dy = dy.contiguous()
+        N, Lc, CH = x.shape
+        G = to_g.shape[0]
+        dx = torch.empty_like(x)
+        dgate = torch.empty_like(gate)
+        pin = _Ptrs([x.data_ptr()], [Lc * CH], [0, Lc])
+        pdin = _Ptrs([dy.data_ptr()], [Lc * CH], [0, Lc])
+        pdout = _Ptrs([dx.data_ptr()], [Lc * CH], [0, Lc])
+        call("efl_s2act_bwd", Lc, G, CH, 0, 0, *pin.args(), *pdin.args(), *pdout.args(), 0, ptr(gate), CH, ptr(dgate),
+             CH, ptr(to_g), ptr(from_g), N)
+        return dgate, dx, None, None

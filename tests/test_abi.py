@@ -1,0 +1,38 @@
+"""The C-ABI library loads on a machine without a GPU and exports every symbol include/efl.h declares."""
+import ctypes
+import os
+import re
+
+from tests.conftest import ROOT
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "efl.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(efl_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib_path = os.path.join(ROOT, "singa_b200", "libefl.so")
+    assert os.path.isfile(lib_path), "run __graft_entry__.build() first"
+    lib = ctypes.CDLL(lib_path)
+    names = declared_symbols()
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/efl.h but not exported"
+
+
+def test_python_binding_covers_header():
+    from singa_b200 import _lib
+    bound = set(_lib.SIGNATURES) | {"efl_version", "efl_last_error_string", "efl_gemm_tn_splits", "efl_device_cc"}
+    assert set(declared_symbols()) <= bound | {"efl_tc_selftest"} or set(declared_symbols()) - bound == set(), \
+        set(declared_symbols()) - bound
+    assert _lib.LIB.efl_version() >= 100
+
+
+def test_ops_refuse_cpu_tensors():
+    import pytest
+    import torch
+    from singa_b200 import _lib, ops
+    with pytest.raises(_lib.EflError):
+        ops.wigner_from_rotmat(torch.eye(3).repeat(4, 1, 1), 6, 2)

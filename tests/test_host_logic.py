@@ -1,0 +1,91 @@
+"""Host-side logic that needs no GPU: state_dict surface, chunk planning, weight re-layouts, synthetic inputs."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_loader as rl
+from singa_b200 import synthetic as syn
+from singa_b200.embedding import DEFAULT_CONFIG, EquivariantEmbedding, pack_feature_bits
+from tests.conftest import ROOT
+
+
+def test_state_dict_surface_matches_reference_listing():
+    """Names, shapes and dtypes of all 2979 entries (115 parameters + 2864 buffers)."""
+    listing = json.load(open(os.path.join(ROOT, "tests", "golden", "state_dict_surface.json")))
+    model = EquivariantEmbedding(DEFAULT_CONFIG, device="cpu")
+    sd = model.state_dict()
+    assert len(sd) == len(listing) == 2979
+    assert len(list(model.named_parameters())) == 115
+    for name, (shape, dtype) in listing.items():
+        assert name in sd, name
+        assert list(sd[name].shape) == shape and str(sd[name].dtype) == dtype, name
+    assert sum(p.numel() for p in model.parameters()) == 10671552
+
+
+@pytest.mark.skipif(not rl.reference_available(), reason="needs /root/reference (build container only)")
+def test_same_seed_gives_reference_initialisation():
+    ef, emb = rl.load_reference()
+    torch.manual_seed(0)
+    ref = emb.EquivariantEmbedding(rl.EasyDict(rl.DEFAULT_EMBEDDING_CONFIG), device="cpu")
+    torch.manual_seed(0)
+    mine = EquivariantEmbedding(DEFAULT_CONFIG, device="cpu")
+    a, b = ref.state_dict(), mine.state_dict()
+    assert set(a) == set(b)
+    for k in a:
+        if a[k].dtype.is_floating_point:
+            assert float((a[k] - b[k]).abs().max()) < 1e-6, k
+        else:
+            assert torch.equal(a[k], b[k]), k
+    mine.load_state_dict(a, strict=True)
+
+
+def test_feature_bit_pack_equals_string_route():
+    rs = np.random.RandomState(0)
+    x = np.zeros((50, 59), dtype=np.float32)
+    x[:, -15:] = rs.randint(0, 2, size=(50, 15))
+    x[:, -8] = rs.uniform(-0.5, 0.5, size=50)
+    xt = torch.from_numpy(x)
+    expect = [int("".join(map(str, xt[i, -15:].type(torch.long).tolist())), 2) for i in range(50)]
+    assert pack_feature_bits(xt).tolist() == expect
+
+
+def test_chunk_plan_covers_all_destinations():
+    from singa_b200.ops import plan_chunks
+    rs = np.random.RandomState(1)
+    deg = rs.randint(0, 90, size=500)
+    deg[17] = 5000  # one destination above the limit
+    rowptr = np.concatenate([[0], np.cumsum(deg)])
+    chunks = plan_chunks(rowptr, 1000)
+    assert chunks[0][0] == 0 and chunks[-1][1] == 500
+    for (a0, a1, e0, e1), (b0, b1, f0, f1) in zip(chunks, chunks[1:]):
+        assert a1 == b0 and e1 == f0
+    for n0, n1, e0, e1 in chunks:
+        assert e0 == rowptr[n0] and e1 == rowptr[n1] and n1 > n0
+        assert e1 - e0 <= 1000 or n1 - n0 == 1
+    assert plan_chunks(np.array([0, 0, 0]), 10) == [(0, 2, 0, 0)]
+
+
+def test_weight_interleave_roundtrip():
+    from singa_b200.ops import _deinterleave_rows, _interleave_rows
+    w = torch.arange(24.0).view(6, 4)
+    wi = _interleave_rows(w)
+    assert torch.equal(wi[0], w[0]) and torch.equal(wi[1], w[3]) and torch.equal(wi[2], w[1])
+    assert torch.equal(_deinterleave_rows(wi), w)
+
+
+def test_synthetic_complex_shape():
+    g = syn.make_complex(0, n_protein=120, n_ligand=15)
+    assert g["ei_pp"].shape[0] == 2 and g["ei_pp"].dtype == torch.int64
+    src, dst = g["ei_pp"]
+    d = (g["pos_p"][src] - g["pos_p"][dst]).norm(dim=1)
+    assert float(d.max()) < 8.0 and float(d.min()) >= 1.19
+    assert torch.equal(g["ei_lp"][0], g["ei_pl"][1]) and torch.equal(g["ei_lp"][1], g["ei_pl"][0])
+    b = syn.collate([g, syn.make_complex(1, n_protein=80, n_ligand=10)])
+    assert b["z_p"].numel() == 200 and int(b["ei_pp"].max()) < 200 and b["ptr_p"].tolist() == [0, 120, 200]
+    # portable parameters are reproducible
+    p1 = syn.portable_parameters([("a.weight", (3, 4)), ("b.bias", (5,))], 3)
+    p2 = syn.portable_parameters([("b.bias", (5,)), ("a.weight", (3, 4))], 3)
+    assert torch.equal(p1["a.weight"], p2["a.weight"]) and torch.equal(p1["b.bias"], p2["b.bias"])
