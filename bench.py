@@ -1,0 +1,322 @@
+#!/usr/bin/env python
+"""bench.py -- EF_layers forward+backward throughput on synthetic CrossDocked-shaped complexes.
+
+One "step" = one pass of the hot path over one batch: EquivariantEmbedding forward (4 passes x 3 TransBlockV2
+layers: frames -> Wigner rows -> edge-degree embedding -> attention blocks -> norms) + backward of a fixed linear
+loss + gradient all-reduce (N>1) + Adam update.  Workload = BASELINE.json configs[1]: batch 32 complexes of
+~450 protein atoms, 8 A radius graph (~28 k edges each), lmax 6, mmax 2, per GPU (weak scaling).
+Metric: edges/s = directed edges of the batch (all four edge sets) pushed through the 3-layer stack, fwd+bwd, per
+second, summed over ranks.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--precision fp32|bf16]
+
+Prints ONE JSON line on rank 0 (see DESIGN.md "Measurement" for every key).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "EF_layers fwd+bwd edges/sec"
+UNIT = "edges/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default=os.environ.get("EFL_PRECISION", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--batch", type=int, default=32, help="complexes per GPU")
+    ap.add_argument("--atoms", type=int, default=None, help="fix protein atoms per complex (default U{400..500})")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget-s", type=float, default=25.0)
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------------------------
+def make_batch(rank: int, batch: int, atoms):
+    from singa_b200 import synthetic as syn
+    graphs = [syn.make_complex(1000 * rank + i, n_protein=atoms) for i in range(batch)]
+    return syn.collate(graphs), graphs
+
+
+def count_edges(g) -> int:
+    return int(sum(g[k].shape[1] for k in ("ei_pp", "ei_ll", "ei_lp", "ei_pl")))
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(path):
+        p = json.load(open(path))
+        return dict(hbm=p["hbm_gbs"], tensor=p.get("bf16_tflops_sustained", p["bf16_tflops"]), source="measured")
+    return dict(hbm=6650.0, tensor=1400.0, source="fallback")
+
+
+# ----------------------------------------------------------------------------------------------
+# reference / CPU arm: the oracle port on the host cores (the reference is pure Python and cannot travel)
+# ----------------------------------------------------------------------------------------------
+def cpu_sample_graph(budget_s: float):
+    """A sub-ball of complex seed 0 sized so that one fwd+bwd of the CPU port fits ``budget_s``.
+    Calibrated at ~1.0 k edges/s per 8 threads for the 3-layer stack."""
+    from singa_b200 import synthetic as syn
+    cores = os.cpu_count() or 1
+    est_rate = 1000.0 * max(1.0, min(cores, 32) / 8.0) ** 0.7
+    target_edges = max(1500.0, est_rate * budget_s)
+    n = 60
+    while n < 450:
+        g = syn.make_complex(0, n_protein=n, n_ligand=24)
+        if count_edges(g) >= target_edges:
+            return g, n
+        n += 20
+    return syn.make_complex(0, n_protein=n, n_ligand=24), n
+
+
+def run_cpu_port(graph, steps: int, warmup: int):
+    """fwd+bwd of oracle/ef_oracle.py (the CPU port of the reference algorithm) on all host threads."""
+    from oracle import ef_oracle as eo
+    from singa_b200 import so3_constants as sc
+    from singa_b200 import synthetic as syn
+    from singa_b200.embedding import DEFAULT_CONFIG, EquivariantEmbedding
+    torch.set_num_threads(os.cpu_count() or 1)
+    torch.manual_seed(0)
+    shapes = EquivariantEmbedding(DEFAULT_CONFIG, device="cpu")
+    syn.load_portable_parameters(shapes, 0)
+    p = {k: v.detach().clone().requires_grad_(v.dtype.is_floating_point and k in dict(shapes.named_parameters()))
+         for k, v in shapes.state_dict().items()}
+    f32 = lambda a: torch.tensor(a, dtype=torch.float32)
+    to62, fr62 = sc.s2_grid_matrices(6, 2)
+    to66, fr66 = sc.s2_grid_matrices(6, 6)
+    t = eo.Tables(6, 2, [sc.j_matrix(l) for l in range(7)], f32(to62), f32(fr62), f32(to66), f32(fr66))
+    rnd = syn.frame_randoms(graph, 1)
+    frames = {}
+    for key, (s, d, ei) in dict(pp=("pos_p", "pos_p", "ei_pp"), ll=("pos_l", "pos_l", "ei_ll"),
+                                lp=("pos_l", "pos_p", "ei_lp")).items():
+        frames[key] = eo.edge_rot_mat(graph[s][graph[ei][0]] - graph[d][graph[ei][1]], rnd[key])
+    times = []
+    for it in range(warmup + steps):
+        for v in p.values():
+            v.grad = None
+        t0 = time.perf_counter()
+        out = eo.embedding_forward(p, graph, frames, t, dict(DEFAULT_CONFIG))
+        loss = out["protein_atoms"].sum() * 0.5 + out["ligand_atoms"].sum()
+        loss.backward()
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt)
+    return float(np.mean(times))
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    total = max(1, args.steps + args.warmup)
+    graph, n = cpu_sample_graph(max(4.0, 180.0 / total))
+    edges = count_edges(graph)
+    sec = run_cpu_port(graph, args.steps, args.warmup)
+    val = edges / sec
+    cores = os.cpu_count() or 1
+    sample = f"one synthetic complex (seed 0) cut to {n} protein + 24 ligand atoms, {edges} edges, 8 A radius graph"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "EF_layers fwd+bwd, batch 32 synthetic CrossDocked-shaped complexes (~450 atoms, 8 A "
+                               "cutoff, lmax=6, mmax=2)", "sample": sample},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ----------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    if args.impl == "reference":
+        reference_arm(args)
+        return
+    import torch.distributed as dist
+    from singa_b200 import _lib, ops
+    from singa_b200 import synthetic as syn
+    from singa_b200.embedding import DEFAULT_CONFIG, EquivariantEmbedding
+    from singa_b200.parallel import GradientBucket
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    ops.set_precision(args.precision)
+
+    batch, _ = make_batch(rank, args.batch, args.atoms)
+    edges = count_edges(batch)
+    host = {k: v.pin_memory() for k, v in batch.items()}
+    resident = {k: v.to(dev) for k, v in host.items()}
+    h2d_bytes = int(sum(v.numel() * v.element_size() for v in host.values()))
+
+    torch.manual_seed(0)
+    model = EquivariantEmbedding(DEFAULT_CONFIG, device=dev)
+    syn.load_portable_parameters(model, 0)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+    bucket = GradientBucket(model.parameters())
+    rs = np.random.RandomState(7)
+    Rp = torch.from_numpy(rs.normal(size=(resident["z_p"].numel(), 49, 16)).astype(np.float32)).to(dev)
+    Rl = torch.from_numpy(rs.normal(size=(resident["z_l"].numel(), 49, 16)).astype(np.float32)).to(dev)
+
+    def step(g):
+        opt.zero_grad(set_to_none=True)
+        out = model(syn.GraphView(g))
+        loss = (out[syn.PROTEIN].embedding * Rp).sum() + (out[syn.LIGAND].embedding * Rl).sum()
+        loss.backward()
+        bucket.allreduce_()
+        opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, n):
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(n):
+            fn()
+        b.record()
+        barrier()
+        ms = torch.tensor([a.elapsed_time(b)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms) / n
+
+    for _ in range(max(args.warmup, 3)):
+        step(resident)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = _lib.launch_count
+    _lib.start_profile()
+    ms_dev = timed(lambda: step(resident), args.steps)
+    prof = _lib.stop_profile()
+    launches = _lib.launch_count - launches0
+
+    def e2e_step():
+        g = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+        return float(step(g).item())
+
+    e2e_step()
+    ms_e2e = timed(e2e_step, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+
+    tot_edges = torch.tensor([float(edges)], device=dev)
+    if world > 1:
+        dist.all_reduce(tot_edges)
+    tot_edges = float(tot_edges)
+
+    if rank == 0:
+        pk = peaks()
+        top = max(prof.items(), key=lambda kv: kv[1]["ms"]) if prof else (None, None)
+        roofline = None
+        if top[0] is not None:
+            name, d = top
+            tensor = "gemm" in name
+            per_launch_work = d["work"] / max(d["calls"], 1)
+            per_launch_s = d["ms"] * 1e-3 / max(d["calls"], 1)
+            achieved = per_launch_work / per_launch_s / (1e12 if tensor else 1e9)
+            peak = pk["tensor"] if tensor else pk["hbm"]
+            traffic = None
+            tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+            if os.path.isfile(tpath):
+                traffic = json.load(open(tpath)).get(name)
+            roofline = {"kernel": name, "bound": "tensor" if tensor else "hbm", "achieved": achieved, "peak": peak,
+                        "unit": "TFLOP/s" if tensor else "GB/s", "frac": achieved / peak, "traffic": traffic,
+                        "peak_source": pk["source"], "share_of_step": d["ms"] / (ms_dev * args.steps),
+                        "launches": d["calls"]}
+        breakdown = {k: round(v["ms"] / args.steps, 3) for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}
+        line = {
+            "metric": METRIC, "value": tot_edges / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+            "config": {"workload": "EF_layers fwd+bwd, batch 32 synthetic CrossDocked-shaped complexes (~450 atoms, "
+                                   "8 A cutoff, lmax=6, mmax=2) per GPU", "complexes_per_gpu": args.batch,
+                       "edges_per_gpu": edges, "layers": 3, "passes": 4, "parallelism": f"dp{world}",
+                       "gemm_precision": args.precision, "l2": "inputs and per-chunk activations >> 126 MB L2",
+                       "complexes_per_s": args.batch * world / (ms_dev * 1e-3)},
+            "e2e": {"value": tot_edges / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
+                    "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e},
+            "gpu_launches": launches, "roofline": roofline, "clocks": clocks, "kernel_ms_per_step": breakdown,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            graph, n = cpu_sample_graph(args.cpu_budget_s)
+            sec = run_cpu_port(graph, 1, 0)
+            e = count_edges(graph)
+            line["cpu_baseline"] = {
+                "value": e / sec, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
+                "sample": f"one synthetic complex (seed 0) cut to {n} protein + 24 ligand atoms, {e} edges, fwd+bwd "
+                          f"once, {sec:.1f} s"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

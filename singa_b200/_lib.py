@@ -77,9 +77,46 @@ def stream_ptr():
     return torch.cuda.current_stream().cuda_stream
 
 
-def call(name: str, *args):
-    """Invoke an entry point; the trailing stream argument is appended here."""
-    rc = getattr(LIB, name)(*args, stream_ptr())
+# kernels launched per entry point (for the launch counter bench.py reports)
+_LAUNCHES = {"efl_gemm_tn_f32": 2, "efl_colsum": 2, "efl_tc_gemm_tn": 2}
+launch_count = 0
+_profile = None  # None, or a list receiving (name, work, start_event, end_event)
+
+
+def start_profile():
+    """Record a CUDA-event pair around every entry-point call (on the launching stream) until stop_profile()."""
+    global _profile
+    _profile = []
+
+
+def stop_profile():
+    """-> {name: dict(ms=total ms, calls=n, work=sum of algorithmic work units passed by the caller)}"""
+    global _profile
+    rec, _profile = _profile or [], None
+    torch.cuda.synchronize()
+    out = {}
+    for name, work, a, b in rec:
+        d = out.setdefault(name, dict(ms=0.0, calls=0, work=0.0))
+        d["ms"] += a.elapsed_time(b)
+        d["calls"] += 1
+        d["work"] += work
+    return out
+
+
+def call(name: str, *args, work: float = 0.0, tag: str = None):
+    """Invoke an entry point; the trailing stream argument is appended here.  ``work`` is the algorithmic
+    FLOPs (GEMMs) or bytes (HBM-bound kernels) of this call, used only by the profiler."""
+    global launch_count
+    launch_count += _LAUNCHES.get(name, 1)
+    if _profile is not None:
+        a = torch.cuda.Event(enable_timing=True)
+        b = torch.cuda.Event(enable_timing=True)
+        a.record()
+        rc = getattr(LIB, name)(*args, stream_ptr())
+        b.record()
+        _profile.append((tag or name, work, a, b))
+    else:
+        rc = getattr(LIB, name)(*args, stream_ptr())
     if rc != 0:
         raise EflError(f"{name} failed (code {rc}): {LIB.efl_last_error_string().decode()}")
 

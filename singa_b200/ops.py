@@ -155,7 +155,7 @@ class _Ptrs:
 def _gemm_nt(epi, A, B, bias, C, ldc, C0, ldc0, nsplit, M, N, K):
     if A.dtype == torch.float32:
         call("efl_gemm_nt_f32", epi, ptr(A), A.stride(0), ptr(B), B.stride(0), ptr(bias), ptr(C), ldc, ptr(C0), ldc0,
-             nsplit, M, N, K)
+             nsplit, M, N, K, work=2.0 * M * N * K)
     else:
         from . import tc_gemm
         tc_gemm.gemm_nt(epi, A, B, bias, C, ldc, C0, ldc0, nsplit, M, N, K)
@@ -166,7 +166,7 @@ def _gemm_tn(A, B, C, accumulate, Mred, N1, N2):
         splits = LIB.efl_gemm_tn_splits(Mred)
         ws = torch.empty(splits * N1 * N2, dtype=torch.float32, device=A.device)
         call("efl_gemm_tn_f32", ptr(A), A.stride(0), ptr(B), B.stride(0), ptr(C), C.stride(0), int(accumulate), ptr(ws),
-             Mred, N1, N2)
+             Mred, N1, N2, work=2.0 * Mred * N1 * N2)
     else:
         from . import tc_gemm
         tc_gemm.gemm_tn(A, B, C, accumulate, Mred, N1, N2)
@@ -279,7 +279,7 @@ def _chunk_forward(d: AttnDims, ws: _Workspace, w1: _Weights, w2: _Weights, x_sr
     bf16 = int(ws.A[0].dtype == torch.bfloat16)
     call("efl_rotate_in_fwd", d.lmax, d.mmax, d.C, bf16, ptr(x_src), ptr(x_dst), ptr(csr.src_sorted),
          ptr(csr.dst_sorted), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.A[0]), ptr(ws.A[1]),
-         ptr(ws.A[2]), e0, Ec)
+         ptr(ws.A[2]), e0, Ec, work=Ec * _bytes_rotate_in(d, ws.A[0].element_size(), wig.shape[1]))
     # so2_conv_1 (EF_layers.py:807-875)
     _gemm_nt(1, ws.A[0], w1.w0, w1.b0, ws.Hb[0], d.ms[0] * H, ws.extra, ws.extra_w, ws.extra_w, Ec,
              ws.extra_w + d.ms[0] * H, d.ms[0] * C2)
@@ -301,7 +301,20 @@ def _chunk_forward(d: AttnDims, ws: _Workspace, w1: _Weights, w2: _Weights, x_sr
                  d.ms[m] * H)
     if out is not None:
         call("efl_rotate_back_aggregate_fwd", d.lmax, d.mmax, d.heads, d.value_ch, bf16, ptr(ws.V[0]), ptr(ws.V[1]),
-             ptr(ws.V[2]), ptr(alpha), ptr(csr.rowptr), ptr(csr.perm), ptr(wig), ptr(out), n0, n1, e0)
+             ptr(ws.V[2]), ptr(alpha), ptr(csr.rowptr), ptr(csr.perm), ptr(wig), ptr(out), n0, n1, e0,
+             work=Ec * _bytes_rotate_back(d, ws.V[0].element_size(), wig.shape[1]) + (n1 - n0) * out[0].numel() * 4)
+
+
+def _bytes_rotate_in(d: AttnDims, es: int, wsz: int) -> float:
+    """Algorithmic HBM bytes per edge of rotate-in: two node rows, Wigner rows, radial scale,
+    indices; writes the m-primary operands."""
+    L = (d.lmax + 1) ** 2
+    return 2 * L * d.C * 4 + wsz * 4 + d.M * 2 * d.C * 4 + 12 + d.M * 2 * d.C * es
+
+
+def _bytes_rotate_back(d: AttnDims, es: int, wsz: int) -> float:
+    """Algorithmic HBM bytes per edge of rotate-back+aggregate: value rows, alpha, Wigner rows, index."""
+    return d.M * d.heads * d.value_ch * es + d.heads * 4 + wsz * 4 + 4
 
 
 class EdgeAttentionFunction(torch.autograd.Function):
