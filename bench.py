@@ -38,7 +38,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--precision", default=os.environ.get("EFL_PRECISION", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--precision", default=os.environ.get("EFL_PRECISION", "bf16"), choices=["fp32", "bf16"])
     ap.add_argument("--batch", type=int, default=32, help="complexes per GPU")
     ap.add_argument("--atoms", type=int, default=None, help="fix protein atoms per complex (default U{400..500})")
     ap.add_argument("--no-cpu-baseline", action="store_true")

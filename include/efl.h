@@ -121,6 +121,15 @@ int efl_gemm_tn_f32(const float* A, long long lda, const float* B, long long ldb
 int efl_colsum(int bf16, const void* X, long long ld, int rows, int cols, float* out, int accumulate,
                float* workspace, void* stream);
 
+/* The same linear maps on the 5th-generation tensor cores: bf16 operands, fp32 accumulation in TMEM
+ * (tcgen05.mma), operands staged by TMA, persistent warp-specialised CTAs.  Same epilogues as
+ * efl_gemm_nt_f32; C is bf16 (C0 fp32).  N (and N2) must be multiples of 16; row pitches multiples of 8. */
+int efl_tc_gemm_nt(int epilogue, const void* A, long long lda, const void* B, long long ldb, const float* bias,
+                   void* C, long long ldc, float* C0, long long ldc0, int nsplit, int M, int N, int K, void* stream);
+int efl_tc_gemm_tn_splits(int Mred, int N1, int N2);
+int efl_tc_gemm_tn(const void* A, long long lda, const void* B, long long ldb, float* C, long long ldc,
+                   int accumulate, float* workspace, int Mred, int N1, int N2, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -36,6 +36,8 @@ SIGNATURES = {
     "efl_gemm_nt_f32": "iplplpplpliiiip",
     "efl_gemm_tn_f32": "plplplipiiip",
     "efl_colsum": "ipliipipp",
+    "efl_tc_gemm_nt": "iplplpplpliiiip",
+    "efl_tc_gemm_tn": "plplplipiiip",
 }
 
 
@@ -57,6 +59,8 @@ def _load():
     lib.efl_version.restype = _I
     lib.efl_gemm_tn_splits.argtypes = [_I]
     lib.efl_gemm_tn_splits.restype = _I
+    lib.efl_tc_gemm_tn_splits.argtypes = [_I, _I, _I]
+    lib.efl_tc_gemm_tn_splits.restype = _I
     return lib
 
 

@@ -1,0 +1,472 @@
+// bf16 tensor-core GEMMs for the SO(2) linear maps: tcgen05.mma with TMEM accumulators, operands staged by TMA
+// (128-byte swizzle) through a 4-stage mbarrier pipeline, persistent warp-specialised CTAs (one per SM):
+//   warp 0   TMA producer          warp 1   MMA issuer (one elected lane)
+//   warp 2   TMEM allocator        warps 4-7 epilogue (tcgen05.ld -> registers -> fused epilogue -> global)
+// Two 256-column TMEM accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
+//
+//   NT : C[i, n] = sum_k A[i, k] B[n, k]     both operands K-major      (forward, dgrad)
+//   TN : P[z][n1, n2] = sum_{i in split z} A[i, n1] B[i, n2]   both operands MN-major (wgrad, split over edges,
+//        partials reduced in fixed order by splitk_reduce)
+// NT epilogues as in gemm_simt.cu (0 plain, 1 split, 2 complex combine); outputs bf16 (fp32 for the split part).
+//
+// Replaces the cuBLAS mm calls under SO2_Convolution / SO2_m_Convolution (reference EF_layers.py:721-729, 807-875).
+#include <cuda.h>
+#include "efl_common.cuh"
+
+namespace efl {
+namespace tc {
+
+constexpr int BM = 128;         // UMMA M (rows of the accumulator = TMEM lanes)
+constexpr int BK = 64;          // 64 bf16 = 128 bytes = one swizzle span
+constexpr int UMMA_K = 16;
+constexpr int STAGES = 4;
+constexpr int MAX_BN = 256;
+constexpr int A_BYTES = BM * BK * 2;       // 16 KB
+constexpr int B_BYTES = MAX_BN * BK * 2;   // 32 KB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int TMEM_COLS = 512;
+constexpr int NUM_THREADS = 256;
+
+struct Params {
+  int mode;      // 0 NT, 1 TN
+  int M, N, K;   // NT: C is [M, N], reduce K.  TN: M = N1 (rows of C), N = N2, K = reduced rows of this launch
+  int BN;        // accumulator columns per tile (multiple of 16, <= 256)
+  int epi;
+  __nv_bfloat16* C;
+  long long ldc;
+  float* C0;
+  long long ldc0;
+  int nsplit;
+  const float* bias;
+  float* P;      // TN partials [splits, N1, N2]
+  int splits;
+  int kb_per_split;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra WAIT_DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "WAIT_DONE:\n\t"
+      "}" ::"r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, "
+      "[%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// shared-memory matrix descriptor, SWIZZLE_128B, Blackwell version bit (cute::UMMA::SmemDescriptor)
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;  // version = 1
+  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+  return d;
+}
+
+// instruction descriptor (cute::UMMA::InstrDescriptor): fp32 accumulate, bf16 x bf16
+__device__ __forceinline__ uint32_t make_idesc(int n, int mn_major) {
+  uint32_t d = 0;
+  d |= 1u << 4;                        // c_format = F32
+  d |= 1u << 7;                        // a_format = BF16
+  d |= 1u << 10;                       // b_format = BF16
+  d |= (uint32_t)(mn_major ? 1 : 0) << 15;  // a_major
+  d |= (uint32_t)(mn_major ? 1 : 0) << 16;  // b_major
+  d |= (uint32_t)(n >> 3) << 17;       // n_dim
+  d |= (uint32_t)(BM >> 4) << 24;      // m_dim
+  return d;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* full = bars;                 // [STAGES]
+  uint64_t* empty = bars + STAGES;       // [STAGES]
+  uint64_t* tfull = bars + 2 * STAGES;   // [2]
+  uint64_t* tempty = bars + 2 * STAGES + 2;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tn = p.mode == 1;
+  const int m_tiles = (p.M + BM - 1) / BM;
+  const int n_tiles = p.N / p.BN;
+  const int kb_total = (p.K + BK - 1) / BK;
+  const int work_items = m_tiles * n_tiles * (tn ? p.splits : 1);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull[a], 1);
+      mbar_init(&tempty[a], 128);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"((uint32_t)TMEM_COLS));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // number of 64-wide MN blocks of the B operand in TN mode
+  const int b_blocks = (p.BN + 63) / 64;
+  const uint32_t stage_tx = tn ? (uint32_t)((2 + b_blocks) * 64 * 128) : (uint32_t)(A_BYTES + p.BN * 128);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = blockIdx.x; w < work_items; w += gridDim.x) {
+        int z = 0, t = w;
+        if (tn) { z = w / (m_tiles * n_tiles); t = w % (m_tiles * n_tiles); }
+        const int m_blk = t / n_tiles, n_blk = t % n_tiles;
+        const int kb0 = tn ? z * p.kb_per_split : 0;
+        const int kb1 = tn ? min(kb_total, kb0 + p.kb_per_split) : kb_total;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * STAGE_BYTES;
+          uint8_t* sb = sa + A_BYTES;
+          mbar_expect_tx(&full[stage], stage_tx);
+          if (!tn) {
+            tma_load_2d(sa, &mapA, &full[stage], kb * BK, m_blk * BM);
+            tma_load_2d(sb, &mapB, &full[stage], kb * BK, n_blk * p.BN);
+          } else {
+            for (int b = 0; b < 2; ++b) tma_load_2d(sa + b * 8192, &mapA, &full[stage], m_blk * BM + b * 64, kb * BK);
+            for (int b = 0; b < b_blocks; ++b)
+              tma_load_2d(sb + b * 8192, &mapB, &full[stage], n_blk * p.BN + b * 64, kb * BK);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const uint32_t idesc = make_idesc(p.BN, tn);
+    for (int w = blockIdx.x; w < work_items; w += gridDim.x) {
+      int z = 0;
+      if (tn) z = w / (m_tiles * n_tiles);
+      const int kb0 = tn ? z * p.kb_per_split : 0;
+      const int kb1 = tn ? min(kb_total, kb0 + p.kb_per_split) : kb_total;
+      mbar_wait(&tempty[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + (uint32_t)(acc * MAX_BN);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&full[stage], phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            uint64_t ad, bd;
+            if (!tn) {
+              ad = make_desc(sa + k * 32, 16, 1024);
+              bd = make_desc(sb + k * 32, 16, 1024);
+            } else {
+              ad = make_desc(sa + k * 2048, 8192, 1024);
+              bd = make_desc(sb + k * 2048, 8192, 1024);
+            }
+            tc_mma(tmem_d, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          tc_commit(&empty[stage]);
+          if (kb == kb1 - 1) tc_commit(&tfull[acc]);
+        }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  } else if (warp >= 4) {
+    const int q = warp & 3;
+    const int row_in_tile = q * 32 + lane;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int w = blockIdx.x; w < work_items; w += gridDim.x) {
+      int z = 0, t = w;
+      if (tn) { z = w / (m_tiles * n_tiles); t = w % (m_tiles * n_tiles); }
+      const int m_blk = t / n_tiles, n_blk = t % n_tiles;
+      const int row = m_blk * BM + row_in_tile;
+      const bool row_ok = row < p.M;
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr0 = tmem_base + (uint32_t)(acc * MAX_BN) + ((uint32_t)(q * 32) << 16);
+      for (int c0 = 0; c0 < p.BN; c0 += 16) {
+        uint32_t v[16];
+        tc_ld16(taddr0 + (uint32_t)c0, v);
+        tc_ld_wait();
+        const int col = n_blk * p.BN + c0;
+        if (tn) {
+          if (row_ok) {
+            float4* dst = reinterpret_cast<float4*>(p.P + ((size_t)z * p.M + row) * p.N + col);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
+                                   __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+          }
+        } else if (p.epi == 2) {
+          // complex combine: partner row = lane ^ 1, column pairs (2q, 2q+1) -> output column q
+          float o[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float mine_e = __uint_as_float(v[2 * j]);
+            const float mine_o = __uint_as_float(v[2 * j + 1]);
+            const float other_o = __shfl_xor_sync(0xffffffffu, mine_o, 1);
+            o[j] = (lane & 1) ? (mine_e + other_o) : (mine_e - other_o);
+          }
+          if (row_ok) {
+            uint4 pk = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]),
+                                  pack_bf16(o[6], o[7]));
+            *reinterpret_cast<uint4*>(p.C + (size_t)row * p.ldc + col / 2) = pk;
+          }
+        } else {
+          float f[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]) + (p.bias ? __ldg(p.bias + col + j) : 0.f);
+          if (row_ok) {
+            if (p.epi == 1 && col < p.nsplit) {
+              float4* dst = reinterpret_cast<float4*>(p.C0 + (size_t)row * p.ldc0 + col);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+            } else {
+              const int cc = col - (p.epi == 1 ? p.nsplit : 0);
+              uint4* dst = reinterpret_cast<uint4*>(p.C + (size_t)row * p.ldc + cc);
+              dst[0] = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]),
+                                  pack_bf16(f[6], f[7]));
+              dst[1] = make_uint4(pack_bf16(f[8], f[9]), pack_bf16(f[10], f[11]), pack_bf16(f[12], f[13]),
+                                  pack_bf16(f[14], f[15]));
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tempty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TMEM_COLS));
+  }
+}
+
+}  // namespace tc
+}  // namespace efl
+
+// ---------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------
+using namespace efl;
+using efl::tc::Params;
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// 2-D bf16 row-major [rows, cols] (leading dimension ld elements); box = {64 columns (128 B), box_rows}
+static int make_map(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld, int box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) {
+    efl_set_error("cuTensorMapEncodeTiled not available from the driver");
+    return EFL_ERR_UNSUPPORTED;
+  }
+  if (((uintptr_t)base & 15) || ((ld * 2) & 15)) {
+    efl_set_error("tc_gemm: operand base and row pitch must be 16-byte aligned");
+    return EFL_ERR_ARG;
+  }
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1u, 1u};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    efl_set_error("cuTensorMapEncodeTiled failed");
+    return EFL_ERR_ARG;
+  }
+  return EFL_OK;
+}
+
+// largest multiple of 16 that divides n and is <= 256
+static int pick_bn(int n) {
+  for (int bn = 256; bn >= 16; bn -= 16)
+    if (n % bn == 0) return bn;
+  return 0;
+}
+
+static int num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const Params& p, int work_items, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(efl::tc::tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         efl::tc::SMEM_BYTES);
+    if (e != cudaSuccess) {
+      efl_set_error(cudaGetErrorString(e));
+      return (int)e;
+    }
+    attr_set = true;
+  }
+  const int grid = work_items < num_sms() ? work_items : num_sms();
+  efl::tc::tc_gemm_kernel<<<grid, efl::tc::NUM_THREADS, efl::tc::SMEM_BYTES, s>>>(ma, mb, p);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+// C[M, N(/2 for epilogue 2)] = A[M, K] . B[N, K]^T; bf16 operands, fp32 accumulate.
+extern "C" int efl_tc_gemm_nt(int epilogue, const void* A, long long lda, const void* B, long long ldb,
+                              const float* bias, void* C, long long ldc, float* C0, long long ldc0, int nsplit, int M,
+                              int N, int K, void* stream) {
+  if (M <= 0 || N <= 0) return EFL_OK;
+  const int bn = pick_bn(N);
+  EFL_REQUIRE(bn > 0, "efl_tc_gemm_nt: N must be a multiple of 16");
+  EFL_REQUIRE(epilogue >= 0 && epilogue <= 2, "efl_tc_gemm_nt: unknown epilogue");
+  EFL_REQUIRE(epilogue != 2 || (M % 2 == 0), "efl_tc_gemm_nt: complex epilogue needs even M");
+  EFL_REQUIRE(epilogue != 1 || (nsplit % 16 == 0), "efl_tc_gemm_nt: nsplit must be a multiple of 16");
+  EFL_REQUIRE((ldc % 8) == 0 && ((uintptr_t)C & 15) == 0, "efl_tc_gemm_nt: C must be 16-byte aligned with ldc % 8 == 0");
+  CUtensorMap ma, mb;
+  int rc = make_map(&ma, A, M, K, lda, efl::tc::BM);
+  if (rc) return rc;
+  rc = make_map(&mb, B, N, K, ldb, bn);
+  if (rc) return rc;
+  Params p{};
+  p.mode = 0; p.M = M; p.N = N; p.K = K; p.BN = bn; p.epi = epilogue;
+  p.C = (__nv_bfloat16*)C; p.ldc = ldc; p.C0 = C0; p.ldc0 = ldc0; p.nsplit = nsplit; p.bias = bias;
+  p.P = nullptr; p.splits = 1; p.kb_per_split = 0;
+  const int tiles = ((M + efl::tc::BM - 1) / efl::tc::BM) * (N / bn);
+  return launch(ma, mb, p, tiles, (cudaStream_t)stream);
+}
+
+// split count for the weight-gradient GEMM: fill the SMs, keep >= 8 k-blocks per split
+extern "C" int efl_tc_gemm_tn_splits(int Mred, int N1, int N2) {
+  const int bn = pick_bn(N2);
+  if (bn <= 0) return 1;
+  const int tiles = ((N1 + efl::tc::BM - 1) / efl::tc::BM) * (N2 / bn);
+  const int kb = (Mred + efl::tc::BK - 1) / efl::tc::BK;
+  int s = (num_sms() + tiles - 1) / tiles;
+  if (s > kb / 8) s = kb / 8;
+  if (s < 1) s = 1;
+  const int per = (kb + s - 1) / s;
+  return (kb + per - 1) / per;
+}
+
+// defined in gemm_simt.cu
+namespace efl {
+__global__ void splitk_reduce_kernel(const float* __restrict__ P, int splits, long long n, float* __restrict__ C,
+                                     long long ldc, int N2, int accumulate);
+}
+
+// C[N1, N2] (+)= A[Mred, N1]^T . B[Mred, N2]; workspace: efl_tc_gemm_tn_splits(...) * N1 * N2 floats
+extern "C" int efl_tc_gemm_tn(const void* A, long long lda, const void* B, long long ldb, float* C, long long ldc,
+                              int accumulate, float* workspace, int Mred, int N1, int N2, void* stream) {
+  if (N1 <= 0 || N2 <= 0) return EFL_OK;
+  const int bn = pick_bn(N2);
+  EFL_REQUIRE(bn > 0, "efl_tc_gemm_tn: N2 must be a multiple of 16");
+  EFL_REQUIRE(Mred > 0, "efl_tc_gemm_tn: empty reduction");
+  CUtensorMap ma, mb;
+  int rc = make_map(&ma, A, Mred, N1, lda, efl::tc::BK);
+  if (rc) return rc;
+  rc = make_map(&mb, B, Mred, N2, ldb, efl::tc::BK);
+  if (rc) return rc;
+  const int splits = efl_tc_gemm_tn_splits(Mred, N1, N2);
+  const int kb = (Mred + efl::tc::BK - 1) / efl::tc::BK;
+  Params p{};
+  p.mode = 1; p.M = N1; p.N = N2; p.K = Mred; p.BN = bn; p.epi = 0;
+  p.P = workspace; p.splits = splits; p.kb_per_split = (kb + splits - 1) / splits;
+  const int tiles = ((N1 + efl::tc::BM - 1) / efl::tc::BM) * (N2 / bn);
+  cudaStream_t s = (cudaStream_t)stream;
+  rc = launch(ma, mb, p, tiles * splits, s);
+  if (rc) return rc;
+  const long long n = (long long)N1 * N2;
+  efl::splitk_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(workspace, splits, n, C, ldc, N2, accumulate);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
