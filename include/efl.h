@@ -117,7 +117,7 @@ int efl_gemm_nt_f32(int epilogue, const float* A, long long lda, const float* B,
 int efl_gemm_tn_splits(int Mred);
 int efl_gemm_tn_f32(const float* A, long long lda, const float* B, long long ldb, float* C, long long ldc,
                     int accumulate, float* workspace, int Mred, int N1, int N2, void* stream);
-/* Bias gradients: out[c] (+)= sum_r X[r,c]; workspace (rows/4096 + 1) * cols floats. */
+/* Bias gradients: out[c] (+)= sum_r X[r,c]; workspace (rows/512 + 2) * cols floats. */
 int efl_colsum(int bf16, const void* X, long long ld, int rows, int cols, float* out, int accumulate,
                float* workspace, void* stream);
 
@@ -129,6 +129,15 @@ int efl_tc_gemm_nt(int epilogue, const void* A, long long lda, const void* B, lo
 int efl_tc_gemm_tn_splits(int Mred, int N1, int N2);
 int efl_tc_gemm_tn(const void* A, long long lda, const void* B, long long ldb, float* C, long long ldc,
                    int accumulate, float* workspace, int Mred, int N1, int N2, void* stream);
+
+/* SeparableS2Activation of the edge path (:1757-1773) on the tensor cores, bf16 buffers: per edge two (fwd) or
+ * three (bwd) tcgen05 MMAs with the channel axis as M; the grid values live only in TMEM.  h0..h2: hidden rows
+ * (plain split buffers); fwd: out0..out2 plain split buffers; bwd: d0..d2 = d(out) rows, out0 = first hidden column
+ * of the so2_conv_1 m=0 dY buffer (row pitch ld0), out1/out2 dup-layout buffers, dgate = its gate column.
+ * T, F: to/from grid matrices [G, M] fp32 with m-primary columns. */
+int efl_s2act_tc(int bwd, int lmax, int mmax, int G, const void* h0, const void* h1, const void* h2, const void* d0,
+                 const void* d1, const void* d2, void* out0, void* out1, void* out2, long long ld0, void* dgate,
+                 const float* gate, long long gate_ld, const float* T, const float* F, int Ec, void* stream);
 
 #ifdef __cplusplus
 }

@@ -38,6 +38,7 @@ SIGNATURES = {
     "efl_colsum": "ipliipipp",
     "efl_tc_gemm_nt": "iplplpplpliiiip",
     "efl_tc_gemm_tn": "plplplipiiip",
+    "efl_s2act_tc": "iiii" "ppppppppp" "l" "p" "p" "l" "pp" "i" "p",
 }
 
 

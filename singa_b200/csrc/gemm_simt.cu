@@ -218,12 +218,12 @@ extern "C" int efl_gemm_tn_f32(const float* A, long long lda, const float* B, lo
   return EFL_OK;
 }
 
-// workspace: ceil(rows / 4096) * cols floats
+// workspace: (ceil(rows / 512) + 1) * cols floats
 extern "C" int efl_colsum(int bf16, const void* X, long long ld, int rows, int cols, float* out, int accumulate,
                           float* workspace, void* stream) {
   if (cols <= 0) return EFL_OK;
   cudaStream_t s = (cudaStream_t)stream;
-  const int rpb = 4096;
+  const int rpb = 512;
   const int nb = rows > 0 ? (rows + rpb - 1) / rpb : 1;
   dim3 grid((cols + 127) / 128, nb), block(128);
   if (bf16) colsum_partial_kernel<__nv_bfloat16><<<grid, block, 0, s>>>((const __nv_bfloat16*)X, ld, rows, cols, rpb, workspace);

@@ -10,8 +10,7 @@
 // NT epilogues as in gemm_simt.cu (0 plain, 1 split, 2 complex combine); outputs bf16 (fp32 for the split part).
 //
 // Replaces the cuBLAS mm calls under SO2_Convolution / SO2_m_Convolution (reference EF_layers.py:721-729, 807-875).
-#include <cuda.h>
-#include "efl_common.cuh"
+#include "tc_common.cuh"
 
 namespace efl {
 namespace tc {
@@ -43,92 +42,6 @@ struct Params {
   int splits;
   int kb_per_split;
 };
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "WAIT_LOOP:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra WAIT_DONE;\n\t"
-      "bra WAIT_LOOP;\n\t"
-      "WAIT_DONE:\n\t"
-      "}" ::"r"(smem_u32(bar)), "r"(parity)
-      : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
-          smem_u32(smem_dst)),
-      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
-      : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-               : "memory");
-}
-__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-      "}" ::"r"(tmem_d),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
-      : "memory");
-}
-__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t* v) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, "
-      "[%16];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-      : "r"(taddr)
-      : "memory");
-}
-__device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// shared-memory matrix descriptor, SWIZZLE_128B, Blackwell version bit (cute::UMMA::SmemDescriptor)
-__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  uint64_t d = 0;
-  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
-  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
-  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
-  d |= (uint64_t)1 << 46;  // version = 1
-  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
-  return d;
-}
-
-// instruction descriptor (cute::UMMA::InstrDescriptor): fp32 accumulate, bf16 x bf16
-__device__ __forceinline__ uint32_t make_idesc(int n, int mn_major) {
-  uint32_t d = 0;
-  d |= 1u << 4;                        // c_format = F32
-  d |= 1u << 7;                        // a_format = BF16
-  d |= 1u << 10;                       // b_format = BF16
-  d |= (uint32_t)(mn_major ? 1 : 0) << 15;  // a_major
-  d |= (uint32_t)(mn_major ? 1 : 0) << 16;  // b_major
-  d |= (uint32_t)(n >> 3) << 17;       // n_dim
-  d |= (uint32_t)(BM >> 4) << 24;      // m_dim
-  return d;
-}
-
-__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
-  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&h);
-}
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const Params p) {
@@ -342,7 +255,7 @@ static EncodeTiledFn get_encode() {
 }
 
 // 2-D bf16 row-major [rows, cols] (leading dimension ld elements); box = {64 columns (128 B), box_rows}
-static int make_map(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld, int box_rows) {
+int efl_make_map_bf16(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld, int box_rows) {
   EncodeTiledFn enc = get_encode();
   if (!enc) {
     efl_set_error("cuTensorMapEncodeTiled not available from the driver");
@@ -373,7 +286,7 @@ static int pick_bn(int n) {
   return 0;
 }
 
-static int num_sms() {
+int efl_num_sms() {
   static int n = 0;
   if (!n) {
     int dev = 0;
@@ -395,7 +308,7 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const Params& p,
     }
     attr_set = true;
   }
-  const int grid = work_items < num_sms() ? work_items : num_sms();
+  const int grid = work_items < efl_num_sms() ? work_items : efl_num_sms();
   efl::tc::tc_gemm_kernel<<<grid, efl::tc::NUM_THREADS, efl::tc::SMEM_BYTES, s>>>(ma, mb, p);
   EFL_CHECK_LAUNCH();
   return EFL_OK;
@@ -413,9 +326,9 @@ extern "C" int efl_tc_gemm_nt(int epilogue, const void* A, long long lda, const 
   EFL_REQUIRE(epilogue != 1 || (nsplit % 16 == 0), "efl_tc_gemm_nt: nsplit must be a multiple of 16");
   EFL_REQUIRE((ldc % 8) == 0 && ((uintptr_t)C & 15) == 0, "efl_tc_gemm_nt: C must be 16-byte aligned with ldc % 8 == 0");
   CUtensorMap ma, mb;
-  int rc = make_map(&ma, A, M, K, lda, efl::tc::BM);
+  int rc = efl_make_map_bf16(&ma, A, M, K, lda, efl::tc::BM);
   if (rc) return rc;
-  rc = make_map(&mb, B, N, K, ldb, bn);
+  rc = efl_make_map_bf16(&mb, B, N, K, ldb, bn);
   if (rc) return rc;
   Params p{};
   p.mode = 0; p.M = M; p.N = N; p.K = K; p.BN = bn; p.epi = epilogue;
@@ -431,7 +344,7 @@ extern "C" int efl_tc_gemm_tn_splits(int Mred, int N1, int N2) {
   if (bn <= 0) return 1;
   const int tiles = ((N1 + efl::tc::BM - 1) / efl::tc::BM) * (N2 / bn);
   const int kb = (Mred + efl::tc::BK - 1) / efl::tc::BK;
-  int s = (num_sms() + tiles - 1) / tiles;
+  int s = (efl_num_sms() + tiles - 1) / tiles;
   if (s > kb / 8) s = kb / 8;
   if (s < 1) s = 1;
   const int per = (kb + s - 1) / s;
@@ -452,9 +365,9 @@ extern "C" int efl_tc_gemm_tn(const void* A, long long lda, const void* B, long 
   EFL_REQUIRE(bn > 0, "efl_tc_gemm_tn: N2 must be a multiple of 16");
   EFL_REQUIRE(Mred > 0, "efl_tc_gemm_tn: empty reduction");
   CUtensorMap ma, mb;
-  int rc = make_map(&ma, A, Mred, N1, lda, efl::tc::BK);
+  int rc = efl_make_map_bf16(&ma, A, Mred, N1, lda, efl::tc::BK);
   if (rc) return rc;
-  rc = make_map(&mb, B, Mred, N2, ldb, efl::tc::BK);
+  rc = efl_make_map_bf16(&mb, B, Mred, N2, ldb, efl::tc::BK);
   if (rc) return rc;
   const int splits = efl_tc_gemm_tn_splits(Mred, N1, N2);
   const int kb = (Mred + efl::tc::BK - 1) / efl::tc::BK;

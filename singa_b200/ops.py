@@ -21,7 +21,7 @@ from ._lib import LIB, call, check_cuda, ptr
 # GEMM operand precision of the SO(2) linear maps: "fp32" (SIMT, parity mode) or
 # "bf16" (tcgen05 tensor cores, fp32 accumulate).  Set through set_precision().
 _PRECISION = "fp32"
-MAX_CHUNK_EDGES = 65536
+MAX_CHUNK_EDGES = 262144
 
 
 def set_precision(mode: str) -> None:
@@ -173,7 +173,7 @@ def _gemm_tn(A, B, C, accumulate, Mred, N1, N2):
 
 
 def _colsum(X, rows, cols, out, accumulate):
-    ws = torch.empty(((rows + 4095) // 4096 + 1) * cols, dtype=torch.float32, device=X.device)
+    ws = torch.empty(((rows + 511) // 512 + 1) * cols, dtype=torch.float32, device=X.device)
     call("efl_colsum", int(X.dtype == torch.bfloat16), ptr(X), X.stride(0), rows, cols, ptr(out), int(accumulate),
          ptr(ws))
 
@@ -290,10 +290,16 @@ def _chunk_forward(d: AttnDims, ws: _Workspace, w1: _Weights, w2: _Weights, x_sr
          logits.data_ptr() + e0 * d.heads * 4, Ec)
     call("efl_segment_softmax_fwd", ptr(logits), d.heads, ptr(csr.rowptr), ptr(alpha), n0, n1)
     to_g, from_g, G = grids
-    rin = _rowmap_plain(ws.Hb, d, H)
-    rout = _rowmap_plain(ws.B, d, H)
-    call("efl_s2act_fwd", d.M, G, H, bf16, bf16, *rin.args(), *rout.args(),
-         ws.extra.data_ptr() + d.heads * d.alpha_ch * 4, ws.extra_w, ptr(to_g), ptr(from_g), Ec)
+    gate_ptr = ws.extra.data_ptr() + d.heads * d.alpha_ch * 4
+    if bf16:
+        call("efl_s2act_tc", 0, d.lmax, d.mmax, G, ptr(ws.Hb[0]), ptr(ws.Hb[1]), ptr(ws.Hb[2]), None, None, None,
+             ptr(ws.B[0]), ptr(ws.B[1]), ptr(ws.B[2]), d.ms[0] * H, None, gate_ptr, ws.extra_w, ptr(to_g), ptr(from_g),
+             Ec, work=Ec * 4.0 * G * d.M * H, tag="efl_s2act_tc_fwd")
+    else:
+        rin = _rowmap_plain(ws.Hb, d, H)
+        rout = _rowmap_plain(ws.B, d, H)
+        call("efl_s2act_fwd", d.M, G, H, bf16, bf16, *rin.args(), *rout.args(), gate_ptr, ws.extra_w, ptr(to_g),
+             ptr(from_g), Ec)
     # so2_conv_2
     _gemm_nt(0, ws.B[0], w2.w0, w2.b0, ws.V[0], d.ms[0] * VH, None, 0, 0, Ec, d.ms[0] * VH, d.ms[0] * H)
     for m in range(1, d.mmax + 1):
@@ -400,14 +406,21 @@ class EdgeAttentionFunction(torch.autograd.Function):
                 _gemm_nt(0, ws.dY2[m], w2.wmt[m - 1], None, ws.dB[m], d.ms[m] * H, None, 0, 0, 2 * Ec, d.ms[m] * H,
                          2 * d.ms[m] * VH)
             # ---- S2 activation backward -> dY1 (m0: [d alpha_in | d gate | d hidden rows]; m>0 dup layout)
-            rin = _rowmap_plain(ws.Hb, d, H)
-            rdin = _rowmap_plain(ws.dB, d, H)
             ld1 = ws.extra_w + d.ms[0] * H
-            rdout = _rowmap_dup(ws.dY1, d, H, ws.extra_w, ld1)
             es = ws.dY1[0].element_size()
-            call("efl_s2act_bwd", d.M, G, H, bf16, bf16, *rin.args(), *rdin.args(), *rdout.args(), 1,
-                 ws.extra.data_ptr() + d.heads * d.alpha_ch * 4, ws.extra_w,
-                 ws.dY1[0].data_ptr() + d.heads * d.alpha_ch * es, ld1, ptr(to_g), ptr(from_g), Ec)
+            gate_ptr = ws.extra.data_ptr() + d.heads * d.alpha_ch * 4
+            dgate_ptr = ws.dY1[0].data_ptr() + d.heads * d.alpha_ch * es
+            if bf16:
+                call("efl_s2act_tc", 1, d.lmax, d.mmax, G, ptr(ws.Hb[0]), ptr(ws.Hb[1]), ptr(ws.Hb[2]), ptr(ws.dB[0]),
+                     ptr(ws.dB[1]), ptr(ws.dB[2]), ws.dY1[0].data_ptr() + ws.extra_w * es, ptr(ws.dY1[1]),
+                     ptr(ws.dY1[2]), ld1, dgate_ptr, gate_ptr, ws.extra_w, ptr(to_g), ptr(from_g), Ec,
+                     work=Ec * 6.0 * G * d.M * H, tag="efl_s2act_tc_bwd")
+            else:
+                rin = _rowmap_plain(ws.Hb, d, H)
+                rdin = _rowmap_plain(ws.dB, d, H)
+                rdout = _rowmap_dup(ws.dY1, d, H, ws.extra_w, ld1)
+                call("efl_s2act_bwd", d.M, G, H, bf16, bf16, *rin.args(), *rdin.args(), *rdout.args(), 1, gate_ptr,
+                     ws.extra_w, dgate_ptr, ld1, ptr(to_g), ptr(from_g), Ec)
             # ---- softmax + alpha-logit backward -> first heads*alpha columns of dY1[0]
             call("efl_segment_softmax_bwd", ptr(alpha), ptr(dalpha), d.heads, ptr(csr.rowptr), ptr(dlogits), n0, n1)
             call("efl_alpha_logits_bwd", ptr(ws.extra), ws.extra_w, d.heads, d.alpha_ch, ptr(lw), ptr(lb), ptr(ad),
