@@ -139,6 +139,28 @@ int efl_s2act_tc(int bwd, int lmax, int mmax, int G, const void* h0, const void*
                  const void* d1, const void* d2, void* out0, void* out1, void* out2, long long ld0, void* dgate,
                  const float* gate, long long gate_ld, const float* T, const float* F, int Ec, void* stream);
 
+/* Node-level variant for FeedForwardNetwork (:234-270): x [N, M, cht] bf16 (cht a multiple of 128), gate
+ * [N, gate_ld] fp32, T/F [G, M] fp32; fwd: out [N, M, cht]; bwd: dy -> out = d x, dgate [N, cht] (bf16). */
+int efl_s2act_tc_nodes(int bwd, int M, int G, int cht, const void* x, const void* dy, void* out, void* dgate,
+                       const float* gate, long long gate_ld, const float* T, const float* F, int N, void* stream);
+
+/* SO3_LinearV2 (:624-674), fp32: out[n,i,:] = x[n,i,:] W[l(i)]^T (+bias on i=0); x [N,L,Cin], W [lmax+1,Cout,Cin].
+ * bwd_data takes the per-degree transposed weights Wt [lmax+1,Cin,Cout]; bwd_weight needs L*Cout*Cin floats. */
+int efl_so3_linear_fwd(const float* x, const float* W, const float* bias, float* out, int N, int lmax, int Cin,
+                       int Cout, void* stream);
+int efl_so3_linear_bwd_data(const float* dout, const float* Wt, float* dx, int N, int lmax, int Cin, int Cout,
+                            void* stream);
+int efl_so3_linear_bwd_weight(const float* dout, const float* x, float* dW, float* workspace, int N, int lmax,
+                              int Cin, int Cout, void* stream);
+
+/* EquivariantRMSNormArraySphericalHarmonicsV2 as built by get_normalization_layer (:2099-2192, :2254-2273):
+ * centred l=0, degree-balanced RMS, per-degree gain gamma [lmax+1,16], bias beta [16] on l=0.  One warp per node.
+ * bwd writes per-block partials of (d gamma | d beta) into part [nblocks, (lmax+2)*16]. */
+int efl_rmsnorm_sh_fwd(int lmax, int C, const float* x, const float* gamma, const float* beta, float eps, float* y,
+                       int N, void* stream);
+int efl_rmsnorm_sh_bwd(int lmax, int C, const float* x, const float* gamma, float eps, const float* dy, float* dx,
+                       float* part, int nblocks, int N, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

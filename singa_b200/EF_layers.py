@@ -543,6 +543,8 @@ class SO3_LinearV2(nn.Module):
         self.register_buffer('expand_index', get_l_to_all_m_expand_index(lmax, device))
 
     def apply_tensor(self, x: Tensor) -> Tensor:
+        if x.is_cuda:
+            return _get_ops().SO3LinearFunction.apply(x, self.weight, self.bias)
         outs = []
         for l in range(self.lmax + 1):
             blk = x[:, l * l:(l + 1) ** 2, :]
@@ -596,6 +598,10 @@ class EquivariantRMSNormArraySphericalHarmonicsV2(nn.Module):
     @torch.amp.autocast('cuda', enabled=False)
     def forward(self, node_input):
         x = node_input
+        if (x.is_cuda and self.affine and self.centering and self.std_balance_degrees
+                and self.normalization == 'component' and self.num_channels == 16 and self.lmax in (4, 6, 8)
+                and x.dtype == torch.float32):
+            return _get_ops().RMSNormSHFunction.apply(x, self.affine_weight, self.affine_bias, self.lmax, self.eps)
         if self.centering:
             x0 = x[:, 0:1, :]
             x = torch.cat((x0 - x0.mean(dim=2, keepdim=True), x[:, 1:, :]), dim=1)

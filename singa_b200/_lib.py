@@ -39,6 +39,12 @@ SIGNATURES = {
     "efl_tc_gemm_nt": "iplplpplpliiiip",
     "efl_tc_gemm_tn": "plplplipiiip",
     "efl_s2act_tc": "iiii" "ppppppppp" "l" "p" "p" "l" "pp" "i" "p",
+    "efl_s2act_tc_nodes": "iiii" "ppppp" "l" "pp" "i" "p",
+    "efl_so3_linear_fwd": "ppppiiiip",
+    "efl_so3_linear_bwd_data": "pppiiiip",
+    "efl_so3_linear_bwd_weight": "ppppiiiip",
+    "efl_rmsnorm_sh_fwd": "iipppfpip",
+    "efl_rmsnorm_sh_bwd": "iippfpppiip",
 }
 
 
@@ -83,7 +89,7 @@ def stream_ptr():
 
 
 # kernels launched per entry point (for the launch counter bench.py reports)
-_LAUNCHES = {"efl_gemm_tn_f32": 2, "efl_colsum": 2, "efl_tc_gemm_tn": 2}
+_LAUNCHES = {"efl_gemm_tn_f32": 2, "efl_colsum": 2, "efl_tc_gemm_tn": 2, "efl_so3_linear_bwd_weight": 2}
 launch_count = 0
 _profile = None  # None, or a list receiving (name, work, start_event, end_event)
 

@@ -24,11 +24,22 @@ __global__ void __launch_bounds__(256) gemm_nt_kernel(const TA* __restrict__ A, 
                                                       const TA* __restrict__ B, long long ldb,
                                                       const float* __restrict__ bias, TC* __restrict__ C,
                                                       long long ldc, float* __restrict__ C0, long long ldc0,
-                                                      int nsplit, int M, int N, int K) {
+                                                      int nsplit, int M, int N, int K, long long az = 0,
+                                                      long long bz = 0, long long cz = 0) {
   __shared__ float sA[BK][BM + 4];
   __shared__ float sB[BK][BN + 4];
   const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
   const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  if (gridDim.z > 1) {
+    // batched over coefficient index z (SO3_LinearV2): operand z of A/C, weight block of degree l(z)
+    const int z = blockIdx.z;
+    int l = 0;
+    while ((l + 1) * (l + 1) <= z) ++l;
+    A += z * az;
+    B += l * bz;
+    C += z * cz;
+    if (z > 0) bias = nullptr;
+  }
   float acc[4][4];
 #pragma unroll
   for (int i = 0; i < 4; ++i)
@@ -97,13 +108,20 @@ template <typename TA>
 __global__ void __launch_bounds__(256) gemm_tn_kernel(const TA* __restrict__ A, long long lda,
                                                       const TA* __restrict__ B, long long ldb,
                                                       float* __restrict__ P /* [splits, N1, N2] */, int Mred,
-                                                      int N1, int N2, int rows_per_split) {
+                                                      int N1, int N2, int rows_per_split, long long az = 0,
+                                                      long long bz = 0) {
   __shared__ float sA[BK][BM + 4];
   __shared__ float sB[BK][BN + 4];
   const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
   const int a0 = blockIdx.y * BM, b0 = blockIdx.x * BN;
-  const int i_begin = blockIdx.z * rows_per_split;
-  const int i_end = min(Mred, i_begin + rows_per_split);
+  int i_begin = blockIdx.z * rows_per_split;
+  int i_end = min(Mred, i_begin + rows_per_split);
+  if (az != 0) {  // batched over z: full reduction per batch entry, partial z goes to P[z]
+    A += blockIdx.z * az;
+    B += blockIdx.z * bz;
+    i_begin = 0;
+    i_end = Mred;
+  }
   float acc[4][4];
 #pragma unroll
   for (int i = 0; i < 4; ++i)
@@ -171,9 +189,66 @@ __global__ void colsum_partial_kernel(const T* __restrict__ X, long long ld, int
   P[(size_t)blockIdx.y * cols + c] = acc;
 }
 
+// dW[l] = sum_{z in degree l} P[z]
+__global__ void so3_wgrad_reduce_kernel(const float* __restrict__ P, float* __restrict__ dW, int lmax, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  for (int l = 0; l <= lmax; ++l) {
+    float acc = 0.f;
+    for (int z = l * l; z < (l + 1) * (l + 1); ++z) acc += P[(size_t)z * n + i];
+    dW[(size_t)l * n + i] = acc;
+  }
+}
+
 }  // namespace efl
 
 using namespace efl;
+
+// SO3_LinearV2 (reference EF_layers.py:655-671): out[n, i, :] = x[n, i, :] W[l(i)]^T (+ bias on i = 0).
+// x [N, L, Cin], W [lmax+1, Cout, Cin], out [N, L, Cout]; fp32.
+extern "C" int efl_so3_linear_fwd(const float* x, const float* W, const float* bias, float* out, int N, int lmax,
+                                  int Cin, int Cout, void* stream) {
+  if (N <= 0) return EFL_OK;
+  const int L = (lmax + 1) * (lmax + 1);
+  dim3 grid((Cout + BN - 1) / BN, (N + BM - 1) / BM, L), block(256);
+  gemm_nt_kernel<float, float, 0><<<grid, block, 0, (cudaStream_t)stream>>>(
+      x, (long long)L * Cin, W, Cin, bias, out, (long long)L * Cout, nullptr, 0, 0, N, Cout, Cin, Cin,
+      (long long)Cout * Cin, Cout);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+// d x[n, i, :] = d out[n, i, :] W[l(i)];  Wt = W transposed per degree: [lmax+1, Cin, Cout]
+extern "C" int efl_so3_linear_bwd_data(const float* dout, const float* Wt, float* dx, int N, int lmax, int Cin,
+                                       int Cout, void* stream) {
+  if (N <= 0) return EFL_OK;
+  const int L = (lmax + 1) * (lmax + 1);
+  dim3 grid((Cin + BN - 1) / BN, (N + BM - 1) / BM, L), block(256);
+  gemm_nt_kernel<float, float, 0><<<grid, block, 0, (cudaStream_t)stream>>>(
+      dout, (long long)L * Cout, Wt, Cout, nullptr, dx, (long long)L * Cin, nullptr, 0, 0, N, Cin, Cout, Cout,
+      (long long)Cout * Cin, Cin);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+// d W[l] = sum_{i in l} sum_n d out[n, i, :]^T x[n, i, :];  workspace: L * Cout * Cin floats
+extern "C" int efl_so3_linear_bwd_weight(const float* dout, const float* x, float* dW, float* workspace, int N,
+                                         int lmax, int Cin, int Cout, void* stream) {
+  const int L = (lmax + 1) * (lmax + 1);
+  const long long n = (long long)Cout * Cin;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (N <= 0) {
+    cudaMemsetAsync(dW, 0, sizeof(float) * n * (lmax + 1), s);
+    return EFL_OK;
+  }
+  dim3 grid((Cin + BN - 1) / BN, (Cout + BM - 1) / BM, L), block(256);
+  gemm_tn_kernel<float><<<grid, block, 0, s>>>(dout, (long long)L * Cout, x, (long long)L * Cin, workspace, N, Cout,
+                                              Cin, N, Cout, Cin);
+  EFL_CHECK_LAUNCH();
+  so3_wgrad_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(workspace, dW, lmax, n);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
 
 extern "C" int efl_gemm_nt_f32(int epilogue, const float* A, long long lda, const float* B, long long ldb,
                                const float* bias, float* C, long long ldc, float* C0, long long ldc0, int nsplit,

@@ -22,7 +22,7 @@ namespace s2tc {
 using namespace efl::tc;
 
 constexpr int CH = 128;
-constexpr int STAGES = 4;
+constexpr int MAX_STAGES = 4;
 constexpr int MAX_GROUPS = 4;
 constexpr int MAX_THREADS = (4 + 4 * MAX_GROUPS) * 32;
 constexpr int TMEM_COLS = 512;
@@ -34,6 +34,9 @@ struct Params {
   int first[3];            // first m-primary row of each buffer
   int ms[3];               // degrees per order
   int Ec;
+  int stages;              // operand ring depth (<= MAX_STAGES)
+  int ncb, cht;            // channel blocks of 128 per item row, total channels (row pitch)
+  int dup;                 // bwd: write order>0 rows in the dup layout (edge path) or plainly (node path)
   int NG;                  // worker groups (edges in flight per CTA)
   int gstride;             // TMEM columns per group: [D1 (aliased by D2) | D3 (bwd)]
   const float* T;          // to_grid   [G, M] fp32, m-primary columns
@@ -72,7 +75,7 @@ struct Layout {
   int off_T, off_F0, off_S, off_B2, off_bar, s_bytes, sbo;
   int total;
 };
-__host__ __device__ inline Layout make_layout(int KP, int GP, int bwd, int NG) {
+__host__ __device__ inline Layout make_layout(int KP, int GP, int bwd, int NG, int STAGES) {
   Layout L;
   L.blk_bytes = KP * 128;
   L.stage_bytes = 2 * L.blk_bytes * (bwd ? 2 : 1);
@@ -88,17 +91,23 @@ __host__ __device__ inline Layout make_layout(int KP, int GP, int bwd, int NG) {
   return L;
 }
 
-template <int KPC>
-__global__ void __launch_bounds__(MAX_THREADS, 1)
+template <int MS0, int MS1, int MS2, int GP, bool BWD, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1)
 s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant__ CUtensorMap mapH1,
                 const __grid_constant__ CUtensorMap mapH2, const __grid_constant__ CUtensorMap mapD0,
                 const __grid_constant__ CUtensorMap mapD1, const __grid_constant__ CUtensorMap mapD2, const Params p) {
+  constexpr int M = MS0 + 2 * MS1 + 2 * MS2;       // coefficient rows per item
+  constexpr int F1 = MS0, F2 = MS0 + 2 * MS1;      // first row of the order-1 / order-2 buffers
+  constexpr int R0 = MS0, R1 = 2 * MS1, R2 = 2 * MS2;
+  constexpr int KP = (M + 15) / 16 * 16, KPC = KP / 16;
+  constexpr bool DUP = BWD && MS1 > 0;             // edge backward writes the dup layout
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  const Layout L = make_layout(p.KP, p.GP, p.bwd, p.NG);
+  const Layout L = make_layout(KP, GP, BWD, p.NG, p.stages);
+  const int STAGES = p.stages;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
   uint64_t* h_full = bars;             // [STAGES]
-  uint64_t* h_empty = bars + STAGES;   // [STAGES]
+  uint64_t* h_empty = bars + MAX_STAGES;
   uint64_t* d1_full = bars + 8;        // [MAX_GROUPS]
   uint64_t* s_ready = bars + 12;
   uint64_t* d2_full = bars + 16;
@@ -117,20 +126,20 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
     __nv_bfloat16* sT = reinterpret_cast<__nv_bfloat16*>(smem + L.off_T);
     __nv_bfloat16* sF0 = reinterpret_cast<__nv_bfloat16*>(smem + L.off_F0);
     __nv_bfloat16* sB2 = reinterpret_cast<__nv_bfloat16*>(smem + L.off_B2);
-    for (int i = threadIdx.x; i < p.G * p.M; i += blockDim.x) {
-      const int g = i / p.M, j = i % p.M;
+    for (int i = threadIdx.x; i < p.G * M; i += blockDim.x) {
+      const int g = i / M, j = i % M;
       const float t = p.T[i], f = p.F[i];
       // K-major, 128B swizzle, rows g (128 B each), K index j < 64
       const int off_sw = g * 64 + ((((j >> 3) ^ (g & 7)) << 3) | (j & 7));
       sT[off_sw] = __float2bfloat16_rn(t);
-      if (p.bwd) sF0[off_sw] = __float2bfloat16_rn(j == 0 ? 0.f : f);
+      if (BWD) sF0[off_sw] = __float2bfloat16_rn(j == 0 ? 0.f : f);
       // K-major, no swizzle: rows j, K index g: (j/8)*sbo + (g/8)*128 + (j%8)*16 + (g%8)*2 bytes
       const int off_ns = ((j >> 3) * L.sbo + (g >> 3) * 128 + (j & 7) * 16) / 2 + (g & 7);
-      sB2[off_ns] = __float2bfloat16_rn(p.bwd ? t : f);
+      sB2[off_ns] = __float2bfloat16_rn(BWD ? t : f);
     }
   }
   if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; ++s) { mbar_init(&h_full[s], 1); mbar_init(&h_empty[s], 1); }
+    for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(&h_full[s], 1); mbar_init(&h_empty[s], 1); }
     for (int g = 0; g < MAX_GROUPS; ++g) {
       mbar_init(&d1_full[g], 1);
       mbar_init(&s_ready[g], 128);
@@ -149,28 +158,30 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const int n_mine = (p.Ec - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // edges of this CTA
-  const int row_bytes_total = p.M * 256;  // bytes per edge per operand (M rows x 128 ch x 2 B)
+  const int n_items = p.Ec * p.ncb;
+  const int n_mine = (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // items of this CTA
+  const int row_bytes_total = M * 256;  // bytes per edge per operand (M rows x 128 ch x 2 B)
 
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
       for (int i = 0; i < n_mine; ++i) {
-        const int e = blockIdx.x + i * gridDim.x;
+        const int it = blockIdx.x + i * gridDim.x;
+        const int e = it / p.ncb, cb = it % p.ncb;
         mbar_wait(&h_empty[stage], phase ^ 1);
         uint8_t* st = smem + stage * L.stage_bytes;
-        mbar_expect_tx(&h_full[stage], (uint32_t)(row_bytes_total * (p.bwd ? 2 : 1)));
+        mbar_expect_tx(&h_full[stage], (uint32_t)(row_bytes_total * (BWD ? 2 : 1)));
         for (int hb = 0; hb < 2; ++hb) {
           uint8_t* blk = st + hb * L.blk_bytes;
-          tma_load_2d(blk + p.first[0] * 128, &mapH0, &h_full[stage], hb * 64, e * p.rows[0]);
-          tma_load_2d(blk + p.first[1] * 128, &mapH1, &h_full[stage], hb * 64, e * p.rows[1]);
-          tma_load_2d(blk + p.first[2] * 128, &mapH2, &h_full[stage], hb * 64, e * p.rows[2]);
-          if (p.bwd) {
+          tma_load_2d(blk + 0, &mapH0, &h_full[stage], cb * CH + hb * 64, e * R0);
+          if (R1 > 0) tma_load_2d(blk + F1 * 128, &mapH1, &h_full[stage], cb * CH + hb * 64, e * R1);
+          if (R2 > 0) tma_load_2d(blk + F2 * 128, &mapH2, &h_full[stage], cb * CH + hb * 64, e * R2);
+          if (BWD) {
             uint8_t* dblk = st + 2 * L.blk_bytes + hb * L.blk_bytes;
-            tma_load_2d(dblk + p.first[0] * 128, &mapD0, &h_full[stage], hb * 64, e * p.rows[0]);
-            tma_load_2d(dblk + p.first[1] * 128, &mapD1, &h_full[stage], hb * 64, e * p.rows[1]);
-            tma_load_2d(dblk + p.first[2] * 128, &mapD2, &h_full[stage], hb * 64, e * p.rows[2]);
+            tma_load_2d(dblk + 0, &mapD0, &h_full[stage], cb * CH + hb * 64, e * R0);
+            if (R1 > 0) tma_load_2d(dblk + F1 * 128, &mapD1, &h_full[stage], cb * CH + hb * 64, e * R1);
+            if (R2 > 0) tma_load_2d(dblk + F2 * 128, &mapD2, &h_full[stage], cb * CH + hb * 64, e * R2);
           }
         }
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -184,12 +195,14 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
     int stage = 0;
     uint32_t phase = 0;
     const int NG = p.NG, lag = p.NG - 1;
-    const uint32_t idesc1 = make_idesc2(p.GP, 1, 0);   // A = operand tile (MN-major), B = T/F0 (K-major)
-    const uint32_t idesc2 = make_idesc2(p.KP, 0, 0);   // A = S (K-major), B = B2 (K-major)
+    const uint32_t idesc1 = make_idesc2(GP, 1, 0);   // A = operand tile (MN-major), B = T/F0 (K-major)
+    const uint32_t idesc2 = make_idesc2(KP, 0, 0);   // A = S (K-major), B = B2 (K-major)
     const uint32_t sT = smem_u32(smem + L.off_T), sF0 = smem_u32(smem + L.off_F0), sB2 = smem_u32(smem + L.off_B2);
     for (int i = 0; i < n_mine + lag; ++i) {
+      for (int pass = 0; pass < 2; ++pass) {
+      // second GEMM: before the first GEMM of edge i when lag > 0, after it when the pipeline has one group
       const int j = i - lag;
-      if (j >= 0 && j < n_mine) {
+      if (((lag > 0) == (pass == 0)) && j >= 0 && j < n_mine) {
         const int g = j % NG;
         const uint32_t k_th = (uint32_t)(j / NG);
         mbar_wait(&s_ready[g], k_th & 1);
@@ -197,14 +210,14 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
         if (lane == 0) {
           const uint32_t sS = smem_u32(smem + L.off_S + g * L.s_bytes);
           const uint32_t d2 = tmem_base + (uint32_t)(g * p.gstride);
-          for (int k = 0; k < p.GP / 16; ++k)
+          for (int k = 0; k < GP / 16; ++k)
             tc_mma(d2, make_desc_noswz(sS + k * 256, 128, (uint32_t)L.sbo), make_desc_noswz(sB2 + k * 256, 128, (uint32_t)L.sbo),
                    idesc2, k > 0 ? 1u : 0u);
           tc_commit(&d2_full[g]);
         }
         __syncwarp();
       }
-      if (i < n_mine) {
+      if (pass == 0 && i < n_mine) {
         const int g = i % NG;
         const uint32_t k_th = (uint32_t)(i / NG);
         mbar_wait(&h_full[stage], phase);
@@ -213,13 +226,13 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
         if (lane == 0) {
           const uint32_t sa = smem_u32(smem + stage * L.stage_bytes);
           const uint32_t d1 = tmem_base + (uint32_t)(g * p.gstride);
-          for (int k = 0; k < p.KP / 16; ++k)
+          for (int k = 0; k < KP / 16; ++k)
             tc_mma(d1, make_desc(sa + k * 2048, (uint32_t)L.blk_bytes, 1024), make_desc(sT + k * 32, 16, 1024), idesc1,
                    k > 0 ? 1u : 0u);
-          if (p.bwd) {
+          if (BWD) {
             const uint32_t sd = sa + 2 * L.blk_bytes;
-            const uint32_t d3 = d1 + (uint32_t)p.GP;
-            for (int k = 0; k < p.KP / 16; ++k)
+            const uint32_t d3 = d1 + (uint32_t)GP;
+            for (int k = 0; k < KP / 16; ++k)
               tc_mma(d3, make_desc(sd + k * 2048, (uint32_t)L.blk_bytes, 1024), make_desc(sF0 + k * 32, 16, 1024),
                      idesc1, k > 0 ? 1u : 0u);
           }
@@ -229,6 +242,7 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
+      }
     }
   } else if (warp >= 4 && warp < 4 + 4 * p.NG) {
     // ---- worker groups: thread = channel ----
@@ -237,29 +251,31 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
     const int c = q * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
     const uint32_t d1 = tmem_base + (uint32_t)(g * p.gstride) + lane_addr;
-    const uint32_t d3 = d1 + (uint32_t)p.GP;
+    const uint32_t d3 = d1 + (uint32_t)GP;
     const uint32_t d2 = d1;
     uint8_t* sS = smem + L.off_S + g * L.s_bytes + (c >> 3) * L.sbo + (c & 7) * 16;
-    const int f1 = p.first[1], f2 = p.first[2], ms1 = p.ms[1], ms2 = p.ms[2], nM = p.M;
     uint32_t k_th = 0;
     for (int i = g; i < n_mine; i += p.NG, ++k_th) {
-      const int e = blockIdx.x + i * gridDim.x;
+      const int it = blockIdx.x + i * gridDim.x;
+      const int e = it / p.ncb, cc = (it % p.ncb) * CH + c;
+      const size_t cht = (size_t)p.cht;
       // gate path first: its global loads overlap the wait below
-      const float gt = p.gate[(size_t)e * p.gate_ld + c];
+      const float gt = p.gate[(size_t)e * p.gate_ld + cc];
       float y0;
-      if (!p.bwd) y0 = silu_fast(gt);
-      else y0 = __bfloat162float(p.dy0[(size_t)e * p.rows[0] * CH + c]) * dsilu_fast(gt);
+      if (!BWD) y0 = silu_fast(gt);
+      else y0 = __bfloat162float(p.dy0[(size_t)e * R0 * cht + cc]) * dsilu_fast(gt);
       mbar_wait(&d1_full[g], k_th & 1);
       tc_fence_after();
-      if (!p.bwd) {
-        for (int g0 = 0; g0 < p.GP; g0 += 32) {
+      if (!BWD) {
+#pragma unroll 1
+        for (int g0 = 0; g0 < GP; g0 += 32) {
           uint32_t v[32];
           tc_ld16(d1 + (uint32_t)g0, v);
-          if (g0 + 16 < p.GP) tc_ld16(d1 + (uint32_t)(g0 + 16), v + 16);
+          if (g0 + 16 < GP) tc_ld16(d1 + (uint32_t)(g0 + 16), v + 16);
           tc_ld_wait();
 #pragma unroll
           for (int h = 0; h < 4; ++h) {
-            if (g0 + 8 * h < p.GP) {
+            if (g0 + 8 * h < GP) {
               float s[8];
 #pragma unroll
               for (int t = 0; t < 8; ++t) s[t] = silu_fast(__uint_as_float(v[8 * h + t]));
@@ -269,7 +285,8 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
           }
         }
       } else {
-        for (int g0 = 0; g0 < p.GP; g0 += 16) {
+#pragma unroll 1
+        for (int g0 = 0; g0 < GP; g0 += 16) {
           uint32_t v[16], w[16];
           tc_ld16(d1 + (uint32_t)g0, v);
           tc_ld16(d3 + (uint32_t)g0, w);
@@ -295,43 +312,36 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
       tc_ld_wait();
       tc_fence_before();
       mbar_arrive(&d2_free[g]);
-      if (!p.bwd) {
-        yv[0] = __float_as_uint(y0);
-        __nv_bfloat16* o0 = p.out[0] + (size_t)e * p.rows[0] * CH + c;
-        __nv_bfloat16* o1 = p.out[1] + (size_t)e * p.rows[1] * CH + c;
-        __nv_bfloat16* o2 = p.out[2] + (size_t)e * p.rows[2] * CH + c;
+      if (!DUP) {
+        if (!BWD) yv[0] = __float_as_uint(y0);
+        else p.dgate[(size_t)e * p.ld0 + cc] = __float2bfloat16_rn(y0);
+        __nv_bfloat16* o0 = p.out[0] + (size_t)e * R0 * cht + cc;
+        __nv_bfloat16* o1 = p.out[1] + (size_t)e * R1 * cht + cc;
+        __nv_bfloat16* o2 = p.out[2] + (size_t)e * R2 * cht + cc;
 #pragma unroll
-        for (int j = 0; j < 16 * KPC; ++j) {
-          if (j < nM) {
-            __nv_bfloat16* o = j >= f2 ? o2 + (j - f2) * CH : (j >= f1 ? o1 + (j - f1) * CH : o0 + j * CH);
-            *o = __float2bfloat16_rn(__uint_as_float(yv[j]));
-          }
+        for (int j = 0; j < M; ++j) {
+          __nv_bfloat16* o = j >= F2 ? o2 + (size_t)(j - F2) * cht : (j >= F1 ? o1 + (size_t)(j - F1) * cht : o0 + (size_t)j * cht);
+          *o = __float2bfloat16_rn(__uint_as_float(yv[j]));
         }
       } else {
         p.dgate[(size_t)e * p.ld0 + c] = __float2bfloat16_rn(y0);
         __nv_bfloat16* o0 = p.out[0] + (size_t)e * p.ld0 + c;
-        __nv_bfloat16* o1 = p.out[1] + (size_t)e * 4 * ms1 * CH + 2 * c;
-        __nv_bfloat16* o2 = p.out[2] + (size_t)e * 4 * ms2 * CH + 2 * c;
 #pragma unroll
-        for (int j = 0; j < 16 * KPC; ++j) {
-          if (j < f1) {
-            o0[j * CH] = __float2bfloat16_rn(__uint_as_float(yv[j]));
-          } else if (j < nM) {
-            const bool two = j >= f2;
-            const int ms = two ? ms2 : ms1;
-            const int t = j - (two ? f2 : f1);
-            if (t < ms) {
-              // +m ("real") row t; partner -m row is yv[j + ms]
-              uint32_t gi_u = 0u;
+        for (int j = 0; j < F1; ++j) o0[j * CH] = __float2bfloat16_rn(__uint_as_float(yv[j]));
+        // order m > 0: row t of the +m block pairs with row t of the -m block (MS rows later)
+        __nv_bfloat16* o1 = p.out[1] + (size_t)e * 4 * MS1 * CH + 2 * c;
 #pragma unroll
-              for (int jj = 0; jj < 16 * KPC; ++jj) gi_u = (jj == j + ms) ? yv[jj] : gi_u;
-              const float gr = __uint_as_float(yv[j]), gi = __uint_as_float(gi_u);
-              __nv_bfloat16* r0 = (two ? o2 : o1) + (size_t)t * 2 * CH;
-              __nv_bfloat16* r1 = r0 + 2 * ms * CH;
-              *reinterpret_cast<uint32_t*>(r0) = pack_bf16(gr, gi);
-              *reinterpret_cast<uint32_t*>(r1) = pack_bf16(gi, -gr);
-            }
-          }
+        for (int t = 0; t < MS1; ++t) {
+          const float gr = __uint_as_float(yv[F1 + t]), gi = __uint_as_float(yv[F1 + MS1 + t]);
+          *reinterpret_cast<uint32_t*>(o1 + (size_t)t * 2 * CH) = pack_bf16(gr, gi);
+          *reinterpret_cast<uint32_t*>(o1 + (size_t)(t + MS1) * 2 * CH) = pack_bf16(gi, -gr);
+        }
+        __nv_bfloat16* o2 = p.out[2] + (size_t)e * 4 * MS2 * CH + 2 * c;
+#pragma unroll
+        for (int t = 0; t < MS2; ++t) {
+          const float gr = __uint_as_float(yv[F2 + t]), gi = __uint_as_float(yv[F2 + MS2 + t]);
+          *reinterpret_cast<uint32_t*>(o2 + (size_t)t * 2 * CH) = pack_bf16(gr, gi);
+          *reinterpret_cast<uint32_t*>(o2 + (size_t)(t + MS2) * 2 * CH) = pack_bf16(gi, -gr);
         }
       }
     }
@@ -354,6 +364,55 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
 int efl_make_map_bf16(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld, int box_rows);
 int efl_num_sms();
 
+static int s2_launch(efl::s2tc::Params& p, const void* const* hs, const void* const* ds, long long n_rows_items,
+                     cudaStream_t st) {
+  using namespace efl::s2tc;
+  p.gstride = p.bwd ? 2 * p.GP : p.GP;
+  p.NG = TMEM_COLS / p.gstride;
+  if (p.NG > MAX_GROUPS) p.NG = MAX_GROUPS;
+  if (p.KP > 48 && p.NG > 2) p.NG = 2;
+  p.stages = MAX_STAGES;
+  Layout L = make_layout(p.KP, p.GP, p.bwd, p.NG, p.stages);
+  const int limit = 227 * 1024;
+  if (L.total > limit) { p.stages = 2; L = make_layout(p.KP, p.GP, p.bwd, p.NG, p.stages); }
+  EFL_REQUIRE(L.total <= limit, "efl_s2act_tc: shared memory budget exceeded");
+  CUtensorMap mh[3], md[3];
+  for (int s = 0; s < 3; ++s) {
+    const int r = p.rows[s] > 0 ? p.rows[s] : 1;
+    int rc = efl_make_map_bf16(&mh[s], hs[p.rows[s] > 0 ? s : 0], n_rows_items * r, p.cht, p.cht, r);
+    if (rc) return rc;
+    rc = efl_make_map_bf16(&md[s], p.bwd ? ds[p.rows[s] > 0 ? s : 0] : hs[p.rows[s] > 0 ? s : 0], n_rows_items * r,
+                           p.cht, p.cht, r);
+    if (rc) return rc;
+  }
+  const long long items = (long long)p.Ec * p.ncb;
+  const int grid = items < efl_num_sms() ? (int)items : efl_num_sms();
+  const int threads = (4 + 4 * p.NG) * 32;
+  const size_t smem = (size_t)L.total;
+#define S2_LAUNCH(MS0, MS1, MS2, GPV, MAXT)                                                                       \
+  {                                                                                                              \
+    if (p.bwd) {                                                                                                 \
+      auto kern = s2act_tc_kernel<MS0, MS1, MS2, GPV, true, MAXT>;                                               \
+      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, limit);                            \
+      kern<<<grid, threads, smem, st>>>(mh[0], mh[1], mh[2], md[0], md[1], md[2], p);                            \
+    } else {                                                                                                     \
+      auto kern = s2act_tc_kernel<MS0, MS1, MS2, GPV, false, MAXT>;                                              \
+      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, limit);                            \
+      kern<<<grid, threads, smem, st>>>(mh[0], mh[1], mh[2], md[0], md[1], md[2], p);                            \
+    }                                                                                                            \
+  }
+  if (p.ms[0] == 7 && p.ms[1] == 6 && p.ms[2] == 5 && p.GP == 80) S2_LAUNCH(7, 6, 5, 80, MAX_THREADS)
+  else if (p.ms[0] == 9 && p.ms[1] == 8 && p.ms[2] == 7 && p.GP == 96) S2_LAUNCH(9, 8, 7, 96, MAX_THREADS)
+  else if (p.ms[0] == 49 && p.ms[1] == 0 && p.GP == 224) S2_LAUNCH(49, 0, 0, 224, 384)
+  else {
+    efl_set_error("efl_s2act_tc: built for (lmax,mmax,G) = (6,2,70), (8,2,90) and node blocks (49 rows, G=210)");
+    return EFL_ERR_UNSUPPORTED;
+  }
+#undef S2_LAUNCH
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
 // fwd: h0..h2 hidden rows (plain split buffers, bf16) -> out0..out2 (plain split buffers); gate [Ec, gate_ld] fp32.
 // bwd: additionally d0..d2 = d(out) rows; out0 = &dY1_0[0][hidden column], out1/out2 dup-layout buffers, ld0 = row
 //      pitch of dY1_0, dgate = &dY1_0[0][gate column].  T/F: to/from grid [G, M] fp32 with m-primary columns.
@@ -372,40 +431,39 @@ extern "C" int efl_s2act_tc(int bwd, int lmax, int mmax, int G, const void* h0, 
   p.M = p.rows[0] + p.rows[1] + p.rows[2];
   p.KP = (p.M + 15) / 16 * 16;
   p.G = G; p.GP = (G + 15) / 16 * 16;
-  EFL_REQUIRE(p.KP <= 64 && p.GP <= 96, "efl_s2act_tc: coefficient / grid size out of range");
-  p.Ec = Ec; p.T = T; p.F = F; p.gate = gate; p.gate_ld = gate_ld;
+  EFL_REQUIRE(p.KP <= 64 && p.GP <= 224, "efl_s2act_tc: coefficient / grid size out of range");
+  p.Ec = Ec; p.ncb = 1; p.cht = CH; p.dup = 1;
+  p.T = T; p.F = F; p.gate = gate; p.gate_ld = gate_ld;
   p.out[0] = (__nv_bfloat16*)out0; p.out[1] = (__nv_bfloat16*)out1; p.out[2] = (__nv_bfloat16*)out2;
   p.ld0 = ld0; p.dgate = (__nv_bfloat16*)dgate; p.dy0 = (const __nv_bfloat16*)d0;
-  CUtensorMap mh[3], md[3];
   const void* hs[3] = {h0, h1, h2};
   const void* ds[3] = {d0, d1, d2};
-  for (int s = 0; s < 3; ++s) {
-    int rc = efl_make_map_bf16(&mh[s], hs[s], (long long)Ec * p.rows[s], CH, CH, p.rows[s]);
-    if (rc) return rc;
-    rc = efl_make_map_bf16(&md[s], bwd ? ds[s] : hs[s], (long long)Ec * p.rows[s], CH, CH, p.rows[s]);
-    if (rc) return rc;
-  }
-  p.gstride = bwd ? 2 * p.GP : p.GP;
-  p.NG = TMEM_COLS / p.gstride;
-  if (p.NG > MAX_GROUPS) p.NG = MAX_GROUPS;
-  const Layout L = make_layout(p.KP, p.GP, bwd, p.NG);
-  EFL_REQUIRE(L.total <= 200 * 1024, "efl_s2act_tc: shared memory budget exceeded");
-  static int attr_done = 0;
-  if (attr_done < L.total) {
-    cudaError_t e = cudaFuncSetAttribute(s2act_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(s2act_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(s2act_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    if (e != cudaSuccess) { efl_set_error(cudaGetErrorString(e)); return (int)e; }
-    attr_done = 200 * 1024;
-  }
-  const int grid = Ec < efl_num_sms() ? Ec : efl_num_sms();
-  const int threads = (4 + 4 * p.NG) * 32;
-  cudaStream_t st = (cudaStream_t)stream;
-  if (p.KP == 32) s2act_tc_kernel<2><<<grid, threads, L.total, st>>>(mh[0], mh[1], mh[2], md[0], md[1], md[2], p);
-  else if (p.KP == 48) s2act_tc_kernel<3><<<grid, threads, L.total, st>>>(mh[0], mh[1], mh[2], md[0], md[1], md[2], p);
-  else s2act_tc_kernel<4><<<grid, threads, L.total, st>>>(mh[0], mh[1], mh[2], md[0], md[1], md[2], p);
-  EFL_CHECK_LAUNCH();
-  return EFL_OK;
+  return s2_launch(p, hs, ds, Ec, (cudaStream_t)stream);
+}
+
+// Node-level variant (FeedForwardNetwork, EF_layers.py:234-270): x [N, M, cht] bf16 (l-primary rows, cht a multiple
+// of 128), gate [N, gate_ld] fp32, T/F [G, M] fp32.  fwd: out [N, M, cht] bf16.  bwd: dy [N, M, cht] -> out = d x,
+// dgate [N, cht] bf16.
+extern "C" int efl_s2act_tc_nodes(int bwd, int M, int G, int cht, const void* x, const void* dy, void* out,
+                                  void* dgate, const float* gate, long long gate_ld, const float* T, const float* F,
+                                  int N, void* stream) {
+  using namespace efl::s2tc;
+  if (N <= 0) return EFL_OK;
+  EFL_REQUIRE(cht % CH == 0, "efl_s2act_tc_nodes: channels must be a multiple of 128");
+  Params p{};
+  p.bwd = bwd;
+  p.ms[0] = M; p.ms[1] = 0; p.ms[2] = 0;
+  p.rows[0] = M; p.rows[1] = 0; p.rows[2] = 0;
+  p.first[0] = 0; p.first[1] = M; p.first[2] = M;
+  p.M = M;
+  p.KP = (M + 15) / 16 * 16;
+  p.G = G; p.GP = (G + 15) / 16 * 16;
+  EFL_REQUIRE(p.KP <= 64 && p.GP <= 224, "efl_s2act_tc_nodes: coefficient / grid size out of range");
+  p.Ec = N; p.ncb = cht / CH; p.cht = cht; p.dup = 0;
+  p.T = T; p.F = F; p.gate = gate; p.gate_ld = gate_ld;
+  p.out[0] = p.out[1] = p.out[2] = (__nv_bfloat16*)out;
+  p.ld0 = cht; p.dgate = (__nv_bfloat16*)dgate; p.dy0 = (const __nv_bfloat16*)dy;
+  const void* hs[3] = {x, x, x};
+  const void* ds[3] = {dy, dy, dy};
+  return s2_launch(p, hs, ds, N, (cudaStream_t)stream);
 }

@@ -25,7 +25,7 @@ constexpr int B_BYTES = MAX_BN * BK * 2;   // 32 KB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 constexpr int TMEM_COLS = 512;
-constexpr int NUM_THREADS = 256;
+constexpr int NUM_THREADS = 384;   // 4 control warps + 8 epilogue warps
 
 struct Params {
   int mode;      // 0 NT, 1 TN
@@ -68,7 +68,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], 128);
+      mbar_init(&tempty[a], 256);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -155,6 +155,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     }
   } else if (warp >= 4) {
     const int q = warp & 3;
+    const int eh = (warp - 4) >> 2;
     const int row_in_tile = q * 32 + lane;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -167,50 +168,59 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr0 = tmem_base + (uint32_t)(acc * MAX_BN) + ((uint32_t)(q * 32) << 16);
-      for (int c0 = 0; c0 < p.BN; c0 += 16) {
-        uint32_t v[16];
-        tc_ld16(taddr0 + (uint32_t)c0, v);
+      // two warps share a lane quarter: warp-half `eh` takes every other 32-column block
+      for (int cb = 32 * eh; cb < p.BN; cb += 64) {
+        uint32_t vv[32];
+        const bool two = cb + 16 < p.BN;
+        tc_ld16(taddr0 + (uint32_t)cb, vv);
+        if (two) tc_ld16(taddr0 + (uint32_t)(cb + 16), vv + 16);
         tc_ld_wait();
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          if (hh == 1 && !two) break;
+          const uint32_t* v = vv + 16 * hh;
+          const int c0 = cb + 16 * hh;
         const int col = n_blk * p.BN + c0;
-        if (tn) {
-          if (row_ok) {
-            float4* dst = reinterpret_cast<float4*>(p.P + ((size_t)z * p.M + row) * p.N + col);
+          if (tn) {
+            if (row_ok) {
+              float4* dst = reinterpret_cast<float4*>(p.P + ((size_t)z * p.M + row) * p.N + col);
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-              dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
-                                   __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
-          }
-        } else if (p.epi == 2) {
-          // complex combine: partner row = lane ^ 1, column pairs (2q, 2q+1) -> output column q
-          float o[8];
+              for (int j = 0; j < 4; ++j)
+                dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
+                                     __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+            }
+          } else if (p.epi == 2) {
+            // complex combine: partner row = lane ^ 1, column pairs (2q, 2q+1) -> output column q
+            float o[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float mine_e = __uint_as_float(v[2 * j]);
-            const float mine_o = __uint_as_float(v[2 * j + 1]);
-            const float other_o = __shfl_xor_sync(0xffffffffu, mine_o, 1);
-            o[j] = (lane & 1) ? (mine_e + other_o) : (mine_e - other_o);
-          }
-          if (row_ok) {
-            uint4 pk = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]),
-                                  pack_bf16(o[6], o[7]));
-            *reinterpret_cast<uint4*>(p.C + (size_t)row * p.ldc + col / 2) = pk;
-          }
-        } else {
-          float f[16];
+            for (int j = 0; j < 8; ++j) {
+              const float mine_e = __uint_as_float(v[2 * j]);
+              const float mine_o = __uint_as_float(v[2 * j + 1]);
+              const float other_o = __shfl_xor_sync(0xffffffffu, mine_o, 1);
+              o[j] = (lane & 1) ? (mine_e + other_o) : (mine_e - other_o);
+            }
+            if (row_ok) {
+              uint4 pk = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]),
+                                    pack_bf16(o[6], o[7]));
+              *reinterpret_cast<uint4*>(p.C + (size_t)row * p.ldc + col / 2) = pk;
+            }
+          } else {
+            float f[16];
 #pragma unroll
-          for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]) + (p.bias ? __ldg(p.bias + col + j) : 0.f);
-          if (row_ok) {
-            if (p.epi == 1 && col < p.nsplit) {
-              float4* dst = reinterpret_cast<float4*>(p.C0 + (size_t)row * p.ldc0 + col);
+            for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]) + (p.bias ? __ldg(p.bias + col + j) : 0.f);
+            if (row_ok) {
+              if (p.epi == 1 && col < p.nsplit) {
+                float4* dst = reinterpret_cast<float4*>(p.C0 + (size_t)row * p.ldc0 + col);
 #pragma unroll
-              for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
-            } else {
-              const int cc = col - (p.epi == 1 ? p.nsplit : 0);
-              uint4* dst = reinterpret_cast<uint4*>(p.C + (size_t)row * p.ldc + cc);
-              dst[0] = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]),
-                                  pack_bf16(f[6], f[7]));
-              dst[1] = make_uint4(pack_bf16(f[8], f[9]), pack_bf16(f[10], f[11]), pack_bf16(f[12], f[13]),
-                                  pack_bf16(f[14], f[15]));
+                for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+              } else {
+                const int cc = col - (p.epi == 1 ? p.nsplit : 0);
+                uint4* dst = reinterpret_cast<uint4*>(p.C + (size_t)row * p.ldc + cc);
+                dst[0] = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]),
+                                    pack_bf16(f[6], f[7]));
+                dst[1] = make_uint4(pack_bf16(f[8], f[9]), pack_bf16(f[10], f[11]), pack_bf16(f[12], f[13]),
+                                    pack_bf16(f[14], f[15]));
+              }
             }
           }
         }

@@ -485,15 +485,25 @@ class EdgeDegreeFunction(torch.autograd.Function):
 # node-level separable S2 activation (FeedForwardNetwork)
 # ---------------------------------------------------------------------------
 class NodeS2ActFunction(torch.autograd.Function):
-    """(gate [N, CH], x [N, L, CH]) -> SeparableS2Activation output [N, L, CH] on the (lmax, lmax) grid."""
+    """(gate [N, CH], x [N, L, CH]) -> SeparableS2Activation output [N, L, CH] on the (lmax, lmax) grid.
+    bf16 mode: tcgen05 kernel on bf16 copies (fp32 accumulation); fp32 mode: SIMT kernel."""
 
     @staticmethod
     def forward(ctx, gate, x, to_g, from_g):
         check_cuda(gate, x)
-        gate = gate.contiguous()
-        x = x.contiguous()
+        gate = gate.contiguous().float()
         N, Lc, CH = x.shape
         G = to_g.shape[0]
+        tc = _PRECISION == "bf16" and CH % 128 == 0 and Lc <= 64 and G <= 224
+        ctx.tc = tc
+        if tc:
+            xb = x.to(torch.bfloat16).contiguous()
+            yb = torch.empty_like(xb)
+            call("efl_s2act_tc_nodes", 0, Lc, G, CH, ptr(xb), None, ptr(yb), None, ptr(gate), CH, ptr(to_g), ptr(from_g),
+                 N, work=N * 4.0 * G * Lc * CH, tag="efl_s2act_tc_nodes_fwd")
+            ctx.save_for_backward(gate, xb, to_g, from_g)
+            return yb.float()
+        x = x.contiguous()
         y = torch.empty_like(x)
         pin = _Ptrs([x.data_ptr()], [Lc * CH], [0, Lc])
         pout = _Ptrs([y.data_ptr()], [Lc * CH], [0, Lc])
@@ -504,9 +514,16 @@ class NodeS2ActFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         gate, x, to_g, from_g = ctx.saved_tensors
-        dy = dy.contiguous()
         N, Lc, CH = x.shape
         G = to_g.shape[0]
+        if ctx.tc:
+            dyb = dy.to(torch.bfloat16).contiguous()
+            dxb = torch.empty_like(x)
+            dgb = torch.empty(N, CH, dtype=torch.bfloat16, device=x.device)
+            call("efl_s2act_tc_nodes", 1, Lc, G, CH, ptr(x), ptr(dyb), ptr(dxb), ptr(dgb), ptr(gate), CH, ptr(to_g),
+                 ptr(from_g), N, work=N * 6.0 * G * Lc * CH, tag="efl_s2act_tc_nodes_bwd")
+            return dgb.float(), dxb.float(), None, None
+        dy = dy.contiguous()
         dx = torch.empty_like(x)
         dgate = torch.empty_like(gate)
         pin = _Ptrs([x.data_ptr()], [Lc * CH], [0, Lc])
@@ -515,3 +532,74 @@ class NodeS2ActFunction(torch.autograd.Function):
         call("efl_s2act_bwd", Lc, G, CH, 0, 0, *pin.args(), *pdin.args(), *pdout.args(), 0, ptr(gate), CH, ptr(dgate),
              CH, ptr(to_g), ptr(from_g), N)
         return dgate, dx, None, None
+
+
+# ---------------------------------------------------------------------------
+# node-level SO3_LinearV2 and RMS norm
+# ---------------------------------------------------------------------------
+class SO3LinearFunction(torch.autograd.Function):
+    """x [N, L, Cin], weight [lmax+1, Cout, Cin], bias [Cout] -> [N, L, Cout] (EF_layers.py:655-671)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        check_cuda(x, weight, bias)
+        x = x.contiguous().float()
+        w = weight.detach().contiguous().float()
+        N, L, Cin = x.shape
+        lmax, Cout = w.shape[0] - 1, w.shape[1]
+        out = torch.empty(N, L, Cout, dtype=torch.float32, device=x.device)
+        call("efl_so3_linear_fwd", ptr(x), ptr(w), ptr(bias.detach().contiguous().float()), ptr(out), N, lmax, Cin, Cout,
+             work=2.0 * N * L * Cin * Cout)
+        ctx.save_for_backward(x, w)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, w = ctx.saved_tensors
+        dout = dout.contiguous().float()
+        N, L, Cin = x.shape
+        lmax, Cout = w.shape[0] - 1, w.shape[1]
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            wt = w.transpose(1, 2).contiguous()
+            dx = torch.empty_like(x)
+            call("efl_so3_linear_bwd_data", ptr(dout), ptr(wt), ptr(dx), N, lmax, Cin, Cout, work=2.0 * N * L * Cin * Cout)
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty_like(w)
+            ws = torch.empty(L * Cout * Cin, dtype=torch.float32, device=x.device)
+            call("efl_so3_linear_bwd_weight", ptr(dout), ptr(x), ptr(dw), ptr(ws), N, lmax, Cin, Cout,
+                 work=2.0 * N * L * Cin * Cout)
+        if ctx.needs_input_grad[2]:
+            db = dout[:, 0, :].sum(dim=0)
+        return dx, dw, db
+
+
+class RMSNormSHFunction(torch.autograd.Function):
+    """Centred, degree-balanced RMS norm with per-degree gain and l=0 bias (EF_layers.py:2099-2192)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, lmax, eps):
+        check_cuda(x, gamma, beta)
+        x = x.contiguous().float()
+        N, L, C = x.shape
+        y = torch.empty_like(x)
+        g = gamma.detach().contiguous().float()
+        call("efl_rmsnorm_sh_fwd", lmax, C, ptr(x), ptr(g), ptr(beta.detach().contiguous().float()), float(eps), ptr(y), N,
+             work=2.0 * x.numel() * 4)
+        ctx.save_for_backward(x, g)
+        ctx.misc = (lmax, eps)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, g = ctx.saved_tensors
+        lmax, eps = ctx.misc
+        dy = dy.contiguous().float()
+        N, L, C = x.shape
+        dx = torch.empty_like(x)
+        nblk = max(1, min(296, (N + 7) // 8))
+        part = torch.empty(nblk, (lmax + 2) * C, dtype=torch.float32, device=x.device)
+        call("efl_rmsnorm_sh_bwd", lmax, C, ptr(x), ptr(g), float(eps), ptr(dy), ptr(dx), ptr(part), nblk, N,
+             work=3.0 * x.numel() * 4)
+        tot = part.sum(dim=0)
+        return dx, tot[:(lmax + 1) * C].view(lmax + 1, C), tot[(lmax + 1) * C:], None, None
