@@ -10,7 +10,7 @@
  * caller; all work is enqueued on `stream` (a cudaStream_t passed as void*), no synchronisation inside;
  * return 0 on success, otherwise a cudaError_t value or an EFL_ERR_* code, with a message available from
  * efl_last_error_string() (thread-local).  Shapes use L=(lmax+1)^2 coefficients, M kept coefficients with
- * |m|<=mmax, WSZ = sum_l min(2l+1, 2mmax+1)*(2l+1) Wigner floats per edge; built for (lmax,mmax) in
+ * |m|<=mmax, WSZ = sum_l min(2l+1, 2mmax+1)*pad4(2l+1) Wigner floats per edge (rows padded to 16 bytes); built for (lmax,mmax) in
  * {(6,2), (8,2), (4,2)}.
  *
  * Edge operand layout ("m-primary, split by order"): for order m a dense [rows_m*Ec, (lmax+1-m)*CH] matrix,
@@ -64,11 +64,15 @@ int efl_rotate_back_aggregate_fwd(int lmax, int mmax, int heads, int value_ch, i
                                   const void* v1, const void* v2, const float* alpha, const int* rowptr,
                                   const int* perm, const float* wig, float* out, int n0, int n1, int e0,
                                   void* stream);
-/* Backward: dout [Nt,L,heads*value] -> dy0..dy2 (d value, dup layout for m>0) and dalpha [E,heads]. */
+/* Backward: dout [Nt,L,heads*value] -> dy0..dy2 (d value, dup layout for m>0) and dalpha
+ * [efl_rotate_back_parts(lmax,mmax), E, heads]: one partial plane per degree group (planes part_stride floats
+ * apart), summed in fixed order by efl_segment_softmax_bwd. */
+int efl_rotate_back_parts(int lmax, int mmax);
 int efl_rotate_back_aggregate_bwd(int lmax, int mmax, int heads, int value_ch, int bf16, const void* v0,
                                   const void* v1, const void* v2, void* dy0, void* dy1, void* dy2,
                                   const float* alpha, const int* rowptr, const int* perm, const float* wig,
-                                  const float* dout, float* dalpha, int n0, int n1, int e0, void* stream);
+                                  const float* dout, float* dalpha, long long part_stride, int n0, int n1, int e0,
+                                  void* stream);
 
 /* EdgeDegreeEmbedding tail (:116-147): m0 [E,(lmax+1)*C] (rad_func output, original order) -> out [Nt,L,C]. */
 int efl_edge_degree_fwd(int lmax, int mmax, int C, const float* m0, const int* rowptr, const int* perm,
@@ -89,8 +93,9 @@ int efl_alpha_logits_bwd(const float* extra, int ld, int heads, int alpha_ch, co
  * exp(x - max_seg) / (sum_seg + 1e-16), one warp per destination in [n0,n1). */
 int efl_segment_softmax_fwd(const float* logits, int heads, const int* rowptr, float* alpha, int n0, int n1,
                             void* stream);
-int efl_segment_softmax_bwd(const float* alpha, const float* dalpha, int heads, const int* rowptr, float* dlogits,
-                            int n0, int n1, void* stream);
+/* dalpha: nparts planes [E,heads], part_stride floats apart (nparts = 1 for a plain gradient). */
+int efl_segment_softmax_bwd(const float* alpha, const float* dalpha, int nparts, long long part_stride, int heads,
+                            const int* rowptr, float* dlogits, int n0, int n1, void* stream);
 
 /* SeparableS2Activation / S2Activation (:1736-1773) with the SO3_Grid matrices (:531-621) given as
  * to_grid, from_grid [G, M] (G = res_beta*res_alpha).  Row maps (HOST arrays): nseg segments, base[nseg]

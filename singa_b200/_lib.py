@@ -24,13 +24,13 @@ SIGNATURES = {
     "efl_rotate_in_bwd": "iiiipppppppippppp" "iip",
     "efl_segment_sum_rows": "piiiipppiip",
     "efl_rotate_back_aggregate_fwd": "iiiiipppppppp" "iiip",
-    "efl_rotate_back_aggregate_bwd": "iiiiipppppppppppp" "iiip",
+    "efl_rotate_back_aggregate_bwd": "iiiiipppppppppppp" "liiip",
     "efl_edge_degree_fwd": "iiippppfpip",
     "efl_edge_degree_bwd": "iiipppfpip",
     "efl_alpha_logits_fwd": "piiippppip",
     "efl_alpha_logits_bwd": "piiippppp" "iipiip",
     "efl_segment_softmax_fwd": "pippiip",
-    "efl_segment_softmax_bwd": "ppippiip",
+    "efl_segment_softmax_bwd": "ppilippiip",
     "efl_s2act_fwd": "iiiii" "ippp" "ippp" "plpplp",
     "efl_s2act_bwd": "iiiii" "ippp" "ippp" "ippp" "i" "plplpplp",
     "efl_gemm_nt_f32": "iplplpplpliiiip",
@@ -68,6 +68,8 @@ def _load():
     lib.efl_gemm_tn_splits.restype = _I
     lib.efl_tc_gemm_tn_splits.argtypes = [_I, _I, _I]
     lib.efl_tc_gemm_tn_splits.restype = _I
+    lib.efl_rotate_back_parts.argtypes = [_I, _I]
+    lib.efl_rotate_back_parts.restype = _I
     return lib
 
 

@@ -21,23 +21,65 @@ __device__ __forceinline__ float dslrelu(float x) {
   return 0.5f * (1.f + kSlope) + 0.5f * (1.f - kSlope) * ((2.f * s - 1.f) + 2.f * x * s * (1.f - s));
 }
 
-// one warp per edge, lane = alpha channel (A == 32)
+// One warp per edge; lane = (head h = lane >> 2, quarter q = lane & 3) owns channels [8q, 8q+8) of head h, loaded
+// as two float4 (the row pitch and the head offset are multiples of 16 bytes).  LayerNorm statistics are reduced
+// over the 4 lanes of a head with two shuffles.  heads <= 8; lanes of absent heads idle.
+struct Lane8 {
+  float v[8];
+};
+__device__ __forceinline__ Lane8 load8(const float* p) {
+  Lane8 r;
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+  r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+__device__ __forceinline__ float quad_sum(float v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  return v;
+}
+__device__ __forceinline__ void store8(float* p, const float* o) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(o[0], o[1], o[2], o[3]);
+  reinterpret_cast<float4*>(p)[1] = make_float4(o[4], o[5], o[6], o[7]);
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float* o) {
+  __nv_bfloat162 h0 = __floats2bfloat162_rn(o[0], o[1]), h1 = __floats2bfloat162_rn(o[2], o[3]);
+  __nv_bfloat162 h2 = __floats2bfloat162_rn(o[4], o[5]), h3 = __floats2bfloat162_rn(o[6], o[7]);
+  uint4 u;
+  u.x = *reinterpret_cast<uint32_t*>(&h0);
+  u.y = *reinterpret_cast<uint32_t*>(&h1);
+  u.z = *reinterpret_cast<uint32_t*>(&h2);
+  u.w = *reinterpret_cast<uint32_t*>(&h3);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+
 __global__ void __launch_bounds__(256) alpha_logits_fwd_kernel(const float* __restrict__ extra, int ld, int heads,
                                                                const float* __restrict__ ln_w,
                                                                const float* __restrict__ ln_b,
                                                                const float* __restrict__ adot,
                                                                float* __restrict__ logits, int Ec) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= Ec) return;
-  const float w = ln_w[lane], b = ln_b[lane];
-  for (int h = 0; h < heads; ++h) {
-    const float v = extra[(size_t)warp * ld + h * 32 + lane];
-    const float mean = warp_sum(v) * (1.f / 32.f);
-    const float d = v - mean;
-    const float var = warp_sum(d * d) * (1.f / 32.f);
-    const float y = d * rsqrtf(var + kLnEps) * w + b;
-    const float s = warp_sum(slrelu(y) * adot[h * 32 + lane]);
-    if (lane == 0) logits[(size_t)warp * heads + h] = s;
+  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const int h = lane >> 2, q = lane & 3;
+  const bool on = h < heads;
+  const int hc = on ? h : 0;
+  const Lane8 w = load8(ln_w + 8 * q), b = load8(ln_b + 8 * q), ad = load8(adot + hc * 32 + 8 * q);
+  for (int e = blockIdx.x * nw + wib; e < Ec; e += gridDim.x * nw) {
+    const Lane8 x = load8(extra + (size_t)e * ld + hc * 32 + 8 * q);
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += x.v[j];
+    const float mean = quad_sum(s) * (1.f / 32.f);
+    float vs = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) vs = fmaf(x.v[j] - mean, x.v[j] - mean, vs);
+    const float rstd = rsqrtf(quad_sum(vs) * (1.f / 32.f) + kLnEps);
+    float acc = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc = fmaf(slrelu((x.v[j] - mean) * rstd * w.v[j] + b.v[j]), ad.v[j], acc);
+    acc = quad_sum(acc);
+    if (on && q == 0) logits[(size_t)e * heads + h] = acc;
   }
 }
 
@@ -52,43 +94,64 @@ __global__ void __launch_bounds__(256) alpha_logits_bwd_kernel(const float* __re
                                                                TOut* __restrict__ dextra, int ldo,
                                                                float* __restrict__ part, int Ec) {
   extern __shared__ float sp[];  // [8 warps][heads*32 + 64]
-  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nw = blockDim.x >> 5;
+  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const int h = lane >> 2, q = lane & 3;
+  const bool on = h < heads;
+  const int hc = on ? h : 0;
   const int stride = heads * 32 + 64;
-  const float w = ln_w[lane], b = ln_b[lane];
-  float g_w = 0.f, g_b = 0.f;
-  float g_dot[8];
+  const Lane8 w = load8(ln_w + 8 * q), b = load8(ln_b + 8 * q), ad = load8(adot + hc * 32 + 8 * q);
+  float g_w[8], g_b[8], g_dot[8];
 #pragma unroll
-  for (int h = 0; h < 8; ++h) g_dot[h] = 0.f;
+  for (int j = 0; j < 8; ++j) g_w[j] = g_b[j] = g_dot[j] = 0.f;
   for (int e = blockIdx.x * nw + wib; e < Ec; e += gridDim.x * nw) {
+    const Lane8 x = load8(extra + (size_t)e * ld + hc * 32 + 8 * q);
+    const float dl = on ? __ldg(dlogits + (size_t)e * heads + h) : 0.f;
+    float s = 0.f;
 #pragma unroll
-    for (int h = 0; h < 8; ++h) {
-      if (h < heads) {
-        const float v = extra[(size_t)e * ld + h * 32 + lane];
-        const float mean = warp_sum(v) * (1.f / 32.f);
-        const float d = v - mean;
-        const float var = warp_sum(d * d) * (1.f / 32.f);
-        const float rstd = rsqrtf(var + kLnEps);
-        const float xh = d * rstd;
-        const float y = xh * w + b;
-        const float dl = dlogits[(size_t)e * heads + h];
-        g_dot[h] += dl * slrelu(y);
-        const float dy = dl * adot[h * 32 + lane] * dslrelu(y);
-        g_w += dy * xh;
-        g_b += dy;
-        const float dxh = dy * w;
-        const float m1 = warp_sum(dxh) * (1.f / 32.f);
-        const float m2 = warp_sum(dxh * xh) * (1.f / 32.f);
-        dextra[(size_t)e * ldo + h * 32 + lane] = from_f<TOut>(rstd * (dxh - m1 - xh * m2));
-      }
+    for (int j = 0; j < 8; ++j) s += x.v[j];
+    const float mean = quad_sum(s) * (1.f / 32.f);
+    float vs = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) vs = fmaf(x.v[j] - mean, x.v[j] - mean, vs);
+    const float rstd = rsqrtf(quad_sum(vs) * (1.f / 32.f) + kLnEps);
+    float xh[8], dxh[8], m1 = 0.f, m2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      xh[j] = (x.v[j] - mean) * rstd;
+      const float y = xh[j] * w.v[j] + b.v[j];
+      g_dot[j] = fmaf(dl, slrelu(y), g_dot[j]);
+      const float dy = dl * ad.v[j] * dslrelu(y);
+      g_w[j] = fmaf(dy, xh[j], g_w[j]);
+      g_b[j] += dy;
+      dxh[j] = dy * w.v[j];
+      m1 += dxh[j];
+      m2 = fmaf(dxh[j], xh[j], m2);
+    }
+    m1 = quad_sum(m1) * (1.f / 32.f);
+    m2 = quad_sum(m2) * (1.f / 32.f);
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = rstd * (dxh[j] - m1 - xh[j] * m2);
+    if (on) store8(dextra + (size_t)e * ldo + h * 32 + 8 * q, o);
+  }
+  // LayerNorm parameter gradients: sum over the heads (lanes that share q), fixed shuffle order
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+#pragma unroll
+    for (int o = 4; o < 32; o <<= 1) {
+      g_w[j] += __shfl_xor_sync(0xffffffffu, g_w[j], o);
+      g_b[j] += __shfl_xor_sync(0xffffffffu, g_b[j], o);
     }
   }
   float* mine = sp + wib * stride;
 #pragma unroll
-  for (int h = 0; h < 8; ++h)
-    if (h < heads) mine[h * 32 + lane] = g_dot[h];
-  mine[heads * 32 + lane] = g_w;
-  mine[heads * 32 + 32 + lane] = g_b;
+  for (int j = 0; j < 8; ++j) {
+    if (on) mine[h * 32 + 8 * q + j] = g_dot[j];
+    if (h == 0) {
+      mine[heads * 32 + 8 * q + j] = g_w[j];
+      mine[heads * 32 + 32 + 8 * q + j] = g_b[j];
+    }
+  }
   __syncthreads();
   for (int i = threadIdx.x; i < stride; i += blockDim.x) {
     float acc = 0.f;
@@ -118,8 +181,11 @@ __global__ void __launch_bounds__(256) seg_softmax_fwd_kernel(const float* __res
 
 // d logits = alpha * (d alpha - sum_seg alpha * d alpha)   (the 1e-16 in the denominator is
 // immaterial: the reference's autograd differentiates e/(s+1e-16), identical up to 1e-16/s)
+// d alpha arrives as `nparts` partial planes (one per degree group of the rotate-back backward), summed here in
+// fixed order.
 __global__ void __launch_bounds__(256) seg_softmax_bwd_kernel(const float* __restrict__ alpha,
-                                                              const float* __restrict__ dalpha, int heads,
+                                                              const float* __restrict__ dalpha, int nparts,
+                                                              long long part_stride, int heads,
                                                               const int* __restrict__ rowptr,
                                                               float* __restrict__ dlogits, int n0, int n1) {
   const int n = n0 + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
@@ -127,11 +193,17 @@ __global__ void __launch_bounds__(256) seg_softmax_bwd_kernel(const float* __res
   const int kb = rowptr[n], ke = rowptr[n + 1];
   for (int h = 0; h < heads; ++h) {
     float dot = 0.f;
-    for (int k = kb + lane; k < ke; k += 32) dot += alpha[(size_t)k * heads + h] * dalpha[(size_t)k * heads + h];
+    for (int k = kb + lane; k < ke; k += 32) {
+      float da = 0.f;
+      for (int p = 0; p < nparts; ++p) da += dalpha[(size_t)p * part_stride + (size_t)k * heads + h];
+      dot += alpha[(size_t)k * heads + h] * da;
+    }
     dot = warp_sum(dot);
     for (int k = kb + lane; k < ke; k += 32) {
+      float da = 0.f;
+      for (int p = 0; p < nparts; ++p) da += dalpha[(size_t)p * part_stride + (size_t)k * heads + h];
       const float a = alpha[(size_t)k * heads + h];
-      dlogits[(size_t)k * heads + h] = a * (dalpha[(size_t)k * heads + h] - dot);
+      dlogits[(size_t)k * heads + h] = a * (da - dot);
     }
   }
 }
@@ -144,8 +216,11 @@ extern "C" int efl_alpha_logits_fwd(const float* extra, int ld, int heads, int a
                                     const float* ln_b, const float* alpha_dot, float* logits, int Ec, void* stream) {
   if (Ec <= 0) return EFL_OK;
   EFL_REQUIRE(alpha_ch == 32 && heads <= 8, "efl_alpha_logits_fwd: attn_alpha_channels must be 32, heads <= 8");
+  EFL_REQUIRE((ld % 4) == 0 && ((uintptr_t)extra & 15) == 0, "efl_alpha_logits_fwd: extra must be 16-byte aligned, ld % 4 == 0");
   const int warps_per_block = 8;
-  alpha_logits_fwd_kernel<<<(Ec + warps_per_block - 1) / warps_per_block, 256, 0, (cudaStream_t)stream>>>(
+  const int want = (Ec + warps_per_block - 1) / warps_per_block;
+  const int cap = 148 * 8 * 4;
+  alpha_logits_fwd_kernel<<<want < cap ? want : cap, 256, 0, (cudaStream_t)stream>>>(
       extra, ld, heads, ln_w, ln_b, alpha_dot, logits, Ec);
   EFL_CHECK_LAUNCH();
   return EFL_OK;
@@ -157,6 +232,8 @@ extern "C" int efl_alpha_logits_bwd(const float* extra, int ld, int heads, int a
                                     int ldo, int bf16_out, float* part, int nblocks, int Ec, void* stream) {
   EFL_REQUIRE(alpha_ch == 32 && heads <= 8, "efl_alpha_logits_bwd: attn_alpha_channels must be 32, heads <= 8");
   EFL_REQUIRE(nblocks > 0, "efl_alpha_logits_bwd: nblocks must be positive");
+  EFL_REQUIRE((ld % 4) == 0 && (ldo % 8) == 0 && ((uintptr_t)extra & 15) == 0 && ((uintptr_t)dextra & 15) == 0,
+              "efl_alpha_logits_bwd: extra/dextra must be 16-byte aligned (ld % 4 == 0, ldo % 8 == 0)");
   const size_t smem = 8 * (heads * 32 + 64) * sizeof(float);
   if (bf16_out)
     alpha_logits_bwd_kernel<__nv_bfloat16><<<nblocks, 256, smem, (cudaStream_t)stream>>>(
@@ -177,12 +254,13 @@ extern "C" int efl_segment_softmax_fwd(const float* logits, int heads, const int
   return EFL_OK;
 }
 
-extern "C" int efl_segment_softmax_bwd(const float* alpha, const float* dalpha, int heads, const int* rowptr,
-                                       float* dlogits, int n0, int n1, void* stream) {
+extern "C" int efl_segment_softmax_bwd(const float* alpha, const float* dalpha, int nparts, long long part_stride,
+                                       int heads, const int* rowptr, float* dlogits, int n0, int n1, void* stream) {
+  EFL_REQUIRE(nparts >= 1, "efl_segment_softmax_bwd: nparts must be >= 1");
   if (n1 <= n0) return EFL_OK;
   const int nodes = n1 - n0;
-  seg_softmax_bwd_kernel<<<(nodes + 7) / 8, 256, 0, (cudaStream_t)stream>>>(alpha, dalpha, heads, rowptr, dlogits,
-                                                                             n0, n1);
+  seg_softmax_bwd_kernel<<<(nodes + 7) / 8, 256, 0, (cudaStream_t)stream>>>(alpha, dalpha, nparts, part_stride, heads,
+                                                                             rowptr, dlogits, n0, n1);
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }

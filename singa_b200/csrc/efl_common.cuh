@@ -36,15 +36,17 @@ namespace efl {
 //   kept rows            : |m'| <= min(l, MMAX)                          (M entries)
 //   m-primary index      : m=0 block (l=0..LMAX), then for m=1..MMAX the +m block
 //                          (l=m..LMAX, "real") followed by the -m block ("imag")
-//   Wigner store         : for each l the kept rows m' of D^l, each 2l+1 wide (WSZ floats)
+//   Wigner store         : for each l the kept rows m' of D^l, each 2l+1 wide and padded to a multiple of 4 floats
+//                          (16-byte rows: float4 / cp.async staging), WSZ floats per edge (296 for (6,2))
 template <int LMAX, int MMAX>
 struct Tab {
   static constexpr int L = (LMAX + 1) * (LMAX + 1);
   __host__ __device__ static constexpr int nrows(int l) { return (l < MMAX) ? 2 * l + 1 : 2 * MMAX + 1; }
   __host__ __device__ static constexpr int mm(int l) { return l < MMAX ? l : MMAX; }
+  __host__ __device__ static constexpr int rowlen(int l) { return (2 * l + 1 + 3) & ~3; }
   __host__ __device__ static constexpr int woff(int l) {
     int o = 0;
-    for (int k = 0; k < l; ++k) o += nrows(k) * (2 * k + 1);
+    for (int k = 0; k < l; ++k) o += nrows(k) * rowlen(k);
     return o;
   }
   static constexpr int WSZ = woff(LMAX + 1);
@@ -68,7 +70,12 @@ struct Tab {
     return moff(am) + (mp > 0 ? 0 : (LMAX + 1 - am)) + (l - am);
   }
   // index of row m' of degree l inside the Wigner store
-  __host__ __device__ static constexpr int wrow(int l, int mp) { return woff(l) + (mp + mm(l)) * (2 * l + 1); }
+  __host__ __device__ static constexpr int wrow(int l, int mp) { return woff(l) + (mp + mm(l)) * rowlen(l); }
+  // rotate-back work split: one warp per degree group; group 0 = degrees 0..3, group g >= 1 = degree 3 + g
+  // (FMA work per group for (6,2): 70 | 45 | 55 | 65)
+  static constexpr int NG = LMAX > 3 ? LMAX - 2 : 1;
+  __host__ __device__ static constexpr int glo(int g) { return g == 0 ? 0 : 3 + g; }
+  __host__ __device__ static constexpr int ghi(int g) { return g == 0 ? (LMAX < 3 ? LMAX : 3) : 3 + g; }
   // rotate-back rescale sqrt((2l+1)/(2 MMAX+1)) for l > MMAX (EF_layers.py:1530-1549)
   __host__ __device__ static float rescale(int l) {
     return l > MMAX ? sqrtf((float)(2 * l + 1) / (float)(2 * MMAX + 1)) : 1.0f;

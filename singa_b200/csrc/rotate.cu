@@ -161,134 +161,276 @@ __global__ void segment_sum_rows_kernel(const float* __restrict__ buf, int row_e
 }
 
 // ------------------------------------------------------------------------------------------
-// rotate-back + aggregate forward: one CTA per destination node, thread = value channel
+// rotate-back + aggregate: one CTA per destination node, one WARP per degree group (Tab::NG groups, independent,
+// no block-level synchronisation), lane = 4 adjacent value channels (CH / 4 = 28 active lanes).  Per edge a warp
+// streams its rows of V with 8-byte (bf16) / 16-byte (fp32) loads, stages its slice of the edge's Wigner rows
+// in shared memory with cp.async (double buffered, one 16-byte copy per lane) and reads it back as float4
+// broadcasts: 16 FMAs per shared-memory load.  Fixed edge order per destination => bit-deterministic.
 // ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)),
+               "l"(gsrc)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+__device__ __forceinline__ void load4(const float* p, float* v) {
+  const float4 t = *reinterpret_cast<const float4*>(p);
+  v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+__device__ __forceinline__ void load4(const __nv_bfloat16* p, float* v) {
+  const uint2 t = *reinterpret_cast<const uint2*>(p);
+  v[0] = __uint_as_float(t.x << 16); v[1] = __uint_as_float(t.x & 0xffff0000u);
+  v[2] = __uint_as_float(t.y << 16); v[3] = __uint_as_float(t.y & 0xffff0000u);
+}
+__device__ __forceinline__ void store4(float* p, float a, float b, float c, float d) {
+  *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+}
+__device__ __forceinline__ uint32_t bf2(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ void store4(__nv_bfloat16* p, float a, float b, float c, float d) {
+  *reinterpret_cast<uint2*>(p) = make_uint2(bf2(a, b), bf2(c, d));
+}
+__device__ __forceinline__ void store8(float* p, const float* o) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(o[0], o[1], o[2], o[3]);
+  reinterpret_cast<float4*>(p)[1] = make_float4(o[4], o[5], o[6], o[7]);
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float* o) {
+  *reinterpret_cast<uint4*>(p) = make_uint4(bf2(o[0], o[1]), bf2(o[2], o[3]), bf2(o[4], o[5]), bf2(o[6], o[7]));
+}
+
+template <int LMAX, int MMAX>
+struct BackCfg {
+  using T = Tab<LMAX, MMAX>;
+  // floats of Wigner rows a group stages per edge (multiple of 4)
+  __host__ __device__ static constexpr int wn(int g) { return T::woff(T::ghi(g) + 1) - T::woff(T::glo(g)); }
+  __host__ __device__ static constexpr int max_wn() {
+    int m = 0;
+    for (int g = 0; g < T::NG; ++g) m = wn(g) > m ? wn(g) : m;
+    return m;
+  }
+  static constexpr int MAXWN = max_wn();
+  static_assert(MAXWN / 4 <= 32, "one 16-byte cp.async per lane must cover a group's Wigner slice");
+};
+
+// Stage the Wigner slice [W0, W0 + WN) of edge `eo` into `dst` (one 16-byte copy per lane).
+template <int W0, int WN, int WSZ>
+__device__ __forceinline__ void stage_wigner(float* dst, const float* __restrict__ wig, int eo, int lane) {
+  if (lane < WN / 4) cp_async16(dst + 4 * lane, wig + (size_t)eo * WSZ + W0 + 4 * lane);
+}
+
+template <int LMAX, int MMAX, int CH, int VC, typename TIn, int L_LO, int L_HI>
+__device__ __forceinline__ void rotate_back_fwd_group(const OpBufs<LMAX>& V, const float* __restrict__ alpha,
+                                                      int heads, const int* __restrict__ perm,
+                                                      const float* __restrict__ wig, float* __restrict__ out, int n,
+                                                      int kb, int ke, int e0, float* sW /* [2][MAXWN] */, int lane) {
+  using T = Tab<LMAX, MMAX>;
+  constexpr int NC = (L_HI + 1) * (L_HI + 1) - L_LO * L_LO;
+  constexpr int W0 = T::woff(L_LO), WN = T::woff(L_HI + 1) - W0, MAXWN = BackCfg<LMAX, MMAX>::MAXWN;
+  const bool active = lane < CH / 4;
+  const int c4 = active ? 4 * lane : 0;
+  float acc[NC][4];
+#pragma unroll
+  for (int i = 0; i < NC; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  if (kb < ke) stage_wigner<W0, WN, T::WSZ>(sW, wig, perm[kb], lane);
+  cp_async_commit();
+  int buf = 0;
+  for (int k = kb; k < ke; ++k) {
+    if (k + 1 < ke) stage_wigner<W0, WN, T::WSZ>(sW + (buf ^ 1) * MAXWN, wig, perm[k + 1], lane);
+    cp_async_commit();
+    cp_async_wait<1>();
+    __syncwarp();
+    const float* w = sW + buf * MAXWN;
+    const int el = k - e0;
+    const float a = alpha ? __ldg(alpha + (size_t)k * heads + c4 / VC) : 1.f;
+#pragma unroll
+    for (int l = L_LO; l <= L_HI; ++l) {
+      const float sc = a * T::rescale(l);
+#pragma unroll
+      for (int mp = -T::mm(l); mp <= T::mm(l); ++mp) {
+        float v[4];
+        load4(op_ptr<LMAX, TIn>(V.p, el, l, mp, CH, c4), v);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] *= sc;
+        const float4* wr = reinterpret_cast<const float4*>(w + (T::wrow(l, mp) - W0));
+#pragma unroll
+        for (int q = 0; q < T::rowlen(l) / 4; ++q) {
+          const float4 t = wr[q];
+          const float tw[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            if (4 * q + u < 2 * l + 1) {
+              const int i = l * l - L_LO * L_LO + 4 * q + u;
+#pragma unroll
+              for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(tw[u], v[j], acc[i][j]);
+            }
+          }
+        }
+      }
+    }
+    __syncwarp();
+    buf ^= 1;
+  }
+  cp_async_wait<0>();
+  if (active) {
+    float* o = out + ((size_t)n * T::L + L_LO * L_LO) * CH + c4;
+#pragma unroll
+    for (int i = 0; i < NC; ++i) store4(o + (size_t)i * CH, acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+  }
+}
+
 template <int LMAX, int MMAX, int CH, int VC, typename TIn>
-__global__ void __launch_bounds__(128) rotate_back_agg_fwd_kernel(
+__global__ void __launch_bounds__(32 * Tab<LMAX, MMAX>::NG) rotate_back_agg_fwd_kernel(
     OpBufs<LMAX> V, const float* __restrict__ alpha /* [E, heads] sorted */, int heads,
     const int* __restrict__ rowptr, const int* __restrict__ perm, const float* __restrict__ wig,
     float* __restrict__ out /* [Nt, L, CH] */, int n0, int e0) {
   using T = Tab<LMAX, MMAX>;
-  __shared__ float sW[2][T::WSZ + 1];
+  constexpr int MAXWN = BackCfg<LMAX, MMAX>::MAXWN;
+  __shared__ __align__(16) float sW[T::NG][2][MAXWN];
+  const int g = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = n0 + blockIdx.x;
-  const int c = threadIdx.x;
-  const bool active = c < CH;
-  const int cc = active ? c : 0;
   const int kb = rowptr[n], ke = rowptr[n + 1];
-  float acc[T::L];
-#pragma unroll
-  for (int i = 0; i < T::L; ++i) acc[i] = 0.f;
-  int buf = 0;
-  if (kb < ke) {
-    const float* w = wig + (size_t)perm[kb] * T::WSZ;
-    for (int i = threadIdx.x; i < T::WSZ; i += blockDim.x) sW[0][i] = w[i];
+  float* s = &sW[g][0][0];
+#define GROUP(G)                                                                                                   \
+  case G:                                                                                                          \
+    if constexpr (G < T::NG)                                                                                       \
+      rotate_back_fwd_group<LMAX, MMAX, CH, VC, TIn, T::glo(G), T::ghi(G)>(V, alpha, heads, perm, wig, out, n, kb, \
+                                                                            ke, e0, s, lane);                      \
+    break;
+  switch (g) {
+    GROUP(0) GROUP(1) GROUP(2) GROUP(3) GROUP(4) GROUP(5)
+    default: break;
   }
-  __syncthreads();
-  for (int k = kb; k < ke; ++k) {
-    if (k + 1 < ke) {
-      const float* w = wig + (size_t)perm[k + 1] * T::WSZ;
-      for (int i = threadIdx.x; i < T::WSZ; i += blockDim.x) sW[buf ^ 1][i] = w[i];
-    }
-    const int el = k - e0;
-    const float a = alpha ? alpha[(size_t)k * heads + cc / VC] : 1.f;
-#pragma unroll
-    for (int l = 0; l <= LMAX; ++l) {
-      const float sc = a * T::rescale(l);
-#pragma unroll
-      for (int mp = -T::mm(l); mp <= T::mm(l); ++mp) {
-        const float v = sc * to_f<TIn>(*op_ptr<LMAX, TIn>(V.p, el, l, mp, CH, cc));
-        const float* wr = &sW[buf][T::wrow(l, mp)];
-#pragma unroll
-        for (int nn = 0; nn < 2 * l + 1; ++nn) acc[l * l + nn] = fmaf(wr[nn], v, acc[l * l + nn]);
-      }
-    }
-    __syncthreads();
-    buf ^= 1;
-  }
-  if (active) {
-    float* o = out + (size_t)n * T::L * CH + c;
-#pragma unroll
-    for (int i = 0; i < T::L; ++i) o[i * CH] = acc[i];
-  }
+#undef GROUP
 }
 
 // backward: d out[n] -> dV (written in the duplicated "dY" layout the SO(2) dgrad/wgrad GEMMs
 // consume: row 2e = [d re | d im], row 2e+1 = [d im | -d re], columns interleaved (re_q, im_q))
-// and d alpha[e, h] = sum_{j, c in h} dva[j, c] * V[e, j, c].
-template <int LMAX, int MMAX, int CH, int VC, typename TIn, typename TOut>
-__global__ void __launch_bounds__(128) rotate_back_agg_bwd_kernel(
-    OpBufs<LMAX> V, OpBufs<LMAX> dY, const float* __restrict__ alpha, int heads,
-    const int* __restrict__ rowptr, const int* __restrict__ perm, const float* __restrict__ wig,
-    const float* __restrict__ dout /* [Nt, L, CH] */, float* __restrict__ dalpha /* [E, heads] sorted */,
-    int n0, int e0) {
+// and per-group partials of d alpha[e, h] = sum_{j, c in h} dva[j, c] * V[e, j, c]  (dalpha [NG, Etot, heads];
+// the segment-softmax backward sums the NG partials in fixed order).
+template <int LMAX, int MMAX, int CH, int VC, typename TIn, typename TOut, int L_LO, int L_HI>
+__device__ __forceinline__ void rotate_back_bwd_group(const OpBufs<LMAX>& V, const OpBufs<LMAX>& dY,
+                                                      const float* __restrict__ alpha, int heads,
+                                                      const int* __restrict__ perm, const float* __restrict__ wig,
+                                                      const float* __restrict__ dout, float* __restrict__ dalpha_g,
+                                                      int n, int kb, int ke, int e0, float* sW, int lane) {
   using T = Tab<LMAX, MMAX>;
-  __shared__ float sW[2][T::WSZ + 1];
-  const int n = n0 + blockIdx.x;
-  const int c = threadIdx.x;
-  const bool active = c < CH;
-  const int cc = active ? c : 0;
-  const int kb = rowptr[n], ke = rowptr[n + 1];
-  float dy[T::L];
+  constexpr int NC = (L_HI + 1) * (L_HI + 1) - L_LO * L_LO;
+  constexpr int W0 = T::woff(L_LO), WN = T::woff(L_HI + 1) - W0, MAXWN = BackCfg<LMAX, MMAX>::MAXWN;
+  const bool active = lane < CH / 4;
+  const int c4 = active ? 4 * lane : 0;
+  float dy[NC][4];
   {
-    const float* d = dout + (size_t)n * T::L * CH + cc;
+    const float* d = dout + ((size_t)n * T::L + L_LO * L_LO) * CH + c4;
 #pragma unroll
-    for (int i = 0; i < T::L; ++i) dy[i] = d[i * CH];
+    for (int i = 0; i < NC; ++i) load4(d + (size_t)i * CH, dy[i]);
   }
+  if (kb < ke) stage_wigner<W0, WN, T::WSZ>(sW, wig, perm[kb], lane);
+  cp_async_commit();
   int buf = 0;
-  if (kb < ke) {
-    const float* w = wig + (size_t)perm[kb] * T::WSZ;
-    for (int i = threadIdx.x; i < T::WSZ; i += blockDim.x) sW[0][i] = w[i];
-  }
-  __syncthreads();
   for (int k = kb; k < ke; ++k) {
-    if (k + 1 < ke) {
-      const float* w = wig + (size_t)perm[k + 1] * T::WSZ;
-      for (int i = threadIdx.x; i < T::WSZ; i += blockDim.x) sW[buf ^ 1][i] = w[i];
-    }
+    if (k + 1 < ke) stage_wigner<W0, WN, T::WSZ>(sW + (buf ^ 1) * MAXWN, wig, perm[k + 1], lane);
+    cp_async_commit();
+    cp_async_wait<1>();
+    __syncwarp();
+    const float* w = sW + buf * MAXWN;
     const int el = k - e0;
-    const float a = alpha[(size_t)k * heads + cc / VC];
+    const float a = __ldg(alpha + (size_t)k * heads + c4 / VC);
     float da = 0.f;
 #pragma unroll
-    for (int l = 0; l <= LMAX; ++l) {
+    for (int l = L_LO; l <= L_HI; ++l) {
       const float rs = T::rescale(l);
-      float dre[2 * MMAX + 1];  // index mp + MMAX
+      float dre[2 * MMAX + 1][4];  // index mp + MMAX
 #pragma unroll
       for (int mp = -T::mm(l); mp <= T::mm(l); ++mp) {
-        const float* wr = &sW[buf][T::wrow(l, mp)];
-        float g = 0.f;
+        float g4[4] = {0.f, 0.f, 0.f, 0.f};
+        const float4* wr = reinterpret_cast<const float4*>(w + (T::wrow(l, mp) - W0));
 #pragma unroll
-        for (int nn = 0; nn < 2 * l + 1; ++nn) g = fmaf(wr[nn], dy[l * l + nn], g);
-        g *= rs;
-        const float v = to_f<TIn>(*op_ptr<LMAX, TIn>(V.p, el, l, mp, CH, cc));
-        da = fmaf(g, v, da);
-        dre[mp + MMAX] = g * a;
+        for (int q = 0; q < T::rowlen(l) / 4; ++q) {
+          const float4 t = wr[q];
+          const float tw[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            if (4 * q + u < 2 * l + 1) {
+              const int i = l * l - L_LO * L_LO + 4 * q + u;
+#pragma unroll
+              for (int j = 0; j < 4; ++j) g4[j] = fmaf(tw[u], dy[i][j], g4[j]);
+            }
+          }
+        }
+        float v[4];
+        load4(op_ptr<LMAX, TIn>(V.p, el, l, mp, CH, c4), v);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          g4[j] *= rs;
+          da = fmaf(g4[j], v[j], da);
+          dre[mp + MMAX][j] = g4[j] * a;
+        }
       }
       if (active) {
-        // m = 0 row: plain
-        reinterpret_cast<TOut*>(dY.p[0])[(size_t)el * (LMAX + 1) * CH + l * CH + c] = from_f<TOut>(dre[MMAX]);
+        store4(reinterpret_cast<TOut*>(dY.p[0]) + ((size_t)el * (LMAX + 1) + l) * CH + c4, dre[MMAX][0], dre[MMAX][1],
+               dre[MMAX][2], dre[MMAX][3]);
 #pragma unroll
         for (int am = 1; am <= T::mm(l); ++am) {
           const int half = (LMAX + 1 - am) * CH;
-          TOut* base = reinterpret_cast<TOut*>(dY.p[am]);
-          const float gr = dre[MMAX + am], gi = dre[MMAX - am];
-          const int q = (l - am) * CH + c;
-          TOut* r0 = base + ((size_t)el * 2) * (2 * half) + 2 * q;
-          TOut* r1 = r0 + 2 * half;
-          r0[0] = from_f<TOut>(gr);
-          r0[1] = from_f<TOut>(gi);
-          r1[0] = from_f<TOut>(gi);
-          r1[1] = from_f<TOut>(-gr);
+          TOut* r0 = reinterpret_cast<TOut*>(dY.p[am]) + ((size_t)el * 2) * (2 * half) + 2 * ((l - am) * CH + c4);
+          float o0[8], o1[8];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float gr = dre[MMAX + am][j], gi = dre[MMAX - am][j];
+            o0[2 * j] = gr; o0[2 * j + 1] = gi;
+            o1[2 * j] = gi; o1[2 * j + 1] = -gr;
+          }
+          store8(r0, o0);
+          store8(r0 + 2 * half, o1);
         }
       }
     }
-    // reduce d alpha over the VC channels of a head (VC-aligned groups inside a warp)
+    // d alpha partial of this degree group: sum over the VC channels of a head = VC/4 adjacent lanes
     if (!active) da = 0.f;
 #pragma unroll
-    for (int o = VC / 2; o > 0; o >>= 1) da += __shfl_xor_sync(0xffffffffu, da, o);
-    if (active && (c % VC) == 0) dalpha[(size_t)k * heads + c / VC] = da;
-    __syncthreads();
+    for (int o = VC / 8; o > 0; o >>= 1) da += __shfl_xor_sync(0xffffffffu, da, o);
+    if (active && (lane % (VC / 4)) == 0) dalpha_g[(size_t)k * heads + c4 / VC] = da;
+    __syncwarp();
     buf ^= 1;
   }
+  cp_async_wait<0>();
+}
+
+template <int LMAX, int MMAX, int CH, int VC, typename TIn, typename TOut>
+__global__ void __launch_bounds__(32 * Tab<LMAX, MMAX>::NG) rotate_back_agg_bwd_kernel(
+    OpBufs<LMAX> V, OpBufs<LMAX> dY, const float* __restrict__ alpha, int heads,
+    const int* __restrict__ rowptr, const int* __restrict__ perm, const float* __restrict__ wig,
+    const float* __restrict__ dout /* [Nt, L, CH] */, float* __restrict__ dalpha /* [NG, Etot, heads] sorted */,
+    long long part_stride, int n0, int e0) {
+  using T = Tab<LMAX, MMAX>;
+  constexpr int MAXWN = BackCfg<LMAX, MMAX>::MAXWN;
+  __shared__ __align__(16) float sW[T::NG][2][MAXWN];
+  const int g = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = n0 + blockIdx.x;
+  const int kb = rowptr[n], ke = rowptr[n + 1];
+  float* s = &sW[g][0][0];
+  float* dag = dalpha + (size_t)g * part_stride;
+#define GROUP(G)                                                                                                 \
+  case G:                                                                                                        \
+    if constexpr (G < T::NG)                                                                                     \
+      rotate_back_bwd_group<LMAX, MMAX, CH, VC, TIn, TOut, T::glo(G), T::ghi(G)>(V, dY, alpha, heads, perm, wig, \
+                                                                                  dout, dag, n, kb, ke, e0, s,   \
+                                                                                  lane);                         \
+    break;
+  switch (g) {
+    GROUP(0) GROUP(1) GROUP(2) GROUP(3) GROUP(4) GROUP(5)
+    default: break;
+  }
+#undef GROUP
 }
 
 // ------------------------------------------------------------------------------------------
@@ -418,6 +560,11 @@ extern "C" int efl_segment_sum_rows(const float* buf, int L, int ldc, int coff, 
   return EFL_OK;
 }
 
+extern "C" int efl_rotate_back_parts(int lmax, int mmax) {
+  (void)mmax;
+  return lmax > 3 ? lmax - 2 : 1;  // Tab::NG: degree groups = partial d-alpha planes of the backward
+}
+
 extern "C" int efl_rotate_back_aggregate_fwd(int lmax, int mmax, int heads, int value_ch, int bf16_in,
                                              const void* v0, const void* v1, const void* v2, const float* alpha,
                                              const int* rowptr, const int* perm, const float* wig, float* out,
@@ -425,10 +572,11 @@ extern "C" int efl_rotate_back_aggregate_fwd(int lmax, int mmax, int heads, int 
   if (n1 <= n0) return EFL_OK;
   EFL_REQUIRE(heads * value_ch == 112 && value_ch == 16, "efl_rotate_back_aggregate_fwd: needs heads*value == 112, value == 16");
   cudaStream_t s = (cudaStream_t)stream;
-  dim3 grid(n1 - n0), block(128);
+  dim3 grid(n1 - n0);
 #define CALL(LM, MM)                                                                                           \
   {                                                                                                            \
     OpBufs<LM> o{{(void*)v0, (void*)v1, (void*)v2}};                                                           \
+    dim3 block(32 * Tab<LM, MM>::NG);                                                                          \
     if (bf16_in)                                                                                               \
       rotate_back_agg_fwd_kernel<LM, MM, 112, 16, __nv_bfloat16><<<grid, block, 0, s>>>(o, alpha, heads,       \
                                                                                         rowptr, perm, wig,     \
@@ -446,22 +594,23 @@ extern "C" int efl_rotate_back_aggregate_fwd(int lmax, int mmax, int heads, int 
 extern "C" int efl_rotate_back_aggregate_bwd(int lmax, int mmax, int heads, int value_ch, int bf16,
                                              const void* v0, const void* v1, const void* v2, void* dy0, void* dy1,
                                              void* dy2, const float* alpha, const int* rowptr, const int* perm,
-                                             const float* wig, const float* dout, float* dalpha, int n0, int n1,
-                                             int e0, void* stream) {
+                                             const float* wig, const float* dout, float* dalpha,
+                                             long long part_stride, int n0, int n1, int e0, void* stream) {
   if (n1 <= n0) return EFL_OK;
   EFL_REQUIRE(heads * value_ch == 112 && value_ch == 16, "efl_rotate_back_aggregate_bwd: needs heads*value == 112, value == 16");
   cudaStream_t s = (cudaStream_t)stream;
-  dim3 grid(n1 - n0), block(128);
+  dim3 grid(n1 - n0);
 #define CALL(LM, MM)                                                                                           \
   {                                                                                                            \
     OpBufs<LM> vi{{(void*)v0, (void*)v1, (void*)v2}};                                                          \
     OpBufs<LM> dyo{{dy0, dy1, dy2}};                                                                           \
+    dim3 block(32 * Tab<LM, MM>::NG);                                                                          \
     if (bf16)                                                                                                  \
       rotate_back_agg_bwd_kernel<LM, MM, 112, 16, __nv_bfloat16, __nv_bfloat16><<<grid, block, 0, s>>>(        \
-          vi, dyo, alpha, heads, rowptr, perm, wig, dout, dalpha, n0, e0);                                     \
+          vi, dyo, alpha, heads, rowptr, perm, wig, dout, dalpha, part_stride, n0, e0);                        \
     else                                                                                                       \
       rotate_back_agg_bwd_kernel<LM, MM, 112, 16, float, float><<<grid, block, 0, s>>>(                        \
-          vi, dyo, alpha, heads, rowptr, perm, wig, dout, dalpha, n0, e0);                                     \
+          vi, dyo, alpha, heads, rowptr, perm, wig, dout, dalpha, part_stride, n0, e0);                        \
   }
   DISPATCH_LM(lmax, mmax, CALL)
 #undef CALL

@@ -4,7 +4,7 @@
 // (reference model/EF_layers.py:485-528, 2207-2229).  The reference materialises two
 // dense [E, L, L] tensors; only the rows with |m'| <= mmax of each diagonal block are
 // ever used (rotate: wigner[:, mask, :], rotate_inv: wigner_inv[:, :, mask]), so this
-// kernel emits exactly those rows: WSZ floats per edge (235 for lmax 6, mmax 2).
+// kernel emits exactly those rows (235 values for lmax 6, mmax 2), each padded to 16 bytes: WSZ = 296 floats/edge.
 //
 // D^l = Z(alpha) J_l Z(beta) J_l Z(gamma) with Z(a)[m,m] = cos(m a), Z(a)[m,-m] = -sin(m a).
 // One warp per edge; lane j owns kept row j.
@@ -105,7 +105,8 @@ __global__ void __launch_bounds__(128) wigner_kernel(const float* __restrict__ r
     int joff = 0;
     for (int k = 0; k < l; ++k) joff += (2 * k + 1) * (2 * k + 1);
     const float* J = sJ + joff;
-    float* o = out + T::woff(l) + (mp + T::mm(l)) * (2 * l + 1);
+    float* o = out + T::wrow(l, mp);
+    for (int k = 2 * l + 1; k < T::rowlen(l); ++k) o[k] = 0.f;  // row padding (16-byte rows)
     const float(*sA)[2] = sSC[warp][0];
     const float(*sB)[2] = sSC[warp][1];
     const float(*sG)[2] = sSC[warp][2];

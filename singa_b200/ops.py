@@ -10,6 +10,7 @@ re-runs the forward kernels chunk by chunk before the gradient kernels.
 from __future__ import annotations
 
 import ctypes
+import os
 from dataclasses import dataclass, field
 
 import numpy as np
@@ -22,6 +23,26 @@ from ._lib import LIB, call, check_cuda, ptr
 # "bf16" (tcgen05 tensor cores, fp32 accumulate).  Set through set_precision().
 _PRECISION = "fp32"
 MAX_CHUNK_EDGES = 262144
+# Saved-for-backward policy (SURVEY.md 8a note): keep the chunk's edge activations (A, extra, hidden, S2 output,
+# values: ~25 KB/edge in bf16) when they fit a fraction of the free HBM, otherwise recompute them in backward.
+# "auto" | "save" | "recompute"
+_SAVE_POLICY = os.environ.get("EFL_SAVE_POLICY", "auto")
+_SAVE_FREE_FRACTION = float(os.environ.get("EFL_SAVE_FREE_FRACTION", "0.45"))
+
+
+def set_save_policy(mode: str) -> None:
+    global _SAVE_POLICY
+    if mode not in ("auto", "save", "recompute"):
+        raise ValueError("save policy must be 'auto', 'save' or 'recompute'")
+    _SAVE_POLICY = mode
+
+
+def _should_save(nbytes: int, device) -> bool:
+    if _SAVE_POLICY != "auto":
+        return _SAVE_POLICY == "save"
+    free, _ = torch.cuda.mem_get_info(device)
+    cached = torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device)
+    return nbytes < _SAVE_FREE_FRACTION * (free + cached)
 
 
 def set_precision(mode: str) -> None:
@@ -51,7 +72,9 @@ def jd_device(lmax: int, device) -> torch.Tensor:
 
 
 def wigner_size(lmax: int, mmax: int) -> int:
-    return sum(min(2 * l + 1, 2 * mmax + 1) * (2 * l + 1) for l in range(lmax + 1))
+    """Floats per edge of the Wigner store: kept rows |m'| <= mmax of each D^l, rows padded to 4 floats
+    (csrc/efl_common.cuh Tab::WSZ)."""
+    return sum(min(2 * l + 1, 2 * mmax + 1) * ((2 * l + 1 + 3) // 4 * 4) for l in range(lmax + 1))
 
 
 def wigner_from_rotmat(rot: torch.Tensor, lmax: int, mmax: int) -> torch.Tensor:
@@ -209,23 +232,30 @@ class AttnDims:
 
 
 class _Workspace:
-    """Chunk-sized edge buffers.  Operand layout per order m: dense [rows_m*Ec, ms[m]*CH]."""
+    """Chunk-sized edge buffers.  Operand layout per order m: dense [rows_m*Ec, ms[m]*CH].
+    ``forward`` buffers: A (rotate-in output), extra (alpha/gate columns), Hb (so2_conv_1 hidden), B (S2 output),
+    V (so2_conv_2 values); ``backward`` buffers: the matching gradients."""
 
-    def __init__(self, d: AttnDims, Ec: int, dtype, device, backward: bool):
+    def __init__(self, d: AttnDims, Ec: int, dtype, device, forward: bool = True, backward: bool = False):
         C2, H, VH = 2 * d.C, d.H, d.heads * d.value_ch
         self.extra_w = d.heads * d.alpha_ch + H
         e = lambda r, c, dt=dtype: torch.empty(max(r, 1), c, dtype=dt, device=device)
         rows = [Ec] + [2 * Ec] * d.mmax
-        self.A = [e(rows[m], d.ms[m] * C2) for m in range(d.mmax + 1)]
-        self.extra = e(Ec, self.extra_w, torch.float32)
-        self.Hb = [e(rows[m], d.ms[m] * H) for m in range(d.mmax + 1)]
-        self.B = [e(rows[m], d.ms[m] * H) for m in range(d.mmax + 1)]
-        self.V = [e(rows[m], d.ms[m] * VH) for m in range(d.mmax + 1)]
+        if forward:
+            self.A = [e(rows[m], d.ms[m] * C2) for m in range(d.mmax + 1)]
+            self.extra = e(Ec, self.extra_w, torch.float32)
+            self.Hb = [e(rows[m], d.ms[m] * H) for m in range(d.mmax + 1)]
+            self.B = [e(rows[m], d.ms[m] * H) for m in range(d.mmax + 1)]
+            self.V = [e(rows[m], d.ms[m] * VH) for m in range(d.mmax + 1)]
         if backward:
             self.dY2 = [e(Ec, d.ms[0] * VH)] + [e(2 * Ec, 2 * d.ms[m] * VH) for m in range(1, d.mmax + 1)]
             self.dB = [e(rows[m], d.ms[m] * H) for m in range(d.mmax + 1)]
             self.dY1 = [e(Ec, self.extra_w + d.ms[0] * H)] + [e(2 * Ec, 2 * d.ms[m] * H) for m in range(1, d.mmax + 1)]
             self.dA = [e(rows[m], d.ms[m] * C2) for m in range(d.mmax + 1)]
+
+    @staticmethod
+    def forward_bytes_per_edge(d: AttnDims, es: int) -> int:
+        return d.M * (2 * d.C + 2 * d.H + d.heads * d.value_ch) * es + (d.heads * d.alpha_ch + d.H) * 4
 
 
 def _rowmap_plain(bufs, d: AttnDims, CH, esz_offset=0, col_offset0=0, ld0=None):
@@ -323,6 +353,14 @@ def _bytes_rotate_back(d: AttnDims, es: int, wsz: int) -> float:
     return d.M * d.heads * d.value_ch * es + d.heads * 4 + wsz * 4 + 4
 
 
+def _bytes_rotate_back_bwd(d: AttnDims, es: int, wsz: int) -> float:
+    """Backward: value rows and Wigner rows read, d value written in the dup layout (m=0 rows once, m>0 rows
+    as two interleaved rows of double width), d alpha partials."""
+    VH = d.heads * d.value_ch
+    dup = (d.ms[0] + 4 * sum(d.ms[1:])) * VH * es
+    return d.M * VH * es + wsz * 4 + dup + d.heads * 4 * 5 + 4
+
+
 class EdgeAttentionFunction(torch.autograd.Function):
     """x_src, x_dst, rad, conv1 (W0,b0,W1,W2), alpha LN (w,b), alpha_dot, conv2 (W0,b0,W1,W2)
     -> aggregated messages [num_dst, L, heads*value] (input of ``proj``)."""
@@ -344,15 +382,23 @@ class EdgeAttentionFunction(torch.autograd.Function):
         logits = torch.empty(max(E, 1), d.heads, dtype=torch.float32, device=dev)
         alpha = torch.empty(max(E, 1), d.heads, dtype=torch.float32, device=dev)
         maxE = max((c[3] - c[2] for c in csr.chunks), default=0)
-        ws = _Workspace(d, maxE, dtype, dev, backward=False)
+        es = 4 if dtype == torch.float32 else 2
+        save = (any(ctx.needs_input_grad) and E > 0
+                and _should_save(E * _Workspace.forward_bytes_per_edge(d, es), dev))
+        ws = None if save else _Workspace(d, maxE, dtype, dev)
         w1 = _Weights([c1w0, c1b0, c1w1, c1w2], dtype, need_t=False)
         w2 = _Weights([c2w0, c2b0, c2w1, c2w2], dtype, need_t=False)
         lw, lb, ad = ln_w.detach().contiguous(), ln_b.detach().contiguous(), adot.detach().contiguous()
+        saved = []
         for chunk in csr.chunks:
+            if save:
+                ws = _Workspace(d, chunk[3] - chunk[2], dtype, dev)
+                saved.append(ws)
             _chunk_forward(d, ws, w1, w2, x_src, x_dst, rad, csr, wig, lw, lb, ad, logits, alpha, grids, chunk, out)
         ctx.save_for_backward(x_src, x_dst, rad, c1w0, c1b0, c1w1, c1w2, ln_w, ln_b, adot, c2w0, c2b0, c2w1, c2w2,
                               logits, alpha)
         ctx.misc = (csr, wig, grids, d, dtype)
+        ctx.saved_ws = saved if save else None
         return out
 
     @staticmethod
@@ -367,7 +413,9 @@ class EdgeAttentionFunction(torch.autograd.Function):
         C2, H, VH = 2 * d.C, d.H, d.heads * d.value_ch
         bf16 = int(dtype == torch.bfloat16)
         maxE = max((c[3] - c[2] for c in csr.chunks), default=0)
-        ws = _Workspace(d, maxE, dtype, dev, backward=True)
+        saved_ws = ctx.saved_ws
+        ctx.saved_ws = None
+        wsr = _Workspace(d, maxE, dtype, dev, forward=saved_ws is None, backward=True)
         w1 = _Weights([c1w0, c1b0, c1w1, c1w2], dtype, need_t=True)
         w2 = _Weights([c2w0, c2b0, c2w1, c2w2], dtype, need_t=True)
         lw, lb, ad = ln_w.detach().contiguous(), ln_b.detach().contiguous(), adot.detach().contiguous()
@@ -378,24 +426,33 @@ class EdgeAttentionFunction(torch.autograd.Function):
         g_c2wm = [f32(*c2w1.shape), f32(*c2w2.shape)]
         drad = torch.zeros_like(rad)
         dxe = torch.empty(max(E, 1), L, C2, dtype=torch.float32, device=dev)
-        dalpha = torch.empty(max(E, 1), d.heads, dtype=torch.float32, device=dev)
+        nparts = LIB.efl_rotate_back_parts(d.lmax, d.mmax)
+        dalpha = torch.empty(nparts, max(E, 1), d.heads, dtype=torch.float32, device=dev)
         dlogits = torch.empty(max(E, 1), d.heads, dtype=torch.float32, device=dev)
-        nblk = 148
+        nblk = 148 * 4
         stride = d.heads * d.alpha_ch + 2 * d.alpha_ch
         part_all = f32(stride)
         part = torch.empty(nblk, stride, dtype=torch.float32, device=dev)
         to_g, from_g, G = grids
         first = True
-        for chunk in csr.chunks:
+        for ci, chunk in enumerate(csr.chunks):
             n0, n1, e0, e1 = chunk
             Ec = e1 - e0
             if Ec == 0:
                 continue
-            _chunk_forward(d, ws, w1, w2, x_src, x_dst, rad, csr, wig, lw, lb, ad, logits, alpha, grids, chunk, None)
+            if saved_ws is None:
+                ws = wsr
+                _chunk_forward(d, ws, w1, w2, x_src, x_dst, rad, csr, wig, lw, lb, ad, logits, alpha, grids, chunk,
+                               None)
+            else:
+                ws = saved_ws[ci]
+                saved_ws[ci] = None     # release the chunk's activations as soon as its gradients are done
+                ws.dY2, ws.dB, ws.dY1, ws.dA = wsr.dY2, wsr.dB, wsr.dY1, wsr.dA
             # ---- rotate-back + aggregate backward -> dV (dup layout), d alpha
             call("efl_rotate_back_aggregate_bwd", d.lmax, d.mmax, d.heads, d.value_ch, bf16, ptr(ws.V[0]),
                  ptr(ws.V[1]), ptr(ws.V[2]), ptr(ws.dY2[0]), ptr(ws.dY2[1]), ptr(ws.dY2[2]), ptr(alpha),
-                 ptr(csr.rowptr), ptr(csr.perm), ptr(wig), ptr(dout), ptr(dalpha), n0, n1, e0)
+                 ptr(csr.rowptr), ptr(csr.perm), ptr(wig), ptr(dout), ptr(dalpha), dalpha.stride(0), n0, n1, e0,
+                 work=Ec * _bytes_rotate_back_bwd(d, ws.V[0].element_size(), wig.shape[1]))
             # ---- so2_conv_2 backward
             acc = not first
             _gemm_tn(ws.dY2[0], ws.B[0], g_c2w0, acc, Ec, d.ms[0] * VH, d.ms[0] * H)
@@ -422,7 +479,8 @@ class EdgeAttentionFunction(torch.autograd.Function):
                 call("efl_s2act_bwd", d.M, G, H, bf16, bf16, *rin.args(), *rdin.args(), *rdout.args(), 1, gate_ptr,
                      ws.extra_w, dgate_ptr, ld1, ptr(to_g), ptr(from_g), Ec)
             # ---- softmax + alpha-logit backward -> first heads*alpha columns of dY1[0]
-            call("efl_segment_softmax_bwd", ptr(alpha), ptr(dalpha), d.heads, ptr(csr.rowptr), ptr(dlogits), n0, n1)
+            call("efl_segment_softmax_bwd", ptr(alpha), ptr(dalpha), nparts, dalpha.stride(0), d.heads, ptr(csr.rowptr),
+                 ptr(dlogits), n0, n1)
             call("efl_alpha_logits_bwd", ptr(ws.extra), ws.extra_w, d.heads, d.alpha_ch, ptr(lw), ptr(lb), ptr(ad),
                  dlogits.data_ptr() + e0 * d.heads * 4, ptr(ws.dY1[0]), ld1, bf16, ptr(part), nblk, Ec)
             part_all += part.sum(dim=0)

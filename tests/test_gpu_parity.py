@@ -30,9 +30,12 @@ def test_wigner_kernel_matches_reference_rows(lmax, key):
     for l in range(lmax + 1):
         nr = min(2 * l + 1, 5)
         blk = rows[:, r:r + nr, l * l:(l + 1) ** 2].reshape(rows.shape[0], -1)
-        got = wig[:, off:off + nr * (2 * l + 1)]
+        rl = (2 * l + 1 + 3) // 4 * 4   # rows are padded to 16 bytes in the Wigner store
+        got = wig[:, off:off + nr * rl].reshape(-1, nr, rl)
+        assert float(got[:, :, 2 * l + 1:].abs().max() if rl > 2 * l + 1 else 0.0) == 0.0
+        got = got[:, :, :2 * l + 1].reshape(rows.shape[0], -1)
         assert float((got - blk).abs().max()) < 5e-6, (l, float((got - blk).abs().max()))
-        off += nr * (2 * l + 1)
+        off += nr * rl
         r += nr
     assert off == wig.shape[1]
 
@@ -172,3 +175,26 @@ def test_example_complex_bf16_mode():
         out = _run_example(model, fx, DEV)
     for k, ref in fx["outputs"].items():
         assert rel_err(out[k].embedding, ref) < 3e-2, (k, rel_err(out[k].embedding, ref))
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_saved_activations_and_recompute_give_identical_gradients(precision):
+    """The saved-for-backward policy (ops.set_save_policy) only chooses between keeping a chunk's edge activations
+    and re-running the same forward kernels in backward: gradients must be bit-identical."""
+    from singa_b200 import ops
+    fx = load_golden("example_3wi2.pt")
+    grads = {}
+    old = ops._SAVE_POLICY
+    try:
+        for policy in ("save", "recompute"):
+            ops.set_save_policy(policy)
+            model = build_model(DEV, 0, precision)
+            out = _run_example(model, fx, DEV)
+            (out[PROTEIN].embedding.sum() + 2.0 * out[LIGAND].embedding.sum()).backward()
+            grads[policy] = {n: p.grad.clone() for n, p in model.named_parameters() if p.grad is not None}
+    finally:
+        ops.set_save_policy(old)
+        ops.set_precision("fp32")
+    assert grads["save"].keys() == grads["recompute"].keys()
+    for n in grads["save"]:
+        assert torch.equal(grads["save"][n], grads["recompute"][n]), n
