@@ -162,20 +162,38 @@ __global__ void segment_sum_rows_kernel(const float* __restrict__ buf, int row_e
 
 // ------------------------------------------------------------------------------------------
 // rotate-back + aggregate: one CTA per destination node, one WARP per degree group (Tab::NG groups, independent,
-// no block-level synchronisation), lane = 4 adjacent value channels (CH / 4 = 28 active lanes).  Per edge a warp
-// streams its rows of V with 8-byte (bf16) / 16-byte (fp32) loads, stages its slice of the edge's Wigner rows
-// in shared memory with cp.async (double buffered, one 16-byte copy per lane) and reads it back as float4
-// broadcasts: 16 FMAs per shared-memory load.  Fixed edge order per destination => bit-deterministic.
+// no block-level synchronisation), lane = 4 adjacent value channels (CH / 4 = 28 active lanes).
+// Per edge a warp needs its rows of V (5 contiguous segments: m=0, +1, -1, +2, -2) and its slice of the edge's
+// Wigner rows.  One elected lane streams them into a per-warp NST-stage shared-memory ring with 1-D bulk async
+// copies (cp.async.bulk, completion on an mbarrier: the TMA engine, UBLKCP in SASS), NST edges ahead of the
+// math, so HBM latency is hidden without register staging.  The math reads V as 8/16-byte vectors and the
+// Wigner rows as float4 broadcasts: 16 FMAs per shared-memory load.  Fixed edge order per destination =>
+// bit-deterministic; no atomics.
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)),
-               "l"(gsrc)
-               : "memory");
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init_(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count));
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+__device__ __forceinline__ void mbar_expect_tx_(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "RB_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra RB_DONE;\n\t"
+      "bra RB_WAIT;\n\t"
+      "RB_DONE:\n\t"
+      "}" ::"r"(smem_addr(bar)), "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_addr(smem_dst)),
+               "l"(gsrc), "r"(bytes), "r"(smem_addr(bar))
+               : "memory");
 }
 
 __device__ __forceinline__ void load4(const float* p, float* v) {
@@ -205,34 +223,85 @@ __device__ __forceinline__ void store8(__nv_bfloat16* p, const float* o) {
   *reinterpret_cast<uint4*>(p) = make_uint4(bf2(o[0], o[1]), bf2(o[2], o[3]), bf2(o[4], o[5]), bf2(o[6], o[7]));
 }
 
-template <int LMAX, int MMAX>
-struct BackCfg {
+constexpr int RB_NST = 4;  // ring stages (edges in flight per warp)
+
+// Shared-memory stage of one degree group [L_LO, L_HI]: V segments (m=0, +1, -1, +2, -2; degrees ascending inside
+// a segment) followed by the group's Wigner slice.
+template <int LMAX, int MMAX, int CH, typename TIn, int L_LO, int L_HI>
+struct GroupCfg {
   using T = Tab<LMAX, MMAX>;
-  // floats of Wigner rows a group stages per edge (multiple of 4)
-  __host__ __device__ static constexpr int wn(int g) { return T::woff(T::ghi(g) + 1) - T::woff(T::glo(g)); }
-  __host__ __device__ static constexpr int max_wn() {
-    int m = 0;
-    for (int g = 0; g < T::NG; ++g) m = wn(g) > m ? wn(g) : m;
-    return m;
+  static constexpr int ROWB = CH * (int)sizeof(TIn);
+  __host__ __device__ static constexpr int la(int am) { return L_LO > am ? L_LO : am; }
+  __host__ __device__ static constexpr int nl(int am) { return L_HI >= la(am) ? L_HI - la(am) + 1 : 0; }
+  __host__ __device__ static constexpr int seg_off(int am, int neg) {
+    int o = 0;
+    if (am > 0) o += nl(0) * ROWB;
+    for (int k = 1; k < am; ++k) o += 2 * nl(k) * ROWB;
+    if (am > 0 && neg) o += nl(am) * ROWB;
+    return o;
   }
-  static constexpr int MAXWN = max_wn();
-  static_assert(MAXWN / 4 <= 32, "one 16-byte cp.async per lane must cover a group's Wigner slice");
+  static constexpr int VBYTES = seg_off(MMAX + 1, 0);
+  static constexpr int W0 = T::woff(L_LO);
+  static constexpr int WBYTES = (T::woff(L_HI + 1) - W0) * 4;
+  static constexpr int STAGE = VBYTES + WBYTES;
+  __host__ __device__ static constexpr int row_off(int l, int mp) {
+    return seg_off(mp < 0 ? -mp : mp, mp < 0) + (l - la(mp < 0 ? -mp : mp)) * ROWB;
+  }
+  static_assert(ROWB % 16 == 0 && WBYTES % 16 == 0, "bulk copies need 16-byte granularity");
+
+  // lane 0: fill one stage with edge (sorted position k, local index el, original id eo)
+  __device__ static __forceinline__ void issue(uint8_t* stage, uint64_t* bar, const OpBufs<LMAX>& V,
+                                               const float* __restrict__ wig, int el, int eo) {
+    mbar_expect_tx_(bar, STAGE);
+#pragma unroll
+    for (int am = 0; am <= MMAX; ++am) {
+      if (nl(am) > 0) {
+        const TIn* base = reinterpret_cast<const TIn*>(V.p[am]);
+        if (am == 0) {
+          bulk_g2s(stage + seg_off(0, 0), base + ((size_t)el * (LMAX + 1) + la(0)) * CH, nl(0) * ROWB, bar);
+        } else {
+#pragma unroll
+          for (int neg = 0; neg < 2; ++neg)
+            bulk_g2s(stage + seg_off(am, neg),
+                     base + (((size_t)el * 2 + neg) * (LMAX + 1 - am) + (la(am) - am)) * CH, nl(am) * ROWB, bar);
+        }
+      }
+    }
+    bulk_g2s(stage + VBYTES, wig + (size_t)eo * T::WSZ + W0, WBYTES, bar);
+  }
 };
 
-// Stage the Wigner slice [W0, W0 + WN) of edge `eo` into `dst` (one 16-byte copy per lane).
-template <int W0, int WN, int WSZ>
-__device__ __forceinline__ void stage_wigner(float* dst, const float* __restrict__ wig, int eo, int lane) {
-  if (lane < WN / 4) cp_async16(dst + 4 * lane, wig + (size_t)eo * WSZ + W0 + 4 * lane);
-}
+template <int LMAX, int MMAX, int CH, typename TIn>
+struct BackCfg {
+  using T = Tab<LMAX, MMAX>;
+  template <int G>
+  __host__ __device__ static constexpr int stage_bytes() {
+    if constexpr (G < T::NG) return GroupCfg<LMAX, MMAX, CH, TIn, T::glo(G), T::ghi(G)>::STAGE;
+    else return 0;
+  }
+  __host__ __device__ static constexpr int stage_of(int g) {
+    return g == 0 ? stage_bytes<0>() : g == 1 ? stage_bytes<1>() : g == 2 ? stage_bytes<2>()
+         : g == 3 ? stage_bytes<3>() : g == 4 ? stage_bytes<4>() : g == 5 ? stage_bytes<5>() : 0;
+  }
+  static constexpr int BAR_BYTES = 256;  // NG * RB_NST mbarriers (<= 6 * 4 * 8 bytes), keeps the rings 128-byte aligned
+  __host__ __device__ static constexpr int ring_off(int g) {
+    int o = BAR_BYTES;
+    for (int k = 0; k < g; ++k) o += RB_NST * stage_of(k);
+    return o;
+  }
+  static constexpr int SMEM = ring_off(T::NG);
+  static_assert(T::NG <= 6, "at most 6 degree groups");
+};
 
 template <int LMAX, int MMAX, int CH, int VC, typename TIn, int L_LO, int L_HI>
 __device__ __forceinline__ void rotate_back_fwd_group(const OpBufs<LMAX>& V, const float* __restrict__ alpha,
                                                       int heads, const int* __restrict__ perm,
                                                       const float* __restrict__ wig, float* __restrict__ out, int n,
-                                                      int kb, int ke, int e0, float* sW /* [2][MAXWN] */, int lane) {
+                                                      int kb, int ke, int e0, uint8_t* ring, uint64_t* bars,
+                                                      int lane) {
   using T = Tab<LMAX, MMAX>;
+  using G = GroupCfg<LMAX, MMAX, CH, TIn, L_LO, L_HI>;
   constexpr int NC = (L_HI + 1) * (L_HI + 1) - L_LO * L_LO;
-  constexpr int W0 = T::woff(L_LO), WN = T::woff(L_HI + 1) - W0, MAXWN = BackCfg<LMAX, MMAX>::MAXWN;
   const bool active = lane < CH / 4;
   const int c4 = active ? 4 * lane : 0;
   float acc[NC][4];
@@ -240,27 +309,40 @@ __device__ __forceinline__ void rotate_back_fwd_group(const OpBufs<LMAX>& V, con
   for (int i = 0; i < NC; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-  if (kb < ke) stage_wigner<W0, WN, T::WSZ>(sW, wig, perm[kb], lane);
-  cp_async_commit();
-  int buf = 0;
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < RB_NST; ++s) mbar_init_(&bars[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+  // original edge ids of the next 32 edges to issue, one per lane
+  int pbase = kb;
+  int pv = (pbase + lane < ke) ? __ldg(perm + pbase + lane) : 0;
+#pragma unroll
+  for (int s = 0; s < RB_NST; ++s) {
+    const int j = kb + s;
+    const int eo = __shfl_sync(0xffffffffu, pv, s);
+    if (lane == 0 && j < ke) G::issue(ring + s * G::STAGE, &bars[s], V, wig, j - e0, eo);
+  }
+  float a_next = (alpha && kb < ke) ? __ldg(alpha + (size_t)kb * heads + c4 / VC) : 1.f;
+  int s = 0;
+  uint32_t phase = 0;
   for (int k = kb; k < ke; ++k) {
-    if (k + 1 < ke) stage_wigner<W0, WN, T::WSZ>(sW + (buf ^ 1) * MAXWN, wig, perm[k + 1], lane);
-    cp_async_commit();
-    cp_async_wait<1>();
-    __syncwarp();
-    const float* w = sW + buf * MAXWN;
-    const int el = k - e0;
-    const float a = alpha ? __ldg(alpha + (size_t)k * heads + c4 / VC) : 1.f;
+    const float a = a_next;
+    if (alpha && k + 1 < ke) a_next = __ldg(alpha + (size_t)(k + 1) * heads + c4 / VC);
+    mbar_wait_(&bars[s], phase);
+    const uint8_t* st = ring + s * G::STAGE;
+    const float* w = reinterpret_cast<const float*>(st + G::VBYTES);
 #pragma unroll
     for (int l = L_LO; l <= L_HI; ++l) {
       const float sc = a * T::rescale(l);
 #pragma unroll
       for (int mp = -T::mm(l); mp <= T::mm(l); ++mp) {
         float v[4];
-        load4(op_ptr<LMAX, TIn>(V.p, el, l, mp, CH, c4), v);
+        load4(reinterpret_cast<const TIn*>(st + G::row_off(l, mp)) + c4, v);
 #pragma unroll
         for (int j = 0; j < 4; ++j) v[j] *= sc;
-        const float4* wr = reinterpret_cast<const float4*>(w + (T::wrow(l, mp) - W0));
+        const float4* wr = reinterpret_cast<const float4*>(w + (T::wrow(l, mp) - G::W0));
 #pragma unroll
         for (int q = 0; q < T::rowlen(l) / 4; ++q) {
           const float4 t = wr[q];
@@ -276,10 +358,18 @@ __device__ __forceinline__ void rotate_back_fwd_group(const OpBufs<LMAX>& V, con
         }
       }
     }
-    __syncwarp();
-    buf ^= 1;
+    __syncwarp();  // every lane is done with stage s before it is refilled
+    const int jn = k + RB_NST;
+    if (jn < ke) {
+      if (jn - pbase >= 32) {
+        pbase += 32;
+        pv = (pbase + lane < ke) ? __ldg(perm + pbase + lane) : 0;
+      }
+      const int eo = __shfl_sync(0xffffffffu, pv, jn - pbase);
+      if (lane == 0) G::issue(ring + s * G::STAGE, &bars[s], V, wig, jn - e0, eo);
+    }
+    if (++s == RB_NST) { s = 0; phase ^= 1; }
   }
-  cp_async_wait<0>();
   if (active) {
     float* o = out + ((size_t)n * T::L + L_LO * L_LO) * CH + c4;
 #pragma unroll
@@ -293,17 +383,18 @@ __global__ void __launch_bounds__(32 * Tab<LMAX, MMAX>::NG) rotate_back_agg_fwd_
     const int* __restrict__ rowptr, const int* __restrict__ perm, const float* __restrict__ wig,
     float* __restrict__ out /* [Nt, L, CH] */, int n0, int e0) {
   using T = Tab<LMAX, MMAX>;
-  constexpr int MAXWN = BackCfg<LMAX, MMAX>::MAXWN;
-  __shared__ __align__(16) float sW[T::NG][2][MAXWN];
+  using B = BackCfg<LMAX, MMAX, CH, TIn>;
+  extern __shared__ __align__(128) uint8_t rb_smem[];
   const int g = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = n0 + blockIdx.x;
   const int kb = rowptr[n], ke = rowptr[n + 1];
-  float* s = &sW[g][0][0];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(rb_smem) + g * RB_NST;
 #define GROUP(G)                                                                                                   \
   case G:                                                                                                          \
     if constexpr (G < T::NG)                                                                                       \
       rotate_back_fwd_group<LMAX, MMAX, CH, VC, TIn, T::glo(G), T::ghi(G)>(V, alpha, heads, perm, wig, out, n, kb, \
-                                                                            ke, e0, s, lane);                      \
+                                                                            ke, e0, rb_smem + B::ring_off(G), bars, \
+                                                                            lane);                                 \
     break;
   switch (g) {
     GROUP(0) GROUP(1) GROUP(2) GROUP(3) GROUP(4) GROUP(5)
@@ -315,35 +406,49 @@ __global__ void __launch_bounds__(32 * Tab<LMAX, MMAX>::NG) rotate_back_agg_fwd_
 // backward: d out[n] -> dV (written in the duplicated "dY" layout the SO(2) dgrad/wgrad GEMMs
 // consume: row 2e = [d re | d im], row 2e+1 = [d im | -d re], columns interleaved (re_q, im_q))
 // and per-group partials of d alpha[e, h] = sum_{j, c in h} dva[j, c] * V[e, j, c]  (dalpha [NG, Etot, heads];
-// the segment-softmax backward sums the NG partials in fixed order).
+// the segment-softmax backward sums the NG partials in fixed order).  Same ring as the forward.
 template <int LMAX, int MMAX, int CH, int VC, typename TIn, typename TOut, int L_LO, int L_HI>
 __device__ __forceinline__ void rotate_back_bwd_group(const OpBufs<LMAX>& V, const OpBufs<LMAX>& dY,
                                                       const float* __restrict__ alpha, int heads,
                                                       const int* __restrict__ perm, const float* __restrict__ wig,
                                                       const float* __restrict__ dout, float* __restrict__ dalpha_g,
-                                                      int n, int kb, int ke, int e0, float* sW, int lane) {
+                                                      int n, int kb, int ke, int e0, uint8_t* ring, uint64_t* bars,
+                                                      int lane) {
   using T = Tab<LMAX, MMAX>;
+  using G = GroupCfg<LMAX, MMAX, CH, TIn, L_LO, L_HI>;
   constexpr int NC = (L_HI + 1) * (L_HI + 1) - L_LO * L_LO;
-  constexpr int W0 = T::woff(L_LO), WN = T::woff(L_HI + 1) - W0, MAXWN = BackCfg<LMAX, MMAX>::MAXWN;
   const bool active = lane < CH / 4;
   const int c4 = active ? 4 * lane : 0;
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < RB_NST; ++s) mbar_init_(&bars[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+  int pbase = kb;
+  int pv = (pbase + lane < ke) ? __ldg(perm + pbase + lane) : 0;
+#pragma unroll
+  for (int s = 0; s < RB_NST; ++s) {
+    const int j = kb + s;
+    const int eo = __shfl_sync(0xffffffffu, pv, s);
+    if (lane == 0 && j < ke) G::issue(ring + s * G::STAGE, &bars[s], V, wig, j - e0, eo);
+  }
   float dy[NC][4];
   {
     const float* d = dout + ((size_t)n * T::L + L_LO * L_LO) * CH + c4;
 #pragma unroll
     for (int i = 0; i < NC; ++i) load4(d + (size_t)i * CH, dy[i]);
   }
-  if (kb < ke) stage_wigner<W0, WN, T::WSZ>(sW, wig, perm[kb], lane);
-  cp_async_commit();
-  int buf = 0;
+  float a_next = kb < ke ? __ldg(alpha + (size_t)kb * heads + c4 / VC) : 1.f;
+  int s = 0;
+  uint32_t phase = 0;
   for (int k = kb; k < ke; ++k) {
-    if (k + 1 < ke) stage_wigner<W0, WN, T::WSZ>(sW + (buf ^ 1) * MAXWN, wig, perm[k + 1], lane);
-    cp_async_commit();
-    cp_async_wait<1>();
-    __syncwarp();
-    const float* w = sW + buf * MAXWN;
+    const float a = a_next;
+    if (k + 1 < ke) a_next = __ldg(alpha + (size_t)(k + 1) * heads + c4 / VC);
+    mbar_wait_(&bars[s], phase);
+    const uint8_t* st = ring + s * G::STAGE;
+    const float* w = reinterpret_cast<const float*>(st + G::VBYTES);
     const int el = k - e0;
-    const float a = __ldg(alpha + (size_t)k * heads + c4 / VC);
     float da = 0.f;
 #pragma unroll
     for (int l = L_LO; l <= L_HI; ++l) {
@@ -352,7 +457,7 @@ __device__ __forceinline__ void rotate_back_bwd_group(const OpBufs<LMAX>& V, con
 #pragma unroll
       for (int mp = -T::mm(l); mp <= T::mm(l); ++mp) {
         float g4[4] = {0.f, 0.f, 0.f, 0.f};
-        const float4* wr = reinterpret_cast<const float4*>(w + (T::wrow(l, mp) - W0));
+        const float4* wr = reinterpret_cast<const float4*>(w + (T::wrow(l, mp) - G::W0));
 #pragma unroll
         for (int q = 0; q < T::rowlen(l) / 4; ++q) {
           const float4 t = wr[q];
@@ -367,7 +472,7 @@ __device__ __forceinline__ void rotate_back_bwd_group(const OpBufs<LMAX>& V, con
           }
         }
         float v[4];
-        load4(op_ptr<LMAX, TIn>(V.p, el, l, mp, CH, c4), v);
+        load4(reinterpret_cast<const TIn*>(st + G::row_off(l, mp)) + c4, v);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           g4[j] *= rs;
@@ -400,9 +505,17 @@ __device__ __forceinline__ void rotate_back_bwd_group(const OpBufs<LMAX>& V, con
     for (int o = VC / 8; o > 0; o >>= 1) da += __shfl_xor_sync(0xffffffffu, da, o);
     if (active && (lane % (VC / 4)) == 0) dalpha_g[(size_t)k * heads + c4 / VC] = da;
     __syncwarp();
-    buf ^= 1;
+    const int jn = k + RB_NST;
+    if (jn < ke) {
+      if (jn - pbase >= 32) {
+        pbase += 32;
+        pv = (pbase + lane < ke) ? __ldg(perm + pbase + lane) : 0;
+      }
+      const int eo = __shfl_sync(0xffffffffu, pv, jn - pbase);
+      if (lane == 0) G::issue(ring + s * G::STAGE, &bars[s], V, wig, jn - e0, eo);
+    }
+    if (++s == RB_NST) { s = 0; phase ^= 1; }
   }
-  cp_async_wait<0>();
 }
 
 template <int LMAX, int MMAX, int CH, int VC, typename TIn, typename TOut>
@@ -412,19 +525,18 @@ __global__ void __launch_bounds__(32 * Tab<LMAX, MMAX>::NG) rotate_back_agg_bwd_
     const float* __restrict__ dout /* [Nt, L, CH] */, float* __restrict__ dalpha /* [NG, Etot, heads] sorted */,
     long long part_stride, int n0, int e0) {
   using T = Tab<LMAX, MMAX>;
-  constexpr int MAXWN = BackCfg<LMAX, MMAX>::MAXWN;
-  __shared__ __align__(16) float sW[T::NG][2][MAXWN];
+  using B = BackCfg<LMAX, MMAX, CH, TIn>;
+  extern __shared__ __align__(128) uint8_t rb_smem[];
   const int g = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = n0 + blockIdx.x;
   const int kb = rowptr[n], ke = rowptr[n + 1];
-  float* s = &sW[g][0][0];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(rb_smem) + g * RB_NST;
   float* dag = dalpha + (size_t)g * part_stride;
 #define GROUP(G)                                                                                                 \
   case G:                                                                                                        \
     if constexpr (G < T::NG)                                                                                     \
-      rotate_back_bwd_group<LMAX, MMAX, CH, VC, TIn, TOut, T::glo(G), T::ghi(G)>(V, dY, alpha, heads, perm, wig, \
-                                                                                  dout, dag, n, kb, ke, e0, s,   \
-                                                                                  lane);                         \
+      rotate_back_bwd_group<LMAX, MMAX, CH, VC, TIn, TOut, T::glo(G), T::ghi(G)>(                                \
+          V, dY, alpha, heads, perm, wig, dout, dag, n, kb, ke, e0, rb_smem + B::ring_off(G), bars, lane);       \
     break;
   switch (g) {
     GROUP(0) GROUP(1) GROUP(2) GROUP(3) GROUP(4) GROUP(5)
@@ -560,6 +672,22 @@ extern "C" int efl_segment_sum_rows(const float* buf, int L, int ldc, int coff, 
   return EFL_OK;
 }
 
+// launch with dynamic shared memory (opt-in above 48 KB, set once per instantiation)
+#define RB_LAUNCH(KERNEL, SMEM_BYTES, ...)                                                              \
+  {                                                                                                     \
+    static bool attr_done = false;                                                                      \
+    if (!attr_done) {                                                                                   \
+      cudaError_t ae = cudaFuncSetAttribute(KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize,        \
+                                            SMEM_BYTES);                                                \
+      if (ae != cudaSuccess) {                                                                          \
+        efl_set_error(cudaGetErrorString(ae));                                                          \
+        return (int)ae;                                                                                 \
+      }                                                                                                 \
+      attr_done = true;                                                                                 \
+    }                                                                                                   \
+    KERNEL<<<grid, block, SMEM_BYTES, s>>>(__VA_ARGS__);                                                \
+  }
+
 extern "C" int efl_rotate_back_parts(int lmax, int mmax) {
   (void)mmax;
   return lmax > 3 ? lmax - 2 : 1;  // Tab::NG: degree groups = partial d-alpha planes of the backward
@@ -578,12 +706,11 @@ extern "C" int efl_rotate_back_aggregate_fwd(int lmax, int mmax, int heads, int 
     OpBufs<LM> o{{(void*)v0, (void*)v1, (void*)v2}};                                                           \
     dim3 block(32 * Tab<LM, MM>::NG);                                                                          \
     if (bf16_in)                                                                                               \
-      rotate_back_agg_fwd_kernel<LM, MM, 112, 16, __nv_bfloat16><<<grid, block, 0, s>>>(o, alpha, heads,       \
-                                                                                        rowptr, perm, wig,     \
-                                                                                        out, n0, e0);          \
+      RB_LAUNCH((rotate_back_agg_fwd_kernel<LM, MM, 112, 16, __nv_bfloat16>),                                  \
+                (BackCfg<LM, MM, 112, __nv_bfloat16>::SMEM), o, alpha, heads, rowptr, perm, wig, out, n0, e0)  \
     else                                                                                                       \
-      rotate_back_agg_fwd_kernel<LM, MM, 112, 16, float><<<grid, block, 0, s>>>(o, alpha, heads, rowptr, perm, \
-                                                                                wig, out, n0, e0);             \
+      RB_LAUNCH((rotate_back_agg_fwd_kernel<LM, MM, 112, 16, float>), (BackCfg<LM, MM, 112, float>::SMEM), o,  \
+                alpha, heads, rowptr, perm, wig, out, n0, e0)                                                  \
   }
   DISPATCH_LM(lmax, mmax, CALL)
 #undef CALL
@@ -606,11 +733,12 @@ extern "C" int efl_rotate_back_aggregate_bwd(int lmax, int mmax, int heads, int 
     OpBufs<LM> dyo{{dy0, dy1, dy2}};                                                                           \
     dim3 block(32 * Tab<LM, MM>::NG);                                                                          \
     if (bf16)                                                                                                  \
-      rotate_back_agg_bwd_kernel<LM, MM, 112, 16, __nv_bfloat16, __nv_bfloat16><<<grid, block, 0, s>>>(        \
-          vi, dyo, alpha, heads, rowptr, perm, wig, dout, dalpha, part_stride, n0, e0);                        \
+      RB_LAUNCH((rotate_back_agg_bwd_kernel<LM, MM, 112, 16, __nv_bfloat16, __nv_bfloat16>),                   \
+                (BackCfg<LM, MM, 112, __nv_bfloat16>::SMEM), vi, dyo, alpha, heads, rowptr, perm, wig, dout,   \
+                dalpha, part_stride, n0, e0)                                                                   \
     else                                                                                                       \
-      rotate_back_agg_bwd_kernel<LM, MM, 112, 16, float, float><<<grid, block, 0, s>>>(                        \
-          vi, dyo, alpha, heads, rowptr, perm, wig, dout, dalpha, part_stride, n0, e0);                        \
+      RB_LAUNCH((rotate_back_agg_bwd_kernel<LM, MM, 112, 16, float, float>), (BackCfg<LM, MM, 112, float>::SMEM), \
+                vi, dyo, alpha, heads, rowptr, perm, wig, dout, dalpha, part_stride, n0, e0)                   \
   }
   DISPATCH_LM(lmax, mmax, CALL)
 #undef CALL

@@ -23,7 +23,9 @@ constexpr int MAX_BN = 256;
 constexpr int A_BYTES = BM * BK * 2;       // 16 KB
 constexpr int B_BYTES = MAX_BN * BK * 2;   // 32 KB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int STG_BYTES = 32 * 128;        // per epilogue warp: 32 rows x 128 bytes
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 1024 /*barriers*/ + 8 * STG_BYTES;
+static_assert(SMEM_BYTES <= 232448, "shared memory budget (227 KB per CTA)");
 constexpr int TMEM_COLS = 512;
 constexpr int NUM_THREADS = 384;   // 4 control warps + 8 epilogue warps
 
@@ -154,76 +156,114 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else if (warp >= 4) {
+    // Epilogue: TMEM -> registers -> (bias / complex combine / convert) -> per-warp 32x128-byte staging tile in
+    // shared memory (16-byte chunks XOR-swizzled by row, conflict-free both ways) -> coalesced 128-byte row
+    // stores (8 lanes per row, 4 rows per instruction).  A direct lane=row store would touch 32 cache lines per
+    // instruction and made the LSU, not the tensor pipe, the limiter of the short-K shapes.
     const int q = warp & 3;
     const int eh = (warp - 4) >> 2;
-    const int row_in_tile = q * 32 + lane;
+    uint8_t* stg = smem + STAGES * STAGE_BYTES + 1024 + (warp - 4) * STG_BYTES;
+    const uint32_t stg_w = smem_u32(stg) + (uint32_t)lane * 128u;   // this lane's row (write phase)
+    const int swz = lane & 7;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int w = blockIdx.x; w < work_items; w += gridDim.x) {
       int z = 0, t = w;
       if (tn) { z = w / (m_tiles * n_tiles); t = w % (m_tiles * n_tiles); }
       const int m_blk = t / n_tiles, n_blk = t % n_tiles;
-      const int row = m_blk * BM + row_in_tile;
-      const bool row_ok = row < p.M;
+      const int row0 = m_blk * BM + q * 32;
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr0 = tmem_base + (uint32_t)(acc * MAX_BN) + ((uint32_t)(q * 32) << 16);
-      // two warps share a lane quarter: warp-half `eh` takes every other 32-column block
-      for (int cb = 32 * eh; cb < p.BN; cb += 64) {
-        uint32_t vv[32];
-        const bool two = cb + 16 < p.BN;
-        tc_ld16(taddr0 + (uint32_t)cb, vv);
-        if (two) tc_ld16(taddr0 + (uint32_t)(cb + 16), vv + 16);
-        tc_ld_wait();
+      int blk = 0;
+      for (int c = 0; c < p.BN; ++blk) {
+        const int gcol = n_blk * p.BN + c;  // global accumulator column of the block
+        // block kind: 0 = bf16, 64 columns; 1 = fp32, 32 columns; 2 = complex combine, 128 accumulator -> 64 bf16
+        int kind = 0, limit = p.BN;
+        if (tn) kind = 1;
+        else if (p.epi == 2) kind = 2;
+        else if (p.epi == 1 && gcol < p.nsplit) { kind = 1; limit = min(p.BN, p.nsplit - n_blk * p.BN); }
+        const int width = kind == 0 ? 64 : (kind == 1 ? 32 : 128);
+        const int wcols = min(width, limit - c);  // multiple of 16
+        if ((blk & 1) == eh) {
+          const int ngrp = wcols >> 4;
+          for (int g0 = 0; g0 < ngrp; g0 += 2) {
+            uint32_t vv[32];
+            const bool two = g0 + 1 < ngrp;
+            tc_ld16(taddr0 + (uint32_t)(c + 16 * g0), vv);
+            if (two) tc_ld16(taddr0 + (uint32_t)(c + 16 * g0 + 16), vv + 16);
+            tc_ld_wait();
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-          if (hh == 1 && !two) break;
-          const uint32_t* v = vv + 16 * hh;
-          const int c0 = cb + 16 * hh;
-        const int col = n_blk * p.BN + c0;
-          if (tn) {
-            if (row_ok) {
-              float4* dst = reinterpret_cast<float4*>(p.P + ((size_t)z * p.M + row) * p.N + col);
+            for (int hh = 0; hh < 2; ++hh) {
+              if (hh == 1 && !two) break;
+              const uint32_t* v = vv + 16 * hh;
+              const int gi = g0 + hh;
+              const int col = gcol + 16 * gi;
+              if (kind == 2) {
+                // complex combine: partner row = lane ^ 1, column pairs (2j, 2j+1) -> output column j
+                float o[8];
 #pragma unroll
-              for (int j = 0; j < 4; ++j)
-                dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
-                                     __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
-            }
-          } else if (p.epi == 2) {
-            // complex combine: partner row = lane ^ 1, column pairs (2q, 2q+1) -> output column q
-            float o[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float mine_e = __uint_as_float(v[2 * j]);
-              const float mine_o = __uint_as_float(v[2 * j + 1]);
-              const float other_o = __shfl_xor_sync(0xffffffffu, mine_o, 1);
-              o[j] = (lane & 1) ? (mine_e + other_o) : (mine_e - other_o);
-            }
-            if (row_ok) {
-              uint4 pk = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]),
-                                    pack_bf16(o[6], o[7]));
-              *reinterpret_cast<uint4*>(p.C + (size_t)row * p.ldc + col / 2) = pk;
-            }
-          } else {
-            float f[16];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]) + (p.bias ? __ldg(p.bias + col + j) : 0.f);
-            if (row_ok) {
-              if (p.epi == 1 && col < p.nsplit) {
-                float4* dst = reinterpret_cast<float4*>(p.C0 + (size_t)row * p.ldc0 + col);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+                for (int j = 0; j < 8; ++j) {
+                  const float mine_e = __uint_as_float(v[2 * j]);
+                  const float mine_o = __uint_as_float(v[2 * j + 1]);
+                  const float other_o = __shfl_xor_sync(0xffffffffu, mine_o, 1);
+                  o[j] = (lane & 1) ? (mine_e + other_o) : (mine_e - other_o);
+                }
+                st_shared_v4(stg_w + (uint32_t)((gi ^ swz) << 4), pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]),
+                             pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
               } else {
-                const int cc = col - (p.epi == 1 ? p.nsplit : 0);
-                uint4* dst = reinterpret_cast<uint4*>(p.C + (size_t)row * p.ldc + cc);
-                dst[0] = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]),
-                                    pack_bf16(f[6], f[7]));
-                dst[1] = make_uint4(pack_bf16(f[8], f[9]), pack_bf16(f[10], f[11]), pack_bf16(f[12], f[13]),
-                                    pack_bf16(f[14], f[15]));
+                float f[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                  f[j] = __uint_as_float(v[j]) + ((!tn && p.bias) ? __ldg(p.bias + col + j) : 0.f);
+                if (kind == 1) {
+#pragma unroll
+                  for (int j = 0; j < 4; ++j)
+                    st_shared_v4(stg_w + (uint32_t)(((4 * gi + j) ^ swz) << 4), __float_as_uint(f[4 * j]),
+                                 __float_as_uint(f[4 * j + 1]), __float_as_uint(f[4 * j + 2]),
+                                 __float_as_uint(f[4 * j + 3]));
+                } else {
+                  st_shared_v4(stg_w + (uint32_t)(((2 * gi) ^ swz) << 4), pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]),
+                               pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+                  st_shared_v4(stg_w + (uint32_t)(((2 * gi + 1) ^ swz) << 4), pack_bf16(f[8], f[9]),
+                               pack_bf16(f[10], f[11]), pack_bf16(f[12], f[13]), pack_bf16(f[14], f[15]));
+                }
               }
             }
           }
+          __syncwarp();
+          // coalesced write-out: lane -> (row 4*it + lane/8, 16-byte chunk lane%8)
+          const int nchunks = kind == 0 ? (wcols >> 3) : (kind == 1 ? (wcols >> 2) : (wcols >> 4));
+          const int ch = lane & 7;
+          uint8_t* gbase;
+          long long pitch;  // bytes
+          if (tn) {
+            gbase = reinterpret_cast<uint8_t*>(p.P + ((size_t)z * p.M) * p.N + gcol);
+            pitch = (long long)p.N * 4;
+          } else if (kind == 1) {
+            gbase = reinterpret_cast<uint8_t*>(p.C0 + gcol);
+            pitch = p.ldc0 * 4;
+          } else if (kind == 2) {
+            gbase = reinterpret_cast<uint8_t*>(p.C + gcol / 2);
+            pitch = p.ldc * 2;
+          } else {
+            gbase = reinterpret_cast<uint8_t*>(p.C + (gcol - (p.epi == 1 ? p.nsplit : 0)));
+            pitch = p.ldc * 2;
+          }
+          if (ch < nchunks) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+              const int r = 4 * it + (lane >> 3);
+              const int grow = row0 + r;
+              if (grow < p.M) {
+                const uint4 val = ld_shared_v4(smem_u32(stg) + (uint32_t)(r * 128 + ((ch ^ (r & 7)) << 4)));
+                *reinterpret_cast<uint4*>(gbase + (size_t)grow * pitch + ch * 16) = val;
+              }
+            }
+          }
+          __syncwarp();
         }
+        c += wcols;
       }
       tc_fence_before();
       mbar_arrive(&tempty[acc]);
@@ -348,16 +388,29 @@ extern "C" int efl_tc_gemm_nt(int epilogue, const void* A, long long lda, const 
   return launch(ma, mb, p, tiles, (cudaStream_t)stream);
 }
 
-// split count for the weight-gradient GEMM: fill the SMs, keep >= 8 k-blocks per split
+// Split count for the weight-gradient GEMM.  Work items = tiles x splits run on a persistent grid of one CTA per
+// SM, so the count is chosen against wave quantisation: the smallest split (>= 8 k-blocks each) whose last wave is
+// >= 94 % full, else the best-filled one; at most 4 waves' worth of partial planes.
 extern "C" int efl_tc_gemm_tn_splits(int Mred, int N1, int N2) {
   const int bn = pick_bn(N2);
   if (bn <= 0) return 1;
   const int tiles = ((N1 + efl::tc::BM - 1) / efl::tc::BM) * (N2 / bn);
   const int kb = (Mred + efl::tc::BK - 1) / efl::tc::BK;
-  int s = (efl_num_sms() + tiles - 1) / tiles;
-  if (s > kb / 8) s = kb / 8;
-  if (s < 1) s = 1;
-  const int per = (kb + s - 1) / s;
+  const int sms = efl_num_sms();
+  int smax = kb / 8;
+  if (smax < 1) smax = 1;
+  const int cap = (4 * sms + tiles - 1) / tiles;
+  if (smax > cap) smax = cap;
+  int best = 1;
+  double best_eff = 0.0;
+  for (int s = 1; s <= smax; ++s) {
+    const int items = tiles * s;
+    const int waves = (items + sms - 1) / sms;
+    const double eff = (double)items / ((double)waves * sms);
+    if (eff > best_eff + 1e-9) { best_eff = eff; best = s; }
+    if (eff >= 0.94) { best = s; break; }
+  }
+  const int per = (kb + best - 1) / best;
   return (kb + per - 1) / per;
 }
 

@@ -83,7 +83,8 @@ def wigner_from_rotmat(rot: torch.Tensor, lmax: int, mmax: int) -> torch.Tensor:
     rot = rot.detach().to(torch.float32).contiguous()
     E = rot.shape[0]
     wig = torch.empty(E, wigner_size(lmax, mmax), dtype=torch.float32, device=rot.device)
-    call("efl_wigner_from_rotmat", lmax, mmax, ptr(rot), ptr(jd_device(lmax, rot.device)), ptr(wig), E)
+    call("efl_wigner_from_rotmat", lmax, mmax, ptr(rot), ptr(jd_device(lmax, rot.device)), ptr(wig), E,
+         work=E * (36.0 + wig.shape[1] * 4))
     return wig
 
 
@@ -198,7 +199,7 @@ def _gemm_tn(A, B, C, accumulate, Mred, N1, N2):
 def _colsum(X, rows, cols, out, accumulate):
     ws = torch.empty(((rows + 511) // 512 + 1) * cols, dtype=torch.float32, device=X.device)
     call("efl_colsum", int(X.dtype == torch.bfloat16), ptr(X), X.stride(0), rows, cols, ptr(out), int(accumulate),
-         ptr(ws))
+         ptr(ws), work=float(rows) * cols * X.element_size())
 
 
 # ---------------------------------------------------------------------------
@@ -317,7 +318,7 @@ def _chunk_forward(d: AttnDims, ws: _Workspace, w1: _Weights, w2: _Weights, x_sr
         _gemm_nt(2, ws.A[m], w1.wm[m - 1], None, ws.Hb[m], d.ms[m] * H, None, 0, 0, 2 * Ec, 2 * d.ms[m] * H,
                  d.ms[m] * C2)
     call("efl_alpha_logits_fwd", ptr(ws.extra), ws.extra_w, d.heads, d.alpha_ch, ptr(ln_w), ptr(ln_b), ptr(adot),
-         logits.data_ptr() + e0 * d.heads * 4, Ec)
+         logits.data_ptr() + e0 * d.heads * 4, Ec, work=Ec * d.heads * (d.alpha_ch + 1) * 4.0)
     call("efl_segment_softmax_fwd", ptr(logits), d.heads, ptr(csr.rowptr), ptr(alpha), n0, n1)
     to_g, from_g, G = grids
     gate_ptr = ws.extra.data_ptr() + d.heads * d.alpha_ch * 4
@@ -482,7 +483,8 @@ class EdgeAttentionFunction(torch.autograd.Function):
             call("efl_segment_softmax_bwd", ptr(alpha), ptr(dalpha), nparts, dalpha.stride(0), d.heads, ptr(csr.rowptr),
                  ptr(dlogits), n0, n1)
             call("efl_alpha_logits_bwd", ptr(ws.extra), ws.extra_w, d.heads, d.alpha_ch, ptr(lw), ptr(lb), ptr(ad),
-                 dlogits.data_ptr() + e0 * d.heads * 4, ptr(ws.dY1[0]), ld1, bf16, ptr(part), nblk, Ec)
+                 dlogits.data_ptr() + e0 * d.heads * 4, ptr(ws.dY1[0]), ld1, bf16, ptr(part), nblk, Ec,
+                 work=Ec * d.heads * ((d.alpha_ch + 1) * 4.0 + d.alpha_ch * ws.dY1[0].element_size()))
             part_all += part.sum(dim=0)
             # ---- so2_conv_1 backward
             _gemm_tn(ws.dY1[0], ws.A[0], g_c1w0, acc, Ec, ld1, d.ms[0] * C2)
@@ -495,14 +497,16 @@ class EdgeAttentionFunction(torch.autograd.Function):
             # ---- rotate-in backward -> d rad, per-edge d x
             call("efl_rotate_in_bwd", d.lmax, d.mmax, d.C, bf16, ptr(x_src), ptr(x_dst), ptr(csr.src_sorted),
                  ptr(csr.dst_sorted), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.dA[0]), ptr(ws.dA[1]),
-                 ptr(ws.dA[2]), ptr(drad), ptr(dxe), e0, Ec)
+                 ptr(ws.dA[2]), ptr(drad), ptr(dxe), e0, Ec,
+                 work=Ec * (_bytes_rotate_in(d, ws.dA[0].element_size(), wig.shape[1]) + d.M * C2 * 4 + L * C2 * 4))
             first = False
         # ---- gather backward: deterministic segment sums over the dst CSR and the src grouping
         dx_dst = torch.empty_like(x_dst)
         dx_src = torch.empty_like(x_src)
-        call("efl_segment_sum_rows", ptr(dxe), L, C2, d.C, d.C, ptr(csr.rowptr), None, ptr(dx_dst), csr.num_dst, 0)
+        call("efl_segment_sum_rows", ptr(dxe), L, C2, d.C, d.C, ptr(csr.rowptr), None, ptr(dx_dst), csr.num_dst, 0,
+             work=(E + csr.num_dst) * L * d.C * 4.0)
         call("efl_segment_sum_rows", ptr(dxe), L, C2, 0, d.C, ptr(csr.src_ptr), ptr(csr.src_idx), ptr(dx_src),
-             csr.num_src, 0)
+             csr.num_src, 0, work=(E + csr.num_src) * L * d.C * 4.0 + E * 4.0)
         ha = d.heads * d.alpha_ch
         g_adot = part_all[:ha].view(d.heads, d.alpha_ch)
         g_lnw = part_all[ha:ha + d.alpha_ch]
