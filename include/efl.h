@@ -158,6 +158,30 @@ int efl_so3_linear_bwd_data(const float* dout, const float* Wt, float* dx, int N
 int efl_so3_linear_bwd_weight(const float* dout, const float* x, float* dW, float* workspace, int N, int lmax,
                               int Cin, int Cout, void* stream);
 
+/* Operand layout kernels that put SO3_LinearV2 (:624-674) on efl_tc_gemm_nt / efl_tc_gemm_tn.  rows = N*(lmax+1)^2.
+ * expand: x [rows, C] fp32 -> xe [rows, KP] bf16; expand=1 puts x[r,:] in column block l(i) (zeros elsewhere) and a 1
+ * in bias_col on i=0 rows (bias_col < 0: none); expand=0 is a plain bf16 cast with zero padding.
+ * select: y[r, c] = ye[r, l(i)*C + c] (+ bias[c] on i=0), ye fp32 with row pitch ld. */
+int efl_so3_expand(const float* x, void* xe, long long rows, int lmax, int C, int KP, int expand, int bias_col,
+                   void* stream);
+int efl_so3_select(const float* ye, long long ld, const float* bias, float* y, long long rows, int lmax, int C,
+                   void* stream);
+
+/* RadialFunction (:1634-1657) for edge_channels_list [K0, 16, 16] + output width NO, fused:
+ * Linear(K0,16) -> LayerNorm(16) -> SiLU -> Linear(16,16) -> LayerNorm(16) -> SiLU -> Linear(16,NO).  x [E,K0] -> out [E,NO]
+ * fp32.  Weights in the nn.Linear / nn.LayerNorm layouts of RadialFunction.net.{0,1,3,4,6}.  Backward recomputes the
+ * hidden activations and writes per-CTA parameter-gradient partials part [nblocks, efl_radial_mlp_part_size(K0,NO)]:
+ *   dW3 [NO,16] | db3 [NO] | dW2 [16,16] | db2 | dg2 | dbeta2 | dW1 [16,K0] | db1 | dg1 | dbeta1   (summed by the caller
+ * in fixed order: deterministic, no atomics).  K0 in {16,32,48,64}, NO % 4 == 0, NO <= 768. */
+int efl_radial_mlp_part_size(int K0, int NO);
+int efl_radial_mlp_fwd(const float* x, int K0, const float* W1, const float* b1, const float* g1, const float* be1,
+                       const float* W2, const float* b2, const float* g2, const float* be2, const float* W3,
+                       const float* b3, int NO, float* out, int E, void* stream);
+int efl_radial_mlp_bwd(const float* x, int K0, const float* W1, const float* b1, const float* g1, const float* be1,
+                       const float* W2, const float* b2, const float* g2, const float* be2, const float* W3,
+                       const float* b3, int NO, const float* dout, float* dx, float* part, int nblocks, int E,
+                       void* stream);
+
 /* EquivariantRMSNormArraySphericalHarmonicsV2 as built by get_normalization_layer (:2099-2192, :2254-2273):
  * centred l=0, degree-balanced RMS, per-degree gain gamma [lmax+1,16], bias beta [16] on l=0.  One warp per node.
  * bwd writes per-block partials of (d gamma | d beta) into part [nblocks, (lmax+2)*16]. */

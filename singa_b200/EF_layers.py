@@ -402,7 +402,13 @@ class RadialFunction(nn.Module):
         self.net = nn.Sequential(*layers)
 
     def forward(self, inputs):
-        return self.net(inputs)
+        if inputs.is_cuda:
+            ops = _get_ops()
+            if ops.RadialMLPFunction.eligible(self.net):
+                n = self.net
+                return ops.RadialMLPFunction.apply(inputs, n[0].weight, n[0].bias, n[1].weight, n[1].bias, n[3].weight,
+                                                   n[3].bias, n[4].weight, n[4].bias, n[6].weight, n[6].bias)
+        return self.net(inputs)  # other channel lists (not built by model/Embedding.py): library ops
 
 
 class SmoothLeakyReLU(nn.Module):
@@ -543,16 +549,7 @@ class SO3_LinearV2(nn.Module):
         self.register_buffer('expand_index', get_l_to_all_m_expand_index(lmax, device))
 
     def apply_tensor(self, x: Tensor) -> Tensor:
-        if x.is_cuda:
-            return _get_ops().SO3LinearFunction.apply(x, self.weight, self.bias)
-        outs = []
-        for l in range(self.lmax + 1):
-            blk = x[:, l * l:(l + 1) ** 2, :]
-            y = blk @ self.weight[l].t()
-            if l == 0:
-                y = y + self.bias
-            outs.append(y)
-        return torch.cat(outs, dim=1)
+        return _get_ops().SO3LinearFunction.apply(x, self.weight, self.bias)  # raises on CPU tensors
 
     def forward(self, input_embedding):
         out = SO3_Embedding(0, input_embedding.lmax_list.copy(), self.out_features, device=self.device,
@@ -1089,6 +1086,18 @@ class FeedForwardNetwork(nn.Module):
 
     def forward(self, input_embedding):
         gate = self.gating_linear(input_embedding.embedding[:, 0, :])
+        ops = _get_ops()
+        x = input_embedding.embedding
+        g = self.SO3_grid[self.max_lmax][self.max_lmax]
+        if ops.FFNFunction.eligible(x.shape[2], self.hidden_channels, self.output_channels, x.shape[1],
+                                                  g.to_grid_mat.shape[0] * g.to_grid_mat.shape[1]):
+            to_g, from_g = _grid_flat(g)
+            l1, l2 = self.so3_linear_1, self.so3_linear_2
+            out = SO3_Embedding(0, input_embedding.lmax_list.copy(), self.output_channels, device=self.device,
+                                dtype=input_embedding.dtype)
+            out.set_lmax_mmax(input_embedding.lmax_list.copy(), input_embedding.lmax_list.copy())
+            out.set_embedding(ops.FFNFunction.apply(x, l1.weight, l1.bias, gate, l2.weight, l2.bias, to_g, from_g))
+            return out
         hidden = self.so3_linear_1(input_embedding)
         hidden.embedding = self.s2_act(gate, hidden.embedding, self.SO3_grid)
         return self.so3_linear_2(hidden)

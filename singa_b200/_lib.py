@@ -43,6 +43,10 @@ SIGNATURES = {
     "efl_so3_linear_fwd": "ppppiiiip",
     "efl_so3_linear_bwd_data": "pppiiiip",
     "efl_so3_linear_bwd_weight": "ppppiiiip",
+    "efl_so3_expand": "ppliiiiip",
+    "efl_so3_select": "plppliip",
+    "efl_radial_mlp_fwd": "pi" + "p" * 10 + "ipip",
+    "efl_radial_mlp_bwd": "pi" + "p" * 10 + "ipppiip",
     "efl_rmsnorm_sh_fwd": "iipppfpip",
     "efl_rmsnorm_sh_bwd": "iippfpppiip",
 }
@@ -68,6 +72,8 @@ def _load():
     lib.efl_gemm_tn_splits.restype = _I
     lib.efl_tc_gemm_tn_splits.argtypes = [_I, _I, _I]
     lib.efl_tc_gemm_tn_splits.restype = _I
+    lib.efl_radial_mlp_part_size.argtypes = [_I, _I]
+    lib.efl_radial_mlp_part_size.restype = _I
     lib.efl_rotate_back_parts.argtypes = [_I, _I]
     lib.efl_rotate_back_parts.restype = _I
     return lib

@@ -597,10 +597,120 @@ class NodeS2ActFunction(torch.autograd.Function):
 
 
 # ---------------------------------------------------------------------------
+# RadialFunction
+# ---------------------------------------------------------------------------
+class RadialMLPFunction(torch.autograd.Function):
+    """RadialFunction (EF_layers.py:1634-1657) with hidden width 16 as one kernel forward and one backward
+    (csrc/radial.cu); only x is kept for backward.  params: W1,b1,g1,be1,W2,b2,g2,be2,W3,b3."""
+
+    @staticmethod
+    def eligible(net) -> bool:
+        if len(net) != 7:
+            return False
+        l1, n1, _, l2, n2, _, l3 = net
+        return (isinstance(l1, torch.nn.Linear) and isinstance(l2, torch.nn.Linear) and isinstance(l3, torch.nn.Linear)
+                and isinstance(n1, torch.nn.LayerNorm) and isinstance(n2, torch.nn.LayerNorm)
+                and l1.out_features == 16 and l2.in_features == 16 and l2.out_features == 16 and l3.in_features == 16
+                and l1.in_features in (16, 32, 48, 64) and l3.out_features % 4 == 0 and l3.out_features <= 768
+                and abs(n1.eps - 1e-5) < 1e-12 and abs(n2.eps - 1e-5) < 1e-12)
+
+    @staticmethod
+    def forward(ctx, x, *params):
+        check_cuda(x, *params)
+        x = x.contiguous().float()
+        ps = [q.detach().contiguous().float() for q in params]
+        E, K0 = x.shape
+        NO = ps[8].shape[0]
+        out = torch.empty(E, NO, dtype=torch.float32, device=x.device)
+        call("efl_radial_mlp_fwd", ptr(x), K0, *[ptr(q) for q in ps], NO, ptr(out), E, work=E * 4.0 * (K0 + NO))
+        ctx.save_for_backward(x, *ps)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, *ps = ctx.saved_tensors
+        E, K0 = x.shape
+        NO = ps[8].shape[0]
+        dout = dout.contiguous().float()
+        dx = torch.empty_like(x)
+        psz = LIB.efl_radial_mlp_part_size(K0, NO)
+        nblk = max(1, min(2 * 148, (E + 31) // 32))
+        part = torch.empty(nblk, psz, dtype=torch.float32, device=x.device)
+        call("efl_radial_mlp_bwd", ptr(x), K0, *[ptr(q) for q in ps], NO, ptr(dout), ptr(dx), ptr(part), nblk, E,
+             work=E * 4.0 * (2 * K0 + NO))
+        t = part.sum(dim=0)
+        o = 0
+
+        def take(*shape):
+            nonlocal o
+            n = int(np.prod(shape))
+            v = t[o:o + n].view(*shape)
+            o += n
+            return v
+
+        dW3, db3 = take(NO, 16), take(NO)
+        dW2, db2, dg2, dbe2 = take(16, 16), take(16), take(16), take(16)
+        dW1, db1, dg1, dbe1 = take(16, K0), take(16), take(16), take(16)
+        return (dx, dW1, db1, dg1, dbe1, dW2, db2, dg2, dbe2, dW3, db3)
+
+
+# ---------------------------------------------------------------------------
 # node-level SO3_LinearV2 and RMS norm
 # ---------------------------------------------------------------------------
+def _pad(n: int, m: int) -> int:
+    return (n + m - 1) // m * m
+
+
+def _so3_expand(x, lmax: int, KP: int, expand: bool, bias_col: int = -1):
+    """x [N, L, C] fp32 -> bf16 GEMM operand [N*L, KP] (csrc/so3lin.cu): degree-block expanded, or a plain cast."""
+    N, L, C = x.shape
+    xe = torch.empty(N * L, KP, dtype=torch.bfloat16, device=x.device)
+    call("efl_so3_expand", ptr(x), ptr(xe), N * L, lmax, C, KP, int(expand), bias_col,
+         work=N * L * (C * 4.0 + KP * 2.0))
+    return xe
+
+
+def _so3_select(ye, bias, N: int, lmax: int, C: int):
+    """ye [N*L, >= (lmax+1)*C] fp32 -> y [N, L, C]: column block l(i) of each row (+ bias on i = 0)."""
+    L = (lmax + 1) ** 2
+    y = torch.empty(N, L, C, dtype=torch.float32, device=ye.device)
+    call("efl_so3_select", ptr(ye), ye.stride(0), ptr(bias), ptr(y), N * L, lmax, C, work=N * L * C * 8.0)
+    return y
+
+
+def _so3_w_expand_in(w, bias, KP: int):
+    """[lmax+1, Cout, Cin] (+ bias) -> B operand [Cout, KP] bf16 with the W[l] side by side and the bias column."""
+    nl, Cout, Cin = w.shape
+    we = torch.zeros(Cout, KP, dtype=torch.float32, device=w.device)
+    we[:, :nl * Cin] = w.permute(1, 0, 2).reshape(Cout, nl * Cin)
+    if bias is not None:
+        we[:, nl * Cin] = bias
+    return we.to(torch.bfloat16)
+
+
+def _so3_w_stack(w, NP: int):
+    """[lmax+1, Cout, Cin] -> B operand [NP, Cin] bf16, the W[l] stacked (zero rows up to NP)."""
+    nl, Cout, Cin = w.shape
+    wa = torch.zeros(NP, Cin, dtype=torch.float32, device=w.device)
+    wa[:nl * Cout] = w.reshape(nl * Cout, Cin)
+    return wa.to(torch.bfloat16)
+
+
+def _f32_from_gemm(A, B, M, N, K):
+    """fp32 [M, N] = A[M, K] B[N, K]^T on the tensor cores (split epilogue with every column on the fp32 side)."""
+    out = torch.empty(M, N, dtype=torch.float32, device=A.device)
+    _gemm_nt(1, A, B, None, out, 8, out, N, N, M, N, K)
+    return out
+
+
+def _so3_tc_ok(Cin: int, Cout: int) -> bool:
+    return _PRECISION == "bf16" and Cin % 16 == 0 and Cout % 16 == 0
+
+
 class SO3LinearFunction(torch.autograd.Function):
-    """x [N, L, Cin], weight [lmax+1, Cout, Cin], bias [Cout] -> [N, L, Cout] (EF_layers.py:655-671)."""
+    """x [N, L, Cin], weight [lmax+1, Cout, Cin], bias [Cout] -> [N, L, Cout] (EF_layers.py:655-671).
+    bf16 mode: one tcgen05 GEMM with the degree selection folded into an operand (csrc/so3lin.cu);
+    fp32 mode: batched SIMT GEMM."""
 
     @staticmethod
     def forward(ctx, x, weight, bias):
@@ -609,6 +719,24 @@ class SO3LinearFunction(torch.autograd.Function):
         w = weight.detach().contiguous().float()
         N, L, Cin = x.shape
         lmax, Cout = w.shape[0] - 1, w.shape[1]
+        ctx.tc = _so3_tc_ok(Cin, Cout) and N > 0
+        if ctx.tc:
+            nl, R = lmax + 1, N * L
+            b = bias.detach().float()
+            if Cin < Cout:  # expand-in
+                KP = _pad(nl * Cin + 1, 64)
+                we = _so3_w_expand_in(w, b, KP)
+                xe = _so3_expand(x, lmax, KP, True, nl * Cin)
+                out = _f32_from_gemm(xe, we, R, Cout, KP).view(N, L, Cout)
+                ctx.save_for_backward(x, we)
+            else:  # select-out
+                NP = _pad(nl * Cout, 16)
+                wa = _so3_w_stack(w, NP)
+                xb = _so3_expand(x, lmax, Cin, False)
+                out = _so3_select(_f32_from_gemm(xb, wa, R, NP, Cin), b.contiguous(), N, lmax, Cout)
+                ctx.save_for_backward(xb, wa)
+            ctx.dims = (N, L, Cin, Cout, lmax)
+            return out
         out = torch.empty(N, L, Cout, dtype=torch.float32, device=x.device)
         call("efl_so3_linear_fwd", ptr(x), ptr(w), ptr(bias.detach().contiguous().float()), ptr(out), N, lmax, Cin, Cout,
              work=2.0 * N * L * Cin * Cout)
@@ -617,8 +745,10 @@ class SO3LinearFunction(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dout):
-        x, w = ctx.saved_tensors
         dout = dout.contiguous().float()
+        if ctx.tc:
+            return SO3LinearFunction._backward_tc(ctx, dout)
+        x, w = ctx.saved_tensors
         N, L, Cin = x.shape
         lmax, Cout = w.shape[0] - 1, w.shape[1]
         dx = dw = db = None
@@ -634,6 +764,107 @@ class SO3LinearFunction(torch.autograd.Function):
         if ctx.needs_input_grad[2]:
             db = dout[:, 0, :].sum(dim=0)
         return dx, dw, db
+
+
+    @staticmethod
+    def _backward_tc(ctx, dout):
+        N, L, Cin, Cout, lmax = ctx.dims
+        nl, R = lmax + 1, N * L
+        dx = dw = db = None
+        if Cin < Cout:
+            x, we = ctx.saved_tensors
+            KP = we.shape[1]
+            dob = _so3_expand(dout, lmax, Cout, False)
+            if ctx.needs_input_grad[0]:
+                KN = _pad(nl * Cin, 16)
+                wet = torch.zeros(KN, Cout, dtype=torch.bfloat16, device=we.device)
+                wet[:nl * Cin] = we[:, :nl * Cin].t()
+                dx = _so3_select(_f32_from_gemm(dob, wet, R, KN, Cout), None, N, lmax, Cin)
+            if ctx.needs_input_grad[1] or ctx.needs_input_grad[2]:
+                xe = _so3_expand(x, lmax, KP, True, nl * Cin)
+                dwe = torch.empty(Cout, KP, dtype=torch.float32, device=x.device)
+                _gemm_tn(dob, xe, dwe, False, R, Cout, KP)
+                dw = dwe[:, :nl * Cin].reshape(Cout, nl, Cin).permute(1, 0, 2).contiguous()
+                db = dwe[:, nl * Cin].contiguous()
+        else:
+            xb, wa = ctx.saved_tensors
+            NP = wa.shape[0]
+            dye = _so3_expand(dout, lmax, NP, True)
+            if ctx.needs_input_grad[0]:
+                dx = _f32_from_gemm(dye, wa.t().contiguous(), R, Cin, NP).view(N, L, Cin)
+            if ctx.needs_input_grad[1]:
+                dwa = torch.empty(NP, Cin, dtype=torch.float32, device=xb.device)
+                _gemm_tn(dye, xb, dwa, False, R, NP, Cin)
+                dw = dwa[:nl * Cout].view(nl, Cout, Cin)
+            if ctx.needs_input_grad[2]:
+                db = dout[:, 0, :].sum(dim=0)
+        return dx, dw, db
+
+
+class FFNFunction(torch.autograd.Function):
+    """FeedForwardNetwork core (EF_layers.py:234-270) in bf16 mode: so3_linear_1 -> SeparableS2Activation on the
+    (lmax, lmax) grid -> so3_linear_2 with the [N, L, hidden] activations kept in bf16 end to end: two tcgen05 GEMMs
+    around the tcgen05 S2 kernel, no fp32 copy of the hidden tensor ever written.
+    (x [N, L, C], w1 [nl, CH, C], b1 [CH], gate [N, CH], w2 [nl, Co, CH], b2 [Co]) -> [N, L, Co] fp32."""
+
+    @staticmethod
+    def eligible(C, CH, Co, L, G) -> bool:
+        return (_PRECISION == "bf16" and C % 16 == 0 and Co % 16 == 0 and CH % 128 == 0 and L <= 64 and G <= 224)
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, gate, w2, b2, to_g, from_g):
+        check_cuda(x, w1, gate, w2)
+        x = x.contiguous().float()
+        gate = gate.contiguous().float()
+        N, L, C = x.shape
+        nl, CH, Co = w1.shape[0], w1.shape[1], w2.shape[1]
+        lmax, R, G = nl - 1, N * L, to_g.shape[0]
+        KP = _pad(nl * C + 1, 64)
+        NP = _pad(nl * Co, 16)
+        w1e = _so3_w_expand_in(w1.detach().float(), b1.detach().float(), KP)
+        w2a = _so3_w_stack(w2.detach().float(), NP)
+        xe = _so3_expand(x, lmax, KP, True, nl * C)
+        h = torch.empty(R, CH, dtype=torch.bfloat16, device=x.device)
+        _gemm_nt(0, xe, w1e, None, h, CH, None, 0, 0, R, CH, KP)
+        del xe
+        yb = torch.empty_like(h)
+        call("efl_s2act_tc_nodes", 0, L, G, CH, ptr(h), None, ptr(yb), None, ptr(gate), CH, ptr(to_g), ptr(from_g), N,
+             work=N * 4.0 * G * L * CH, tag="efl_s2act_tc_nodes_fwd")
+        out = _so3_select(_f32_from_gemm(yb, w2a, R, NP, CH), b2.detach().float().contiguous(), N, lmax, Co)
+        ctx.save_for_backward(x, gate, h, yb, w1e, w2a, to_g, from_g)
+        ctx.dims = (N, L, C, CH, Co, lmax, G)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, gate, h, yb, w1e, w2a, to_g, from_g = ctx.saved_tensors
+        N, L, C, CH, Co, lmax, G = ctx.dims
+        nl, R = lmax + 1, N * L
+        KP, NP = w1e.shape[1], w2a.shape[0]
+        dout = dout.contiguous().float()
+        dye = _so3_expand(dout, lmax, NP, True)
+        dyb = torch.empty(R, CH, dtype=torch.bfloat16, device=x.device)
+        _gemm_nt(0, dye, w2a.t().contiguous(), None, dyb, CH, None, 0, 0, R, CH, NP)
+        dw2a = torch.empty(NP, CH, dtype=torch.float32, device=x.device)
+        _gemm_tn(dye, yb, dw2a, False, R, NP, CH)
+        dw2 = dw2a[:nl * Co].view(nl, Co, CH)
+        db2 = dout[:, 0, :].sum(dim=0)
+        del dye
+        dh = torch.empty_like(h)
+        dgb = torch.empty(N, CH, dtype=torch.bfloat16, device=x.device)
+        call("efl_s2act_tc_nodes", 1, L, G, CH, ptr(h), ptr(dyb), ptr(dh), ptr(dgb), ptr(gate), CH, ptr(to_g),
+             ptr(from_g), N, work=N * 6.0 * G * L * CH, tag="efl_s2act_tc_nodes_bwd")
+        del dyb
+        KN = _pad(nl * C, 16)
+        w1t = torch.zeros(KN, CH, dtype=torch.bfloat16, device=x.device)
+        w1t[:nl * C] = w1e[:, :nl * C].t()
+        dx = _so3_select(_f32_from_gemm(dh, w1t, R, KN, CH), None, N, lmax, C)
+        xe = _so3_expand(x, lmax, KP, True, nl * C)
+        dw1e = torch.empty(CH, KP, dtype=torch.float32, device=x.device)
+        _gemm_tn(dh, xe, dw1e, False, R, CH, KP)
+        dw1 = dw1e[:, :nl * C].reshape(CH, nl, C).permute(1, 0, 2).contiguous()
+        db1 = dw1e[:, nl * C].contiguous()
+        return dx, dw1, db1, dgb.float(), dw2, db2, None, None
 
 
 class RMSNormSHFunction(torch.autograd.Function):
