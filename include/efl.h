@@ -182,6 +182,29 @@ int efl_radial_mlp_bwd(const float* x, int K0, const float* W1, const float* b1,
                        const float* b3, int NO, const float* dout, float* dx, float* part, int nblocks, int E,
                        void* stream);
 
+/* radius_graph (torch-cluster 1.6.3 radius_graph, un-vendored; reference gen.py:17) as a cell-list
+ * neighbour search emitting a destination-sorted CSR: edge (j -> i) iff j != i (unless loop), same batch item and
+ * ((xi-xj)^2 + (yi-yj)^2) + (zi-zj)^2 < r*r in fp32 (separately rounded); at most cap sources per target (smallest
+ * indices kept); targets ascending, sources ascending inside a target.  pos [N,3] fp32, batch [N] int32 or NULL.
+ *  bbox : box_out [B,6] floats (min xyz | max xyz) for the host to size the grid; box_ws B*6 uints scratch.
+ *  count: cells of edge cs >= r (nx*ny*nz per batch item, origin [B,3] device floats); writes cell_of [N],
+ *         cell_start [ncells+1], sorted [N] float4, deg [2*(N+1)] (full | capped), rowptr_full/rowptr_cap [N+1];
+ *         scratch 2*(ncells+1) ints, temp efl_radius_graph_temp_bytes(max(N, ncells) + 1) bytes.
+ *  fill : col [rowptr_full[N]] sources, every row sorted ascending; max_deg = largest full degree.
+ *  emit : edge_index [2,E] int64, E = rowptr_cap[N]; flow 0: row 0 = sources (source_to_target), 1: swapped. */
+int efl_radius_graph_bbox(const float* pos, const int* batch, int N, int nbatch, void* box_ws, float* box_out,
+                          void* stream);
+long long efl_radius_graph_temp_bytes(long long max_items);
+int efl_radius_graph_count(const float* pos, const int* batch, int N, int nbatch, const float* origin, float cs, int nx,
+                           int ny, int nz, float r, int loop, int cap, int* cell_of, int* cell_start, int* scratch,
+                           void* sorted, int* deg, int* rowptr_full, int* rowptr_cap, void* temp, long long temp_bytes,
+                           void* stream);
+int efl_radius_graph_fill(int N, int nbatch, float cs, int nx, int ny, int nz, float r, int loop, const int* cell_of,
+                          const int* cell_start, const void* sorted, const int* rowptr_full, int* col, int max_deg,
+                          void* stream);
+int efl_radius_graph_emit(const int* rowptr_full, const int* rowptr_cap, const int* col, int N, long long E,
+                          long long* edge_index, int flow_target_to_source, void* stream);
+
 /* EquivariantRMSNormArraySphericalHarmonicsV2 as built by get_normalization_layer (:2099-2192, :2254-2273):
  * centred l=0, degree-balanced RMS, per-degree gain gamma [lmax+1,16], bias beta [16] on l=0.  One warp per node.
  * bwd writes per-block partials of (d gamma | d beta) into part [nblocks, (lmax+2)*16]. */

@@ -399,3 +399,43 @@ def embedding_forward(p, graph: dict, frames: dict, t: Tables, hp: dict, compute
     out["protein_atoms"] = xp + lp
     out["ligand_atoms"] = xl + pl
     return out
+
+
+def radius_graph_bruteforce(pos: torch.Tensor, r: float, batch: torch.Tensor = None, loop: bool = False,
+                            max_num_neighbors: int = 32) -> torch.Tensor:
+    """torch_cluster.radius_graph (torch-cluster 1.6.3, un-vendored; reference gen.py:17) restated as an O(N^2)
+    scan per batch item: edge (j -> i) iff same batch item, j != i (unless loop) and
+    ((xi-xj)^2 + (yi-yj)^2) + (zi-zj)^2 < r*r in fp32 with separately rounded operations (not cdist).
+    At most max_num_neighbors sources per target, smallest source indices kept (the dependency's CUDA kernel scans
+    sources in index order and stops at the cap).  Returns [2, E] int64, row 0 = source j, row 1 = target i,
+    targets ascending and sources ascending inside a target.  Parity unpinned: no reference test or vector holds
+    torch_cluster output."""
+    import numpy as np
+    p = pos.detach().cpu().numpy().astype(np.float32)
+    n = p.shape[0]
+    b = np.zeros(n, dtype=np.int64) if batch is None else batch.detach().cpu().numpy().astype(np.int64)
+    r2 = np.float32(r) * np.float32(r)
+    src, dst = [], []
+    for bi in np.unique(b):
+        ids = np.nonzero(b == bi)[0]
+        q = p[ids]
+        step = max(1, 4_000_000 // max(len(ids), 1))
+        for s0 in range(0, len(ids), step):
+            t = q[s0:s0 + step]
+            dx = (t[:, None, 0] - q[None, :, 0]).astype(np.float32)
+            dy = (t[:, None, 1] - q[None, :, 1]).astype(np.float32)
+            dz = (t[:, None, 2] - q[None, :, 2]).astype(np.float32)
+            d2 = ((dx * dx).astype(np.float32) + (dy * dy).astype(np.float32)).astype(np.float32)
+            d2 = (d2 + (dz * dz).astype(np.float32)).astype(np.float32)
+            hit = d2 < r2
+            if not loop:
+                hit[np.arange(len(t)), np.arange(s0, s0 + len(t))] = False
+            keep = hit & (np.cumsum(hit, axis=1) <= max_num_neighbors)
+            ti, sj = np.nonzero(keep)
+            src.append(ids[sj])
+            dst.append(ids[ti + s0])
+    if not src:
+        return torch.empty(2, 0, dtype=torch.int64)
+    src, dst = np.concatenate(src), np.concatenate(dst)
+    order = np.lexsort((src, dst))
+    return torch.from_numpy(np.stack((src[order], dst[order])).astype(np.int64))

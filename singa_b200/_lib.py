@@ -47,6 +47,10 @@ SIGNATURES = {
     "efl_so3_select": "plppliip",
     "efl_radial_mlp_fwd": "pi" + "p" * 10 + "ipip",
     "efl_radial_mlp_bwd": "pi" + "p" * 10 + "ipppiip",
+    "efl_radius_graph_bbox": "ppiippp",
+    "efl_radius_graph_count": "ppiipfiiifiippppppppl" "p",
+    "efl_radius_graph_fill": "iifiiifippppp" "ip",
+    "efl_radius_graph_emit": "pppilpip",
     "efl_rmsnorm_sh_fwd": "iipppfpip",
     "efl_rmsnorm_sh_bwd": "iippfpppiip",
 }
@@ -74,6 +78,8 @@ def _load():
     lib.efl_tc_gemm_tn_splits.restype = _I
     lib.efl_radial_mlp_part_size.argtypes = [_I, _I]
     lib.efl_radial_mlp_part_size.restype = _I
+    lib.efl_radius_graph_temp_bytes.argtypes = [_L]
+    lib.efl_radius_graph_temp_bytes.restype = _L
     lib.efl_rotate_back_parts.argtypes = [_I, _I]
     lib.efl_rotate_back_parts.restype = _I
     return lib

@@ -1,0 +1,317 @@
+// radius_graph as a cell-list neighbour search that emits a destination-sorted CSR edge list.
+//
+// Replaces torch_cluster.radius_graph (torch-cluster 1.6.3, un-vendored; reference imports it at gen.py:17 and the
+// dataset's `linked_to` edges are radius graphs).  Semantics restated from the published algorithm:
+// edge (j -> i) iff j != i (unless loop), batch[j] == batch[i] and
+//     ((xi-xj)^2 + (yi-yj)^2) + (zi-zj)^2 < r*r        evaluated in fp32 with separately rounded operations
+// (the brute-force oracle's expression, oracle/ef_oracle.py: radius_graph_bruteforce); at most max_num_neighbors
+// sources per target, keeping the smallest source indices (the CUDA kernel of torch-cluster scans sources in index
+// order and stops at the cap).  Output: edge_index[0] = source j, edge_index[1] = target i, grouped by target in
+// ascending i and, inside a target, ascending j - a canonical order, so the edge LIST (not only the set) is
+// reproducible bit for bit and is directly the CSR the attention kernels consume.
+//
+// Pipeline (all HBM-bound integer/byte work; no float atomics; integer atomics only where order is irrelevant):
+//   1 bbox      per-batch bounding boxes, order-preserving uint encoding + atomicMin/Max        (host reads B*6 floats)
+//   2 bin       cell id per point (cell edge = 1.001 r), histogram                                 \
+//   3 scan      cub exclusive sum -> cell_start                                                     |  efl_radius_graph_count
+//   4 scatter   points into cell order as float4 (x, y, z, original index)                          |
+//   5 count     thread per point scans its 27 cells -> deg[i]; capped and full exclusive scans     /   (host reads 2 totals)
+//   6 fill      same scan, writes sources into the full CSR                                        \   efl_radius_graph_fill
+//   7 rowsort   warp per target: bitonic sort of its sources in shared memory                      /
+//   8 emit      first min(deg, cap) sources of each row -> int64 edge_index [2, E]                     efl_radius_graph_emit
+// The scatter order inside a cell depends on atomics, the final result does not (step 7 canonicalises it).
+#include <cub/cub.cuh>
+
+#include "efl_common.cuh"
+
+namespace efl {
+namespace rg {
+
+struct Grid {
+  float cs_inv;
+  int nx, ny, nz;   // cells per batch item along each axis
+  int nbatch;
+};
+
+__device__ __forceinline__ unsigned enc_f(float f) {
+  const unsigned b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float dec_f(unsigned u) {
+  const unsigned b = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(b);
+#else
+  float f;
+  memcpy(&f, &b, 4);
+  return f;
+#endif
+}
+
+__global__ void bbox_init_kernel(unsigned* __restrict__ box, int nbatch) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < nbatch * 6) box[t] = (t % 6 < 3) ? 0xffffffffu : 0u;
+}
+
+// box [B, 6] encoded (min xyz | max xyz)
+__global__ void bbox_kernel(const float* __restrict__ pos, const int* __restrict__ batch, int n,
+                            unsigned* __restrict__ box) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int b = batch ? batch[i] : 0;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    const unsigned e = enc_f(pos[3 * (size_t)i + d]);
+    atomicMin(box + 6 * b + d, e);
+    atomicMax(box + 6 * b + 3 + d, e);
+  }
+}
+
+__global__ void bbox_decode_kernel(const unsigned* __restrict__ box, float* __restrict__ out, int n) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) out[t] = dec_f(box[t]);
+}
+
+__device__ __forceinline__ int cell_coord(float p, float origin, float cs_inv, int n) {
+  int c = (int)floorf((p - origin) * cs_inv);
+  return c < 0 ? 0 : (c >= n ? n - 1 : c);
+}
+
+__global__ void bin_kernel(const float* __restrict__ pos, const int* __restrict__ batch, int n,
+                           const float* __restrict__ origin /* [B,3] */, Grid g, int* __restrict__ cell_of,
+                           int* __restrict__ cell_count) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int b = batch ? batch[i] : 0;
+  const int cx = cell_coord(pos[3 * (size_t)i + 0], origin[3 * b + 0], g.cs_inv, g.nx);
+  const int cy = cell_coord(pos[3 * (size_t)i + 1], origin[3 * b + 1], g.cs_inv, g.ny);
+  const int cz = cell_coord(pos[3 * (size_t)i + 2], origin[3 * b + 2], g.cs_inv, g.nz);
+  const int c = ((b * g.nz + cz) * g.ny + cy) * g.nx + cx;
+  cell_of[i] = c;
+  atomicAdd(cell_count + c, 1);
+}
+
+__global__ void scatter_kernel(const float* __restrict__ pos, int n, const int* __restrict__ cell_of,
+                               const int* __restrict__ cell_start, int* __restrict__ cursor,
+                               float4* __restrict__ sorted) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int c = cell_of[i];
+  const int slot = cell_start[c] + atomicAdd(cursor + c, 1);
+  sorted[slot] = make_float4(pos[3 * (size_t)i], pos[3 * (size_t)i + 1], pos[3 * (size_t)i + 2], __int_as_float(i));
+}
+
+// Visits every point within r of sorted slot s (27-cell stencil).  FILL = false: count; true: write sources.
+template <bool FILL>
+__global__ void __launch_bounds__(128) neighbour_kernel(const float4* __restrict__ sorted, int n,
+                                                        const int* __restrict__ cell_of,
+                                                        const int* __restrict__ cell_start, Grid g, float r2, int loop,
+                                                        int* __restrict__ deg, const int* __restrict__ rowptr,
+                                                        int* __restrict__ col) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  const float4 me = sorted[s];
+  const int i = __float_as_int(me.w);
+  const int c = cell_of[i];
+  const int cx = c % g.nx, cy = (c / g.nx) % g.ny, cz = (c / (g.nx * g.ny)) % g.nz, b = c / (g.nx * g.ny * g.nz);
+  int cnt = 0;
+  int* out = FILL ? col + rowptr[i] : nullptr;
+  for (int dz = -1; dz <= 1; ++dz) {
+    const int z = cz + dz;
+    if (z < 0 || z >= g.nz) continue;
+    for (int dy = -1; dy <= 1; ++dy) {
+      const int y = cy + dy;
+      if (y < 0 || y >= g.ny) continue;
+      // the three x-neighbours are contiguous in cell order: one candidate range per (z, y)
+      const int x0 = cx > 0 ? cx - 1 : 0, x1 = cx + 1 < g.nx ? cx + 1 : g.nx - 1;
+      const int base = ((b * g.nz + z) * g.ny + y) * g.nx;
+      const int q0 = cell_start[base + x0], q1 = cell_start[base + x1 + 1];
+      for (int q = q0; q < q1; ++q) {
+        const float4 o = __ldg(sorted + q);
+        const float ddx = __fsub_rn(me.x, o.x), ddy = __fsub_rn(me.y, o.y), ddz = __fsub_rn(me.z, o.z);
+        const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy)), __fmul_rn(ddz, ddz));
+        if (d2 < r2 && (loop || q != s)) {
+          if (FILL) out[cnt] = __float_as_int(o.w);
+          ++cnt;
+        }
+      }
+    }
+  }
+  if (!FILL) deg[i] = cnt;
+}
+
+__global__ void cap_kernel(const int* __restrict__ deg, int n, int cap, int* __restrict__ deg_cap) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) deg_cap[i] = min(deg[i], cap);
+}
+
+// ascending sort of every CSR row; one warp per row, bitonic network in shared memory (rows <= CAP elements)
+template <int CAP>
+__global__ void __launch_bounds__(256) rowsort_kernel(const int* __restrict__ rowptr, int n, int* __restrict__ col) {
+  __shared__ int buf[8][CAP];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + warp;
+  if (row >= n) return;
+  const int r0 = rowptr[row], len = rowptr[row + 1] - r0;
+  if (len <= 1) return;
+  if (len > CAP) return;  // sorted by rowsort_long_kernel
+  int P = 32;
+  while (P < len) P <<= 1;
+  int* b = buf[warp];
+  for (int t = lane; t < P; t += 32) b[t] = t < len ? col[r0 + t] : 0x7fffffff;
+  __syncwarp();
+  for (int k = 2; k <= P; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = lane; t < (P >> 1); t += 32) {
+        const int lo = ((t & ~(j - 1)) << 1) | (t & (j - 1));  // index with bit j cleared
+        const int hi = lo | j;
+        const bool up = (lo & k) == 0;
+        const int a = b[lo], c = b[hi];
+        if ((a > c) == up) { b[lo] = c; b[hi] = a; }
+      }
+      __syncwarp();
+    }
+  }
+  for (int t = lane; t < len; t += 32) col[r0 + t] = b[t];
+}
+
+// long rows: one CTA per row, bitonic sort in dynamic shared memory (P ints)
+__global__ void __launch_bounds__(256) rowsort_long_kernel(const int* __restrict__ rowptr, int n, int* __restrict__ col,
+                                                           int min_len, int P) {
+  extern __shared__ int lb[];
+  for (int row = blockIdx.x; row < n; row += gridDim.x) {
+    const int r0 = rowptr[row], len = rowptr[row + 1] - r0;
+    if (len <= min_len) continue;  // uniform per CTA
+    for (int t = threadIdx.x; t < P; t += blockDim.x) lb[t] = t < len ? col[r0 + t] : 0x7fffffff;
+    __syncthreads();
+    for (int k = 2; k <= P; k <<= 1) {
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        for (int t = threadIdx.x; t < (P >> 1); t += blockDim.x) {
+          const int lo = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+          const int hi = lo | j;
+          const bool up = (lo & k) == 0;
+          const int a = lb[lo], c = lb[hi];
+          if ((a > c) == up) { lb[lo] = c; lb[hi] = a; }
+        }
+        __syncthreads();
+      }
+    }
+    for (int t = threadIdx.x; t < len; t += blockDim.x) col[r0 + t] = lb[t];
+    __syncthreads();
+  }
+}
+
+// edge_index [2, E] int64: row 0 = sources, row 1 = targets; warp per target
+__global__ void emit_kernel(const int* __restrict__ rowptr_full, const int* __restrict__ rowptr_cap,
+                            const int* __restrict__ col, int n, long long E, long long* __restrict__ edge_index,
+                            int flow_target_to_source) {
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (row >= n) return;
+  const int s0 = rowptr_full[row], d0 = rowptr_cap[row], len = rowptr_cap[row + 1] - d0;
+  long long* src = edge_index + (flow_target_to_source ? E : 0);
+  long long* dst = edge_index + (flow_target_to_source ? 0 : E);
+  for (int t = lane; t < len; t += 32) {
+    src[d0 + t] = col[s0 + t];
+    dst[d0 + t] = row;
+  }
+}
+
+}  // namespace rg
+}  // namespace efl
+
+using namespace efl;
+using efl::rg::Grid;
+
+static inline unsigned nblk(long long n, int t) { return (unsigned)((n + t - 1) / t); }
+
+// box_ws: B*6 uints (scratch); box_out: B*6 floats (min xyz | max xyz per batch item), read by the host to size the grid
+extern "C" int efl_radius_graph_bbox(const float* pos, const int* batch, int N, int nbatch, void* box_ws,
+                                     float* box_out, void* stream) {
+  EFL_REQUIRE(N > 0 && nbatch > 0, "efl_radius_graph_bbox: empty input");
+  cudaStream_t s = (cudaStream_t)stream;
+  rg::bbox_init_kernel<<<nblk(nbatch * 6, 128), 128, 0, s>>>((unsigned*)box_ws, nbatch);
+  rg::bbox_kernel<<<nblk(N, 256), 256, 0, s>>>(pos, batch, N, (unsigned*)box_ws);
+  rg::bbox_decode_kernel<<<nblk(nbatch * 6, 128), 128, 0, s>>>((const unsigned*)box_ws, box_out, nbatch * 6);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+extern "C" long long efl_radius_graph_temp_bytes(long long max_items) {
+  size_t bytes = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, bytes, (const int*)nullptr, (int*)nullptr, (int)max_items);
+  return (long long)bytes;
+}
+
+// Steps 2-5.  origin [B,3] device floats; cell edge cs >= r; ncells = nbatch*nx*ny*nz.
+// Buffers (device): cell_of [N], cell_start [ncells+1], scratch [2*(ncells+1)] ints, sorted [N] float4,
+// deg [2*(N+1)] ints (full | capped), rowptr_full [N+1], rowptr_cap [N+1], temp (efl_radius_graph_temp_bytes(max(N,ncells)+1)).
+extern "C" int efl_radius_graph_count(const float* pos, const int* batch, int N, int nbatch, const float* origin,
+                                      float cs, int nx, int ny, int nz, float r, int loop, int cap, int* cell_of,
+                                      int* cell_start, int* scratch, void* sorted, int* deg, int* rowptr_full,
+                                      int* rowptr_cap, void* temp, long long temp_bytes, void* stream) {
+  EFL_REQUIRE(N > 0 && nbatch > 0 && nx > 0 && ny > 0 && nz > 0, "efl_radius_graph_count: empty input");
+  EFL_REQUIRE(cs >= r && r > 0.f, "efl_radius_graph_count: cell edge must be >= r > 0");
+  const long long ncells_ll = (long long)nbatch * nx * ny * nz;
+  EFL_REQUIRE(ncells_ll < (1ll << 30), "efl_radius_graph_count: too many cells");
+  const int ncells = (int)ncells_ll;
+  cudaStream_t s = (cudaStream_t)stream;
+  Grid g{1.0f / cs, nx, ny, nz, nbatch};
+  int* cell_count = scratch;
+  int* cursor = scratch + (ncells + 1);
+  cudaMemsetAsync(scratch, 0, sizeof(int) * 2 * (size_t)(ncells + 1), s);
+  rg::bin_kernel<<<nblk(N, 256), 256, 0, s>>>(pos, batch, N, origin, g, cell_of, cell_count);
+  size_t tb = (size_t)temp_bytes;
+  cub::DeviceScan::ExclusiveSum(temp, tb, cell_count, cell_start, ncells + 1, s);
+  rg::scatter_kernel<<<nblk(N, 256), 256, 0, s>>>(pos, N, cell_of, cell_start, cursor, (float4*)sorted);
+  int* deg_full = deg;
+  int* deg_cap = deg + (N + 1);
+  cudaMemsetAsync(deg, 0, sizeof(int) * 2 * (size_t)(N + 1), s);
+  rg::neighbour_kernel<false><<<nblk(N, 128), 128, 0, s>>>((const float4*)sorted, N, cell_of, cell_start, g,
+                                                           r * r, loop, deg_full, nullptr, nullptr);
+  rg::cap_kernel<<<nblk(N, 256), 256, 0, s>>>(deg_full, N, cap, deg_cap);
+  tb = (size_t)temp_bytes;
+  cub::DeviceScan::ExclusiveSum(temp, tb, deg_full, rowptr_full, N + 1, s);
+  tb = (size_t)temp_bytes;
+  cub::DeviceScan::ExclusiveSum(temp, tb, deg_cap, rowptr_cap, N + 1, s);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+// Steps 6-7: col [rowptr_full[N]] ints; max_deg = largest full degree (the host read it with the totals).
+extern "C" int efl_radius_graph_fill(int N, int nbatch, float cs, int nx, int ny, int nz, float r, int loop,
+                                     const int* cell_of, const int* cell_start, const void* sorted,
+                                     const int* rowptr_full, int* col, int max_deg, void* stream) {
+  EFL_REQUIRE(N > 0, "efl_radius_graph_fill: empty input");
+  cudaStream_t s = (cudaStream_t)stream;
+  Grid g{1.0f / cs, nx, ny, nz, nbatch};
+  rg::neighbour_kernel<true><<<nblk(N, 128), 128, 0, s>>>((const float4*)sorted, N, cell_of, cell_start, g,
+                                                          r * r, loop, nullptr, rowptr_full, col);
+  rg::rowsort_kernel<1024><<<nblk(N, 8), 256, 0, s>>>(rowptr_full, N, col);
+  if (max_deg > 1024) {
+    int P = 2048;
+    while (P < max_deg) P <<= 1;
+    EFL_REQUIRE(P <= 32768, "efl_radius_graph_fill: more than 32768 neighbours of one point");
+    static int smem_set = 0;
+    if (smem_set < P * 4) {
+      cudaError_t e = cudaFuncSetAttribute(rg::rowsort_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768 * 4);
+      if (e != cudaSuccess) {
+        efl_set_error(cudaGetErrorString(e));
+        return (int)e;
+      }
+      smem_set = 32768 * 4;
+    }
+    rg::rowsort_long_kernel<<<N < 1184 ? N : 1184, 256, (size_t)P * 4, s>>>(rowptr_full, N, col, 1024, P);
+  }
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+// Step 8: edge_index [2, E] int64, E = rowptr_cap[N]; flow 0 = source_to_target (row 0 sources), 1 = target_to_source
+extern "C" int efl_radius_graph_emit(const int* rowptr_full, const int* rowptr_cap, const int* col, int N, long long E,
+                                     long long* edge_index, int flow_target_to_source, void* stream) {
+  if (N <= 0 || E <= 0) return EFL_OK;
+  rg::emit_kernel<<<nblk((long long)N * 32, 256), 256, 0, (cudaStream_t)stream>>>(rowptr_full, rowptr_cap, col, N, E,
+                                                                               edge_index, flow_target_to_source);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}

@@ -12,7 +12,7 @@ cat gpurun_out/${TAG}_bench.json
 if [ "${NCU:-1}" = "1" ]; then
 CMD="python tools/edge_bench.py --profile --batch 8"
 $CMD > gpurun_out/${TAG}_plain_eb.log 2>&1 && \
-timeout 900 ncu --set full --clock-control none --import-source on -k 'regex:kernel' -f -o gpurun_out/${TAG}_edge $CMD > gpurun_out/${TAG}_ncu_edge.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k 'regex:^(tc_gemm|s2act|rotate|segment|alpha|wigner|so3|radial|colsum|splitk|edge_degree|rmsnorm|gemm_)' -c 150 -f -o gpurun_out/${TAG}_edge $CMD > gpurun_out/${TAG}_ncu_edge.log 2>&1
 echo "ncu edge exit $?"
 tail -3 gpurun_out/${TAG}_ncu_edge.log
 CMD2="python bench.py --steps 1 --warmup 1 --batch 4 --no-cpu-baseline"

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Summarise an `ncu --set full` report into a small CSV for profiles/ (one row per kernel launch, or --group to
-aggregate launches by kernel name).  Usage: python tools/ncu_summary.py in.ncu-rep out.csv [--group]"""
+aggregate launches by kernel name).  Usage: python tools/ncu_summary.py in.ncu-rep|raw.csv out.csv [--group]"""
 import csv
 import subprocess
 import sys
@@ -31,7 +31,11 @@ UNIT = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "Tbyte": 1e12,
 def main():
     src, dst = sys.argv[1], sys.argv[2]
     group = "--group" in sys.argv
-    out = subprocess.run(["ncu", "-i", src, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+    if src.endswith(".csv"):  # raw page already exported on the GPU box (ncu -i rep --page raw --csv)
+        out = open(src).read()
+    else:
+        out = subprocess.run(["ncu", "-i", src, "--page", "raw", "--csv"], capture_output=True, text=True,
+                             check=True).stdout
     rows = list(csv.reader(out.splitlines()))
     hdr, units, body = rows[0], rows[1], rows[2:]
     sel = []
