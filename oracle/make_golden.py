@@ -122,9 +122,13 @@ def random_graph(seed, n_src, n_dst, n_edges, homo):
     return torch.from_numpy(ei), torch.from_numpy(vec), torch.from_numpy(rs.uniform(size=(n_edges, 3)).astype(np.float32))
 
 
-def make_attention(ef, emb):
+def make_attention(ef, emb, lmax=6, fname="attention_small.pt"):
+    """TransBlockV2 + EdgeDegreeEmbedding of the unmodified reference on small random graphs; lmax=8 gives the
+    BASELINE.json config-5 coefficient layout (L=81, M=39)."""
     torch.manual_seed(0)
     cfg = rl.EasyDict(rl.DEFAULT_EMBEDDING_CONFIG)
+    cfg.lmax_list = [lmax]
+    L = (lmax + 1) ** 2
     model = emb.EquivariantEmbedding(cfg, device="cpu")
     syn.load_portable_parameters(model, 3)
     block = model.blocks[1]
@@ -135,20 +139,20 @@ def make_attention(ef, emb):
             rot = ef.init_edge_rot_mat(vec)
         model.SO3_rotation[0].set_wigner(rot)
         x_edge = portable_tensor((n_e, 48), seed + 100, 0.7).requires_grad_(True)
-        x_s = portable_tensor((n_s, 49, 16), seed + 200).requires_grad_(True)
-        x_d = x_s if homo else portable_tensor((n_d, 49, 16), seed + 201).requires_grad_(True)
+        x_s = portable_tensor((n_s, L, 16), seed + 200).requires_grad_(True)
+        x_d = x_s if homo else portable_tensor((n_d, L, 16), seed + 201).requires_grad_(True)
         z_s = torch.from_numpy(np.random.RandomState(seed).choice([6, 7, 8, 16], size=n_s))
         z_d = z_s if homo else torch.from_numpy(np.random.RandomState(seed + 1).choice([6, 7, 8, 16], size=n_d))
         model.zero_grad()
         if homo:
-            x = ef.SO3_Embedding(0, [6], 16, dtype=torch.float32, device="cpu")
+            x = ef.SO3_Embedding(0, [lmax], 16, dtype=torch.float32, device="cpu")
             x.set_embedding(x_s * 1.0)
             out = block(x=x, atomic_numbers=z_s, edge_distance=x_edge, edge_index=ei, batch=n_s, hetero=False)
             ede = model.edge_degree_embedding(z_s, x_edge, ei, hetero=False)
         else:
-            xs = ef.SO3_Embedding(0, [6], 16, dtype=torch.float32, device="cpu")
+            xs = ef.SO3_Embedding(0, [lmax], 16, dtype=torch.float32, device="cpu")
             xs.set_embedding(x_s * 1.0)
-            xd = ef.SO3_Embedding(0, [6], 16, dtype=torch.float32, device="cpu")
+            xd = ef.SO3_Embedding(0, [lmax], 16, dtype=torch.float32, device="cpu")
             xd.set_embedding(x_d * 1.0)
             xdict = {syn.LIGAND: xs, syn.PROTEIN: xd}
             zdict = {syn.LIGAND: z_s, syn.PROTEIN: z_d}
@@ -165,8 +169,8 @@ def make_attention(ef, emb):
             x_dst=x_d.detach().clone(), n_dst=n_d, seed=seed, block_out=out.embedding.detach().clone(),
             edge_degree_out=ede.embedding.detach().clone(), grad_x_edge=x_edge.grad.clone(),
             grad_x_src=x_s.grad.clone(), grad_x_dst=x_d.grad.clone(), param_grads=pg, loss=float(loss))
-        print("attention_small", name, "loss", float(loss))
-    torch.save(dict(param_seed=3, block="blocks.1.", cases=cases), os.path.join(GOLDEN_DIR, "attention_small.pt"))
+        print(fname, name, "loss", float(loss))
+    torch.save(dict(param_seed=3, block="blocks.1.", lmax=lmax, cases=cases), os.path.join(GOLDEN_DIR, fname))
 
 
 def make_wigner(ef, emb):
@@ -193,6 +197,7 @@ def main():
     ef, emb = rl.load_reference()
     make_wigner(ef, emb)
     make_attention(ef, emb)
+    make_attention(ef, emb, lmax=8, fname="attention_l8.pt")
     make_example(ef, emb)
 
 

@@ -40,12 +40,14 @@ def load_golden(name):
     return torch.load(os.path.join(GOLDEN, name), map_location="cpu", weights_only=False)
 
 
-def build_model(device, param_seed, precision="fp32", compute_dead_blocks=False):
+def build_model(device, param_seed, precision="fp32", compute_dead_blocks=False, lmax=6):
     from singa_b200 import ops, synthetic
     from singa_b200.embedding import DEFAULT_CONFIG, EquivariantEmbedding
     ops.set_precision(precision)
     torch.manual_seed(0)
-    model = EquivariantEmbedding(DEFAULT_CONFIG, device=device, compute_dead_blocks=compute_dead_blocks)
+    cfg = dict(DEFAULT_CONFIG)
+    cfg["lmax_list"] = [lmax]
+    model = EquivariantEmbedding(cfg, device=device, compute_dead_blocks=compute_dead_blocks)
     synthetic.load_portable_parameters(model, param_seed)
     return model
 
@@ -64,13 +66,14 @@ def oracle_tables(model=None):
     return eo.Tables(6, 2, jd, ex["to62"], ex["from62"], ex["to66"], ex["from66"])
 
 
-def run_attention_case(name: str, device="cuda:0", precision="fp32", return_all=False):
+def run_attention_case(name: str, device="cuda:0", precision="fp32", return_all=False, fixture="attention_small.pt"):
     """TransBlockV2 + EdgeDegreeEmbedding on tests/golden/attention_small.pt[name]: CUDA path vs the
     reference-generated golden.  Returns the max relative error over outputs and gradients."""
     from singa_b200 import EF_layers as ef
-    fx = load_golden("attention_small.pt")
+    fx = load_golden(fixture)
     case = fx["cases"][name]
-    model = build_model(device, fx["param_seed"], precision)
+    lmax = fx.get("lmax", 6)
+    model = build_model(device, fx["param_seed"], precision, lmax=lmax)
     block = model.blocks[1]
     dev = torch.device(device)
     ei = case["edge_index"].to(dev)
@@ -85,7 +88,7 @@ def run_attention_case(name: str, device="cuda:0", precision="fp32", return_all=
     z_d = z_s if homo else torch.from_numpy(np.random.RandomState(seed + 1).choice([6, 7, 8, 16], size=x_d.shape[0])).to(dev)
 
     def emb(t):
-        e = ef.SO3_Embedding(0, [6], 16, dtype=torch.float32, device=dev)
+        e = ef.SO3_Embedding(0, [lmax], 16, dtype=torch.float32, device=dev)
         e.set_embedding(t * 1.0)
         return e
 

@@ -198,3 +198,18 @@ def test_saved_activations_and_recompute_give_identical_gradients(precision):
     assert grads["save"].keys() == grads["recompute"].keys()
     for n in grads["save"]:
         assert torch.equal(grads["save"][n], grads["recompute"][n]), n
+
+
+@pytest.mark.parametrize("name", ["homo", "hetero"])
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_transblock_lmax8_matches_reference_golden(name, precision):
+    """BASELINE.json config 5 coefficient layout (lmax=8: L=81, M=39) against a golden written by the unmodified
+    reference (oracle/make_golden.py: attention_l8.pt)."""
+    from singa_b200 import ops
+    try:
+        errs = run_attention_case(name, DEV, precision, return_all=True, fixture="attention_l8.pt")
+    finally:
+        ops.set_precision("fp32")
+    to, tg = (TOL_OUT_FP32, TOL_GRAD_FP32) if precision == "fp32" else (TOL_OUT_BF16, TOL_GRAD_BF16)
+    bad = {k: v for k, v in errs.items() if v > (to if k in ("block_out", "edge_degree_out") else tg)}
+    assert not bad, bad
