@@ -121,22 +121,36 @@ namespace efl {
 // ------------------------------------------------------------------------------------------
 // backward.  Per-CTA partial layout (floats):
 //   dW3 [NO,16] | db3 [NO] | dW2 [16,16] | db2 | dg2 | dbe2 [16 each] | dW1 [16,K0] | db1 | dg1 | dbe1 [16 each]
+// Per tile of RT edges:
+//   A  recompute the hidden activations (half-warp per edge, lane = hidden unit)
+//   B  dW3 / db3: thread = output column, a2 row of the edge loaded once for the thread's columns
+//   C  d a2 = dout . W3: half-warp owns a chunk of columns with its W3 entries in registers and sweeps the tile's
+//      edges (4 FMAs per shared-memory load); chunk partials combined in fixed order
+//   D  LayerNorm/SiLU backward per edge; d h2, d h1 parked in shared memory; d x written
+//   E  dW2 += dh2^T a1, dW1 += dh1^T x as tile-level outer products (thread = weight element)
 // ------------------------------------------------------------------------------------------
 template <int K0>
-__global__ void __launch_bounds__(RTHREADS) radial_bwd_kernel(const float* __restrict__ x, RadialParams p, int NO,
+__global__ void __launch_bounds__(RTHREADS, 2) radial_bwd_kernel(const float* __restrict__ x, RadialParams p, int NO,
                                                               const float* __restrict__ dout, float* __restrict__ dx,
                                                               float* __restrict__ part, int E) {
   constexpr int MAXS = 3;                 // output columns per thread (NO <= 768)
-  constexpr int HWSZ = RH * (RH + K0 + 6);  // per half-warp parameter-gradient floats
+  constexpr int CWMAX = 48;               // 768 / 16
+  constexpr int NW1 = (RH * K0 + RTHREADS - 1) / RTHREADS;  // dW1 elements per thread
+  constexpr int NWARP = RTHREADS / 32;
   extern __shared__ float sm[];
-  const int SDS = NO + 4;                 // padded row pitch of the d(out) tile (breaks the 2-way bank conflict)
+  const int SDS = NO + 4;                 // padded row pitch of the d(out) tile
   float* sW1 = sm;                        // [16][K0]
   float* sW2 = sW1 + RH * K0;             // [16][16]
   float* sx = sW2 + RH * RH;              // [RT][K0]
   float* sa2 = sx + RT * K0;              // [RT][16]
   float* sa1 = sa2 + RT * RH;             // [RT][16]
-  float* sdh = sa1 + RT * RH;             // [16 half-warps][16]
-  float* sd = sdh + 16 * RH;              // [RT][SDS]  (re-used for the final reduction)
+  float* sdh = sa1 + RT * RH;             // [16 half-warps][16] exchange scratch
+  float* sdh2 = sdh + 16 * RH;            // [RT][16]
+  float* sdh1 = sdh2 + RT * RH;           // [RT][16]
+  float* spart = sdh1 + RT * RH;          // [8 warps][RT][16] chunk partials of d a2
+  float* sda2 = spart + NWARP * RT * RH;  // [RT][16]
+  float* sd = sda2 + RT * RH;             // [RT][SDS]
+  const int CW = (((NO + 15) / 16) + 3) & ~3;  // columns per half-warp chunk (multiple of 4, <= CWMAX)
   for (int i = threadIdx.x; i < RH * K0; i += RTHREADS) sW1[i] = p.W1[i];
   for (int i = threadIdx.x; i < RH * RH; i += RTHREADS) sW2[i] = p.W2[i];
   const int hw = threadIdx.x >> 4, j = threadIdx.x & 15;
@@ -148,11 +162,9 @@ __global__ void __launch_bounds__(RTHREADS) radial_bwd_kernel(const float* __res
 #pragma unroll
     for (int k = 0; k < RH; ++k) dW3[s][k] = 0.f;
   }
-  float dW2[RH], dW1[K0], db2 = 0.f, dg2 = 0.f, dbe2 = 0.f, db1 = 0.f, dg1 = 0.f, dbe1 = 0.f;
+  float dW1[NW1], dW2 = 0.f, db2 = 0.f, dg2 = 0.f, dbe2 = 0.f, db1 = 0.f, dg1 = 0.f, dbe1 = 0.f;
 #pragma unroll
-  for (int i = 0; i < RH; ++i) dW2[i] = 0.f;
-#pragma unroll
-  for (int i = 0; i < K0; ++i) dW1[i] = 0.f;
+  for (int q = 0; q < NW1; ++q) dW1[q] = 0.f;
 
   const int ntiles = (E + RT - 1) / RT;
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -166,6 +178,7 @@ __global__ void __launch_bounds__(RTHREADS) radial_bwd_kernel(const float* __res
           __ldg(reinterpret_cast<const float4*>(dout + (size_t)(e0 + el) * NO) + c4);
     }
     __syncthreads();
+    // ---- A
     Hidden hid[RT / 16];
 #pragma unroll
     for (int r = 0; r < RT / 16; ++r) {
@@ -174,46 +187,65 @@ __global__ void __launch_bounds__(RTHREADS) radial_bwd_kernel(const float* __res
       sa2[el * RH + j] = hid[r].a2;
     }
     __syncthreads();
-    // ---- last layer: dW3, db3 (thread = output column)
+    // ---- B
+    for (int el = 0; el < ne; ++el) {
+      float a[RH];
 #pragma unroll
-    for (int s = 0; s < MAXS; ++s) {
-      const int c = threadIdx.x + s * RTHREADS;
-      if (c < NO) {
-        for (int el = 0; el < ne; ++el) {
+      for (int k = 0; k < RH; k += 4) {
+        const float4 t = *reinterpret_cast<const float4*>(sa2 + el * RH + k);
+        a[k] = t.x; a[k + 1] = t.y; a[k + 2] = t.z; a[k + 3] = t.w;
+      }
+#pragma unroll
+      for (int s = 0; s < MAXS; ++s) {
+        const int c = threadIdx.x + s * RTHREADS;
+        if (c < NO) {
           const float d = sd[el * SDS + c];
           db3[s] += d;
 #pragma unroll
-          for (int k = 0; k < RH; k += 4) {
-            const float4 a = *reinterpret_cast<const float4*>(sa2 + el * RH + k);
-            dW3[s][k] = fmaf(d, a.x, dW3[s][k]);
-            dW3[s][k + 1] = fmaf(d, a.y, dW3[s][k + 1]);
-            dW3[s][k + 2] = fmaf(d, a.z, dW3[s][k + 2]);
-            dW3[s][k + 3] = fmaf(d, a.w, dW3[s][k + 3]);
-          }
+          for (int k = 0; k < RH; ++k) dW3[s][k] = fmaf(d, a[k], dW3[s][k]);
         }
       }
     }
-    // ---- hidden layers: half-warp per edge, lane = hidden unit
+    // ---- C
+    {
+      const int c0 = hw * CW;
+      float w3[CWMAX];
+#pragma unroll
+      for (int cc = 0; cc < CWMAX; ++cc)
+        w3[cc] = (cc < CW && c0 + cc < NO) ? __ldg(p.W3 + (size_t)(c0 + cc) * RH + j) : 0.f;
+      for (int el = 0; el < ne; ++el) {
+        const float* drow = sd + el * SDS + c0;
+        float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f;
+#pragma unroll
+        for (int cc = 0; cc < CWMAX; cc += 4) {
+          if (cc < CW && c0 + cc < NO) {
+            const float4 d = *reinterpret_cast<const float4*>(drow + cc);
+            t0 = fmaf(d.x, w3[cc], t0);
+            t1 = fmaf(d.y, w3[cc + 1], t1);
+            t2 = fmaf(d.z, w3[cc + 2], t2);
+            t3 = fmaf(d.w, w3[cc + 3], t3);
+          }
+        }
+        float acc = (t0 + t1) + (t2 + t3);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 16);
+        if ((threadIdx.x & 16) == 0) spart[((threadIdx.x >> 5) * RT + el) * RH + j] = acc;
+      }
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < ne * RH; t += RTHREADS) {
+      float acc = 0.f;
+#pragma unroll
+      for (int w = 0; w < NWARP; ++w) acc += spart[w * RT * RH + t];
+      sda2[t] = acc;
+    }
+    __syncthreads();
+    // ---- D
 #pragma unroll
     for (int r = 0; r < RT / 16; ++r) {
       const int el = r * 16 + hw;
       const bool ok = el < ne;
       const Hidden& h = hid[r];
-      // d a2[j] = sum_c dout[e, c] W3[c, j]
-      float da2 = 0.f;
-      {
-        const float* drow = sd + (ok ? el : 0) * SDS;
-        float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f;
-        for (int c = 0; c < NO; c += 4) {
-          const float4 d = *reinterpret_cast<const float4*>(drow + c);
-          t0 = fmaf(d.x, __ldg(p.W3 + (size_t)(c + 0) * RH + j), t0);
-          t1 = fmaf(d.y, __ldg(p.W3 + (size_t)(c + 1) * RH + j), t1);
-          t2 = fmaf(d.z, __ldg(p.W3 + (size_t)(c + 2) * RH + j), t2);
-          t3 = fmaf(d.w, __ldg(p.W3 + (size_t)(c + 3) * RH + j), t3);
-        }
-        da2 = ok ? (t0 + t1) + (t2 + t3) : 0.f;
-      }
-      // SiLU, LayerNorm 2
+      const float da2 = ok ? sda2[el * RH + j] : 0.f;
       const float dz2 = da2 * dsiluf_(h.y2);
       dg2 = fmaf(dz2, h.xh2, dg2);
       dbe2 += dz2;
@@ -222,16 +254,13 @@ __global__ void __launch_bounds__(RTHREADS) radial_bwd_kernel(const float* __res
       const float m22 = half_sum(dxh2 * h.xh2) * (1.f / RH);
       const float dh2 = h.r2 * (dxh2 - m21 - h.xh2 * m22);
       db2 += dh2;
-      const float* a1row = sa1 + el * RH;
-#pragma unroll
-      for (int i = 0; i < RH; ++i) dW2[i] = fmaf(dh2, a1row[i], dW2[i]);
+      sdh2[el * RH + j] = dh2;
       sdh[hw * RH + j] = dh2;
       __syncwarp();
       float da1 = 0.f;
 #pragma unroll
       for (int jj = 0; jj < RH; ++jj) da1 = fmaf(sdh[hw * RH + jj], sW2[jj * RH + j], da1);
       __syncwarp();
-      // SiLU, LayerNorm 1
       const float dz1 = da1 * dsiluf_(h.y1);
       dg1 = fmaf(dz1, h.xh1, dg1);
       dbe1 += dz1;
@@ -240,9 +269,7 @@ __global__ void __launch_bounds__(RTHREADS) radial_bwd_kernel(const float* __res
       const float m12 = half_sum(dxh1 * h.xh1) * (1.f / RH);
       const float dh1 = h.r1 * (dxh1 - m11 - h.xh1 * m12);
       db1 += dh1;
-      const float* xrow = sx + (ok ? el : 0) * K0;
-#pragma unroll
-      for (int i = 0; i < K0; ++i) dW1[i] = fmaf(dh1, xrow[i], dW1[i]);
+      sdh1[el * RH + j] = dh1;
       sdh[hw * RH + j] = dh1;
       __syncwarp();
 #pragma unroll
@@ -254,6 +281,24 @@ __global__ void __launch_bounds__(RTHREADS) radial_bwd_kernel(const float* __res
         if (ok) dx[(size_t)(e0 + el) * K0 + i] = acc;
       }
       __syncwarp();
+    }
+    __syncthreads();
+    // ---- E  (rows el >= ne of sdh2/sdh1 hold zeros: d a2 = 0 there)
+    {
+      const int jj = threadIdx.x >> 4, i = threadIdx.x & 15;
+      float acc = 0.f;
+      for (int el = 0; el < RT; ++el) acc = fmaf(sdh2[el * RH + jj], sa1[el * RH + i], acc);
+      dW2 += acc;
+    }
+#pragma unroll
+    for (int q = 0; q < NW1; ++q) {
+      const int idx = threadIdx.x + q * RTHREADS;
+      if (idx < RH * K0) {
+        const int jj = idx / K0, i = idx % K0;
+        float acc = 0.f;
+        for (int el = 0; el < ne; ++el) acc = fmaf(sdh1[el * RH + jj], sx[el * K0 + i], acc);
+        dW1[q] += acc;
+      }
     }
   }
   // ---- per-CTA partials
@@ -269,30 +314,31 @@ __global__ void __launch_bounds__(RTHREADS) radial_bwd_kernel(const float* __res
       my[(size_t)NO * RH + c] = db3[s];
     }
   }
-  __syncthreads();
-  // half-warp accumulators -> shared [16 hw][HWSZ] -> fixed-order sum over the 16 half-warps
-  float* red = sd;
-  {
-    float* m = red + hw * HWSZ;
-#pragma unroll
-    for (int i = 0; i < RH; ++i) m[j * RH + i] = dW2[i];
-    m[RH * RH + j] = db2;
-    m[RH * RH + RH + j] = dg2;
-    m[RH * RH + 2 * RH + j] = dbe2;
-    float* m1 = m + RH * RH + 3 * RH;
-#pragma unroll
-    for (int i = 0; i < K0; ++i) m1[j * K0 + i] = dW1[i];
-    m1[RH * K0 + j] = db1;
-    m1[RH * K0 + RH + j] = dg1;
-    m1[RH * K0 + 2 * RH + j] = dbe1;
-  }
-  __syncthreads();
   float* tail = my + (size_t)NO * (RH + 1);
-  for (int i = threadIdx.x; i < HWSZ; i += RTHREADS) {
+  tail[threadIdx.x] = dW2;                       // [16][16], thread = jj*16 + i
+  float* t1 = tail + RH * RH + 3 * RH;
+#pragma unroll
+  for (int q = 0; q < NW1; ++q) {
+    const int idx = threadIdx.x + q * RTHREADS;
+    if (idx < RH * K0) t1[idx] = dW1[q];
+  }
+  // the six 16-vectors: half-warp accumulators -> shared [16 hw][6][16] -> fixed-order sum
+  __syncthreads();
+  float* red = sd;
+  red[(hw * 6 + 0) * RH + j] = db2;
+  red[(hw * 6 + 1) * RH + j] = dg2;
+  red[(hw * 6 + 2) * RH + j] = dbe2;
+  red[(hw * 6 + 3) * RH + j] = db1;
+  red[(hw * 6 + 4) * RH + j] = dg1;
+  red[(hw * 6 + 5) * RH + j] = dbe1;
+  __syncthreads();
+  if (threadIdx.x < 6 * RH) {
     float acc = 0.f;
 #pragma unroll
-    for (int k = 0; k < 16; ++k) acc += red[k * HWSZ + i];
-    tail[i] = acc;
+    for (int k = 0; k < 16; ++k) acc += red[k * 6 * RH + threadIdx.x];
+    const int v = threadIdx.x / RH, jj = threadIdx.x % RH;
+    float* dst = v < 3 ? tail + RH * RH + v * RH : t1 + RH * K0 + (v - 3) * RH;
+    dst[jj] = acc;
   }
 }
 
@@ -303,9 +349,8 @@ using namespace efl;
 static size_t radial_fwd_smem(int K0) { return sizeof(float) * (RH * K0 + RH * RH + RT * K0 + RT * RH + 16 * RH); }
 static size_t radial_bwd_smem(int K0, int NO) {
   size_t sd = (size_t)RT * (NO + 4);
-  const size_t red = (size_t)16 * RH * (RH + K0 + 6);
-  if (red > sd) sd = red;
-  return sizeof(float) * (RH * K0 + RH * RH + RT * K0 + 2 * RT * RH + 16 * RH + sd);
+  if (sd < 16 * 6 * RH) sd = 16 * 6 * RH;
+  return sizeof(float) * (RH * K0 + RH * RH + RT * K0 + 4 * RT * RH + 16 * RH + (RTHREADS / 32 + 1) * RT * RH + sd);
 }
 
 extern "C" int efl_radial_mlp_part_size(int K0, int NO) { return NO * (RH + 1) + RH * RH + 3 * RH + RH * K0 + 3 * RH; }
