@@ -52,6 +52,14 @@ int efl_rotate_in_bwd(int lmax, int mmax, int C, int bf16_in, const float* x_src
                       const int* src, const int* dst, const int* perm, const float* wig, const float* rad,
                       int rad_ld, const void* da0, const void* da1, const void* da2, float* drad, float* dxe,
                       int e0, int Ec, void* stream);
+/* Node-owned variant: one warp per node sums d x over its edges in registers (fixed order) and writes
+ * dx_out [N,L,C] once; the per-edge d x tensor never exists.  side 0 = destination half: seg_ptr = CSR rowptr,
+ * seg_idx NULL, nodes [n0,n1) of the chunk.  side 1 = source half: seg_ptr/seg_idx = source grouping (sorted
+ * positions, ascending per source), all source nodes, accumulate = 1 from the second chunk on.  drad as above. */
+int efl_rotate_in_bwd_nodes(int lmax, int mmax, int C, int bf16_in, int side, const float* x_node,
+                            const int* seg_ptr, const int* seg_idx, const int* perm, const float* wig,
+                            const float* rad, int rad_ld, const void* da0, const void* da1, const void* da2,
+                            float* drad, float* dx_out, int e0, int Ec, int n0, int n1, int accumulate, void* stream);
 /* Deterministic backward of the gather (:326-328): out[n,i,c] = sum_{k in [ptr[n],ptr[n+1])}
  * buf[idx?idx[k]:k, i, coff+c]; buf rows are L*ldc floats. */
 int efl_segment_sum_rows(const float* buf, int L, int ldc, int coff, int C, const int* ptr, const int* idx,

@@ -22,6 +22,7 @@ SIGNATURES = {
     "efl_wigner_from_rotmat": "iipppip",
     "efl_rotate_in_fwd": "iiiipppppppipppiip",
     "efl_rotate_in_bwd": "iiiipppppppippppp" "iip",
+    "efl_rotate_in_bwd_nodes": "iiiiipppppp" "ipppppiiiiip",
     "efl_segment_sum_rows": "piiiipppiip",
     "efl_rotate_back_aggregate_fwd": "iiiiipppppppp" "iiip",
     "efl_rotate_back_aggregate_bwd": "iiiiipppppppppppp" "liiip",

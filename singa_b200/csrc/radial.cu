@@ -32,12 +32,12 @@ struct RadialParams {
 struct Hidden {
   float h1, xh1, r1, y1, a1, h2, xh2, r2, y2, a2;
 };
-__device__ __forceinline__ Hidden radial_hidden(const float* __restrict__ xs, int K0, const float* __restrict__ sW1,
-                                                const float* __restrict__ sW2, const RadialParams& p, int j,
+__device__ __forceinline__ Hidden radial_hidden(const float* __restrict__ xs, int K0, const float* __restrict__ sW1t,
+                                                const float* __restrict__ sW2t, const RadialParams& p, int j,
                                                 float* __restrict__ a1s /* [16] shared scratch of this half-warp */) {
   Hidden h;
   float acc = __ldg(p.b1 + j);
-  for (int i = 0; i < K0; ++i) acc = fmaf(xs[i], sW1[j * K0 + i], acc);
+  for (int i = 0; i < K0; ++i) acc = fmaf(xs[i], sW1t[i * RH + j], acc);  // [K0][16]: conflict-free
   h.h1 = acc;
   const float m1 = half_sum(acc) * (1.f / RH);
   const float d1 = acc - m1;
@@ -49,7 +49,7 @@ __device__ __forceinline__ Hidden radial_hidden(const float* __restrict__ xs, in
   __syncwarp();
   float acc2 = __ldg(p.b2 + j);
 #pragma unroll
-  for (int i = 0; i < RH; ++i) acc2 = fmaf(a1s[i], sW2[j * RH + i], acc2);
+  for (int i = 0; i < RH; ++i) acc2 = fmaf(a1s[i], sW2t[i * RH + j], acc2);
   h.h2 = acc2;
   const float m2 = half_sum(acc2) * (1.f / RH);
   const float d2 = acc2 - m2;
@@ -67,13 +67,13 @@ __device__ __forceinline__ Hidden radial_hidden(const float* __restrict__ xs, in
 __global__ void __launch_bounds__(RTHREADS) radial_fwd_kernel(const float* __restrict__ x, int K0, RadialParams p,
                                                               int NO, float* __restrict__ out, int E) {
   extern __shared__ float sm[];
-  float* sW1 = sm;                    // [16][K0]
-  float* sW2 = sW1 + RH * K0;         // [16][16]
+  float* sW1 = sm;                    // [K0][16]  (transposed: lane = hidden unit reads consecutive banks)
+  float* sW2 = sW1 + RH * K0;         // [16][16]  (transposed)
   float* sx = sW2 + RH * RH;          // [RT][K0]
   float* sa2 = sx + RT * K0;          // [RT][16]
   float* sa1 = sa2 + RT * RH;         // [16 half-warps][16]
-  for (int i = threadIdx.x; i < RH * K0; i += RTHREADS) sW1[i] = p.W1[i];
-  for (int i = threadIdx.x; i < RH * RH; i += RTHREADS) sW2[i] = p.W2[i];
+  for (int i = threadIdx.x; i < RH * K0; i += RTHREADS) sW1[(i % K0) * RH + i / K0] = p.W1[i];
+  for (int i = threadIdx.x; i < RH * RH; i += RTHREADS) sW2[(i % RH) * RH + i / RH] = p.W2[i];
   const int hw = threadIdx.x >> 4, j = threadIdx.x & 15;
   const int ntiles = (E + RT - 1) / RT;
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(RTHREADS) radial_fwd_kernel(const float* __res
     for (int r = 0; r < RT / 16; ++r) {
       const int el = r * 16 + hw;
       const bool ok = el < ne;
-      const Hidden h = radial_hidden(sx + (ok ? el : 0) * K0, K0, sW1, sW2, p, j, sa1 + hw * RH);
+      const Hidden h = radial_hidden(sx + (ok ? el : 0) * K0, K0, sW1, sW2, p, j, sa1 + hw * RH);  // sW1/sW2 hold the transposes here
       sa2[el * RH + j] = h.a2;
     }
     __syncthreads();
@@ -147,12 +147,22 @@ __global__ void __launch_bounds__(RTHREADS, 2) radial_bwd_kernel(const float* __
   float* sdh = sa1 + RT * RH;             // [16 half-warps][16] exchange scratch
   float* sdh2 = sdh + 16 * RH;            // [RT][16]
   float* sdh1 = sdh2 + RT * RH;           // [RT][16]
-  float* spart = sdh1 + RT * RH;          // [8 warps][RT][16] chunk partials of d a2
-  float* sda2 = spart + NWARP * RT * RH;  // [RT][16]
-  float* sd = sda2 + RT * RH;             // [RT][SDS]
+  float* spart = sdh1 + RT * RH;          // [8 warps][RT/2][16] chunk partials of d a2
+  float* sda2 = spart + NWARP * (RT / 2) * RH;  // [RT][16]
+  float* sW1t = sda2 + RT * RH;           // [K0][16] transposed copies for the forward recompute
+  float* sW2t = sW1t + RH * K0;           // [16][16]
+  float* sd = sW2t + RH * RH;             // [RT][SDS]
   const int CW = (((NO + 15) / 16) + 3) & ~3;  // columns per half-warp chunk (multiple of 4, <= CWMAX)
-  for (int i = threadIdx.x; i < RH * K0; i += RTHREADS) sW1[i] = p.W1[i];
-  for (int i = threadIdx.x; i < RH * RH; i += RTHREADS) sW2[i] = p.W2[i];
+  for (int i = threadIdx.x; i < RH * K0; i += RTHREADS) {
+    const float v = p.W1[i];
+    sW1[i] = v;
+    sW1t[(i % K0) * RH + i / K0] = v;
+  }
+  for (int i = threadIdx.x; i < RH * RH; i += RTHREADS) {
+    const float v = p.W2[i];
+    sW2[i] = v;
+    sW2t[(i % RH) * RH + i / RH] = v;
+  }
   const int hw = threadIdx.x >> 4, j = threadIdx.x & 15;
   const float g1 = __ldg(p.g1 + j), g2 = __ldg(p.g2 + j);
   float dW3[MAXS][RH], db3[MAXS];
@@ -183,7 +193,7 @@ __global__ void __launch_bounds__(RTHREADS, 2) radial_bwd_kernel(const float* __
 #pragma unroll
     for (int r = 0; r < RT / 16; ++r) {
       const int el = r * 16 + hw;
-      hid[r] = radial_hidden(sx + (el < ne ? el : 0) * K0, K0, sW1, sW2, p, j, sa1 + el * RH);
+      hid[r] = radial_hidden(sx + (el < ne ? el : 0) * K0, K0, sW1t, sW2t, p, j, sa1 + el * RH);
       sa2[el * RH + j] = hid[r].a2;
     }
     __syncthreads();
@@ -213,32 +223,36 @@ __global__ void __launch_bounds__(RTHREADS, 2) radial_bwd_kernel(const float* __
 #pragma unroll
       for (int cc = 0; cc < CWMAX; ++cc)
         w3[cc] = (cc < CW && c0 + cc < NO) ? __ldg(p.W3 + (size_t)(c0 + cc) * RH + j) : 0.f;
-      for (int el = 0; el < ne; ++el) {
-        const float* drow = sd + el * SDS + c0;
-        float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f;
+      // two sub-batches of RT/2 edges share one [8 warps][RT/2][16] partial buffer
+      for (int sb = 0; sb < 2; ++sb) {
+        const int el0 = sb * (RT / 2), el1 = min(ne, el0 + RT / 2);
+        for (int el = el0; el < el1; ++el) {
+          const float* drow = sd + el * SDS + c0;
+          float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f;
 #pragma unroll
-        for (int cc = 0; cc < CWMAX; cc += 4) {
-          if (cc < CW && c0 + cc < NO) {
-            const float4 d = *reinterpret_cast<const float4*>(drow + cc);
-            t0 = fmaf(d.x, w3[cc], t0);
-            t1 = fmaf(d.y, w3[cc + 1], t1);
-            t2 = fmaf(d.z, w3[cc + 2], t2);
-            t3 = fmaf(d.w, w3[cc + 3], t3);
+          for (int cc = 0; cc < CWMAX; cc += 4) {
+            if (cc < CW && c0 + cc < NO) {
+              const float4 d = *reinterpret_cast<const float4*>(drow + cc);
+              t0 = fmaf(d.x, w3[cc], t0);
+              t1 = fmaf(d.y, w3[cc + 1], t1);
+              t2 = fmaf(d.z, w3[cc + 2], t2);
+              t3 = fmaf(d.w, w3[cc + 3], t3);
+            }
           }
+          float acc = (t0 + t1) + (t2 + t3);
+          acc += __shfl_xor_sync(0xffffffffu, acc, 16);
+          if ((threadIdx.x & 16) == 0) spart[((threadIdx.x >> 5) * (RT / 2) + (el - el0)) * RH + j] = acc;
         }
-        float acc = (t0 + t1) + (t2 + t3);
-        acc += __shfl_xor_sync(0xffffffffu, acc, 16);
-        if ((threadIdx.x & 16) == 0) spart[((threadIdx.x >> 5) * RT + el) * RH + j] = acc;
+        __syncthreads();
+        for (int t = threadIdx.x; t < (el1 - el0) * RH; t += RTHREADS) {
+          float acc = 0.f;
+#pragma unroll
+          for (int w = 0; w < NWARP; ++w) acc += spart[w * (RT / 2) * RH + t];
+          sda2[el0 * RH + t] = acc;
+        }
+        __syncthreads();
       }
     }
-    __syncthreads();
-    for (int t = threadIdx.x; t < ne * RH; t += RTHREADS) {
-      float acc = 0.f;
-#pragma unroll
-      for (int w = 0; w < NWARP; ++w) acc += spart[w * RT * RH + t];
-      sda2[t] = acc;
-    }
-    __syncthreads();
     // ---- D
 #pragma unroll
     for (int r = 0; r < RT / 16; ++r) {
@@ -350,7 +364,7 @@ static size_t radial_fwd_smem(int K0) { return sizeof(float) * (RH * K0 + RH * R
 static size_t radial_bwd_smem(int K0, int NO) {
   size_t sd = (size_t)RT * (NO + 4);
   if (sd < 16 * 6 * RH) sd = 16 * 6 * RH;
-  return sizeof(float) * (RH * K0 + RH * RH + RT * K0 + 4 * RT * RH + 16 * RH + (RTHREADS / 32 + 1) * RT * RH + sd);
+  return sizeof(float) * (2 * (RH * K0 + RH * RH) + RT * K0 + 4 * RT * RH + 16 * RH + (RTHREADS / 64 + 1) * RT * RH + sd);
 }
 
 extern "C" int efl_radial_mlp_part_size(int K0, int NO) { return NO * (RH + 1) + RH * RH + 3 * RH + RH * K0 + 3 * RH; }

@@ -142,6 +142,107 @@ __global__ void __launch_bounds__(128) rotate_in_bwd_kernel(
   for (int i = 0; i < T::L; ++i) o[i * CH] = dx[i];
 }
 
+// ------------------------------------------------------------------------------------------
+// rotate-in backward, node-owned: one warp per node (destination side: edges of its CSR row; source side: its edges
+// in the source grouping that fall into the chunk), the two half-warps take alternate edges, lane & 15 = channel of
+// that side's half of the src||dst concat.  d x of the node accumulates in registers over its edges in a fixed
+// order (deterministic, no atomics) and is written once: the per-edge [E, L, 2C] gradient tensor of the gather
+// never exists (it cost 6.3 KB/edge written + read back).  x of the node (needed for d rad) is loaded once per node
+// instead of once per edge.
+// ------------------------------------------------------------------------------------------
+template <int LMAX, int MMAX, int C, typename TIn>
+__global__ void __launch_bounds__(128, 4) rotate_in_bwd_node_kernel(
+    const float* __restrict__ x_node, const int* __restrict__ seg_ptr, const int* __restrict__ seg_idx,
+    const int* __restrict__ perm, const float* __restrict__ wig, const float* __restrict__ rad, int rad_ld,
+    OpBufs<LMAX> dA, float* __restrict__ drad, float* __restrict__ dx_out, int coff, int e0, int Ec, int n0, int n1,
+    int accumulate) {
+  using T = Tab<LMAX, MMAX>;
+  static_assert(C == 16, "half-warp = channels of one side");
+  static_assert(T::WSZ % 4 == 0, "Wigner rows are 16-byte padded");
+  constexpr int CH = 2 * C;
+  __shared__ __align__(16) float sW[4][2][T::WSZ];
+  __shared__ float sX[4][T::L][C];  // x of the warp's node (only d rad needs it): shared memory, not registers
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int half = lane >> 4, c = lane & 15;
+  const int n = n0 + blockIdx.x * 4 + warp;
+  if (n >= n1) return;
+  int lo = seg_ptr[n], hi = seg_ptr[n + 1];
+  if (seg_idx) {  // source grouping spans all chunks: keep the positions inside [e0, e0 + Ec)
+    int a = lo, b = hi;
+    while (a < b) { const int m = (a + b) >> 1; if (seg_idx[m] < e0) a = m + 1; else b = m; }
+    const int first = a;
+    b = hi;
+    while (a < b) { const int m = (a + b) >> 1; if (seg_idx[m] < e0 + Ec) a = m + 1; else b = m; }
+    lo = first; hi = a;
+  }
+  float* o = dx_out + (size_t)n * T::L * C + c;
+  if (lo >= hi) {
+    if (!accumulate && half == 0) {
+#pragma unroll
+      for (int i = 0; i < T::L; ++i) o[i * C] = 0.f;
+    }
+    return;
+  }
+  float dx[T::L];
+#pragma unroll
+  for (int i = 0; i < T::L; ++i) dx[i] = 0.f;
+  if (rad) {
+    const float* xp = x_node + (size_t)n * T::L * C;
+    for (int i = lane; i < T::L * C; i += 32) (&sX[warp][0][0])[i] = __ldg(xp + i);
+  }
+  const float* x = &sX[warp][0][c];
+  float* sw = sW[warp][half];
+  for (int it = lo; it < hi; it += 2) {
+    const int k = it + half;
+    const bool act = k < hi;
+    const int pos = act ? (seg_idx ? seg_idx[k] : k) : 0;
+    const int el = pos - e0;
+    const int eo = act ? perm[pos] : 0;
+    __syncwarp();
+    if (act) {
+      const float4* w4 = reinterpret_cast<const float4*>(wig + (size_t)eo * T::WSZ);
+      for (int i = c; i < T::WSZ / 4; i += 16) reinterpret_cast<float4*>(sw)[i] = __ldg(w4 + i);
+    }
+    __syncwarp();
+    if (!act) continue;
+    const float* rd = rad ? rad + (size_t)eo * rad_ld : nullptr;
+    float* drd = rad ? drad + (size_t)eo * rad_ld : nullptr;
+#pragma unroll
+    for (int l = 0; l <= LMAX; ++l) {
+#pragma unroll
+      for (int am = 0; am <= T::mm(l); ++am) {
+        int roff = 0;
+#pragma unroll
+        for (int q = 0; q < am; ++q) roff += (LMAX + 1 - q) * CH;
+        const int rcol = roff + (l - am) * CH + coff + c;
+        const float rv = rd ? __ldg(rd + rcol) : 1.f;
+        float dr = 0.f;
+#pragma unroll
+        for (int sgn = 0; sgn < (am == 0 ? 1 : 2); ++sgn) {
+          const int mp = sgn == 0 ? am : -am;
+          const float* wr = sw + T::wrow(l, mp);
+          const float da = to_f<TIn>(*op_ptr<LMAX, TIn>(dA.p, el, l, mp, CH, coff + c));
+          if (rd) {
+            float xr = 0.f;
+#pragma unroll
+            for (int q = 0; q < 2 * l + 1; ++q) xr = fmaf(wr[q], x[(l * l + q) * C], xr);
+            dr = fmaf(da, xr, dr);
+          }
+          const float dxr = da * rv;
+#pragma unroll
+          for (int q = 0; q < 2 * l + 1; ++q) dx[l * l + q] = fmaf(wr[q], dxr, dx[l * l + q]);
+        }
+        if (rd) drd[rcol] = dr;
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < T::L; ++i) {
+    const float v = dx[i] + __shfl_xor_sync(0xffffffffu, dx[i], 16);
+    if (half == 0) o[i * C] = accumulate ? (o[i * C] + v) : v;
+  }
+}
+
 // out[n, i, c] = sum_{k in [ptr[n], ptr[n+1])} buf[idx ? idx[k] : k, i, coff + c]
 __global__ void segment_sum_rows_kernel(const float* __restrict__ buf, int row_elems /* L*ldc */, int ldc, int coff,
                                         int C, int L, const int* __restrict__ ptr, const int* __restrict__ idx,
@@ -656,6 +757,35 @@ extern "C" int efl_rotate_in_bwd(int lmax, int mmax, int C, int bf16_in, const f
     else                                                                                                       \
       rotate_in_bwd_kernel<LM, MM, 16, float><<<grid, block, 0, s>>>(x_src, x_dst, src, dst, perm, wig, rad,   \
                                                                      rad_ld, o, drad, dxe, e0, Ec);            \
+  }
+  DISPATCH_LM(lmax, mmax, CALL)
+#undef CALL
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+// Node-owned backward of rotate-in.  side 0: destination half (seg_ptr = CSR rowptr, seg_idx NULL, nodes [n0, n1) of
+// the chunk); side 1: source half (seg_ptr/seg_idx = source grouping, all source nodes, accumulate over chunks).
+extern "C" int efl_rotate_in_bwd_nodes(int lmax, int mmax, int C, int bf16_in, int side, const float* x_node,
+                                       const int* seg_ptr, const int* seg_idx, const int* perm, const float* wig,
+                                       const float* rad, int rad_ld, const void* da0, const void* da1,
+                                       const void* da2, float* drad, float* dx_out, int e0, int Ec, int n0, int n1,
+                                       int accumulate, void* stream) {
+  if (n1 <= n0) return EFL_OK;
+  EFL_REQUIRE(C == 16, "efl_rotate_in_bwd_nodes: sphere_channels must be 16");
+  EFL_REQUIRE(side == 0 || seg_idx != nullptr, "efl_rotate_in_bwd_nodes: the source side needs the source grouping");
+  cudaStream_t s = (cudaStream_t)stream;
+  dim3 grid((n1 - n0 + 3) / 4), block(128);
+  const int coff = side == 0 ? C : 0;
+#define CALL(LM, MM)                                                                                             \
+  {                                                                                                              \
+    OpBufs<LM> o{{(void*)da0, (void*)da1, (void*)da2}};                                                          \
+    if (bf16_in)                                                                                                 \
+      rotate_in_bwd_node_kernel<LM, MM, 16, __nv_bfloat16><<<grid, block, 0, s>>>(                              \
+          x_node, seg_ptr, seg_idx, perm, wig, rad, rad_ld, o, drad, dx_out, coff, e0, Ec, n0, n1, accumulate);  \
+    else                                                                                                         \
+      rotate_in_bwd_node_kernel<LM, MM, 16, float><<<grid, block, 0, s>>>(                                      \
+          x_node, seg_ptr, seg_idx, perm, wig, rad, rad_ld, o, drad, dx_out, coff, e0, Ec, n0, n1, accumulate);  \
   }
   DISPATCH_LM(lmax, mmax, CALL)
 #undef CALL

@@ -425,8 +425,9 @@ class EdgeAttentionFunction(torch.autograd.Function):
         g_c1wm = [f32(*c1w1.shape), f32(*c1w2.shape)]       # interleaved row order until the end
         g_c2w0, g_c2b0 = f32(*c2w0.shape), f32(*c2b0.shape)
         g_c2wm = [f32(*c2w1.shape), f32(*c2w2.shape)]
-        drad = torch.zeros_like(rad)
-        dxe = torch.empty(max(E, 1), L, C2, dtype=torch.float32, device=dev)
+        drad = torch.empty_like(rad)   # every column of every edge is written by the rotate-in backward
+        dx_dst = torch.zeros_like(x_dst)
+        dx_src = torch.zeros_like(x_src)
         nparts = LIB.efl_rotate_back_parts(d.lmax, d.mmax)
         dalpha = torch.empty(nparts, max(E, 1), d.heads, dtype=torch.float32, device=dev)
         dlogits = torch.empty(max(E, 1), d.heads, dtype=torch.float32, device=dev)
@@ -494,19 +495,16 @@ class EdgeAttentionFunction(torch.autograd.Function):
                 _gemm_tn(ws.dY1[m], ws.A[m], g_c1wm[m - 1], acc, 2 * Ec, 2 * d.ms[m] * H, d.ms[m] * C2)
                 _gemm_nt(0, ws.dY1[m], w1.wmt[m - 1], None, ws.dA[m], d.ms[m] * C2, None, 0, 0, 2 * Ec,
                          d.ms[m] * C2, 2 * d.ms[m] * H)
-            # ---- rotate-in backward -> d rad, per-edge d x
-            call("efl_rotate_in_bwd", d.lmax, d.mmax, d.C, bf16, ptr(x_src), ptr(x_dst), ptr(csr.src_sorted),
-                 ptr(csr.dst_sorted), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.dA[0]), ptr(ws.dA[1]),
-                 ptr(ws.dA[2]), ptr(drad), ptr(dxe), e0, Ec,
-                 work=Ec * (_bytes_rotate_in(d, ws.dA[0].element_size(), wig.shape[1]) + d.M * C2 * 4 + L * C2 * 4))
+            # ---- rotate-in backward -> d rad and d x, node-owned (no per-edge gradient tensor)
+            wrk = Ec * (_bytes_rotate_in(d, ws.dA[0].element_size(), wig.shape[1]) + d.M * C2 * 4) / 2
+            call("efl_rotate_in_bwd_nodes", d.lmax, d.mmax, d.C, bf16, 0, ptr(x_dst), ptr(csr.rowptr), None,
+                 ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.dA[0]), ptr(ws.dA[1]), ptr(ws.dA[2]),
+                 ptr(drad), ptr(dx_dst), e0, Ec, n0, n1, 0, work=wrk, tag="efl_rotate_in_bwd_dst")
+            call("efl_rotate_in_bwd_nodes", d.lmax, d.mmax, d.C, bf16, 1, ptr(x_src), ptr(csr.src_ptr),
+                 ptr(csr.src_idx), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.dA[0]), ptr(ws.dA[1]),
+                 ptr(ws.dA[2]), ptr(drad), ptr(dx_src), e0, Ec, 0, csr.num_src, 1, work=wrk,
+                 tag="efl_rotate_in_bwd_src")
             first = False
-        # ---- gather backward: deterministic segment sums over the dst CSR and the src grouping
-        dx_dst = torch.empty_like(x_dst)
-        dx_src = torch.empty_like(x_src)
-        call("efl_segment_sum_rows", ptr(dxe), L, C2, d.C, d.C, ptr(csr.rowptr), None, ptr(dx_dst), csr.num_dst, 0,
-             work=(E + csr.num_dst) * L * d.C * 4.0)
-        call("efl_segment_sum_rows", ptr(dxe), L, C2, 0, d.C, ptr(csr.src_ptr), ptr(csr.src_idx), ptr(dx_src),
-             csr.num_src, 0, work=(E + csr.num_src) * L * d.C * 4.0 + E * 4.0)
         ha = d.heads * d.alpha_ch
         g_adot = part_all[:ha].view(d.heads, d.alpha_ch)
         g_lnw = part_all[ha:ha + d.alpha_ch]
