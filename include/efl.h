@@ -213,6 +213,18 @@ int efl_radius_graph_fill(int N, int nbatch, float cs, int nx, int ny, int nz, f
 int efl_radius_graph_emit(const int* rowptr_full, const int* rowptr_cap, const int* col, int N, long long E,
                           long long* edge_index, int flow_target_to_source, void* stream);
 
+/* bf16 mode split of the same MLP: the hidden layers stay SIMT kernels, the 16 -> NO layer and its backward run as
+ * K=16 / N=16 GEMMs of efl_tc_gemm_nt / efl_tc_gemm_tn.  hidden_fwd: x -> a2 [E,16] bf16 (input of the last Linear).
+ * hidden_bwd: d a2 [E,16] fp32 -> dx [E,K0] and part [nblocks, efl_radial_hidden_part_size(K0)]:
+ *   dW2 [16,16] | db2 | dg2 | dbeta2 | dW1 [16,K0] | db1 | dg1 | dbeta1. */
+int efl_radial_hidden_part_size(int K0);
+int efl_radial_hidden_fwd(const float* x, int K0, const float* W1, const float* b1, const float* g1, const float* be1,
+                          const float* W2, const float* b2, const float* g2, const float* be2, void* a2_out, int E,
+                          void* stream);
+int efl_radial_hidden_bwd(const float* x, int K0, const float* W1, const float* b1, const float* g1, const float* be1,
+                          const float* W2, const float* b2, const float* g2, const float* be2, const float* da2,
+                          float* dx, float* part, int nblocks, int E, void* stream);
+
 /* EquivariantRMSNormArraySphericalHarmonicsV2 as built by get_normalization_layer (:2099-2192, :2254-2273):
  * centred l=0, degree-balanced RMS, per-degree gain gamma [lmax+1,16], bias beta [16] on l=0.  One warp per node.
  * bwd writes per-block partials of (d gamma | d beta) into part [nblocks, (lmax+2)*16]. */

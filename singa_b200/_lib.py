@@ -48,6 +48,8 @@ SIGNATURES = {
     "efl_so3_select": "plppliip",
     "efl_radial_mlp_fwd": "pi" + "p" * 10 + "ipip",
     "efl_radial_mlp_bwd": "pi" + "p" * 10 + "ipppiip",
+    "efl_radial_hidden_fwd": "pi" + "p" * 8 + "pip",
+    "efl_radial_hidden_bwd": "pi" + "p" * 8 + "pppiip",
     "efl_radius_graph_bbox": "ppiippp",
     "efl_radius_graph_count": "ppiipfiiifiippppppppl" "p",
     "efl_radius_graph_fill": "iifiiifippppp" "ip",
@@ -79,6 +81,8 @@ def _load():
     lib.efl_tc_gemm_tn_splits.restype = _I
     lib.efl_radial_mlp_part_size.argtypes = [_I, _I]
     lib.efl_radial_mlp_part_size.restype = _I
+    lib.efl_radial_hidden_part_size.argtypes = [_I]
+    lib.efl_radial_hidden_part_size.restype = _I
     lib.efl_radius_graph_temp_bytes.argtypes = [_L]
     lib.efl_radius_graph_temp_bytes.restype = _L
     lib.efl_rotate_back_parts.argtypes = [_I, _I]

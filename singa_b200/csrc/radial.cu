@@ -64,8 +64,10 @@ __device__ __forceinline__ Hidden radial_hidden(const float* __restrict__ xs, in
 // ------------------------------------------------------------------------------------------
 // forward
 // ------------------------------------------------------------------------------------------
+// a2_out != nullptr: hidden layers only, a2 written as bf16 [E,16] (the last layer then runs as a K=16 tcgen05 GEMM)
 __global__ void __launch_bounds__(RTHREADS) radial_fwd_kernel(const float* __restrict__ x, int K0, RadialParams p,
-                                                              int NO, float* __restrict__ out, int E) {
+                                                              int NO, float* __restrict__ out,
+                                                              __nv_bfloat16* __restrict__ a2_out, int E) {
   extern __shared__ float sm[];
   float* sW1 = sm;                    // [K0][16]  (transposed: lane = hidden unit reads consecutive banks)
   float* sW2 = sW1 + RH * K0;         // [16][16]  (transposed)
@@ -87,7 +89,9 @@ __global__ void __launch_bounds__(RTHREADS) radial_fwd_kernel(const float* __res
       const bool ok = el < ne;
       const Hidden h = radial_hidden(sx + (ok ? el : 0) * K0, K0, sW1, sW2, p, j, sa1 + hw * RH);  // sW1/sW2 hold the transposes here
       sa2[el * RH + j] = h.a2;
+      if (a2_out != nullptr && ok) a2_out[(size_t)(e0 + el) * RH + j] = __float2bfloat16_rn(h.a2);
     }
+    if (a2_out != nullptr) continue;
     __syncthreads();
     // last layer: thread = output column (strided by the block size); W3 row in registers
     for (int c = threadIdx.x; c < NO; c += RTHREADS) {
@@ -358,6 +362,144 @@ __global__ void __launch_bounds__(RTHREADS, 2) radial_bwd_kernel(const float* __
 
 }  // namespace efl
 
+
+namespace efl {
+
+// ------------------------------------------------------------------------------------------
+// hidden-layer backward (bf16 mode): d a2 [E,16] fp32 comes from the tcgen05 GEMM dout . W3; this kernel does phases
+// A, D, E of radial_bwd_kernel only.  Per-CTA partial layout (floats):
+//   dW2 [16,16] | db2 | dg2 | dbe2 [16 each] | dW1 [16,K0] | db1 | dg1 | dbe1 [16 each]
+// ------------------------------------------------------------------------------------------
+template <int K0>
+__global__ void __launch_bounds__(RTHREADS) radial_hidden_bwd_kernel(const float* __restrict__ x, RadialParams p,
+                                                                     const float* __restrict__ da2_in,
+                                                                     float* __restrict__ dx, float* __restrict__ part,
+                                                                     int E) {
+  constexpr int NW1 = (RH * K0 + RTHREADS - 1) / RTHREADS;
+  extern __shared__ float sm[];
+  float* sW1 = sm;                        // [16][K0]
+  float* sW2 = sW1 + RH * K0;             // [16][16]
+  float* sW1t = sW2 + RH * RH;            // [K0][16]
+  float* sW2t = sW1t + RH * K0;           // [16][16]
+  float* sx = sW2t + RH * RH;             // [RT][K0]
+  float* sa1 = sx + RT * K0;              // [RT][16]
+  float* sdh = sa1 + RT * RH;             // [16 half-warps][16]
+  float* sdh2 = sdh + 16 * RH;            // [RT][16]
+  float* sdh1 = sdh2 + RT * RH;           // [RT][16]
+  float* sda2 = sdh1 + RT * RH;           // [RT][16]  (re-used for the final reduction: 16*6*16 floats fit in sda2..)
+  for (int i = threadIdx.x; i < RH * K0; i += RTHREADS) {
+    const float v = p.W1[i];
+    sW1[i] = v;
+    sW1t[(i % K0) * RH + i / K0] = v;
+  }
+  for (int i = threadIdx.x; i < RH * RH; i += RTHREADS) {
+    const float v = p.W2[i];
+    sW2[i] = v;
+    sW2t[(i % RH) * RH + i / RH] = v;
+  }
+  const int hw = threadIdx.x >> 4, j = threadIdx.x & 15;
+  const float g1 = __ldg(p.g1 + j), g2 = __ldg(p.g2 + j);
+  float dW1[NW1], dW2 = 0.f, db2 = 0.f, dg2 = 0.f, dbe2 = 0.f, db1 = 0.f, dg1 = 0.f, dbe1 = 0.f;
+#pragma unroll
+  for (int q = 0; q < NW1; ++q) dW1[q] = 0.f;
+  const int ntiles = (E + RT - 1) / RT;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int e0 = tile * RT;
+    const int ne = min(RT, E - e0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < ne * K0; i += RTHREADS) sx[i] = x[(size_t)e0 * K0 + i];
+    for (int i = threadIdx.x; i < RT * RH; i += RTHREADS) sda2[i] = i < ne * RH ? da2_in[(size_t)e0 * RH + i] : 0.f;
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < RT / 16; ++r) {
+      const int el = r * 16 + hw;
+      const bool ok = el < ne;
+      const Hidden h = radial_hidden(sx + (ok ? el : 0) * K0, K0, sW1t, sW2t, p, j, sa1 + el * RH);
+      const float da2 = ok ? sda2[el * RH + j] : 0.f;
+      const float dz2 = da2 * dsiluf_(h.y2);
+      dg2 = fmaf(dz2, h.xh2, dg2);
+      dbe2 += dz2;
+      const float dxh2 = dz2 * g2;
+      const float m21 = half_sum(dxh2) * (1.f / RH);
+      const float m22 = half_sum(dxh2 * h.xh2) * (1.f / RH);
+      const float dh2 = h.r2 * (dxh2 - m21 - h.xh2 * m22);
+      db2 += dh2;
+      sdh2[el * RH + j] = dh2;
+      sdh[hw * RH + j] = dh2;
+      __syncwarp();
+      float da1 = 0.f;
+#pragma unroll
+      for (int jj = 0; jj < RH; ++jj) da1 = fmaf(sdh[hw * RH + jj], sW2[jj * RH + j], da1);
+      __syncwarp();
+      const float dz1 = da1 * dsiluf_(h.y1);
+      dg1 = fmaf(dz1, h.xh1, dg1);
+      dbe1 += dz1;
+      const float dxh1 = dz1 * g1;
+      const float m11 = half_sum(dxh1) * (1.f / RH);
+      const float m12 = half_sum(dxh1 * h.xh1) * (1.f / RH);
+      const float dh1 = h.r1 * (dxh1 - m11 - h.xh1 * m12);
+      db1 += dh1;
+      sdh1[el * RH + j] = dh1;
+      sdh[hw * RH + j] = dh1;
+      __syncwarp();
+#pragma unroll
+      for (int t = 0; t < K0 / 16; ++t) {
+        const int i = j + 16 * t;
+        float acc = 0.f;
+#pragma unroll
+        for (int jj = 0; jj < RH; ++jj) acc = fmaf(sdh[hw * RH + jj], sW1[jj * K0 + i], acc);
+        if (ok) dx[(size_t)(e0 + el) * K0 + i] = acc;
+      }
+      __syncwarp();
+    }
+    __syncthreads();
+    {
+      const int jj = threadIdx.x >> 4, i = threadIdx.x & 15;
+      float acc = 0.f;
+      for (int el = 0; el < RT; ++el) acc = fmaf(sdh2[el * RH + jj], sa1[el * RH + i], acc);
+      dW2 += acc;
+    }
+#pragma unroll
+    for (int q = 0; q < NW1; ++q) {
+      const int idx = threadIdx.x + q * RTHREADS;
+      if (idx < RH * K0) {
+        const int jj = idx / K0, i = idx % K0;
+        float acc = 0.f;
+        for (int el = 0; el < ne; ++el) acc = fmaf(sdh1[el * RH + jj], sx[el * K0 + i], acc);
+        dW1[q] += acc;
+      }
+    }
+  }
+  const int PSZ = RH * RH + 3 * RH + RH * K0 + 3 * RH;
+  float* tail = part + (size_t)blockIdx.x * PSZ;
+  tail[threadIdx.x] = dW2;
+  float* t1 = tail + RH * RH + 3 * RH;
+#pragma unroll
+  for (int q = 0; q < NW1; ++q) {
+    const int idx = threadIdx.x + q * RTHREADS;
+    if (idx < RH * K0) t1[idx] = dW1[q];
+  }
+  __syncthreads();
+  float* red = sx;  // RT*K0 >= 16*6*16 for K0 >= 48; smaller K0: host sizes sx accordingly
+  red[(hw * 6 + 0) * RH + j] = db2;
+  red[(hw * 6 + 1) * RH + j] = dg2;
+  red[(hw * 6 + 2) * RH + j] = dbe2;
+  red[(hw * 6 + 3) * RH + j] = db1;
+  red[(hw * 6 + 4) * RH + j] = dg1;
+  red[(hw * 6 + 5) * RH + j] = dbe1;
+  __syncthreads();
+  if (threadIdx.x < 6 * RH) {
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) acc += red[k * 6 * RH + threadIdx.x];
+    const int v = threadIdx.x / RH, jj = threadIdx.x % RH;
+    float* dst = v < 3 ? tail + RH * RH + v * RH : t1 + RH * K0 + (v - 3) * RH;
+    dst[jj] = acc;
+  }
+}
+
+}  // namespace efl
+
 using namespace efl;
 
 static size_t radial_fwd_smem(int K0) { return sizeof(float) * (RH * K0 + RH * RH + RT * K0 + RT * RH + 16 * RH); }
@@ -379,7 +521,7 @@ extern "C" int efl_radial_mlp_fwd(const float* x, int K0, const float* W1, const
   RadialParams p{W1, b1, g1, be1, W2, b2, g2, be2, W3, b3};
   const int ntiles = (E + RT - 1) / RT;
   const int grid = ntiles < 148 * 4 ? ntiles : 148 * 4;
-  radial_fwd_kernel<<<grid, RTHREADS, radial_fwd_smem(K0), (cudaStream_t)stream>>>(x, K0, p, NO, out, E);
+  radial_fwd_kernel<<<grid, RTHREADS, radial_fwd_smem(K0), (cudaStream_t)stream>>>(x, K0, p, NO, out, nullptr, E);
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }
@@ -414,6 +556,43 @@ extern "C" int efl_radial_mlp_bwd(const float* x, int K0, const float* W1, const
   else if (K0 == 32) RLAUNCH(32)
   else RLAUNCH(64)
 #undef RLAUNCH
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+// ---- bf16 mode: hidden layers only; the 16 -> NO layer and its backward run on efl_tc_gemm_nt / efl_tc_gemm_tn ----
+extern "C" int efl_radial_hidden_part_size(int K0) { return RH * RH + 3 * RH + RH * K0 + 3 * RH; }
+
+// x [E,K0] fp32 -> a2 [E,16] bf16 (activation entering the last Linear)
+extern "C" int efl_radial_hidden_fwd(const float* x, int K0, const float* W1, const float* b1, const float* g1,
+                                     const float* be1, const float* W2, const float* b2, const float* g2,
+                                     const float* be2, void* a2_out, int E, void* stream) {
+  if (E <= 0) return EFL_OK;
+  EFL_REQUIRE(K0 > 0 && K0 <= 64 && K0 % 4 == 0, "efl_radial_hidden_fwd: K0 <= 64, K0 % 4 == 0");
+  RadialParams p{W1, b1, g1, be1, W2, b2, g2, be2, nullptr, nullptr};
+  const int ntiles = (E + RT - 1) / RT;
+  const int grid = ntiles < 148 * 4 ? ntiles : 148 * 4;
+  radial_fwd_kernel<<<grid, RTHREADS, radial_fwd_smem(K0), (cudaStream_t)stream>>>(x, K0, p, 0, nullptr,
+                                                                                  (__nv_bfloat16*)a2_out, E);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+// da2 [E,16] fp32 -> dx [E,K0] and part [nblocks, efl_radial_hidden_part_size(K0)]
+extern "C" int efl_radial_hidden_bwd(const float* x, int K0, const float* W1, const float* b1, const float* g1,
+                                     const float* be1, const float* W2, const float* b2, const float* g2,
+                                     const float* be2, const float* da2, float* dx, float* part, int nblocks, int E,
+                                     void* stream) {
+  EFL_REQUIRE(nblocks > 0, "efl_radial_hidden_bwd: nblocks must be positive");
+  EFL_REQUIRE(K0 == 48 || K0 == 16 || K0 == 32 || K0 == 64, "efl_radial_hidden_bwd: K0 in {16,32,48,64}");
+  RadialParams p{W1, b1, g1, be1, W2, b2, g2, be2, nullptr, nullptr};
+  const int sxf = RT * K0 > 16 * 6 * RH ? RT * K0 : 16 * 6 * RH;
+  const size_t smem = sizeof(float) * (2 * (RH * K0 + RH * RH) + sxf + 4 * RT * RH + 16 * RH);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (K0 == 48) radial_hidden_bwd_kernel<48><<<nblocks, RTHREADS, smem, s>>>(x, p, da2, dx, part, E);
+  else if (K0 == 16) radial_hidden_bwd_kernel<16><<<nblocks, RTHREADS, smem, s>>>(x, p, da2, dx, part, E);
+  else if (K0 == 32) radial_hidden_bwd_kernel<32><<<nblocks, RTHREADS, smem, s>>>(x, p, da2, dx, part, E);
+  else radial_hidden_bwd_kernel<64><<<nblocks, RTHREADS, smem, s>>>(x, p, da2, dx, part, E);
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }

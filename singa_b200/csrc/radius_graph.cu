@@ -53,17 +53,38 @@ __global__ void bbox_init_kernel(unsigned* __restrict__ box, int nbatch) {
   if (t < nbatch * 6) box[t] = (t % 6 < 3) ? 0xffffffffu : 0u;
 }
 
-// box [B, 6] encoded (min xyz | max xyz)
-__global__ void bbox_kernel(const float* __restrict__ pos, const int* __restrict__ batch, int n,
-                            unsigned* __restrict__ box) {
+// box [B, 6] encoded (min xyz | max xyz).  The batch vector is sorted, so a CTA whose first and last point share a
+// batch item reduces in shared memory and issues 6 global atomics instead of 6 per point.
+__global__ void __launch_bounds__(256) bbox_kernel(const float* __restrict__ pos, const int* __restrict__ batch, int n,
+                                                   unsigned* __restrict__ box) {
+  __shared__ unsigned sb[6];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int b = batch ? batch[i] : 0;
+  const int first = blockIdx.x * blockDim.x, last = min(n, first + (int)blockDim.x) - 1;
+  const int bf = batch ? batch[first] : 0, bl = batch ? batch[last] : 0;
+  const bool uniform = bf == bl;
+  if (threadIdx.x < 6) sb[threadIdx.x] = threadIdx.x < 3 ? 0xffffffffu : 0u;
+  __syncthreads();
+  if (i < n) {
+    const int b = batch ? batch[i] : 0;
 #pragma unroll
-  for (int d = 0; d < 3; ++d) {
-    const unsigned e = enc_f(pos[3 * (size_t)i + d]);
-    atomicMin(box + 6 * b + d, e);
-    atomicMax(box + 6 * b + 3 + d, e);
+    for (int d = 0; d < 3; ++d) {
+      unsigned e = enc_f(pos[3 * (size_t)i + d]);
+      if (uniform) {
+        const unsigned lo = __reduce_min_sync(__activemask(), e), hi = __reduce_max_sync(__activemask(), e);
+        if ((threadIdx.x & 31) == 0 || i == first) {
+          atomicMin(sb + d, lo);
+          atomicMax(sb + 3 + d, hi);
+        }
+      } else {
+        atomicMin(box + 6 * b + d, e);
+        atomicMax(box + 6 * b + 3 + d, e);
+      }
+    }
+  }
+  __syncthreads();
+  if (uniform && threadIdx.x < 6) {
+    if (threadIdx.x < 3) atomicMin(box + 6 * bf + threadIdx.x, sb[threadIdx.x]);
+    else atomicMax(box + 6 * bf + threadIdx.x, sb[threadIdx.x]);
   }
 }
 

@@ -619,13 +619,60 @@ class RadialMLPFunction(torch.autograd.Function):
         ps = [q.detach().contiguous().float() for q in params]
         E, K0 = x.shape
         NO = ps[8].shape[0]
+        ctx.tc = _PRECISION == "bf16" and NO % 16 == 0 and E > 0
+        if ctx.tc:
+            # hidden layers SIMT -> a2 bf16; last layer = K=16 tcgen05 GEMM with the bias in the epilogue
+            a2 = torch.empty(E, 16, dtype=torch.bfloat16, device=x.device)
+            call("efl_radial_hidden_fwd", ptr(x), K0, *[ptr(q) for q in ps[:8]], ptr(a2), E, work=E * (4.0 * K0 + 32))
+            w3b = ps[8].to(torch.bfloat16)
+            out = torch.empty(E, NO, dtype=torch.float32, device=x.device)
+            _gemm_nt(1, a2, w3b, ps[9], out, 8, out, NO, NO, E, NO, 16)
+            ctx.save_for_backward(x, a2, w3b, *ps[:8])
+            return out
         out = torch.empty(E, NO, dtype=torch.float32, device=x.device)
         call("efl_radial_mlp_fwd", ptr(x), K0, *[ptr(q) for q in ps], NO, ptr(out), E, work=E * 4.0 * (K0 + NO))
         ctx.save_for_backward(x, *ps)
         return out
 
     @staticmethod
+    def _split(t, K0, NO):
+        o = 0
+
+        def take(*shape):
+            nonlocal o
+            n = int(np.prod(shape))
+            v = t[o:o + n].view(*shape)
+            o += n
+            return v
+
+        if NO:
+            dW3, db3 = take(NO, 16), take(NO)
+        else:
+            dW3 = db3 = None
+        dW2, db2, dg2, dbe2 = take(16, 16), take(16), take(16), take(16)
+        dW1, db1, dg1, dbe1 = take(16, K0), take(16), take(16), take(16)
+        return dW1, db1, dg1, dbe1, dW2, db2, dg2, dbe2, dW3, db3
+
+    @staticmethod
     def backward(ctx, dout):
+        if ctx.tc:
+            x, a2, w3b, *ps = ctx.saved_tensors
+            E, K0 = x.shape
+            NO = w3b.shape[0]
+            dob = dout.contiguous().to(torch.bfloat16)
+            da2 = _f32_from_gemm(dob, w3b.t().contiguous(), E, 16, NO)
+            dW3 = torch.empty(NO, 16, dtype=torch.float32, device=x.device)
+            _gemm_tn(dob, a2, dW3, False, E, NO, 16)
+            db3 = torch.empty(NO, dtype=torch.float32, device=x.device)
+            _colsum(dob, E, NO, db3, False)
+            dx = torch.empty_like(x)
+            psz = LIB.efl_radial_hidden_part_size(K0)
+            nblk = max(1, min(4 * 148, (E + 31) // 32))
+            part = torch.empty(nblk, psz, dtype=torch.float32, device=x.device)
+            call("efl_radial_hidden_bwd", ptr(x), K0, *[ptr(q) for q in ps], ptr(da2), ptr(dx), ptr(part), nblk, E,
+                 work=E * (8.0 * K0 + 64))
+            g = RadialMLPFunction._split(part.sum(dim=0), K0, 0)
+            return (dx, *g[:8], dW3, db3)
         x, *ps = ctx.saved_tensors
         E, K0 = x.shape
         NO = ps[8].shape[0]
@@ -636,20 +683,7 @@ class RadialMLPFunction(torch.autograd.Function):
         part = torch.empty(nblk, psz, dtype=torch.float32, device=x.device)
         call("efl_radial_mlp_bwd", ptr(x), K0, *[ptr(q) for q in ps], NO, ptr(dout), ptr(dx), ptr(part), nblk, E,
              work=E * 4.0 * (2 * K0 + NO))
-        t = part.sum(dim=0)
-        o = 0
-
-        def take(*shape):
-            nonlocal o
-            n = int(np.prod(shape))
-            v = t[o:o + n].view(*shape)
-            o += n
-            return v
-
-        dW3, db3 = take(NO, 16), take(NO)
-        dW2, db2, dg2, dbe2 = take(16, 16), take(16), take(16), take(16)
-        dW1, db1, dg1, dbe1 = take(16, K0), take(16), take(16), take(16)
-        return (dx, dW1, db1, dg1, dbe1, dW2, db2, dg2, dbe2, dW3, db3)
+        return (dx, *RadialMLPFunction._split(part.sum(dim=0), K0, NO))
 
 
 # ---------------------------------------------------------------------------
