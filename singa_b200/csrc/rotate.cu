@@ -160,6 +160,7 @@ __global__ void __launch_bounds__(128, 4) rotate_in_bwd_node_kernel(
   static_assert(C == 16, "half-warp = channels of one side");
   static_assert(T::WSZ % 4 == 0, "Wigner rows are 16-byte padded");
   constexpr int CH = 2 * C;
+  constexpr int NPAIR = (LMAX + 1) * (MMAX + 1) - MMAX * (MMAX + 1) / 2;  // (l, |m'|) pairs
   __shared__ __align__(16) float sW[4][2][T::WSZ];
   __shared__ float sX[4][T::L][C];  // x of the warp's node (only d rad needs it): shared memory, not registers
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -198,6 +199,29 @@ __global__ void __launch_bounds__(128, 4) rotate_in_bwd_node_kernel(
     const int pos = act ? (seg_idx ? seg_idx[k] : k) : 0;
     const int el = pos - e0;
     const int eo = act ? perm[pos] : 0;
+    // every global load of this edge is issued before the first store of the iteration (the d rad stores would
+    // otherwise order the loads behind them): d A rows and radial values of the lane's channel into registers
+    const float* rd = rad ? rad + (size_t)eo * rad_ld : nullptr;
+    float* drd = rad ? drad + (size_t)eo * rad_ld : nullptr;
+    float da_r[T::M], rv_r[NPAIR];
+    {
+      int t = 0, s2 = 0;
+#pragma unroll
+      for (int l = 0; l <= LMAX; ++l) {
+#pragma unroll
+        for (int am = 0; am <= T::mm(l); ++am) {
+          int roff = 0;
+#pragma unroll
+          for (int q = 0; q < am; ++q) roff += (LMAX + 1 - q) * CH;
+          rv_r[s2++] = (act && rd) ? __ldg(rd + roff + (l - am) * CH + coff + c) : 1.f;
+#pragma unroll
+          for (int sgn = 0; sgn < (am == 0 ? 1 : 2); ++sgn) {
+            const int mp = sgn == 0 ? am : -am;
+            da_r[t++] = act ? to_f<TIn>(*op_ptr<LMAX, TIn>(dA.p, el, l, mp, CH, coff + c)) : 0.f;
+          }
+        }
+      }
+    }
     __syncwarp();
     if (act) {
       const float4* w4 = reinterpret_cast<const float4*>(wig + (size_t)eo * T::WSZ);
@@ -205,8 +229,7 @@ __global__ void __launch_bounds__(128, 4) rotate_in_bwd_node_kernel(
     }
     __syncwarp();
     if (!act) continue;
-    const float* rd = rad ? rad + (size_t)eo * rad_ld : nullptr;
-    float* drd = rad ? drad + (size_t)eo * rad_ld : nullptr;
+    int t = 0, s2 = 0;
 #pragma unroll
     for (int l = 0; l <= LMAX; ++l) {
 #pragma unroll
@@ -215,13 +238,13 @@ __global__ void __launch_bounds__(128, 4) rotate_in_bwd_node_kernel(
 #pragma unroll
         for (int q = 0; q < am; ++q) roff += (LMAX + 1 - q) * CH;
         const int rcol = roff + (l - am) * CH + coff + c;
-        const float rv = rd ? __ldg(rd + rcol) : 1.f;
+        const float rv = rv_r[s2++];
         float dr = 0.f;
 #pragma unroll
         for (int sgn = 0; sgn < (am == 0 ? 1 : 2); ++sgn) {
           const int mp = sgn == 0 ? am : -am;
           const float* wr = sw + T::wrow(l, mp);
-          const float da = to_f<TIn>(*op_ptr<LMAX, TIn>(dA.p, el, l, mp, CH, coff + c));
+          const float da = da_r[t++];
           if (rd) {
             float xr = 0.f;
 #pragma unroll

@@ -45,6 +45,11 @@ def _should_save(nbytes: int, device) -> bool:
     return nbytes < _SAVE_FREE_FRACTION * (free + cached)
 
 
+# backward of rotate-in: "nodes" = node-owned accumulation (no per-edge gradient tensor), "edges" = per-edge d x
+# followed by two segment sums.  Both deterministic; chosen by measurement (tools/edge_bench.py).
+ROTATE_IN_BWD = os.environ.get("EFL_ROTIN_BWD", "nodes")
+
+
 def set_precision(mode: str) -> None:
     global _PRECISION
     if mode not in ("fp32", "bf16"):
@@ -428,6 +433,7 @@ class EdgeAttentionFunction(torch.autograd.Function):
         drad = torch.empty_like(rad)   # every column of every edge is written by the rotate-in backward
         dx_dst = torch.zeros_like(x_dst)
         dx_src = torch.zeros_like(x_src)
+        dxe = None
         nparts = LIB.efl_rotate_back_parts(d.lmax, d.mmax)
         dalpha = torch.empty(nparts, max(E, 1), d.heads, dtype=torch.float32, device=dev)
         dlogits = torch.empty(max(E, 1), d.heads, dtype=torch.float32, device=dev)
@@ -495,16 +501,29 @@ class EdgeAttentionFunction(torch.autograd.Function):
                 _gemm_tn(ws.dY1[m], ws.A[m], g_c1wm[m - 1], acc, 2 * Ec, 2 * d.ms[m] * H, d.ms[m] * C2)
                 _gemm_nt(0, ws.dY1[m], w1.wmt[m - 1], None, ws.dA[m], d.ms[m] * C2, None, 0, 0, 2 * Ec,
                          d.ms[m] * C2, 2 * d.ms[m] * H)
-            # ---- rotate-in backward -> d rad and d x, node-owned (no per-edge gradient tensor)
-            wrk = Ec * (_bytes_rotate_in(d, ws.dA[0].element_size(), wig.shape[1]) + d.M * C2 * 4) / 2
-            call("efl_rotate_in_bwd_nodes", d.lmax, d.mmax, d.C, bf16, 0, ptr(x_dst), ptr(csr.rowptr), None,
-                 ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.dA[0]), ptr(ws.dA[1]), ptr(ws.dA[2]),
-                 ptr(drad), ptr(dx_dst), e0, Ec, n0, n1, 0, work=wrk, tag="efl_rotate_in_bwd_dst")
-            call("efl_rotate_in_bwd_nodes", d.lmax, d.mmax, d.C, bf16, 1, ptr(x_src), ptr(csr.src_ptr),
-                 ptr(csr.src_idx), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.dA[0]), ptr(ws.dA[1]),
-                 ptr(ws.dA[2]), ptr(drad), ptr(dx_src), e0, Ec, 0, csr.num_src, 1, work=wrk,
-                 tag="efl_rotate_in_bwd_src")
+            # ---- rotate-in backward -> d rad and d x
+            if ROTATE_IN_BWD == "nodes":  # node-owned: no per-edge gradient tensor
+                wrk = Ec * (_bytes_rotate_in(d, ws.dA[0].element_size(), wig.shape[1]) + d.M * C2 * 4) / 2
+                call("efl_rotate_in_bwd_nodes", d.lmax, d.mmax, d.C, bf16, 0, ptr(x_dst), ptr(csr.rowptr), None,
+                     ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.dA[0]), ptr(ws.dA[1]), ptr(ws.dA[2]),
+                     ptr(drad), ptr(dx_dst), e0, Ec, n0, n1, 0, work=wrk, tag="efl_rotate_in_bwd_dst")
+                call("efl_rotate_in_bwd_nodes", d.lmax, d.mmax, d.C, bf16, 1, ptr(x_src), ptr(csr.src_ptr),
+                     ptr(csr.src_idx), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.dA[0]),
+                     ptr(ws.dA[1]), ptr(ws.dA[2]), ptr(drad), ptr(dx_src), e0, Ec, 0, csr.num_src, 1, work=wrk,
+                     tag="efl_rotate_in_bwd_src")
+            else:  # edge-owned: per-edge d x [E, L, 2C] + two deterministic segment sums after the loop
+                if dxe is None:
+                    dxe = torch.empty(max(E, 1), L, C2, dtype=torch.float32, device=dev)
+                call("efl_rotate_in_bwd", d.lmax, d.mmax, d.C, bf16, ptr(x_src), ptr(x_dst), ptr(csr.src_sorted),
+                     ptr(csr.dst_sorted), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.dA[0]),
+                     ptr(ws.dA[1]), ptr(ws.dA[2]), ptr(drad), ptr(dxe), e0, Ec,
+                     work=Ec * (_bytes_rotate_in(d, ws.dA[0].element_size(), wig.shape[1]) + d.M * C2 * 4 + L * C2 * 4))
             first = False
+        if dxe is not None:
+            call("efl_segment_sum_rows", ptr(dxe), L, C2, d.C, d.C, ptr(csr.rowptr), None, ptr(dx_dst), csr.num_dst, 0,
+                 work=(E + csr.num_dst) * L * d.C * 4.0)
+            call("efl_segment_sum_rows", ptr(dxe), L, C2, 0, d.C, ptr(csr.src_ptr), ptr(csr.src_idx), ptr(dx_src),
+                 csr.num_src, 0, work=(E + csr.num_src) * L * d.C * 4.0 + E * 4.0)
         ha = d.heads * d.alpha_ch
         g_adot = part_all[:ha].view(d.heads, d.alpha_ch)
         g_lnw = part_all[ha:ha + d.alpha_ch]
