@@ -10,6 +10,8 @@
 // NT epilogues as in gemm_simt.cu (0 plain, 1 split, 2 complex combine); outputs bf16 (fp32 for the split part).
 //
 // Replaces the cuBLAS mm calls under SO2_Convolution / SO2_m_Convolution (reference EF_layers.py:721-729, 807-875).
+#include <string.h>
+
 #include "tc_common.cuh"
 
 namespace efl {
@@ -43,10 +45,12 @@ struct Params {
   float* P;      // TN partials [splits, N1, N2]
   int splits;
   int kb_per_split;
+  int tma_c, tma_c0;  // output tensor maps valid: full-width blocks leave through TMA stores
 };
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const Params p) {
+tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+               const __grid_constant__ CUtensorMap mapC, const __grid_constant__ CUtensorMap mapC0, const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
@@ -165,8 +169,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     uint8_t* stg = smem + STAGES * STAGE_BYTES + 1024 + (warp - 4) * STG_BYTES;
     const uint32_t stg_w = smem_u32(stg) + (uint32_t)lane * 128u;   // this lane's row (write phase)
     const int swz = lane & 7;
+    // Full-width blocks (128 bytes per row) leave through ONE TMA store of the staging tile (the XOR swizzle above
+    // is the tensor map's 128-byte swizzle; rows beyond M are clipped by the hardware); narrower tail blocks take
+    // the manual row stores.
     int acc = 0;
     uint32_t acc_phase = 0;
+    bool pending = false;  // a bulk store may still be reading this warp's staging tile
     for (int w = blockIdx.x; w < work_items; w += gridDim.x) {
       int z = 0, t = w;
       if (tn) { z = w / (m_tiles * n_tiles); t = w % (m_tiles * n_tiles); }
@@ -187,6 +195,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         const int wcols = min(width, limit - c);  // multiple of 16
         if ((blk & 1) == eh) {
           const int ngrp = wcols >> 4;
+          const bool use_tma = wcols == width && ((kind == 1) ? p.tma_c0 : p.tma_c);
+          if (pending) {
+            if (lane == 0) tma_store_wait_read();
+            __syncwarp();
+            pending = false;
+          }
           for (int g0 = 0; g0 < ngrp; g0 += 2) {
             uint32_t vv[32];
             const bool two = g0 + 1 < ngrp;
@@ -213,9 +227,19 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                              pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
               } else {
                 float f[16];
+                if (!tn && p.bias) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j)
-                  f[j] = __uint_as_float(v[j]) + ((!tn && p.bias) ? __ldg(p.bias + col + j) : 0.f);
+                  for (int j = 0; j < 16; j += 4) {
+                    const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col + j));
+                    f[j] = __uint_as_float(v[j]) + b4.x;
+                    f[j + 1] = __uint_as_float(v[j + 1]) + b4.y;
+                    f[j + 2] = __uint_as_float(v[j + 2]) + b4.z;
+                    f[j + 3] = __uint_as_float(v[j + 3]) + b4.w;
+                  }
+                } else {
+#pragma unroll
+                  for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
+                }
                 if (kind == 1) {
 #pragma unroll
                   for (int j = 0; j < 4; ++j)
@@ -230,6 +254,20 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 }
               }
             }
+          }
+          if (use_tma) {
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+              if (tn) tma_store_3d(&mapC0, stg, gcol, row0, z);
+              else if (kind == 1) tma_store_2d(&mapC0, stg, gcol, row0);
+              else if (kind == 2) tma_store_2d(&mapC, stg, gcol / 2, row0);
+              else tma_store_2d(&mapC, stg, gcol - (p.epi == 1 ? p.nsplit : 0), row0);
+              tma_store_commit();
+            }
+            pending = true;
+            c += wcols;
+            continue;
           }
           __syncwarp();
           // coalesced write-out: lane -> (row 4*it + lane/8, 16-byte chunk lane%8)
@@ -269,6 +307,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
       mbar_arrive(&tempty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (pending && lane == 0) tma_store_wait_read();
   }
 
   tc_fence_before();
@@ -329,6 +368,29 @@ int efl_make_map_bf16(CUtensorMap* map, const void* base, long long rows, long l
   return EFL_OK;
 }
 
+// Output tile map for the epilogue's TMA stores: row-major [planes,] rows x cols, box = 32 rows x 128 bytes, 128-byte
+// swizzle.  Returns 0 and sets *ok = 1 when the layout qualifies (16-byte aligned base and pitches); *ok = 0
+// otherwise (the epilogue then uses its manual row stores).
+static int make_out_map(CUtensorMap* map, int* ok, int is_f32, const void* base, long long planes, long long rows,
+                        long long cols, long long ld) {
+  *ok = 0;
+  memset(map, 0, sizeof(*map));
+  EncodeTiledFn enc = get_encode();
+  const int esz = is_f32 ? 4 : 2;
+  const int bcols = 128 / esz;
+  if (!enc || base == nullptr || cols < bcols || rows <= 0 || ((uintptr_t)base & 15) || ((ld * esz) & 15)) return EFL_OK;
+  cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)(planes > 0 ? planes : 1)};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * esz, (cuuint64_t)ld * esz * (cuuint64_t)rows};
+  cuuint32_t box[3] = {(cuuint32_t)bcols, 32u, 1u};
+  cuuint32_t estr[3] = {1u, 1u, 1u};
+  const int rank = planes > 0 ? 3 : 2;
+  CUresult r = enc(map, is_f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank,
+                   const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r == CUDA_SUCCESS) *ok = 1;
+  return EFL_OK;
+}
+
 // largest multiple of 16 that divides n and is <= 256
 static int pick_bn(int n) {
   for (int bn = 256; bn >= 16; bn -= 16)
@@ -347,7 +409,8 @@ int efl_num_sms() {
   return n;
 }
 
-static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const Params& p, int work_items, cudaStream_t s) {
+static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mc0,
+                  const Params& p, int work_items, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(efl::tc::tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -359,7 +422,7 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const Params& p,
     attr_set = true;
   }
   const int grid = work_items < efl_num_sms() ? work_items : efl_num_sms();
-  efl::tc::tc_gemm_kernel<<<grid, efl::tc::NUM_THREADS, efl::tc::SMEM_BYTES, s>>>(ma, mb, p);
+  efl::tc::tc_gemm_kernel<<<grid, efl::tc::NUM_THREADS, efl::tc::SMEM_BYTES, s>>>(ma, mb, mc, mc0, p);
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }
@@ -384,8 +447,12 @@ extern "C" int efl_tc_gemm_nt(int epilogue, const void* A, long long lda, const 
   p.mode = 0; p.M = M; p.N = N; p.K = K; p.BN = bn; p.epi = epilogue;
   p.C = (__nv_bfloat16*)C; p.ldc = ldc; p.C0 = C0; p.ldc0 = ldc0; p.nsplit = nsplit; p.bias = bias;
   p.P = nullptr; p.splits = 1; p.kb_per_split = 0;
+  CUtensorMap mc, mc0;
+  const long long ccols = epilogue == 2 ? N / 2 : (epilogue == 1 ? N - nsplit : N);
+  make_out_map(&mc, &p.tma_c, 0, ccols > 0 ? C : nullptr, 0, M, ccols, ldc);
+  make_out_map(&mc0, &p.tma_c0, 1, epilogue == 1 ? C0 : nullptr, 0, M, nsplit, ldc0);
   const int tiles = ((M + efl::tc::BM - 1) / efl::tc::BM) * (N / bn);
-  return launch(ma, mb, p, tiles, (cudaStream_t)stream);
+  return launch(ma, mb, mc, mc0, p, tiles, (cudaStream_t)stream);
 }
 
 // Split count for the weight-gradient GEMM.  Work items = tiles x splits run on a persistent grid of one CTA per
@@ -439,7 +506,10 @@ extern "C" int efl_tc_gemm_tn(const void* A, long long lda, const void* B, long 
   p.P = workspace; p.splits = splits; p.kb_per_split = (kb + splits - 1) / splits;
   const int tiles = ((N1 + efl::tc::BM - 1) / efl::tc::BM) * (N2 / bn);
   cudaStream_t s = (cudaStream_t)stream;
-  rc = launch(ma, mb, p, tiles * splits, s);
+  CUtensorMap mc, mc0;
+  make_out_map(&mc, &p.tma_c, 0, nullptr, 0, 0, 0, 0);
+  make_out_map(&mc0, &p.tma_c0, 1, workspace, splits, N1, N2, N2);
+  rc = launch(ma, mb, mc, mc0, p, tiles * splits, s);
   if (rc) return rc;
   const long long n = (long long)N1 * N2;
   efl::splitk_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(workspace, splits, n, C, ldc, N2, accumulate);
