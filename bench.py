@@ -289,6 +289,9 @@ def main():
                 traffic = json.load(open(tpath)).get(name)
             roofline = {"kernel": name, "bound": "tensor" if tensor else "hbm", "achieved": achieved, "peak": peak,
                         "unit": "TFLOP/s" if tensor else "GB/s", "frac": achieved / peak, "traffic": traffic,
+                        "traffic_unit": "dram bytes per launch (ncu --set full, profiles/ncu_traffic.json: one "
+                                        "edge-layer pass of 225 240 edges, chunk size comparable to this run's)",
+                        "algorithmic_per_launch": per_launch_work, "ms_per_launch": per_launch_s * 1e3,
                         "peak_source": pk["source"], "share_of_step": d["ms"] / (ms_dev * args.steps),
                         "launches": d["calls"]}
         breakdown = {k: round(v["ms"] / args.steps, 3) for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}
