@@ -14,6 +14,8 @@
 // Persistent CTAs, 12 warps: warp 0 TMA loader, warp 1 MMA issuer, warp 2 TMEM allocator, warps 4-7 and 8-11
 // two worker groups handling alternate edges (thread = channel = TMEM lane), each with private TMEM accumulators
 // and a private S buffer, so the SiLU of one edge overlaps the MMAs / output of the other.
+#include <cuda_fp16.h>
+
 #include "tc_common.cuh"
 
 namespace efl {
@@ -54,6 +56,23 @@ __device__ __forceinline__ float silu_fast(float x) {
   float t;
   asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
   return fmaf(h, t, h);
+}
+// SiLU of two fp32 accumulator values, evaluated in packed fp16 (one MUFU op for both): x*sigmoid(x) = h + h*tanh(h),
+// h = x/2.  Result = fp16x2 operand word (lo = first value).  fp16 keeps 11 mantissa bits (the bf16 operand it
+// replaces kept 8).
+__device__ __forceinline__ uint32_t silu_f16x2(uint32_t lo_f32_bits, uint32_t hi_f32_bits) {
+  uint32_t r;
+  asm("{\n\t"
+      ".reg .b32 x, h, t, c;\n\t"
+      "cvt.rn.f16x2.f32 x, %2, %1;\n\t"
+      "mov.b32 c, 0x38003800;\n\t"
+      "mul.f16x2 h, x, c;\n\t"
+      "tanh.approx.f16x2 t, h;\n\t"
+      "fma.rn.f16x2 %0, h, t, h;\n\t"
+      "}"
+      : "=r"(r)
+      : "f"(__uint_as_float(lo_f32_bits)), "f"(__uint_as_float(hi_f32_bits)));
+  return r;
 }
 __device__ __forceinline__ float dsilu_fast(float x) {
   float t;
@@ -135,7 +154,9 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
       if (BWD) sF0[off_sw] = __float2bfloat16_rn(j == 0 ? 0.f : f);
       // K-major, no swizzle: rows j, K index g: (j/8)*sbo + (g/8)*128 + (j%8)*16 + (g%8)*2 bytes
       const int off_ns = ((j >> 3) * L.sbo + (g >> 3) * 128 + (j & 7) * 16) / 2 + (g & 7);
-      sB2[off_ns] = __float2bfloat16_rn(BWD ? t : f);
+      // forward: S and from_grid are fp16 operands (SiLU is evaluated in packed f16x2), backward: bf16
+      if (BWD) sB2[off_ns] = __float2bfloat16_rn(t);
+      else reinterpret_cast<__half*>(sB2)[off_ns] = __float2half_rn(f);
     }
   }
   if (threadIdx.x == 0) {
@@ -196,7 +217,8 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
     uint32_t phase = 0;
     const int NG = p.NG, lag = p.NG - 1;
     const uint32_t idesc1 = make_idesc2(GP, 1, 0);   // A = operand tile (MN-major), B = T/F0 (K-major)
-    const uint32_t idesc2 = make_idesc2(KP, 0, 0);   // A = S (K-major), B = B2 (K-major)
+    // A = S (K-major), B = B2 (K-major); forward: both fp16 (a_format = b_format = 0)
+    const uint32_t idesc2 = BWD ? make_idesc2(KP, 0, 0) : (make_idesc2(KP, 0, 0) & ~((1u << 7) | (1u << 10)));
     const uint32_t sT = smem_u32(smem + L.off_T), sF0 = smem_u32(smem + L.off_F0), sB2 = smem_u32(smem + L.off_B2);
     for (int i = 0; i < n_mine + lag; ++i) {
       for (int pass = 0; pass < 2; ++pass) {
@@ -276,11 +298,10 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
 #pragma unroll
           for (int h = 0; h < 4; ++h) {
             if (g0 + 8 * h < GP) {
-              float s[8];
+              uint32_t s2[4];
 #pragma unroll
-              for (int t = 0; t < 8; ++t) s[t] = silu_fast(__uint_as_float(v[8 * h + t]));
-              *reinterpret_cast<uint4*>(sS + ((g0 >> 3) + h) * 128) =
-                  make_uint4(pack_bf16(s[0], s[1]), pack_bf16(s[2], s[3]), pack_bf16(s[4], s[5]), pack_bf16(s[6], s[7]));
+              for (int t = 0; t < 4; ++t) s2[t] = silu_f16x2(v[8 * h + 2 * t], v[8 * h + 2 * t + 1]);
+              *reinterpret_cast<uint4*>(sS + ((g0 >> 3) + h) * 128) = make_uint4(s2[0], s2[1], s2[2], s2[3]);
             }
           }
         }
