@@ -1179,14 +1179,52 @@ class TransBlockV2(nn.Module):
 # ---------------------------------------------------------------------------
 # edge frames
 # ---------------------------------------------------------------------------
-def init_edge_rot_mat(edge_distance_vec, device: str = 'cuda'):
+class _DeferredFrameChecks:
+    """The two data-dependent checks of init_edge_rot_mat (shortest edge, |cos| of the auxiliary vector) read back
+    asynchronously: the flags go to pinned host memory behind an event, and are evaluated at the next poll / flush
+    instead of stalling the launch queue twice per call (each stall drains the GPU and exposes the launch latency of
+    the small ligand passes).  Same message and same AssertionError as the reference, raised at the next flush."""
+
+    def __init__(self):
+        self.pending = []
+
+    def submit(self, shortest, max_cos):
+        host = torch.empty(2, dtype=torch.float32, pin_memory=True)
+        host.copy_(torch.stack((shortest.float(), max_cos.float())), non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self.pending.append((host, ev))
+        self.flush(wait=False)
+
+    def flush(self, wait: bool = True):
+        keep = []
+        for host, ev in self.pending:
+            if not wait and not ev.query():
+                keep.append((host, ev))
+                continue
+            ev.synchronize()
+            shortest, max_cos = float(host[0]), float(host[1])
+            if shortest < 0.0001:
+                print("Error edge_vec_0_distance: {}".format(shortest))
+            if not max_cos < 0.99:
+                self.pending = []
+                raise AssertionError("init_edge_rot_mat: auxiliary vector parallel to an edge (|cos| >= 0.99)")
+        self.pending = keep
+
+
+FRAME_CHECKS = _DeferredFrameChecks()
+
+
+def init_edge_rot_mat(edge_distance_vec, device: str = 'cuda', defer_checks: bool = False):
     """Random-gauge orthonormal frame per edge, rows (z, x = edge direction, -y); consumes one
     ``torch.rand_like`` draw; prints on edges shorter than 1e-4 and asserts |cos| < 0.99 between the edge and
-    the auxiliary vector, as the reference does (ref :2286-2351)."""
+    the auxiliary vector, as the reference does (ref :2286-2351).  ``defer_checks`` (used by the B200
+    EquivariantEmbedding caller) reads the two flags back asynchronously (FRAME_CHECKS) instead of synchronising."""
     v = edge_distance_vec
     length = v.pow(2).sum(dim=1).sqrt()
     shortest = torch.min(length)
-    if shortest < 0.0001:
+    defer = defer_checks and v.is_cuda and v.shape[0] > 0
+    if not defer and shortest < 0.0001:
         print("Error edge_vec_0_distance: {}".format(shortest))
     ex = v / length.view(-1, 1)
     aux = torch.rand_like(v) - 0.5
@@ -1198,7 +1236,10 @@ def init_edge_rot_mat(edge_distance_vec, device: str = 'cuda'):
     dot_b, dot_c = dot(alt_b), dot(alt_c)
     aux = torch.where(dot(aux) > dot_b, alt_b, aux)
     aux = torch.where(dot(aux) > dot_c, alt_c, aux)
-    assert torch.max(dot(aux)) < 0.99
+    if defer:
+        FRAME_CHECKS.submit(shortest, torch.max(dot(aux)))
+    else:
+        assert torch.max(dot(aux)) < 0.99
     ez = torch.cross(ex, aux, dim=1)
     ez = ez / ez.pow(2).sum(dim=1, keepdim=True).sqrt()
     ez = ez / ez.pow(2).sum(dim=1).sqrt().view(-1, 1)

@@ -26,6 +26,7 @@ import torch.nn as nn
 from .EF_layers import (CoefficientMappingModule, EdgeDegreeEmbedding, GaussianSmearing, ModuleListInfo,
                         SO3_Embedding, SO3_Grid, SO3_Rotation, TransBlockV2, get_normalization_layer,
                         init_edge_rot_mat)
+from . import EF_layers as _ef
 from .synthetic import LIGAND, LL, LP, PL, PP, PROTEIN
 
 _AVG_NUM_MODES = 77.81317
@@ -129,7 +130,8 @@ class EquivariantEmbedding(nn.Module):
 
     # -- helpers ----------------------------------------------------------------------------
     def _set_frames(self, edge_vec, frames, key):
-        rot = frames[key] if frames is not None and key in frames else init_edge_rot_mat(edge_vec)
+        rot = frames[key] if frames is not None and key in frames else init_edge_rot_mat(edge_vec, device=edge_vec.device,
+                                                                                     defer_checks=True)
         for r in self.SO3_rotation:
             r.set_wigner(rot)
 
@@ -178,6 +180,7 @@ class EquivariantEmbedding(nn.Module):
         """g: anything indexable like the reference's HeteroData (g['atomicnum'][nt], g[nt]['x'|'pos'],
         g[(s, rel, d)]['edge_index']).  frames: optional dict(pp=, ll=, lp=) of [E,3,3] edge frames."""
         x_dict = {}
+        _ef.FRAME_CHECKS.flush(wait=True)  # frame checks of the previous call (long complete: no stall)
         zs = {PROTEIN: g['atomicnum'][PROTEIN], LIGAND: g['atomicnum'][LIGAND]}
         pos = {PROTEIN: g[PROTEIN]['pos'], LIGAND: g[LIGAND]['pos']}
         x_dict[PROTEIN] = self._homo_pass(zs[PROTEIN], g[PROTEIN]['x'], pos[PROTEIN], g[PP]['edge_index'], frames, 'pp')
