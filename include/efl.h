@@ -225,6 +225,12 @@ int efl_radial_hidden_bwd(const float* x, int K0, const float* W1, const float* 
                           const float* W2, const float* b2, const float* g2, const float* be2, const float* da2,
                           float* dx, float* part, int nblocks, int E, void* stream);
 
+/* Deterministic gradient of a small-table embedding lookup (source/target element embeddings of the edge scalars,
+ * Embedding.py:97-99): dW[r,c] = sum over lookups e with ids[e] = r of dx[e*ld + c], fixed summation order, no float
+ * atomics.  ids [E] int64; dx already offset to the embedding's columns; workspace nblocks*rows*C floats. */
+int efl_embedding_grad(const long long* ids, const float* dx, long long ld, int E, int rows, int C, float* dW,
+                       float* workspace, int nblocks, void* stream);
+
 /* EquivariantRMSNormArraySphericalHarmonicsV2 as built by get_normalization_layer (:2099-2192, :2254-2273):
  * centred l=0, degree-balanced RMS, per-degree gain gamma [lmax+1,16], bias beta [16] on l=0.  One warp per node.
  * bwd writes per-block partials of (d gamma | d beta) into part [nblocks, (lmax+2)*16]. */

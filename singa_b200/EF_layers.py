@@ -889,6 +889,16 @@ def _edge_csr(edge_index: Tensor, num_src: int, num_dst: int):
     return csr
 
 
+def embedding_lookup(emb: nn.Embedding, ids: Tensor) -> Tensor:
+    """``emb(ids)`` whose backward is the deterministic efl_embedding_grad kernel (torch's embedding backward sums with
+    float atomics).  Plain ``nn.Embedding`` semantics otherwise (no padding_idx / max_norm in the reference's use)."""
+    if emb.weight.is_cuda and emb.padding_idx is None and emb.max_norm is None:
+        ops = _get_ops()
+        if ops.EmbeddingLookupFunction.eligible(emb.weight):
+            return ops.EmbeddingLookupFunction.apply(emb.weight, ids)
+    return emb(ids)
+
+
 def _edge_scalars(module, atomic_numbers, edge_distance, edge_index, hetero, source_target):
     """edge_distance, optionally concatenated with source/target element embeddings (ref :1092-1106, 100-113)."""
     if not module.use_atom_edge_embedding:
@@ -897,8 +907,8 @@ def _edge_scalars(module, atomic_numbers, edge_distance, edge_index, hetero, sou
         z_s, z_t = atomic_numbers[source_target[0]], atomic_numbers[source_target[1]]
     else:
         z_s = z_t = atomic_numbers
-    return torch.cat((edge_distance, module.source_embedding(z_s[edge_index[0]]),
-                      module.target_embedding(z_t[edge_index[1]])), dim=1)
+    return torch.cat((edge_distance, embedding_lookup(module.source_embedding, z_s[edge_index[0]]),
+                      embedding_lookup(module.target_embedding, z_t[edge_index[1]])), dim=1)
 
 
 class EdgeDegreeEmbedding(nn.Module):

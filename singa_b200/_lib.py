@@ -50,6 +50,7 @@ SIGNATURES = {
     "efl_radial_mlp_bwd": "pi" + "p" * 10 + "ipppiip",
     "efl_radial_hidden_fwd": "pi" + "p" * 8 + "pip",
     "efl_radial_hidden_bwd": "pi" + "p" * 8 + "pppiip",
+    "efl_embedding_grad": "ppliiippip",
     "efl_radius_graph_bbox": "ppiippp",
     "efl_radius_graph_count": "ppiipfiiifiippppppppl" "p",
     "efl_radius_graph_fill": "iifiiifippppp" "ip",
@@ -108,7 +109,7 @@ def stream_ptr():
 
 
 # kernels launched per entry point (for the launch counter bench.py reports)
-_LAUNCHES = {"efl_gemm_tn_f32": 2, "efl_colsum": 2, "efl_tc_gemm_tn": 2, "efl_so3_linear_bwd_weight": 2}
+_LAUNCHES = {"efl_embedding_grad": 2, "efl_gemm_tn_f32": 2, "efl_colsum": 2, "efl_tc_gemm_tn": 2, "efl_so3_linear_bwd_weight": 2}
 launch_count = 0
 _profile = None  # None, or a list receiving (name, work, start_event, end_event)
 

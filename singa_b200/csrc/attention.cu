@@ -264,3 +264,72 @@ extern "C" int efl_segment_softmax_bwd(const float* alpha, const float* dalpha, 
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Deterministic gradient of an embedding lookup with few rows (source/target element embeddings of the edge scalars,
+// Embedding.py:97-99: 43 rows x 16 channels, E lookups).  torch's embedding_dense_backward sums with float atomics
+// (run-to-run different bits); here every thread owns private accumulators and all reductions run in a fixed order.
+//   stage 1: CTA b takes a contiguous slice of lookups; thread = (sub-lane s, channel c) adds row e into its private
+//            shared-memory table acc[s][id][c]; the sub-lanes are then summed in order -> part[b][rows][C]
+//   stage 2: dW[r][c] = sum_b part[b][r][c] in order
+// ---------------------------------------------------------------------------------------------------
+namespace efl {
+
+__global__ void __launch_bounds__(256) embedding_grad_partial_kernel(const long long* __restrict__ ids,
+                                                                     const float* __restrict__ dx, long long ld,
+                                                                     int E, int rows, int C, float* __restrict__ part) {
+  extern __shared__ float acc[];  // [S][rows][C]
+  const int S = 256 / C;
+  const int s = threadIdx.x / C, c = threadIdx.x % C;
+  for (int i = threadIdx.x; i < S * rows * C; i += blockDim.x) acc[i] = 0.f;
+  __syncthreads();
+  const int per = (E + gridDim.x - 1) / gridDim.x;
+  const int e0 = blockIdx.x * per, e1 = min(E, e0 + per);
+  if (s < S) {
+    float* mine = acc + (size_t)s * rows * C + c;
+    for (int e = e0 + s; e < e1; e += S) {
+      const long long id = ids[e];
+      if (id >= 0 && id < rows) mine[id * C] += dx[(size_t)e * ld + c];
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < rows * C; i += blockDim.x) {
+    float t = 0.f;
+    for (int k = 0; k < S; ++k) t += acc[(size_t)k * rows * C + i];
+    part[(size_t)blockIdx.x * rows * C + i] = t;
+  }
+}
+
+__global__ void embedding_grad_reduce_kernel(const float* __restrict__ part, int nb, int n, float* __restrict__ dW) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float t = 0.f;
+  for (int b = 0; b < nb; ++b) t += part[(size_t)b * n + i];
+  dW[i] = t;
+}
+
+}  // namespace efl
+
+// ids [E] int64, dx rows of ld floats (pointer already offset to the embedding's columns), dW [rows, C].
+// workspace: nblocks * rows * C floats.  C must divide 256; rows * C * (256 / C) floats of shared memory (<= 200 KB).
+extern "C" int efl_embedding_grad(const long long* ids, const float* dx, long long ld, int E, int rows, int C,
+                                  float* dW, float* workspace, int nblocks, void* stream) {
+  EFL_REQUIRE(C > 0 && 256 % C == 0 && rows > 0 && nblocks > 0, "efl_embedding_grad: C must divide 256");
+  const size_t smem = sizeof(float) * (size_t)(256 / C) * rows * C;
+  EFL_REQUIRE(smem <= 200 * 1024, "efl_embedding_grad: table too large for the shared-memory accumulators");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(efl::embedding_grad_partial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
+    if (e != cudaSuccess) {
+      efl_set_error(cudaGetErrorString(e));
+      return (int)e;
+    }
+  }
+  efl::embedding_grad_partial_kernel<<<nblocks, 256, smem, s>>>(ids, dx, ld, E, rows, C, workspace);
+  EFL_CHECK_LAUNCH();
+  const int n = rows * C;
+  efl::embedding_grad_reduce_kernel<<<(n + 255) / 256, 256, 0, s>>>(workspace, nblocks, n, dW);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}

@@ -136,8 +136,8 @@ class EquivariantEmbedding(nn.Module):
             r.set_wigner(rot)
 
     def _edge_scalars(self, dist, z_src, z_dst, ei):
-        return torch.cat((self.distance_expansion(dist), self.source_embedding(z_src[ei[0]]),
-                          self.target_embedding(z_dst[ei[1]])), dim=1)
+        return torch.cat((self.distance_expansion(dist), _ef.embedding_lookup(self.source_embedding, z_src[ei[0]]),
+                          _ef.embedding_lookup(self.target_embedding, z_dst[ei[1]])), dim=1)
 
     def _seed_nodes(self, z, feats):
         x = SO3_Embedding(len(z), self.lmax_list, self.sphere_channels, device=z.device, dtype=torch.long)

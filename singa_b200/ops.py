@@ -614,6 +614,41 @@ class NodeS2ActFunction(torch.autograd.Function):
 
 
 # ---------------------------------------------------------------------------
+# element-embedding lookup of the edge scalars
+# ---------------------------------------------------------------------------
+class EmbeddingLookupFunction(torch.autograd.Function):
+    """weight[ids] with a deterministic backward (csrc/attention.cu: efl_embedding_grad) instead of the float atomics
+    of torch's embedding_dense_backward.  weight [rows, C] with C | 256 and a small table (source/target element
+    embeddings, Embedding.py:97-99)."""
+
+    @staticmethod
+    def eligible(weight) -> bool:
+        rows, C = weight.shape
+        return weight.is_cuda and 256 % C == 0 and rows * 256 * 4 <= 200 * 1024
+
+    @staticmethod
+    def forward(ctx, weight, ids):
+        check_cuda(weight, ids)
+        ids = ids.contiguous().long()
+        ctx.save_for_backward(ids)
+        ctx.shape = tuple(weight.shape)
+        return weight.detach().index_select(0, ids)
+
+    @staticmethod
+    def backward(ctx, dout):
+        (ids,) = ctx.saved_tensors
+        rows, C = ctx.shape
+        dout = dout if dout.stride(-1) == 1 and dout.dtype == torch.float32 else dout.contiguous().float()
+        E = ids.shape[0]
+        dW = torch.empty(rows, C, dtype=torch.float32, device=dout.device)
+        nblk = max(1, min(2 * 148, (E + 1023) // 1024))
+        ws = torch.empty(nblk * rows * C, dtype=torch.float32, device=dout.device)
+        call("efl_embedding_grad", ptr(ids), ptr(dout), dout.stride(0), E, rows, C, ptr(dW), ptr(ws), nblk,
+             work=E * (C * 4.0 + 8.0))
+        return dW, None
+
+
+# ---------------------------------------------------------------------------
 # RadialFunction
 # ---------------------------------------------------------------------------
 class RadialMLPFunction(torch.autograd.Function):

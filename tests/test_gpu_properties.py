@@ -128,3 +128,31 @@ def test_gradients_are_linear_in_the_upstream_gradient(precision):
     assert not bad, bad
     exact = sum(torch.equal(grads[1][n], 2.0 * grads[0][n]) for n in grads[0])
     assert exact >= len(grads[0]) // 2, (exact, len(grads[0]))
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_training_step_is_bitwise_reproducible(precision):
+    """No float atomics anywhere on the step (segment kernels, split-K planes, per-CTA partials and the embedding
+    gradient all reduce in a fixed order): two identical forward+backward passes give identical bits."""
+    import bench
+    from singa_b200 import ops
+    from singa_b200 import synthetic as syn
+    try:
+        model = build_model(DEV, 4, precision)
+        batch, _ = bench.make_batch(0, 4, None)
+        g = {k: v.to(DEV) for k, v in batch.items()}
+        runs = []
+        for _ in range(2):
+            for p in model.parameters():
+                p.grad = None
+            torch.manual_seed(5)
+            out = model(syn.GraphView(g))
+            (out[PROTEIN].embedding.sum() + out[LIGAND].embedding.sum()).backward()
+            runs.append(({k: out[k].embedding.detach().clone() for k in (PROTEIN, LIGAND)},
+                         {n: p.grad.clone() for n, p in model.named_parameters() if p.grad is not None}))
+    finally:
+        ops.set_precision("fp32")
+    for k in runs[0][0]:
+        assert torch.equal(runs[0][0][k], runs[1][0][k]), k
+    for n in runs[0][1]:
+        assert torch.equal(runs[0][1][n], runs[1][1][n]), n
