@@ -15,6 +15,7 @@
 // two worker groups handling alternate edges (thread = channel = TMEM lane), each with private TMEM accumulators
 // and a private S buffer, so the SiLU of one edge overlaps the MMAs / output of the other.
 #include <cuda_fp16.h>
+#include <stdlib.h>
 
 #include "tc_common.cuh"
 
@@ -25,7 +26,8 @@ using namespace efl::tc;
 
 constexpr int CH = 128;
 constexpr int MAX_STAGES = 4;
-constexpr int MAX_GROUPS = 4;
+constexpr int MAX_GROUPS = 6;   // forward (6,2): 6 x 80 TMEM columns; the per-edge hand-off chain is latency-bound, so
+                                // edges in flight (worker groups) are what buys throughput
 constexpr int MAX_THREADS = (4 + 4 * MAX_GROUPS) * 32;
 constexpr int TMEM_COLS = 512;
 
@@ -49,6 +51,7 @@ struct Params {
   long long ld0;           // row pitch (elements) of out[0] per edge
   __nv_bfloat16* dgate;    // bwd: [Ec, ld0] view, already offset
   const __nv_bfloat16* dy0;  // bwd: order-0 rows of dY (row 0 feeds d gate)
+  int dbg;                   // timing experiment (EFL_S2_DBG=1): load only the first channel half
 };
 
 __device__ __forceinline__ float silu_fast(float x) {
@@ -105,7 +108,7 @@ __host__ __device__ inline Layout make_layout(int KP, int GP, int bwd, int NG, i
   L.s_bytes = (CH / 8) * L.sbo;
   L.off_S = o;  o += NG * L.s_bytes;
   L.off_B2 = o; o += (KP / 8) * L.sbo;
-  L.off_bar = o; o += 256;
+  L.off_bar = o; o += 512;
   L.total = o + 1024;
   return L;
 }
@@ -128,10 +131,10 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
   uint64_t* h_full = bars;             // [STAGES]
   uint64_t* h_empty = bars + MAX_STAGES;
   uint64_t* d1_full = bars + 8;        // [MAX_GROUPS]
-  uint64_t* s_ready = bars + 12;
-  uint64_t* d2_full = bars + 16;
-  uint64_t* d2_free = bars + 20;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
+  uint64_t* s_ready = bars + 8 + MAX_GROUPS;
+  uint64_t* d2_full = bars + 8 + 2 * MAX_GROUPS;
+  uint64_t* d2_free = bars + 8 + 3 * MAX_GROUPS;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8 + 4 * MAX_GROUPS);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   // ---- one-time setup: zero operand stages (pad rows must be 0), S buffers; build constant B operands ----
@@ -192,8 +195,8 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
         const int e = it / p.ncb, cb = it % p.ncb;
         mbar_wait(&h_empty[stage], phase ^ 1);
         uint8_t* st = smem + stage * L.stage_bytes;
-        mbar_expect_tx(&h_full[stage], (uint32_t)(row_bytes_total * (BWD ? 2 : 1)));
-        for (int hb = 0; hb < 2; ++hb) {
+        mbar_expect_tx(&h_full[stage], (uint32_t)(row_bytes_total * (BWD ? 2 : 1)) >> (p.dbg & 1));
+        for (int hb = 0; hb < ((p.dbg & 1) ? 1 : 2); ++hb) {
           uint8_t* blk = st + hb * L.blk_bytes;
           tma_load_2d(blk + 0, &mapH0, &h_full[stage], cb * CH + hb * 64, e * R0);
           if (R1 > 0) tma_load_2d(blk + F1 * 128, &mapH1, &h_full[stage], cb * CH + hb * 64, e * R1);
@@ -209,62 +212,63 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
       }
     }
   } else if (warp == 1) {
-    // ---- MMA issuer ----
-    // iteration i: first GEMM(s) of edge i (group i % NG), then the second GEMM of edge i-(NG-1), whose worker
-    // group has had NG-1 iterations to finish its SiLU.  D2 aliases D1, so edge i may only start once its group
-    // has drained D2 of edge i-NG (d2_free).
+    // ---- MMA issuer 1: first GEMM(s) of every edge (group i % NG).  D2 aliases D1, so edge i may only start once
+    // its group has drained D2 of edge i-NG (d2_free).  The second GEMMs are issued by warp 3: one issuing thread
+    // for both put ~150 dependent instructions and four mbarrier waits per edge on a single thread and left the
+    // worker warps waiting on d1_full/d2_full for 60 % of their time (ncu source view).
     int stage = 0;
     uint32_t phase = 0;
-    const int NG = p.NG, lag = p.NG - 1;
+    const int NG = p.NG;
     const uint32_t idesc1 = make_idesc2(GP, 1, 0);   // A = operand tile (MN-major), B = T/F0 (K-major)
+    const uint32_t sT = smem_u32(smem + L.off_T), sF0 = smem_u32(smem + L.off_F0);
+    for (int i = 0; i < n_mine; ++i) {
+      const int g = i % NG;
+      const uint32_t k_th = (uint32_t)(i / NG);
+      mbar_wait(&h_full[stage], phase);
+      mbar_wait(&d2_free[g], (k_th & 1) ^ 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t sa = smem_u32(smem + stage * L.stage_bytes);
+        const uint32_t d1 = tmem_base + (uint32_t)(g * p.gstride);
+#pragma unroll
+        for (int k = 0; k < KP / 16; ++k)
+          tc_mma(d1, make_desc(sa + k * 2048, (uint32_t)L.blk_bytes, 1024), make_desc(sT + k * 32, 16, 1024), idesc1,
+                 k > 0 ? 1u : 0u);
+        if (BWD) {
+          const uint32_t sd = sa + 2 * L.blk_bytes;
+          const uint32_t d3 = d1 + (uint32_t)GP;
+#pragma unroll
+          for (int k = 0; k < KP / 16; ++k)
+            tc_mma(d3, make_desc(sd + k * 2048, (uint32_t)L.blk_bytes, 1024), make_desc(sF0 + k * 32, 16, 1024),
+                   idesc1, k > 0 ? 1u : 0u);
+        }
+        tc_commit(&h_empty[stage]);
+        tc_commit(&d1_full[g]);
+      }
+      __syncwarp();
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 3) {
+    // ---- MMA issuer 2: second GEMM of every edge, as soon as its worker group has written S (s_ready) ----
+    const int NG = p.NG;
     // A = S (K-major), B = B2 (K-major); forward: both fp16 (a_format = b_format = 0)
     const uint32_t idesc2 = BWD ? make_idesc2(KP, 0, 0) : (make_idesc2(KP, 0, 0) & ~((1u << 7) | (1u << 10)));
-    const uint32_t sT = smem_u32(smem + L.off_T), sF0 = smem_u32(smem + L.off_F0), sB2 = smem_u32(smem + L.off_B2);
-    for (int i = 0; i < n_mine + lag; ++i) {
-      for (int pass = 0; pass < 2; ++pass) {
-      // second GEMM: before the first GEMM of edge i when lag > 0, after it when the pipeline has one group
-      const int j = i - lag;
-      if (((lag > 0) == (pass == 0)) && j >= 0 && j < n_mine) {
-        const int g = j % NG;
-        const uint32_t k_th = (uint32_t)(j / NG);
-        mbar_wait(&s_ready[g], k_th & 1);
-        tc_fence_after();
-        if (lane == 0) {
-          const uint32_t sS = smem_u32(smem + L.off_S + g * L.s_bytes);
-          const uint32_t d2 = tmem_base + (uint32_t)(g * p.gstride);
-          for (int k = 0; k < GP / 16; ++k)
-            tc_mma(d2, make_desc_noswz(sS + k * 256, 128, (uint32_t)L.sbo), make_desc_noswz(sB2 + k * 256, 128, (uint32_t)L.sbo),
-                   idesc2, k > 0 ? 1u : 0u);
-          tc_commit(&d2_full[g]);
-        }
-        __syncwarp();
+    const uint32_t sB2 = smem_u32(smem + L.off_B2);
+    for (int j = 0; j < n_mine; ++j) {
+      const int g = j % NG;
+      const uint32_t k_th = (uint32_t)(j / NG);
+      mbar_wait(&s_ready[g], k_th & 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t sS = smem_u32(smem + L.off_S + g * L.s_bytes);
+        const uint32_t d2 = tmem_base + (uint32_t)(g * p.gstride);
+#pragma unroll
+        for (int k = 0; k < GP / 16; ++k)
+          tc_mma(d2, make_desc_noswz(sS + k * 256, 128, (uint32_t)L.sbo), make_desc_noswz(sB2 + k * 256, 128, (uint32_t)L.sbo),
+                 idesc2, k > 0 ? 1u : 0u);
+        tc_commit(&d2_full[g]);
       }
-      if (pass == 0 && i < n_mine) {
-        const int g = i % NG;
-        const uint32_t k_th = (uint32_t)(i / NG);
-        mbar_wait(&h_full[stage], phase);
-        mbar_wait(&d2_free[g], (k_th & 1) ^ 1);
-        tc_fence_after();
-        if (lane == 0) {
-          const uint32_t sa = smem_u32(smem + stage * L.stage_bytes);
-          const uint32_t d1 = tmem_base + (uint32_t)(g * p.gstride);
-          for (int k = 0; k < KP / 16; ++k)
-            tc_mma(d1, make_desc(sa + k * 2048, (uint32_t)L.blk_bytes, 1024), make_desc(sT + k * 32, 16, 1024), idesc1,
-                   k > 0 ? 1u : 0u);
-          if (BWD) {
-            const uint32_t sd = sa + 2 * L.blk_bytes;
-            const uint32_t d3 = d1 + (uint32_t)GP;
-            for (int k = 0; k < KP / 16; ++k)
-              tc_mma(d3, make_desc(sd + k * 2048, (uint32_t)L.blk_bytes, 1024), make_desc(sF0 + k * 32, 16, 1024),
-                     idesc1, k > 0 ? 1u : 0u);
-          }
-          tc_commit(&h_empty[stage]);
-          tc_commit(&d1_full[g]);
-        }
-        __syncwarp();
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
-      }
-      }
+      __syncwarp();
     }
   } else if (warp >= 4 && warp < 4 + 4 * p.NG) {
     // ---- worker groups: thread = channel ----
@@ -282,10 +286,11 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
       const int e = it / p.ncb, cc = (it % p.ncb) * CH + c;
       const size_t cht = (size_t)p.cht;
       // gate path first: its global loads overlap the wait below
-      const float gt = p.gate[(size_t)e * p.gate_ld + cc];
-      float y0;
-      if (!BWD) y0 = silu_fast(gt);
-      else y0 = __bfloat162float(p.dy0[(size_t)e * R0 * cht + cc]) * dsilu_fast(gt);
+      // (the loads are issued here; their first use is after the second GEMM, so their latency hides behind the
+      // SiLU phase instead of stalling the warp in front of it)
+      const float gt = __ldg(p.gate + (size_t)e * p.gate_ld + cc);
+      __nv_bfloat16 dy0v = __float2bfloat16_rn(0.f);
+      if (BWD) dy0v = p.dy0[(size_t)e * R0 * cht + cc];
       mbar_wait(&d1_full[g], k_th & 1);
       tc_fence_after();
       if (!BWD) {
@@ -333,6 +338,9 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
       tc_ld_wait();
       tc_fence_before();
       mbar_arrive(&d2_free[g]);
+      float y0;
+      if (!BWD) y0 = silu_fast(gt);
+      else y0 = __bfloat162float(dy0v) * dsilu_fast(gt);
       if (!DUP) {
         if (!BWD) yv[0] = __float_as_uint(y0);
         else p.dgate[(size_t)e * p.ld0 + cc] = __float2bfloat16_rn(y0);
@@ -341,6 +349,7 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
         __nv_bfloat16* o2 = p.out[2] + (size_t)e * R2 * cht + cc;
 #pragma unroll
         for (int j = 0; j < M; ++j) {
+          if (p.dbg & 2) break;
           __nv_bfloat16* o = j >= F2 ? o2 + (size_t)(j - F2) * cht : (j >= F1 ? o1 + (size_t)(j - F1) * cht : o0 + (size_t)j * cht);
           *o = __float2bfloat16_rn(__uint_as_float(yv[j]));
         }
@@ -388,9 +397,12 @@ int efl_num_sms();
 static int s2_launch(efl::s2tc::Params& p, const void* const* hs, const void* const* ds, long long n_rows_items,
                      cudaStream_t st) {
   using namespace efl::s2tc;
+  { const char* d = getenv("EFL_S2_DBG"); p.dbg = d ? atoi(d) : 0; }
   p.gstride = p.bwd ? 2 * p.GP : p.GP;
   p.NG = TMEM_COLS / p.gstride;
-  if (p.NG > MAX_GROUPS) p.NG = MAX_GROUPS;
+  // worker groups: forward of the (6,2) edge shape runs 6 (896 threads, <= 73 registers); everything else <= 4
+  const int ngcap = (!p.bwd && p.ms[0] == 7 && p.ms[1] == 6 && p.GP == 80) ? MAX_GROUPS : 4;
+  if (p.NG > ngcap) p.NG = ngcap;
   if (p.KP > 48 && p.NG > 2) p.NG = 2;
   p.stages = MAX_STAGES;
   Layout L = make_layout(p.KP, p.GP, p.bwd, p.NG, p.stages);
@@ -410,10 +422,10 @@ static int s2_launch(efl::s2tc::Params& p, const void* const* hs, const void* co
   const int grid = items < efl_num_sms() ? (int)items : efl_num_sms();
   const int threads = (4 + 4 * p.NG) * 32;
   const size_t smem = (size_t)L.total;
-#define S2_LAUNCH(MS0, MS1, MS2, GPV, MAXT)                                                                       \
+#define S2_LAUNCH(MS0, MS1, MS2, GPV, MAXT, MAXTB)                                                                \
   {                                                                                                              \
     if (p.bwd) {                                                                                                 \
-      auto kern = s2act_tc_kernel<MS0, MS1, MS2, GPV, true, MAXT>;                                               \
+      auto kern = s2act_tc_kernel<MS0, MS1, MS2, GPV, true, MAXTB>;                                              \
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, limit);                            \
       kern<<<grid, threads, smem, st>>>(mh[0], mh[1], mh[2], md[0], md[1], md[2], p);                            \
     } else {                                                                                                     \
@@ -422,9 +434,9 @@ static int s2_launch(efl::s2tc::Params& p, const void* const* hs, const void* co
       kern<<<grid, threads, smem, st>>>(mh[0], mh[1], mh[2], md[0], md[1], md[2], p);                            \
     }                                                                                                            \
   }
-  if (p.ms[0] == 7 && p.ms[1] == 6 && p.ms[2] == 5 && p.GP == 80) S2_LAUNCH(7, 6, 5, 80, MAX_THREADS)
-  else if (p.ms[0] == 9 && p.ms[1] == 8 && p.ms[2] == 7 && p.GP == 96) S2_LAUNCH(9, 8, 7, 96, MAX_THREADS)
-  else if (p.ms[0] == 49 && p.ms[1] == 0 && p.GP == 224) S2_LAUNCH(49, 0, 0, 224, 384)
+  if (p.ms[0] == 7 && p.ms[1] == 6 && p.ms[2] == 5 && p.GP == 80) S2_LAUNCH(7, 6, 5, 80, MAX_THREADS, 512)
+  else if (p.ms[0] == 9 && p.ms[1] == 8 && p.ms[2] == 7 && p.GP == 96) S2_LAUNCH(9, 8, 7, 96, 640, 640)
+  else if (p.ms[0] == 49 && p.ms[1] == 0 && p.GP == 224) S2_LAUNCH(49, 0, 0, 224, 384, 384)
   else {
     efl_set_error("efl_s2act_tc: built for (lmax,mmax,G) = (6,2,70), (8,2,90) and node blocks (49 rows, G=210)");
     return EFL_ERR_UNSUPPORTED;

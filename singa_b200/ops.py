@@ -48,6 +48,10 @@ def _should_save(nbytes: int, device) -> bool:
 # backward of rotate-in: "nodes" = node-owned accumulation (no per-edge gradient tensor), "edges" = per-edge d x
 # followed by two segment sums.  Both deterministic; chosen by measurement (tools/edge_bench.py).
 ROTATE_IN_BWD = os.environ.get("EFL_ROTIN_BWD", "nodes")
+# bf16 mode, opt-in experiment: rotate-back + aggregate as per-edge tcgen05 MMAs accumulating in TMEM
+# (csrc/rotate_tc.cu).  Correct for (lmax, mmax) = (6, 2) but measured SLOWER than the SIMT kernel (0.93 vs 0.75 ms on
+# 225 k edges): one edge needs 7 small TMA copies and the per-SM issue rate of small boxes (~0.09 us each) bounds it.
+ROTATE_BACK_TC = os.environ.get("EFL_ROTBACK_TC", "0") == "1"
 
 
 def set_precision(mode: str) -> None:
@@ -341,7 +345,12 @@ def _chunk_forward(d: AttnDims, ws: _Workspace, w1: _Weights, w2: _Weights, x_sr
     for m in range(1, d.mmax + 1):
         _gemm_nt(2, ws.B[m], w2.wm[m - 1], None, ws.V[m], d.ms[m] * VH, None, 0, 0, 2 * Ec, 2 * d.ms[m] * VH,
                  d.ms[m] * H)
-    if out is not None:
+    if out is not None and bf16 and ROTATE_BACK_TC:
+        call("efl_rotate_back_aggregate_tc_fwd", d.lmax, d.mmax, d.heads, d.value_ch, ptr(ws.V[0]), ptr(ws.V[1]),
+             ptr(ws.V[2]), ptr(alpha), ptr(csr.rowptr), ptr(csr.perm), ptr(wig), ptr(out), n0, n1, e0, Ec,
+             work=Ec * _bytes_rotate_back(d, ws.V[0].element_size(), wig.shape[1]) + (n1 - n0) * out[0].numel() * 4,
+             tag="efl_rotate_back_aggregate_fwd")
+    elif out is not None:
         call("efl_rotate_back_aggregate_fwd", d.lmax, d.mmax, d.heads, d.value_ch, bf16, ptr(ws.V[0]), ptr(ws.V[1]),
              ptr(ws.V[2]), ptr(alpha), ptr(csr.rowptr), ptr(csr.perm), ptr(wig), ptr(out), n0, n1, e0,
              work=Ec * _bytes_rotate_back(d, ws.V[0].element_size(), wig.shape[1]) + (n1 - n0) * out[0].numel() * 4)
