@@ -25,7 +25,7 @@ namespace s2tc {
 using namespace efl::tc;
 
 constexpr int CH = 128;
-constexpr int MAX_STAGES = 4;
+constexpr int MAX_STAGES = 8;
 constexpr int MAX_GROUPS = 6;   // forward (6,2): 6 x 80 TMEM columns; the per-edge hand-off chain is latency-bound, so
                                 // edges in flight (worker groups) are what buys throughput
 constexpr int MAX_THREADS = (4 + 4 * MAX_GROUPS) * 32;
@@ -60,22 +60,29 @@ __device__ __forceinline__ float silu_fast(float x) {
   asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
   return fmaf(h, t, h);
 }
-// SiLU of two fp32 accumulator values, evaluated in packed fp16 (one MUFU op for both): x*sigmoid(x) = h + h*tanh(h),
-// h = x/2.  Result = fp16x2 operand word (lo = first value).  fp16 keeps 11 mantissa bits (the bf16 operand it
+// SiLU of two fp32 accumulator values GIVEN AS h = x/2 (the to_grid operand in smem is pre-scaled by 1/2, exact in
+// bf16), evaluated in packed fp16: x*sigmoid(x) = h + h*tanh(h).  Result = fp16x2 operand word (lo = first value).  fp16 keeps 11 mantissa bits (the bf16 operand it
 // replaces kept 8).
 __device__ __forceinline__ uint32_t silu_f16x2(uint32_t lo_f32_bits, uint32_t hi_f32_bits) {
   uint32_t r;
   asm("{\n\t"
-      ".reg .b32 x, h, t, c;\n\t"
-      "cvt.rn.f16x2.f32 x, %2, %1;\n\t"
-      "mov.b32 c, 0x38003800;\n\t"
-      "mul.f16x2 h, x, c;\n\t"
+      ".reg .b32 h, t;\n\t"
+      "cvt.rn.f16x2.f32 h, %2, %1;\n\t"
       "tanh.approx.f16x2 t, h;\n\t"
       "fma.rn.f16x2 %0, h, t, h;\n\t"
       "}"
       : "=r"(r)
       : "f"(__uint_as_float(lo_f32_bits)), "f"(__uint_as_float(hi_f32_bits)));
   return r;
+}
+// w * silu'(x) given h = x/2 and w2 = w/2 (both halvings are folded into the constant MMA operands):
+// silu'(x) = (1 + t + h (1 - t^2)) / 2, t = tanh(h)  ->  one MUFU + three FFMA per grid value
+__device__ __forceinline__ float dsilu_times_half(float h, float w) {
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+  const float u = fmaf(-t, t, 1.f);
+  const float v = fmaf(h, u, t);
+  return fmaf(w, v, w);
 }
 __device__ __forceinline__ float dsilu_fast(float x) {
   float t;
@@ -130,11 +137,11 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
   uint64_t* h_full = bars;             // [STAGES]
   uint64_t* h_empty = bars + MAX_STAGES;
-  uint64_t* d1_full = bars + 8;        // [MAX_GROUPS]
-  uint64_t* s_ready = bars + 8 + MAX_GROUPS;
-  uint64_t* d2_full = bars + 8 + 2 * MAX_GROUPS;
-  uint64_t* d2_free = bars + 8 + 3 * MAX_GROUPS;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8 + 4 * MAX_GROUPS);
+  uint64_t* d1_full = bars + 2 * MAX_STAGES;  // [MAX_GROUPS]
+  uint64_t* s_ready = bars + 2 * MAX_STAGES + MAX_GROUPS;
+  uint64_t* d2_full = bars + 2 * MAX_STAGES + 2 * MAX_GROUPS;
+  uint64_t* d2_free = bars + 2 * MAX_STAGES + 3 * MAX_GROUPS;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * MAX_STAGES + 4 * MAX_GROUPS);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   // ---- one-time setup: zero operand stages (pad rows must be 0), S buffers; build constant B operands ----
@@ -153,19 +160,19 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
       const float t = p.T[i], f = p.F[i];
       // K-major, 128B swizzle, rows g (128 B each), K index j < 64
       const int off_sw = g * 64 + ((((j >> 3) ^ (g & 7)) << 3) | (j & 7));
-      sT[off_sw] = __float2bfloat16_rn(t);
+      sT[off_sw] = __float2bfloat16_rn(0.5f * t);  // D1 = x/2 on the grid: what tanh wants (see silu_f16x2)
       if (BWD) sF0[off_sw] = __float2bfloat16_rn(j == 0 ? 0.f : f);
       // K-major, no swizzle: rows j, K index g: (j/8)*sbo + (g/8)*128 + (j%8)*16 + (g%8)*2 bytes
       const int off_ns = ((j >> 3) * L.sbo + (g >> 3) * 128 + (j & 7) * 16) / 2 + (g & 7);
       // forward: S and from_grid are fp16 operands (SiLU is evaluated in packed f16x2), backward: bf16
-      if (BWD) sB2[off_ns] = __float2bfloat16_rn(t);
+      if (BWD) sB2[off_ns] = __float2bfloat16_rn(0.5f * t);  // S holds 2 dG (dsilu_times_half)
       else reinterpret_cast<__half*>(sB2)[off_ns] = __float2half_rn(f);
     }
   }
   if (threadIdx.x == 0) {
-    for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(&h_full[s], 1); mbar_init(&h_empty[s], 1); }
+    for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(&h_full[s], 1); mbar_init(&h_empty[s], BWD ? 2 : 1); }
     for (int g = 0; g < MAX_GROUPS; ++g) {
-      mbar_init(&d1_full[g], 1);
+      mbar_init(&d1_full[g], BWD ? 2 : 1);  // backward: warps 1 and 2 each commit their GEMM
       mbar_init(&s_ready[g], 128);
       mbar_init(&d2_full[g], 1);
       mbar_init(&d2_free[g], 128);
@@ -234,14 +241,32 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
         for (int k = 0; k < KP / 16; ++k)
           tc_mma(d1, make_desc(sa + k * 2048, (uint32_t)L.blk_bytes, 1024), make_desc(sT + k * 32, 16, 1024), idesc1,
                  k > 0 ? 1u : 0u);
-        if (BWD) {
-          const uint32_t sd = sa + 2 * L.blk_bytes;
-          const uint32_t d3 = d1 + (uint32_t)GP;
+        tc_commit(&h_empty[stage]);
+        tc_commit(&d1_full[g]);
+      }
+      __syncwarp();
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else if (BWD && warp == 2) {
+    // ---- backward only, MMA issuer 1b: D3 = dY tile x F0 (to_grid of the upstream gradient), same waits as warp 1 ----
+    int stage = 0;
+    uint32_t phase = 0;
+    const int NG = p.NG;
+    const uint32_t idesc1 = make_idesc2(GP, 1, 0);
+    const uint32_t sF0 = smem_u32(smem + L.off_F0);
+    for (int i = 0; i < n_mine; ++i) {
+      const int g = i % NG;
+      const uint32_t k_th = (uint32_t)(i / NG);
+      mbar_wait(&h_full[stage], phase);
+      mbar_wait(&d2_free[g], (k_th & 1) ^ 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t sd = smem_u32(smem + stage * L.stage_bytes) + 2 * L.blk_bytes;
+        const uint32_t d3 = tmem_base + (uint32_t)(g * p.gstride) + (uint32_t)GP;
 #pragma unroll
-          for (int k = 0; k < KP / 16; ++k)
-            tc_mma(d3, make_desc(sd + k * 2048, (uint32_t)L.blk_bytes, 1024), make_desc(sF0 + k * 32, 16, 1024),
-                   idesc1, k > 0 ? 1u : 0u);
-        }
+        for (int k = 0; k < KP / 16; ++k)
+          tc_mma(d3, make_desc(sd + k * 2048, (uint32_t)L.blk_bytes, 1024), make_desc(sF0 + k * 32, 16, 1024), idesc1,
+                 k > 0 ? 1u : 0u);
         tc_commit(&h_empty[stage]);
         tc_commit(&d1_full[g]);
       }
@@ -311,20 +336,29 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
           }
         }
       } else {
-#pragma unroll 1
-        for (int g0 = 0; g0 < GP; g0 += 16) {
-          uint32_t v[16], w[16];
-          tc_ld16(d1 + (uint32_t)g0, v);
-          tc_ld16(d3 + (uint32_t)g0, w);
-          tc_ld_wait();
+        // 16 grid columns per step; the TMEM loads of step k+1 are in flight while step k is evaluated (only three
+        // worker warps per scheduler in the backward kernel: the load latency would otherwise be exposed every step)
+        constexpr int NCH = GP / 16;
+        uint32_t v[2][16], w[2][16];
+        tc_ld16(d1, v[0]);
+        tc_ld16(d3, w[0]);
+        tc_ld_wait();
+#pragma unroll
+        for (int k = 0; k < NCH; ++k) {
+          if (k + 1 < NCH) {
+            tc_ld16(d1 + 16u * (k + 1), v[(k + 1) & 1]);
+            tc_ld16(d3 + 16u * (k + 1), w[(k + 1) & 1]);
+          }
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
             float s[8];
 #pragma unroll
-            for (int t = 0; t < 8; ++t) s[t] = __uint_as_float(w[8 * h + t]) * dsilu_fast(__uint_as_float(v[8 * h + t]));
-            *reinterpret_cast<uint4*>(sS + ((g0 >> 3) + h) * 128) =
+            for (int t = 0; t < 8; ++t)
+              s[t] = dsilu_times_half(__uint_as_float(v[k & 1][8 * h + t]), __uint_as_float(w[k & 1][8 * h + t]));
+            *reinterpret_cast<uint4*>(sS + (2 * k + h) * 128) =
                 make_uint4(pack_bf16(s[0], s[1]), pack_bf16(s[2], s[3]), pack_bf16(s[4], s[5]), pack_bf16(s[6], s[7]));
           }
+          if (k + 1 < NCH) tc_ld_wait();
         }
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -404,10 +438,12 @@ static int s2_launch(efl::s2tc::Params& p, const void* const* hs, const void* co
   const int ngcap = (!p.bwd && p.ms[0] == 7 && p.ms[1] == 6 && p.GP == 80) ? MAX_GROUPS : 4;
   if (p.NG > ngcap) p.NG = ngcap;
   if (p.KP > 48 && p.NG > 2) p.NG = 2;
-  p.stages = MAX_STAGES;
+  // operand ring: as deep as shared memory allows (<= MAX_STAGES; EFL_S2_STAGES caps it for timing experiments)
+  p.stages = 4;
+  { const char* d = getenv("EFL_S2_STAGES"); if (d && atoi(d) >= 2 && atoi(d) <= MAX_STAGES) p.stages = atoi(d); }
   Layout L = make_layout(p.KP, p.GP, p.bwd, p.NG, p.stages);
   const int limit = 227 * 1024;
-  if (L.total > limit) { p.stages = 2; L = make_layout(p.KP, p.GP, p.bwd, p.NG, p.stages); }
+  while (L.total > limit && p.stages > 2) { --p.stages; L = make_layout(p.KP, p.GP, p.bwd, p.NG, p.stages); }
   EFL_REQUIRE(L.total <= limit, "efl_s2act_tc: shared memory budget exceeded");
   CUtensorMap mh[3], md[3];
   for (int s = 0; s < 3; ++s) {
