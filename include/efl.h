@@ -146,6 +146,9 @@ int efl_colsum(int bf16, const void* X, long long ld, int rows, int cols, float*
 int efl_tc_gemm_nt(int epilogue, const void* A, long long lda, const void* B, long long ldb, const float* bias,
                    void* C, long long ldc, float* C0, long long ldc0, int nsplit, int M, int N, int K, void* stream);
 int efl_tc_gemm_tn_splits(int Mred, int N1, int N2);
+/* CTA-pair (cta_group::2, 256-row tiles) variant of efl_tc_gemm_nt: 0 off (default), 1 large problems, 2 always.
+ * Returns the previous mode; a mode outside 0..2 only queries. */
+int efl_tc_gemm_pair_mode(int mode);
 int efl_tc_gemm_tn(const void* A, long long lda, const void* B, long long ldb, float* C, long long ldc,
                    int accumulate, float* workspace, int Mred, int N1, int N2, void* stream);
 

@@ -81,6 +81,8 @@ def _load():
     lib.efl_gemm_tn_splits.restype = _I
     lib.efl_tc_gemm_tn_splits.argtypes = [_I, _I, _I]
     lib.efl_tc_gemm_tn_splits.restype = _I
+    lib.efl_tc_gemm_pair_mode.argtypes = [_I]
+    lib.efl_tc_gemm_pair_mode.restype = _I
     lib.efl_radial_mlp_part_size.argtypes = [_I, _I]
     lib.efl_radial_mlp_part_size.restype = _I
     lib.efl_radial_hidden_part_size.argtypes = [_I]

@@ -48,6 +48,10 @@ struct Params {
   int tma_c, tma_c0;  // output tensor maps valid: full-width blocks leave through TMA stores
 };
 
+// PAIR: the two CTAs of a (2,1,1) cluster work on one 256-row tile with cta_group::2 MMAs: each CTA stages its own
+// 128 rows of A and HALF of the B tile, so the L2->SM operand traffic per SM drops by a third at BN = 256 (and the
+// shared-memory reads of B halve); accumulators, epilogue and output rows stay per CTA.
+template <bool PAIR>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                const __grid_constant__ CUtensorMap mapC, const __grid_constant__ CUtensorMap mapC0, const Params p) {
@@ -62,7 +66,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tn = p.mode == 1;
-  const int m_tiles = (p.M + BM - 1) / BM;
+  constexpr int TILE_M = PAIR ? 2 * BM : BM;
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;          // 0 = leader (issues the MMAs)
+  const int cta0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;   // first work item of this CTA (pair)
+  const int cta_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int m_tiles = (p.M + TILE_M - 1) / TILE_M;
   const int n_tiles = p.N / p.BN;
   const int kb_total = (p.K + BK - 1) / BK;
   const int work_items = m_tiles * n_tiles * (tn ? p.splits : 1);
@@ -74,58 +82,83 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], 256);
+      mbar_init(&tempty[a], PAIR ? 512 : 256);  // pair: both CTAs' epilogue threads arrive at the leader
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                 "r"((uint32_t)TMEM_COLS));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    if (PAIR) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                   "r"((uint32_t)TMEM_COLS));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::);
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                   "r"((uint32_t)TMEM_COLS));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();   // the peer's barriers must be initialised before anything signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   // number of 64-wide MN blocks of the B operand in TN mode
-  const int b_blocks = (p.BN + 63) / 64;
-  const uint32_t stage_tx = tn ? (uint32_t)((2 + b_blocks) * 64 * 128) : (uint32_t)(A_BYTES + p.BN * 128);
+  const int bn_cta = PAIR ? p.BN / 2 : p.BN;   // B columns staged by this CTA
+  const int b_blocks = (bn_cta + 63) / 64;
+  const uint32_t stage_tx =
+      (tn ? (uint32_t)((2 + b_blocks) * 64 * 128) : (uint32_t)(A_BYTES + bn_cta * 128)) * (PAIR ? 2u : 1u);
 
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int w = blockIdx.x; w < work_items; w += gridDim.x) {
+      for (int w = cta0; w < work_items; w += cta_step) {
         int z = 0, t = w;
         if (tn) { z = w / (m_tiles * n_tiles); t = w % (m_tiles * n_tiles); }
         const int m_blk = t / n_tiles, n_blk = t % n_tiles;
         const int kb0 = tn ? z * p.kb_per_split : 0;
         const int kb1 = tn ? min(kb_total, kb0 + p.kb_per_split) : kb_total;
+        const int a_row = m_blk * TILE_M + (int)rank * BM;        // this CTA's rows of A (NT) / columns (TN)
+        const int b_col = n_blk * p.BN + (int)rank * bn_cta;      // this CTA's part of the B tile
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_BYTES;
-          mbar_expect_tx(&full[stage], stage_tx);
-          if (!tn) {
-            tma_load_2d(sa, &mapA, &full[stage], kb * BK, m_blk * BM);
-            tma_load_2d(sb, &mapB, &full[stage], kb * BK, n_blk * p.BN);
+          if (!PAIR) {
+            mbar_expect_tx(&full[stage], stage_tx);
+            if (!tn) {
+              tma_load_2d(sa, &mapA, &full[stage], kb * BK, a_row);
+              tma_load_2d(sb, &mapB, &full[stage], kb * BK, b_col);
+            } else {
+              for (int b = 0; b < 2; ++b) tma_load_2d(sa + b * 8192, &mapA, &full[stage], a_row + b * 64, kb * BK);
+              for (int b = 0; b < b_blocks; ++b) tma_load_2d(sb + b * 8192, &mapB, &full[stage], b_col + b * 64, kb * BK);
+            }
           } else {
-            for (int b = 0; b < 2; ++b) tma_load_2d(sa + b * 8192, &mapA, &full[stage], m_blk * BM + b * 64, kb * BK);
-            for (int b = 0; b < b_blocks; ++b)
-              tma_load_2d(sb + b * 8192, &mapB, &full[stage], n_blk * p.BN + b * 64, kb * BK);
+            // the leader's barrier collects the bytes of both CTAs (its expect_tx covers both; the peer's bytes may
+            // land first, the phase cannot complete before the leader's arrive)
+            if (rank == 0) mbar_expect_tx(&full[stage], stage_tx);
+            const uint32_t fb = mapa_u32(&full[stage], 0);
+            if (!tn) {
+              tma_load_2d_pair(sa, &mapA, fb, kb * BK, a_row);
+              tma_load_2d_pair(sb, &mapB, fb, kb * BK, b_col);
+            } else {
+              for (int b = 0; b < 2; ++b) tma_load_2d_pair(sa + b * 8192, &mapA, fb, a_row + b * 64, kb * BK);
+              for (int b = 0; b < b_blocks; ++b) tma_load_2d_pair(sb + b * 8192, &mapB, fb, b_col + b * 64, kb * BK);
+            }
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == 1 && rank == 0) {
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    const uint32_t idesc = make_idesc(p.BN, tn);
-    for (int w = blockIdx.x; w < work_items; w += gridDim.x) {
+    // pair: M = 256 (m_dim field = M >> 4 at bit 24)
+    const uint32_t idesc = PAIR ? ((make_idesc(p.BN, tn) & ~(31u << 24)) | ((uint32_t)(256 >> 4) << 24)) : make_idesc(p.BN, tn);
+    for (int w = cta0; w < work_items; w += cta_step) {
       int z = 0;
       if (tn) z = w / (m_tiles * n_tiles);
       const int kb0 = tn ? z * p.kb_per_split : 0;
@@ -149,10 +182,16 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
               ad = make_desc(sa + k * 2048, 8192, 1024);
               bd = make_desc(sb + k * 2048, 8192, 1024);
             }
-            tc_mma(tmem_d, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            if (PAIR) tc_mma_pair(tmem_d, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            else tc_mma(tmem_d, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          tc_commit(&empty[stage]);
-          if (kb == kb1 - 1) tc_commit(&tfull[acc]);
+          if (PAIR) {
+            tc_commit_pair(&empty[stage]);
+            if (kb == kb1 - 1) tc_commit_pair(&tfull[acc]);
+          } else {
+            tc_commit(&empty[stage]);
+            if (kb == kb1 - 1) tc_commit(&tfull[acc]);
+          }
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -175,11 +214,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     int acc = 0;
     uint32_t acc_phase = 0;
     bool pending = false;  // a bulk store may still be reading this warp's staging tile
-    for (int w = blockIdx.x; w < work_items; w += gridDim.x) {
+    const uint32_t tempty_leader0 = PAIR ? mapa_u32(&tempty[0], 0) : 0u;
+    for (int w = cta0; w < work_items; w += cta_step) {
       int z = 0, t = w;
       if (tn) { z = w / (m_tiles * n_tiles); t = w % (m_tiles * n_tiles); }
       const int m_blk = t / n_tiles, n_blk = t % n_tiles;
-      const int row0 = m_blk * BM + q * 32;
+      const int row0 = m_blk * TILE_M + (int)rank * BM + q * 32;
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr0 = tmem_base + (uint32_t)(acc * MAX_BN) + ((uint32_t)(q * 32) << 16);
@@ -304,17 +344,22 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         c += wcols;
       }
       tc_fence_before();
-      mbar_arrive(&tempty[acc]);
+      if (PAIR) mbar_arrive_cluster(tempty_leader0 + 8u * (uint32_t)acc);
+      else mbar_arrive(&tempty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (pending && lane == 0) tma_store_wait_read();
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();   // neither CTA may leave (or free TMEM) while its partner's MMAs/arrives are in flight
+  else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TMEM_COLS));
+    if (PAIR)
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TMEM_COLS));
+    else
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TMEM_COLS));
   }
 }
 
@@ -409,20 +454,64 @@ int efl_num_sms() {
   return n;
 }
 
+// CTA-pair mode of the NT GEMMs: 0 = single-CTA tiles only (default: measured faster or equal on every shape of the
+// path), 1 = pairs for the large NT GEMMs, 2 = pairs for every NT GEMM.  EFL_GEMM_PAIR presets it;
+// efl_tc_gemm_pair_mode() switches it at run time (tests, tools/kernel_bench.py).
+static int g_pair_mode = -1;
+static int pair_mode() {
+  if (g_pair_mode < 0) {
+    const char* e = getenv("EFL_GEMM_PAIR");
+    g_pair_mode = e ? atoi(e) : 0;
+  }
+  return g_pair_mode;
+}
+extern "C" int efl_tc_gemm_pair_mode(int mode) {
+  const int prev = pair_mode();
+  if (mode >= 0 && mode <= 2) g_pair_mode = mode;
+  return prev;
+}
+
 static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mc0,
-                  const Params& p, int work_items, cudaStream_t s) {
+                  const Params& p, int work_items, bool pair, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(efl::tc::tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(efl::tc::tc_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          efl::tc::SMEM_BYTES);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(efl::tc::tc_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               efl::tc::SMEM_BYTES);
     if (e != cudaSuccess) {
       efl_set_error(cudaGetErrorString(e));
       return (int)e;
     }
     attr_set = true;
   }
-  const int grid = work_items < efl_num_sms() ? work_items : efl_num_sms();
-  efl::tc::tc_gemm_kernel<<<grid, efl::tc::NUM_THREADS, efl::tc::SMEM_BYTES, s>>>(ma, mb, mc, mc0, p);
+  if (!pair) {
+    const int grid = work_items < efl_num_sms() ? work_items : efl_num_sms();
+    efl::tc::tc_gemm_kernel<false><<<grid, efl::tc::NUM_THREADS, efl::tc::SMEM_BYTES, s>>>(ma, mb, mc, mc0, p);
+    EFL_CHECK_LAUNCH();
+    return EFL_OK;
+  }
+  // one CTA pair (cluster of 2 = the two SMs of a TPC) per work item, persistent over at most num_sms / 2 pairs
+  int pairs = efl_num_sms() / 2;
+  if (work_items < pairs) pairs = work_items;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(2 * pairs));
+  cfg.blockDim = dim3(efl::tc::NUM_THREADS);
+  cfg.dynamicSmemBytes = efl::tc::SMEM_BYTES;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, efl::tc::tc_gemm_kernel<true>, ma, mb, mc, mc0, p);
+  if (e != cudaSuccess) {
+    efl_set_error(cudaGetErrorString(e));
+    return (int)e;
+  }
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }
@@ -441,7 +530,9 @@ extern "C" int efl_tc_gemm_nt(int epilogue, const void* A, long long lda, const 
   CUtensorMap ma, mb;
   int rc = efl_make_map_bf16(&ma, A, M, K, lda, efl::tc::BM);
   if (rc) return rc;
-  rc = efl_make_map_bf16(&mb, B, N, K, ldb, bn);
+  // CTA pairs pay off once there are enough 256-row tiles to fill the 74 pairs
+  const bool pair = pair_mode() >= 2 || (pair_mode() == 1 && M >= 256 * (efl_num_sms() / 2));
+  rc = efl_make_map_bf16(&mb, B, N, K, ldb, pair ? bn / 2 : bn);
   if (rc) return rc;
   Params p{};
   p.mode = 0; p.M = M; p.N = N; p.K = K; p.BN = bn; p.epi = epilogue;
@@ -451,8 +542,9 @@ extern "C" int efl_tc_gemm_nt(int epilogue, const void* A, long long lda, const 
   const long long ccols = epilogue == 2 ? N / 2 : (epilogue == 1 ? N - nsplit : N);
   make_out_map(&mc, &p.tma_c, 0, ccols > 0 ? C : nullptr, 0, M, ccols, ldc);
   make_out_map(&mc0, &p.tma_c0, 1, epilogue == 1 ? C0 : nullptr, 0, M, nsplit, ldc0);
-  const int tiles = ((M + efl::tc::BM - 1) / efl::tc::BM) * (N / bn);
-  return launch(ma, mb, mc, mc0, p, tiles, (cudaStream_t)stream);
+  const int tile_m = pair ? 2 * efl::tc::BM : efl::tc::BM;
+  const int tiles = ((M + tile_m - 1) / tile_m) * (N / bn);
+  return launch(ma, mb, mc, mc0, p, tiles, pair, (cudaStream_t)stream);
 }
 
 // Split count for the weight-gradient GEMM.  Work items = tiles x splits run on a persistent grid of one CTA per
@@ -509,7 +601,7 @@ extern "C" int efl_tc_gemm_tn(const void* A, long long lda, const void* B, long 
   CUtensorMap mc, mc0;
   make_out_map(&mc, &p.tma_c, 0, nullptr, 0, 0, 0, 0);
   make_out_map(&mc0, &p.tma_c0, 1, workspace, splits, N1, N2, N2);
-  rc = launch(ma, mb, mc, mc0, p, tiles * splits, s);
+  rc = launch(ma, mb, mc, mc0, p, tiles * splits, false, s);
   if (rc) return rc;
   const long long n = (long long)N1 * N2;
   efl::splitk_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(workspace, splits, n, C, ldc, N2, accumulate);

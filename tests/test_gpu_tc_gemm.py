@@ -17,8 +17,17 @@ def _rand(m, n, scale=1.0):
     return (torch.randn(m, n, device=DEV) * scale).to(torch.bfloat16)
 
 
+@pytest.fixture(params=[0, 2], ids=["single_cta", "cta_pair"])
+def pair_mode(request):
+    """Every NT test runs on the single-CTA tiles and on the cta_group::2 pair tiles (256-row tiles, two SMs)."""
+    from singa_b200 import _lib
+    prev = _lib.LIB.efl_tc_gemm_pair_mode(request.param)
+    yield request.param
+    _lib.LIB.efl_tc_gemm_pair_mode(prev)
+
+
 @pytest.mark.parametrize("M,N,K", NT_SHAPES)
-def test_nt_plain(M, N, K):
+def test_nt_plain(M, N, K, pair_mode):
     from singa_b200 import tc_gemm
     torch.manual_seed(M + N + K)
     A, B = _rand(M, K), _rand(N, K, 0.1)
@@ -30,7 +39,7 @@ def test_nt_plain(M, N, K):
     assert err < 1e-2, err
 
 
-def test_nt_split_epilogue():
+def test_nt_split_epilogue(pair_mode):
     from singa_b200 import tc_gemm
     M, N, K, ns = 777, 1248, 224, 352
     A, B = _rand(M, K), _rand(N, K, 0.1)
@@ -43,7 +52,7 @@ def test_nt_split_epilogue():
     assert float((C.float() - ref[:, ns:]).abs().max()) < 1e-2 * float(ref.abs().max())
 
 
-def test_nt_complex_epilogue():
+def test_nt_complex_epilogue(pair_mode):
     from singa_b200 import ops, tc_gemm
     E, K, half = 501, 192, 768
     A = _rand(2 * E, K)
