@@ -20,7 +20,8 @@ namespace tc {
 constexpr int BM = 128;         // UMMA M (rows of the accumulator = TMEM lanes)
 constexpr int BK = 64;          // 64 bf16 = 128 bytes = one swizzle span
 constexpr int UMMA_K = 16;
-constexpr int STAGES = 4;
+constexpr int STAGES = 4;       // ring depth at the largest stage (BN = 256); smaller stages get more, see nstage
+constexpr int MAX_STAGES = 8;
 constexpr int MAX_BN = 256;
 constexpr int A_BYTES = BM * BK * 2;       // 16 KB
 constexpr int B_BYTES = MAX_BN * BK * 2;   // 32 KB
@@ -58,13 +59,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
-  uint64_t* full = bars;                 // [STAGES]
-  uint64_t* empty = bars + STAGES;       // [STAGES]
-  uint64_t* tfull = bars + 2 * STAGES;   // [2]
-  uint64_t* tempty = bars + 2 * STAGES + 2;  // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  uint64_t* full = bars;                     // [MAX_STAGES]
+  uint64_t* empty = bars + MAX_STAGES;       // [MAX_STAGES]
+  uint64_t* tfull = bars + 2 * MAX_STAGES;   // [2]
+  uint64_t* tempty = bars + 2 * MAX_STAGES + 2;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * MAX_STAGES + 4);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   const int tn = p.mode == 1;
   constexpr int TILE_M = PAIR ? 2 * BM : BM;
   const uint32_t rank = PAIR ? cluster_ctarank() : 0u;          // 0 = leader (issues the MMAs)
@@ -76,7 +77,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   const int work_items = m_tiles * n_tiles * (tn ? p.splits : 1);
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; ++s) {
+    for (int s = 0; s < MAX_STAGES; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
@@ -106,11 +107,15 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   // number of 64-wide MN blocks of the B operand in TN mode
   const int bn_cta = PAIR ? p.BN / 2 : p.BN;   // B columns staged by this CTA
   const int b_blocks = (bn_cta + 63) / 64;
-  const uint32_t stage_tx =
-      (tn ? (uint32_t)((2 + b_blocks) * 64 * 128) : (uint32_t)(A_BYTES + bn_cta * 128)) * (PAIR ? 2u : 1u);
+  // One stage = the A block + this CTA's part of the B tile (both multiples of 1 KB = the swizzle atom).  The ring
+  // is as deep as the 192 KB operand region allows: the operand loads are latency-bound (~2500 cycles from "stage
+  // free" to "stage full" under load, ncu r1i), so bytes in flight, not stage count, set the pace.
+  const int stage_bytes = tn ? (2 + b_blocks) * 64 * 128 : A_BYTES + bn_cta * 128;
+  const int nstage = min(MAX_STAGES, (STAGES * STAGE_BYTES) / stage_bytes);
+  const uint32_t stage_tx = (uint32_t)stage_bytes * (PAIR ? 2u : 1u);
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int w = cta0; w < work_items; w += cta_step) {
@@ -123,7 +128,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         const int b_col = n_blk * p.BN + (int)rank * bn_cta;      // this CTA's part of the B tile
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
-          uint8_t* sa = smem + stage * STAGE_BYTES;
+          uint8_t* sa = smem + stage * stage_bytes;
           uint8_t* sb = sa + A_BYTES;
           if (!PAIR) {
             mbar_expect_tx(&full[stage], stage_tx);
@@ -147,17 +152,28 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
               for (int b = 0; b < b_blocks; ++b) tma_load_2d_pair(sb + b * 8192, &mapB, fb, b_col + b * 64, kb * BK);
             }
           }
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == nstage) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1 && rank == 0) {
+    // MMA issuer.  The loop is kept as short as possible: one thread issues four MMAs and the commits per K block,
+    // and at ~110 instructions per K block (descriptor construction, waterfall loops around every tcgen05
+    // instruction) that thread, not the tensor pipe, set the pace (ncu r1i: 750 cycles per K block for every BN,
+    // producer spinning on "empty").  Descriptors differ between stages / K steps only in the 14-bit start-address
+    // field (bytes >> 4), so they are advanced by adds; control flow is warp-uniform, the issuing lane is elected.
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
     // pair: M = 256 (m_dim field = M >> 4 at bit 24)
     const uint32_t idesc = PAIR ? ((make_idesc(p.BN, tn) & ~(31u << 24)) | ((uint32_t)(256 >> 4) << 24)) : make_idesc(p.BN, tn);
+    const uint32_t smem_base = smem_u32(smem);
+    const uint64_t adesc0 = tn ? make_desc(smem_base, 8192, 1024) : make_desc(smem_base, 16, 1024);
+    const uint64_t bdesc0 = tn ? make_desc(smem_base + A_BYTES, 8192, 1024) : make_desc(smem_base + A_BYTES, 16, 1024);
+    const uint64_t kstep = tn ? (2048u >> 4) : (32u >> 4);
+    const uint64_t sstep = (uint64_t)(stage_bytes >> 4);
+    const bool issuer = elect_one();
     for (int w = cta0; w < work_items; w += cta_step) {
       int z = 0;
       if (tn) z = w / (m_tiles * n_tiles);
@@ -169,32 +185,24 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(&full[stage], phase);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
-          const uint32_t sb = sa + A_BYTES;
-#pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            uint64_t ad, bd;
-            if (!tn) {
-              ad = make_desc(sa + k * 32, 16, 1024);
-              bd = make_desc(sb + k * 32, 16, 1024);
-            } else {
-              ad = make_desc(sa + k * 2048, 8192, 1024);
-              bd = make_desc(sb + k * 2048, 8192, 1024);
-            }
-            if (PAIR) tc_mma_pair(tmem_d, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-            else tc_mma(tmem_d, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-          }
+        if (issuer) {
+          const uint64_t ad = adesc0 + sstep * (uint64_t)stage, bd = bdesc0 + sstep * (uint64_t)stage;
           if (PAIR) {
+            tc_mma_pair(tmem_d, ad, bd, idesc, kb > kb0 ? 1u : 0u);
+#pragma unroll
+            for (int k = 1; k < BK / UMMA_K; ++k) tc_mma_pair(tmem_d, ad + kstep * k, bd + kstep * k, idesc, 1u);
             tc_commit_pair(&empty[stage]);
             if (kb == kb1 - 1) tc_commit_pair(&tfull[acc]);
           } else {
+            tc_mma(tmem_d, ad, bd, idesc, kb > kb0 ? 1u : 0u);
+#pragma unroll
+            for (int k = 1; k < BK / UMMA_K; ++k) tc_mma(tmem_d, ad + kstep * k, bd + kstep * k, idesc, 1u);
             tc_commit(&empty[stage]);
             if (kb == kb1 - 1) tc_commit(&tfull[acc]);
           }
         }
         __syncwarp();
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        if (++stage == nstage) { stage = 0; phase ^= 1; }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
@@ -363,6 +371,31 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   }
 }
 
+// C[c, r] (+)= sum_z P[z][r, c]: fixed-order reduction of the split-K planes of a swapped wgrad product (planes are
+// [R, Cc] = C^T), transposed through a 32x33 shared tile so both sides stay coalesced.
+__global__ void splitk_reduce_transposed_kernel(const float* __restrict__ P, int splits, int R, int Cc,
+                                                float* __restrict__ C, long long ldc, int accumulate) {
+  __shared__ float tile[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  const size_t plane = (size_t)R * Cc;
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int r = r0 + j, c = c0 + threadIdx.x;
+    float acc = 0.f;
+    if (r < R && c < Cc)
+      for (int z = 0; z < splits; ++z) acc += P[z * plane + (size_t)r * Cc + c];
+    tile[j][threadIdx.x] = acc;
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int c = c0 + j, r = r0 + threadIdx.x;
+    if (r < R && c < Cc) {
+      float* o = C + (size_t)c * ldc + r;
+      const float v = tile[threadIdx.x][j];
+      *o = accumulate ? (*o + v) : v;
+    }
+  }
+}
+
 }  // namespace tc
 }  // namespace efl
 
@@ -454,16 +487,28 @@ int efl_num_sms() {
   return n;
 }
 
-// CTA-pair mode of the NT GEMMs: 0 = single-CTA tiles only (default: measured faster or equal on every shape of the
-// path), 1 = pairs for the large NT GEMMs, 2 = pairs for every NT GEMM.  EFL_GEMM_PAIR presets it;
-// efl_tc_gemm_pair_mode() switches it at run time (tests, tools/kernel_bench.py).
+// CTA-pair mode: 0 = single-CTA tiles only, 1 = pairs where they measured faster (default; nt_use_pair /
+// tn_use_pair), 2 = pairs for every GEMM (tests).  EFL_GEMM_PAIR presets it; efl_tc_gemm_pair_mode() switches it at
+// run time (tests, tools/kernel_bench.py).
 static int g_pair_mode = -1;
 static int pair_mode() {
   if (g_pair_mode < 0) {
     const char* e = getenv("EFL_GEMM_PAIR");
-    g_pair_mode = e ? atoi(e) : 0;
+    g_pair_mode = e ? atoi(e) : 1;
   }
   return g_pair_mode;
+}
+// NT: pairs pay off when the main loop, not the epilogue, sets the pace (K >= 512) and the half B tile is still a
+// decent MMA operand; there must be enough 256-row tiles to fill the pairs (tools/kernel_bench.py, r1 v4).
+static bool nt_use_pair(int M, int K, int bn) {
+  const int m = pair_mode();
+  if (m >= 2) return true;
+  return m == 1 && M >= 256 * (efl_num_sms() / 2) && K >= 512 && bn >= 128;
+}
+static bool tn_use_pair(int n1, int n2, int bn) {
+  const int m = pair_mode();
+  if (m >= 2) return true;
+  return m == 1 && n2 == bn && (n1 + 255) / 256 * 256 == (n1 + 127) / 128 * 128;
 }
 extern "C" int efl_tc_gemm_pair_mode(int mode) {
   const int prev = pair_mode();
@@ -531,7 +576,7 @@ extern "C" int efl_tc_gemm_nt(int epilogue, const void* A, long long lda, const 
   int rc = efl_make_map_bf16(&ma, A, M, K, lda, efl::tc::BM);
   if (rc) return rc;
   // CTA pairs pay off once there are enough 256-row tiles to fill the 74 pairs
-  const bool pair = pair_mode() >= 2 || (pair_mode() == 1 && M >= 256 * (efl_num_sms() / 2));
+  const bool pair = nt_use_pair(M, K, bn);
   rc = efl_make_map_bf16(&mb, B, N, K, ldb, pair ? bn / 2 : bn);
   if (rc) return rc;
   Params p{};
@@ -547,15 +592,38 @@ extern "C" int efl_tc_gemm_nt(int epilogue, const void* A, long long lda, const 
   return launch(ma, mb, mc, mc0, p, tiles, pair, (cudaStream_t)stream);
 }
 
-// Split count for the weight-gradient GEMM.  Work items = tiles x splits run on a persistent grid of one CTA per
-// SM, so the count is chosen against wave quantisation: the smallest split (>= 8 k-blocks each) whose last wave is
-// >= 94 % full, else the best-filled one; at most 4 waves' worth of partial planes.
-extern "C" int efl_tc_gemm_tn_splits(int Mred, int N1, int N2) {
-  const int bn = pick_bn(N2);
-  if (bn <= 0) return 1;
-  const int tiles = ((N1 + efl::tc::BM - 1) / efl::tc::BM) * (N2 / bn);
+// Plan of one wgrad GEMM  C[N1, N2] = A[Mred, N1]^T B[Mred, N2].
+//  * orientation: the kernel's tile is 128 (M side) x BN (N side, a divisor of the N extent); either operand can
+//    take the M side (the swapped product is C^T, transposed back by the split-K reduction).  The model below - tile
+//    count x max(MMA cycles, operand bytes / 62 B/clk of L2->SM feed per SM) per K block - picked the faster
+//    orientation on all six wgrad shapes of the path (tools/kernel_bench.py --only tnx); a swap must win by 10 %.
+//  * CTA pairs only where the 256-row tiles add no padding and the N side is a single tile (the conv1 shapes).
+//  * split over the reduced (edge) dimension: the output is only N1 x N2, so without splits just (N1/128) x (N2/BN)
+//    CTAs would work; the smallest split (>= 8 K blocks each) whose last wave is >= 94 % full, else the best-filled
+//    one; at most 4 waves' worth of partial planes.
+struct TnPlan {
+  bool swap, pair;
+  int bn, splits;
+};
+static double tn_cost(int n1, int n2) {
+  const int bn = pick_bn(n2);
+  if (bn <= 0) return 1e30;
+  const double tiles = (double)((n1 + 127) / 128) * (n2 / bn);
+  const double mma = 2.0 * bn;                                   // 4 MMAs of bn/2 cycles per K block
+  const double feed = (16384.0 + ((bn + 63) / 64) * 8192.0) / 62.0;
+  return tiles * (mma > feed ? mma : feed);
+}
+static TnPlan tn_plan(int Mred, int N1, int N2) {
+  TnPlan pl{};
+  pl.swap = pair_mode() != 0 && (N1 % 16 == 0) && tn_cost(N2, N1) < 0.9 * tn_cost(N1, N2);
+  const int n1 = pl.swap ? N2 : N1, n2 = pl.swap ? N1 : N2;
+  pl.bn = pick_bn(n2);
+  if (pl.bn <= 0) { pl.splits = 1; return pl; }
+  pl.pair = tn_use_pair(n1, n2, pl.bn);
+  const int tile_m = pl.pair ? 2 * efl::tc::BM : efl::tc::BM;
+  const int tiles = ((n1 + tile_m - 1) / tile_m) * (n2 / pl.bn);
   const int kb = (Mred + efl::tc::BK - 1) / efl::tc::BK;
-  const int sms = efl_num_sms();
+  const int sms = pl.pair ? efl_num_sms() / 2 : efl_num_sms();   // scheduling units: CTAs or CTA pairs
   int smax = kb / 8;
   if (smax < 1) smax = 1;
   const int cap = (4 * sms + tiles - 1) / tiles;
@@ -570,8 +638,11 @@ extern "C" int efl_tc_gemm_tn_splits(int Mred, int N1, int N2) {
     if (eff >= 0.94) { best = s; break; }
   }
   const int per = (kb + best - 1) / best;
-  return (kb + per - 1) / per;
+  pl.splits = (kb + per - 1) / per;
+  return pl;
 }
+
+extern "C" int efl_tc_gemm_tn_splits(int Mred, int N1, int N2) { return tn_plan(Mred, N1, N2).splits; }
 
 // defined in gemm_simt.cu
 namespace efl {
@@ -583,28 +654,39 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ P, int splits, lo
 extern "C" int efl_tc_gemm_tn(const void* A, long long lda, const void* B, long long ldb, float* C, long long ldc,
                               int accumulate, float* workspace, int Mred, int N1, int N2, void* stream) {
   if (N1 <= 0 || N2 <= 0) return EFL_OK;
-  const int bn = pick_bn(N2);
-  EFL_REQUIRE(bn > 0, "efl_tc_gemm_tn: N2 must be a multiple of 16");
+  EFL_REQUIRE(pick_bn(N2) > 0, "efl_tc_gemm_tn: N2 must be a multiple of 16");
   EFL_REQUIRE(Mred > 0, "efl_tc_gemm_tn: empty reduction");
+  const TnPlan pl = tn_plan(Mred, N1, N2);
+  // the kernel computes P[z][n1, n2]; swapped: (n1, n2) = (N2, N1) with the operands exchanged
+  const int n1 = pl.swap ? N2 : N1, n2 = pl.swap ? N1 : N2;
+  const void* Am = pl.swap ? B : A;
+  const void* Bm = pl.swap ? A : B;
+  const long long ldam = pl.swap ? ldb : lda, ldbm = pl.swap ? lda : ldb;
   CUtensorMap ma, mb;
-  int rc = efl_make_map_bf16(&ma, A, Mred, N1, lda, efl::tc::BK);
+  int rc = efl_make_map_bf16(&ma, Am, Mred, n1, ldam, efl::tc::BK);
   if (rc) return rc;
-  rc = efl_make_map_bf16(&mb, B, Mred, N2, ldb, efl::tc::BK);
+  rc = efl_make_map_bf16(&mb, Bm, Mred, n2, ldbm, efl::tc::BK);
   if (rc) return rc;
-  const int splits = efl_tc_gemm_tn_splits(Mred, N1, N2);
+  const int splits = pl.splits;
   const int kb = (Mred + efl::tc::BK - 1) / efl::tc::BK;
   Params p{};
-  p.mode = 1; p.M = N1; p.N = N2; p.K = Mred; p.BN = bn; p.epi = 0;
+  p.mode = 1; p.M = n1; p.N = n2; p.K = Mred; p.BN = pl.bn; p.epi = 0;
   p.P = workspace; p.splits = splits; p.kb_per_split = (kb + splits - 1) / splits;
-  const int tiles = ((N1 + efl::tc::BM - 1) / efl::tc::BM) * (N2 / bn);
+  const int tile_m = pl.pair ? 2 * efl::tc::BM : efl::tc::BM;
+  const int tiles = ((n1 + tile_m - 1) / tile_m) * (n2 / pl.bn);
   cudaStream_t s = (cudaStream_t)stream;
   CUtensorMap mc, mc0;
   make_out_map(&mc, &p.tma_c, 0, nullptr, 0, 0, 0, 0);
-  make_out_map(&mc0, &p.tma_c0, 1, workspace, splits, N1, N2, N2);
-  rc = launch(ma, mb, mc, mc0, p, tiles * splits, false, s);
+  make_out_map(&mc0, &p.tma_c0, 1, workspace, splits, n1, n2, n2);
+  rc = launch(ma, mb, mc, mc0, p, tiles * splits, pl.pair, s);
   if (rc) return rc;
   const long long n = (long long)N1 * N2;
-  efl::splitk_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(workspace, splits, n, C, ldc, N2, accumulate);
+  if (!pl.swap) {
+    efl::splitk_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(workspace, splits, n, C, ldc, N2, accumulate);
+  } else {
+    dim3 grid((unsigned)((N1 + 31) / 32), (unsigned)((N2 + 31) / 32)), block(32, 8);
+    efl::tc::splitk_reduce_transposed_kernel<<<grid, block, 0, s>>>(workspace, splits, N2, N1, C, ldc, accumulate);
+  }
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }

@@ -17,9 +17,10 @@ def _rand(m, n, scale=1.0):
     return (torch.randn(m, n, device=DEV) * scale).to(torch.bfloat16)
 
 
-@pytest.fixture(params=[0, 2], ids=["single_cta", "cta_pair"])
+@pytest.fixture(params=[0, 1, 2], ids=["single_cta", "auto", "cta_pair"])
 def pair_mode(request):
-    """Every NT test runs on the single-CTA tiles and on the cta_group::2 pair tiles (256-row tiles, two SMs)."""
+    """Every GEMM test runs on the single-CTA tiles, on the cta_group::2 pair tiles (256-row tiles, two SMs) and in
+    the default mode, which picks tile mode and wgrad orientation per shape."""
     from singa_b200 import _lib
     prev = _lib.LIB.efl_tc_gemm_pair_mode(request.param)
     yield request.param
@@ -67,8 +68,9 @@ def test_nt_complex_epilogue(pair_mode):
 
 
 @pytest.mark.parametrize("Mred,N1,N2", [(5000, 1248, 224), (9999, 1536, 192), (4097, 2560, 160), (3000, 784, 896),
-                                         (6000, 2688, 768), (64, 128, 64), (130, 144, 16), (131072, 2240, 640)])
-def test_tn(Mred, N1, N2):
+                                         (6000, 2688, 768), (64, 128, 64), (130, 144, 16), (131072, 2240, 640),
+                                         (20000, 1120, 640), (7000, 1344, 768), (300, 48, 1120)])
+def test_tn(Mred, N1, N2, pair_mode):
     from singa_b200 import tc_gemm
     torch.manual_seed(Mred)
     A, B = _rand(Mred, N1, 0.3), _rand(Mred, N2, 0.3)

@@ -85,6 +85,22 @@ def main():
                               "tflops": round(fl / ms / 1e9, 1), "frac_of_measured_peak": round(fl / ms / 1e9 / peak, 3),
                               "algorithmic_GBs": round((Mred * (N1 + N2)) * 2 / ms / 1e6, 1)}))
             del A, B, C
+    if args.only == "tnx":
+        # wgrad orientation experiment: C = A^T B as is, or C^T = B^T A (swapped), single-CTA or CTA-pair tiles
+        from singa_b200 import _lib
+        for name, Mred, N1, N2 in tn:
+            for swapped in (0, 1):
+                n1, n2 = (N2, N1) if swapped else (N1, N2)
+                A, B = rnd(Mred, n1), rnd(Mred, n2)
+                C = torch.zeros(n1, n2, dtype=torch.float32, device=dev)
+                for pm in (0, 2):
+                    prev = _lib.LIB.efl_tc_gemm_pair_mode(pm)
+                    ms = timeit(lambda: tc_gemm.gemm_tn(A, B, C, True, Mred, n1, n2), args.iters)
+                    _lib.LIB.efl_tc_gemm_pair_mode(prev)
+                    print(json.dumps({"shape": name, "swapped": swapped, "pair": pm, "N1": n1, "N2": n2, "ms": round(ms, 4),
+                                      "tflops": round(2.0 * Mred * n1 * n2 / ms / 1e9, 1)}))
+                del A, B, C
+        return
     print(json.dumps({"summary": "all shapes", "ms": round(tot_ms, 3), "tflops": round(tot_fl / tot_ms / 1e9, 1),
                       "peak_tflops_measured_sustained": peak}))
 
