@@ -142,7 +142,7 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
   uint64_t* d2_full = bars + 2 * MAX_STAGES + 2 * MAX_GROUPS;
   uint64_t* d2_free = bars + 2 * MAX_STAGES + 3 * MAX_GROUPS;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * MAX_STAGES + 4 * MAX_GROUPS);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
 
   // ---- one-time setup: zero operand stages (pad rows must be 0), S buffers; build constant B operands ----
   {
@@ -194,7 +194,7 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
   const int row_bytes_total = M * 256;  // bytes per edge per operand (M rows x 128 ch x 2 B)
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int i = 0; i < n_mine; ++i) {
@@ -227,20 +227,24 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
     uint32_t phase = 0;
     const int NG = p.NG;
     const uint32_t idesc1 = make_idesc2(GP, 1, 0);   // A = operand tile (MN-major), B = T/F0 (K-major)
-    const uint32_t sT = smem_u32(smem + L.off_T), sF0 = smem_u32(smem + L.off_F0);
+    // descriptors differ between stages / K steps only in the start-address field (bytes >> 4): advanced by adds;
+    // warp-uniform control flow with an elected issuing lane keeps waterfall loops off every tcgen05 instruction
+    const uint64_t a_desc0 = make_desc(smem_u32(smem), (uint32_t)L.blk_bytes, 1024);
+    const uint64_t t_desc0 = make_desc(smem_u32(smem + L.off_T), 16, 1024);
+    const uint64_t st_step = (uint64_t)(L.stage_bytes >> 4);
+    const bool issuer = elect_one();
     for (int i = 0; i < n_mine; ++i) {
       const int g = i % NG;
       const uint32_t k_th = (uint32_t)(i / NG);
       mbar_wait(&h_full[stage], phase);
       mbar_wait(&d2_free[g], (k_th & 1) ^ 1);
       tc_fence_after();
-      if (lane == 0) {
-        const uint32_t sa = smem_u32(smem + stage * L.stage_bytes);
+      if (issuer) {
+        const uint64_t ad = a_desc0 + st_step * (uint64_t)stage;
         const uint32_t d1 = tmem_base + (uint32_t)(g * p.gstride);
 #pragma unroll
         for (int k = 0; k < KP / 16; ++k)
-          tc_mma(d1, make_desc(sa + k * 2048, (uint32_t)L.blk_bytes, 1024), make_desc(sT + k * 32, 16, 1024), idesc1,
-                 k > 0 ? 1u : 0u);
+          tc_mma(d1, ad + (uint64_t)(k * (2048 >> 4)), t_desc0 + (uint64_t)(k * (32 >> 4)), idesc1, k > 0 ? 1u : 0u);
         tc_commit(&h_empty[stage]);
         tc_commit(&d1_full[g]);
       }
@@ -253,20 +257,22 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
     uint32_t phase = 0;
     const int NG = p.NG;
     const uint32_t idesc1 = make_idesc2(GP, 1, 0);
-    const uint32_t sF0 = smem_u32(smem + L.off_F0);
+    const uint64_t d_desc0 = make_desc(smem_u32(smem) + 2 * L.blk_bytes, (uint32_t)L.blk_bytes, 1024);
+    const uint64_t f_desc0 = make_desc(smem_u32(smem + L.off_F0), 16, 1024);
+    const uint64_t st_step = (uint64_t)(L.stage_bytes >> 4);
+    const bool issuer = elect_one();
     for (int i = 0; i < n_mine; ++i) {
       const int g = i % NG;
       const uint32_t k_th = (uint32_t)(i / NG);
       mbar_wait(&h_full[stage], phase);
       mbar_wait(&d2_free[g], (k_th & 1) ^ 1);
       tc_fence_after();
-      if (lane == 0) {
-        const uint32_t sd = smem_u32(smem + stage * L.stage_bytes) + 2 * L.blk_bytes;
+      if (issuer) {
+        const uint64_t dd = d_desc0 + st_step * (uint64_t)stage;
         const uint32_t d3 = tmem_base + (uint32_t)(g * p.gstride) + (uint32_t)GP;
 #pragma unroll
         for (int k = 0; k < KP / 16; ++k)
-          tc_mma(d3, make_desc(sd + k * 2048, (uint32_t)L.blk_bytes, 1024), make_desc(sF0 + k * 32, 16, 1024), idesc1,
-                 k > 0 ? 1u : 0u);
+          tc_mma(d3, dd + (uint64_t)(k * (2048 >> 4)), f_desc0 + (uint64_t)(k * (32 >> 4)), idesc1, k > 0 ? 1u : 0u);
         tc_commit(&h_empty[stage]);
         tc_commit(&d1_full[g]);
       }
@@ -278,19 +284,21 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
     const int NG = p.NG;
     // A = S (K-major), B = B2 (K-major); forward: both fp16 (a_format = b_format = 0)
     const uint32_t idesc2 = BWD ? make_idesc2(KP, 0, 0) : (make_idesc2(KP, 0, 0) & ~((1u << 7) | (1u << 10)));
-    const uint32_t sB2 = smem_u32(smem + L.off_B2);
+    const uint64_t s_desc0 = make_desc_noswz(smem_u32(smem + L.off_S), 128, (uint32_t)L.sbo);
+    const uint64_t b2_desc0 = make_desc_noswz(smem_u32(smem + L.off_B2), 128, (uint32_t)L.sbo);
+    const uint64_t g_step = (uint64_t)(L.s_bytes >> 4);
+    const bool issuer = elect_one();
     for (int j = 0; j < n_mine; ++j) {
       const int g = j % NG;
       const uint32_t k_th = (uint32_t)(j / NG);
       mbar_wait(&s_ready[g], k_th & 1);
       tc_fence_after();
-      if (lane == 0) {
-        const uint32_t sS = smem_u32(smem + L.off_S + g * L.s_bytes);
+      if (issuer) {
+        const uint64_t sd = s_desc0 + g_step * (uint64_t)g;
         const uint32_t d2 = tmem_base + (uint32_t)(g * p.gstride);
 #pragma unroll
         for (int k = 0; k < GP / 16; ++k)
-          tc_mma(d2, make_desc_noswz(sS + k * 256, 128, (uint32_t)L.sbo), make_desc_noswz(sB2 + k * 256, 128, (uint32_t)L.sbo),
-                 idesc2, k > 0 ? 1u : 0u);
+          tc_mma(d2, sd + (uint64_t)(k * (256 >> 4)), b2_desc0 + (uint64_t)(k * (256 >> 4)), idesc2, k > 0 ? 1u : 0u);
         tc_commit(&d2_full[g]);
       }
       __syncwarp();
