@@ -293,6 +293,58 @@ extern "C" int efl_gemm_tn_f32(const float* A, long long lda, const float* B, lo
   return EFL_OK;
 }
 
+// bf16 rows with 16-byte alignment: each lane owns 8 adjacent columns (one 16-byte load per row), the four warps of
+// a block take rows r0 + w, r0 + w + 4, ... (four loads in flight per lane) and are combined in warp order, so the
+// sum order is fixed.  Same partial layout as colsum_partial_kernel.
+__global__ void __launch_bounds__(128)
+colsum_partial_bf16x8_kernel(const __nv_bfloat16* __restrict__ X, long long ld, int rows, int cols, int rows_per_block,
+                             float* __restrict__ P) {
+  __shared__ float part[4][256];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int c0 = blockIdx.x * 256 + lane * 8;
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(rows, r0 + rows_per_block);
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (c0 < cols) {
+    const __nv_bfloat16* base = X + c0;
+    int r = r0 + w;
+    for (; r + 12 < r1; r += 16) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldg(reinterpret_cast<const uint4*>(base + (long long)(r + 4 * u) * ld));
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v[u]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 f = __bfloat1622float2(h[j]);
+          acc[2 * j] += f.x;
+          acc[2 * j + 1] += f.y;
+        }
+      }
+    }
+    for (; r < r1; r += 4) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(base + (long long)r * ld));
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = __bfloat1622float2(h[j]);
+        acc[2 * j] += f.x;
+        acc[2 * j + 1] += f.y;
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) part[w][lane * 8 + j] = acc[j];
+  __syncthreads();
+  for (int c = threadIdx.x; c < 256; c += 128) {
+    const int col = blockIdx.x * 256 + c;
+    if (col < cols) P[(size_t)blockIdx.y * cols + col] = ((part[0][c] + part[1][c]) + part[2][c]) + part[3][c];
+  }
+}
+
 // workspace: (ceil(rows / 512) + 1) * cols floats
 extern "C" int efl_colsum(int bf16, const void* X, long long ld, int rows, int cols, float* out, int accumulate,
                           float* workspace, void* stream) {
@@ -301,7 +353,11 @@ extern "C" int efl_colsum(int bf16, const void* X, long long ld, int rows, int c
   const int rpb = 512;
   const int nb = rows > 0 ? (rows + rpb - 1) / rpb : 1;
   dim3 grid((cols + 127) / 128, nb), block(128);
-  if (bf16) colsum_partial_kernel<__nv_bfloat16><<<grid, block, 0, s>>>((const __nv_bfloat16*)X, ld, rows, cols, rpb, workspace);
+  if (bf16 && cols % 8 == 0 && ld % 8 == 0 && ((uintptr_t)X & 15) == 0) {
+    dim3 g8((cols + 255) / 256, nb);
+    colsum_partial_bf16x8_kernel<<<g8, 128, 0, s>>>((const __nv_bfloat16*)X, ld, rows, cols, rpb, workspace);
+  } else if (bf16)
+    colsum_partial_kernel<__nv_bfloat16><<<grid, block, 0, s>>>((const __nv_bfloat16*)X, ld, rows, cols, rpb, workspace);
   else colsum_partial_kernel<float><<<grid, block, 0, s>>>((const float*)X, ld, rows, cols, rpb, workspace);
   EFL_CHECK_LAUNCH();
   splitk_reduce_kernel<<<(cols + 255) / 256, 256, 0, s>>>(workspace, nb, cols, out, cols, cols, accumulate);

@@ -149,3 +149,20 @@ def _radial_case(eo, ops, k0, no, e, tol_out, tol_grad):
     assert torch.equal(out, out2) and torch.equal(xg.grad, xg2.grad)
     for a, b in zip(pg, pg2):
         assert torch.equal(a.grad, b.grad)
+
+
+@pytest.mark.parametrize("rows,cols,pitch", [(262144, 1248, 1248), (5003, 784, 800), (37, 576, 576), (1000, 20, 24), (0, 64, 64)])
+def test_bias_gradient_column_sum_bf16(rows, cols, pitch):
+    """efl_colsum (bias gradients of the SO(2) linear maps): vectorised bf16 path (cols, pitch multiples of 8) and the
+    scalar fallback; fp32 accumulation in a fixed order, so repeated calls agree bit for bit."""
+    from singa_b200 import ops
+    torch.manual_seed(rows + cols)
+    X = torch.randn(max(rows, 1), pitch, device=DEV).to(torch.bfloat16)[:rows, :cols]
+    out = torch.full((cols,), 3.0, device=DEV)
+    ops._colsum(X, rows, cols, out, True)
+    ref = X.double().sum(dim=0) + 3.0
+    tol = 1e-5 * max(1.0, float(ref.abs().max())) + 2e-6 * rows ** 0.5
+    assert float((out.double() - ref).abs().max()) <= tol
+    out2 = torch.full((cols,), 3.0, device=DEV)
+    ops._colsum(X, rows, cols, out2, True)
+    assert torch.equal(out, out2)
