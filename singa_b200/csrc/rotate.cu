@@ -150,8 +150,8 @@ __global__ void __launch_bounds__(128) rotate_in_bwd_kernel(
 // never exists (it cost 6.3 KB/edge written + read back).  x of the node (needed for d rad) is loaded once per node
 // instead of once per edge.
 // ------------------------------------------------------------------------------------------
-template <int LMAX, int MMAX, int C, typename TIn>
-__global__ void __launch_bounds__(128, 4) rotate_in_bwd_node_kernel(
+template <int LMAX, int MMAX, int C, typename TIn, int WPB>
+__global__ void __launch_bounds__(32 * WPB, 16 / WPB) rotate_in_bwd_node_kernel(
     const float* __restrict__ x_node, const int* __restrict__ seg_ptr, const int* __restrict__ seg_idx,
     const int* __restrict__ perm, const float* __restrict__ wig, const float* __restrict__ rad, int rad_ld,
     OpBufs<LMAX> dA, float* __restrict__ drad, float* __restrict__ dx_out, int coff, int e0, int Ec, int n0, int n1,
@@ -161,11 +161,11 @@ __global__ void __launch_bounds__(128, 4) rotate_in_bwd_node_kernel(
   static_assert(T::WSZ % 4 == 0, "Wigner rows are 16-byte padded");
   constexpr int CH = 2 * C;
   constexpr int NPAIR = (LMAX + 1) * (MMAX + 1) - MMAX * (MMAX + 1) / 2;  // (l, |m'|) pairs
-  __shared__ __align__(16) float sW[4][2][T::WSZ];
-  __shared__ float sX[4][T::L][C];  // x of the warp's node (only d rad needs it): shared memory, not registers
+  __shared__ __align__(16) float sW[WPB][2][T::WSZ];
+  __shared__ float sX[WPB][T::L][C];  // x of the warp's node (only d rad needs it): shared memory, not registers
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int half = lane >> 4, c = lane & 15;
-  const int n = n0 + blockIdx.x * 4 + warp;
+  const int n = n0 + blockIdx.x * WPB + warp;
   if (n >= n1) return;
   int lo = seg_ptr[n], hi = seg_ptr[n + 1];
   if (seg_idx) {  // source grouping spans all chunks: keep the positions inside [e0, e0 + Ec)
@@ -414,6 +414,13 @@ struct BackCfg {
     return o;
   }
   static constexpr int SMEM = ring_off(T::NG);
+  // one degree group per (single-warp) CTA: barriers + the largest group's ring
+  __host__ __device__ static constexpr int max_stage() {
+    int m = 0;
+    for (int k = 0; k < T::NG; ++k) m = stage_of(k) > m ? stage_of(k) : m;
+    return m;
+  }
+  static constexpr int SMEM_SPLIT = BAR_BYTES + RB_NST * max_stage();
   static_assert(T::NG <= 6, "at most 6 degree groups");
 };
 
@@ -501,24 +508,28 @@ __device__ __forceinline__ void rotate_back_fwd_group(const OpBufs<LMAX>& V, con
   }
 }
 
-template <int LMAX, int MMAX, int CH, int VC, typename TIn>
-__global__ void __launch_bounds__(32 * Tab<LMAX, MMAX>::NG) rotate_back_agg_fwd_kernel(
+// SPLIT: one degree group per single-warp CTA (blockIdx.y = group, nodes fastest).  The groups run different fully
+// unrolled code (16-18 KB each, 64-72 KB per kernel): with all groups in every CTA the instruction cache thrashed
+// (ncu r1k: 29 % / 44 % of the stall samples "no instruction"); split, the CTAs resident on an SM mostly share one
+// group's code.
+template <int LMAX, int MMAX, int CH, int VC, typename TIn, bool SPLIT>
+__global__ void __launch_bounds__(SPLIT ? 32 : 32 * Tab<LMAX, MMAX>::NG) rotate_back_agg_fwd_kernel(
     OpBufs<LMAX> V, const float* __restrict__ alpha /* [E, heads] sorted */, int heads,
     const int* __restrict__ rowptr, const int* __restrict__ perm, const float* __restrict__ wig,
     float* __restrict__ out /* [Nt, L, CH] */, int n0, int e0) {
   using T = Tab<LMAX, MMAX>;
   using B = BackCfg<LMAX, MMAX, CH, TIn>;
   extern __shared__ __align__(128) uint8_t rb_smem[];
-  const int g = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = SPLIT ? (int)blockIdx.y : (int)(threadIdx.x >> 5), lane = threadIdx.x & 31;
   const int n = n0 + blockIdx.x;
   const int kb = rowptr[n], ke = rowptr[n + 1];
-  uint64_t* bars = reinterpret_cast<uint64_t*>(rb_smem) + g * RB_NST;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(rb_smem) + (SPLIT ? 0 : g * RB_NST);
 #define GROUP(G)                                                                                                   \
   case G:                                                                                                          \
     if constexpr (G < T::NG)                                                                                       \
-      rotate_back_fwd_group<LMAX, MMAX, CH, VC, TIn, T::glo(G), T::ghi(G)>(V, alpha, heads, perm, wig, out, n, kb, \
-                                                                            ke, e0, rb_smem + B::ring_off(G), bars, \
-                                                                            lane);                                 \
+      rotate_back_fwd_group<LMAX, MMAX, CH, VC, TIn, T::glo(G), T::ghi(G)>(                                        \
+          V, alpha, heads, perm, wig, out, n, kb, ke, e0, rb_smem + (SPLIT ? B::BAR_BYTES : B::ring_off(G)), bars, \
+          lane);                                                                                                   \
     break;
   switch (g) {
     GROUP(0) GROUP(1) GROUP(2) GROUP(3) GROUP(4) GROUP(5)
@@ -642,8 +653,8 @@ __device__ __forceinline__ void rotate_back_bwd_group(const OpBufs<LMAX>& V, con
   }
 }
 
-template <int LMAX, int MMAX, int CH, int VC, typename TIn, typename TOut>
-__global__ void __launch_bounds__(32 * Tab<LMAX, MMAX>::NG) rotate_back_agg_bwd_kernel(
+template <int LMAX, int MMAX, int CH, int VC, typename TIn, typename TOut, bool SPLIT>
+__global__ void __launch_bounds__(SPLIT ? 32 : 32 * Tab<LMAX, MMAX>::NG) rotate_back_agg_bwd_kernel(
     OpBufs<LMAX> V, OpBufs<LMAX> dY, const float* __restrict__ alpha, int heads,
     const int* __restrict__ rowptr, const int* __restrict__ perm, const float* __restrict__ wig,
     const float* __restrict__ dout /* [Nt, L, CH] */, float* __restrict__ dalpha /* [NG, Etot, heads] sorted */,
@@ -651,16 +662,17 @@ __global__ void __launch_bounds__(32 * Tab<LMAX, MMAX>::NG) rotate_back_agg_bwd_
   using T = Tab<LMAX, MMAX>;
   using B = BackCfg<LMAX, MMAX, CH, TIn>;
   extern __shared__ __align__(128) uint8_t rb_smem[];
-  const int g = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = SPLIT ? (int)blockIdx.y : (int)(threadIdx.x >> 5), lane = threadIdx.x & 31;
   const int n = n0 + blockIdx.x;
   const int kb = rowptr[n], ke = rowptr[n + 1];
-  uint64_t* bars = reinterpret_cast<uint64_t*>(rb_smem) + g * RB_NST;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(rb_smem) + (SPLIT ? 0 : g * RB_NST);
   float* dag = dalpha + (size_t)g * part_stride;
 #define GROUP(G)                                                                                                 \
   case G:                                                                                                        \
     if constexpr (G < T::NG)                                                                                     \
       rotate_back_bwd_group<LMAX, MMAX, CH, VC, TIn, TOut, T::glo(G), T::ghi(G)>(                                \
-          V, dY, alpha, heads, perm, wig, dout, dag, n, kb, ke, e0, rb_smem + B::ring_off(G), bars, lane);       \
+          V, dY, alpha, heads, perm, wig, dout, dag, n, kb, ke, e0,                                              \
+          rb_smem + (SPLIT ? B::BAR_BYTES : B::ring_off(G)), bars, lane);                                        \
     break;
   switch (g) {
     GROUP(0) GROUP(1) GROUP(2) GROUP(3) GROUP(4) GROUP(5)
@@ -798,20 +810,33 @@ extern "C" int efl_rotate_in_bwd_nodes(int lmax, int mmax, int C, int bf16_in, i
   EFL_REQUIRE(C == 16, "efl_rotate_in_bwd_nodes: sphere_channels must be 16");
   EFL_REQUIRE(side == 0 || seg_idx != nullptr, "efl_rotate_in_bwd_nodes: the source side needs the source grouping");
   cudaStream_t s = (cudaStream_t)stream;
-  dim3 grid((n1 - n0 + 3) / 4), block(128);
+  // a warp owns a node; one warp per CTA lets the hardware backfill warp by warp (16 resident per SM at 128
+  // registers), which matters because a chunk has only ~1.5 waves of nodes with very different edge counts
+  static int wpb = 0;
+  if (!wpb) {
+    const char* e = getenv("EFL_ROTIN_WPB");
+    wpb = e ? atoi(e) : 1;
+    if (wpb != 1 && wpb != 2 && wpb != 4) wpb = 1;
+  }
+  dim3 grid((n1 - n0 + wpb - 1) / wpb), block(32 * wpb);
   const int coff = side == 0 ? C : 0;
+#define CALL_W(LM, MM, TIN, W)                                                                                   \
+  rotate_in_bwd_node_kernel<LM, MM, 16, TIN, W><<<grid, block, 0, s>>>(                                          \
+      x_node, seg_ptr, seg_idx, perm, wig, rad, rad_ld, o, drad, dx_out, coff, e0, Ec, n0, n1, accumulate);
 #define CALL(LM, MM)                                                                                             \
   {                                                                                                              \
     OpBufs<LM> o{{(void*)da0, (void*)da1, (void*)da2}};                                                          \
-    if (bf16_in)                                                                                                 \
-      rotate_in_bwd_node_kernel<LM, MM, 16, __nv_bfloat16><<<grid, block, 0, s>>>(                              \
-          x_node, seg_ptr, seg_idx, perm, wig, rad, rad_ld, o, drad, dx_out, coff, e0, Ec, n0, n1, accumulate);  \
-    else                                                                                                         \
-      rotate_in_bwd_node_kernel<LM, MM, 16, float><<<grid, block, 0, s>>>(                                      \
-          x_node, seg_ptr, seg_idx, perm, wig, rad, rad_ld, o, drad, dx_out, coff, e0, Ec, n0, n1, accumulate);  \
+    if (bf16_in) {                                                                                               \
+      if (wpb == 1) CALL_W(LM, MM, __nv_bfloat16, 1) else if (wpb == 2) CALL_W(LM, MM, __nv_bfloat16, 2)        \
+      else CALL_W(LM, MM, __nv_bfloat16, 4)                                                                      \
+    } else {                                                                                                     \
+      if (wpb == 1) CALL_W(LM, MM, float, 1) else if (wpb == 2) CALL_W(LM, MM, float, 2)                        \
+      else CALL_W(LM, MM, float, 4)                                                                              \
+    }                                                                                                            \
   }
   DISPATCH_LM(lmax, mmax, CALL)
 #undef CALL
+#undef CALL_W
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }
@@ -841,6 +866,16 @@ extern "C" int efl_segment_sum_rows(const float* buf, int L, int ldc, int coff, 
     KERNEL<<<grid, block, SMEM_BYTES, s>>>(__VA_ARGS__);                                                \
   }
 
+// EFL_ROTBACK_SPLIT=0 keeps all degree groups in one CTA (one warp each); default: one group per single-warp CTA
+static bool rotback_split() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("EFL_ROTBACK_SPLIT");
+    v = e ? atoi(e) : 1;
+  }
+  return v != 0;
+}
+
 extern "C" int efl_rotate_back_parts(int lmax, int mmax) {
   (void)mmax;
   return lmax > 3 ? lmax - 2 : 1;  // Tab::NG: degree groups = partial d-alpha planes of the backward
@@ -853,20 +888,23 @@ extern "C" int efl_rotate_back_aggregate_fwd(int lmax, int mmax, int heads, int 
   if (n1 <= n0) return EFL_OK;
   EFL_REQUIRE(heads * value_ch == 112 && value_ch == 16, "efl_rotate_back_aggregate_fwd: needs heads*value == 112, value == 16");
   cudaStream_t s = (cudaStream_t)stream;
-  dim3 grid(n1 - n0);
+  const bool split = rotback_split();
+#define FWD(LM, MM, TIN, SP, SM)                                                                               \
+  RB_LAUNCH((rotate_back_agg_fwd_kernel<LM, MM, 112, 16, TIN, SP>), (BackCfg<LM, MM, 112, TIN>::SM), o, alpha,  \
+            heads, rowptr, perm, wig, out, n0, e0)
 #define CALL(LM, MM)                                                                                           \
   {                                                                                                            \
     OpBufs<LM> o{{(void*)v0, (void*)v1, (void*)v2}};                                                           \
-    dim3 block(32 * Tab<LM, MM>::NG);                                                                          \
-    if (bf16_in)                                                                                               \
-      RB_LAUNCH((rotate_back_agg_fwd_kernel<LM, MM, 112, 16, __nv_bfloat16>),                                  \
-                (BackCfg<LM, MM, 112, __nv_bfloat16>::SMEM), o, alpha, heads, rowptr, perm, wig, out, n0, e0)  \
-    else                                                                                                       \
-      RB_LAUNCH((rotate_back_agg_fwd_kernel<LM, MM, 112, 16, float>), (BackCfg<LM, MM, 112, float>::SMEM), o,  \
-                alpha, heads, rowptr, perm, wig, out, n0, e0)                                                  \
+    dim3 grid(n1 - n0, split ? Tab<LM, MM>::NG : 1), block(split ? 32 : 32 * Tab<LM, MM>::NG);                 \
+    if (bf16_in) {                                                                                             \
+      if (split) FWD(LM, MM, __nv_bfloat16, true, SMEM_SPLIT) else FWD(LM, MM, __nv_bfloat16, false, SMEM)     \
+    } else {                                                                                                   \
+      if (split) FWD(LM, MM, float, true, SMEM_SPLIT) else FWD(LM, MM, float, false, SMEM)                     \
+    }                                                                                                          \
   }
   DISPATCH_LM(lmax, mmax, CALL)
 #undef CALL
+#undef FWD
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }
@@ -879,22 +917,24 @@ extern "C" int efl_rotate_back_aggregate_bwd(int lmax, int mmax, int heads, int 
   if (n1 <= n0) return EFL_OK;
   EFL_REQUIRE(heads * value_ch == 112 && value_ch == 16, "efl_rotate_back_aggregate_bwd: needs heads*value == 112, value == 16");
   cudaStream_t s = (cudaStream_t)stream;
-  dim3 grid(n1 - n0);
+  const bool split = rotback_split();
+#define BWD(LM, MM, TIN, SP, SM)                                                                               \
+  RB_LAUNCH((rotate_back_agg_bwd_kernel<LM, MM, 112, 16, TIN, TIN, SP>), (BackCfg<LM, MM, 112, TIN>::SM), vi,  \
+            dyo, alpha, heads, rowptr, perm, wig, dout, dalpha, part_stride, n0, e0)
 #define CALL(LM, MM)                                                                                           \
   {                                                                                                            \
     OpBufs<LM> vi{{(void*)v0, (void*)v1, (void*)v2}};                                                          \
     OpBufs<LM> dyo{{dy0, dy1, dy2}};                                                                           \
-    dim3 block(32 * Tab<LM, MM>::NG);                                                                          \
-    if (bf16)                                                                                                  \
-      RB_LAUNCH((rotate_back_agg_bwd_kernel<LM, MM, 112, 16, __nv_bfloat16, __nv_bfloat16>),                   \
-                (BackCfg<LM, MM, 112, __nv_bfloat16>::SMEM), vi, dyo, alpha, heads, rowptr, perm, wig, dout,   \
-                dalpha, part_stride, n0, e0)                                                                   \
-    else                                                                                                       \
-      RB_LAUNCH((rotate_back_agg_bwd_kernel<LM, MM, 112, 16, float, float>), (BackCfg<LM, MM, 112, float>::SMEM), \
-                vi, dyo, alpha, heads, rowptr, perm, wig, dout, dalpha, part_stride, n0, e0)                   \
+    dim3 grid(n1 - n0, split ? Tab<LM, MM>::NG : 1), block(split ? 32 : 32 * Tab<LM, MM>::NG);                 \
+    if (bf16) {                                                                                                \
+      if (split) BWD(LM, MM, __nv_bfloat16, true, SMEM_SPLIT) else BWD(LM, MM, __nv_bfloat16, false, SMEM)     \
+    } else {                                                                                                   \
+      if (split) BWD(LM, MM, float, true, SMEM_SPLIT) else BWD(LM, MM, float, false, SMEM)                     \
+    }                                                                                                          \
   }
   DISPATCH_LM(lmax, mmax, CALL)
 #undef CALL
+#undef BWD
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }
