@@ -295,6 +295,19 @@ __global__ void segment_sum_rows_kernel(const float* __restrict__ buf, int row_e
 // bit-deterministic; no atomics.
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+// one hardware-elected lane of a converged warp: unlike `lane == 0` the compiler knows the guarded bulk-copy issue
+// runs in one thread of a uniform warp and emits no per-operand waterfall loops around it
+__device__ __forceinline__ bool elect_one_() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void mbar_init_(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count));
 }
@@ -435,6 +448,7 @@ __device__ __forceinline__ void rotate_back_fwd_group(const OpBufs<LMAX>& V, con
   constexpr int NC = (L_HI + 1) * (L_HI + 1) - L_LO * L_LO;
   const bool active = lane < CH / 4;
   const int c4 = active ? 4 * lane : 0;
+  const bool issuer = elect_one_();
   float acc[NC][4];
 #pragma unroll
   for (int i = 0; i < NC; ++i)
@@ -453,7 +467,7 @@ __device__ __forceinline__ void rotate_back_fwd_group(const OpBufs<LMAX>& V, con
   for (int s = 0; s < RB_NST; ++s) {
     const int j = kb + s;
     const int eo = __shfl_sync(0xffffffffu, pv, s);
-    if (lane == 0 && j < ke) G::issue(ring + s * G::STAGE, &bars[s], V, wig, j - e0, eo);
+    if (issuer && j < ke) G::issue(ring + s * G::STAGE, &bars[s], V, wig, j - e0, eo);
   }
   float a_next = (alpha && kb < ke) ? __ldg(alpha + (size_t)kb * heads + c4 / VC) : 1.f;
   int s = 0;
@@ -497,7 +511,7 @@ __device__ __forceinline__ void rotate_back_fwd_group(const OpBufs<LMAX>& V, con
         pv = (pbase + lane < ke) ? __ldg(perm + pbase + lane) : 0;
       }
       const int eo = __shfl_sync(0xffffffffu, pv, jn - pbase);
-      if (lane == 0) G::issue(ring + s * G::STAGE, &bars[s], V, wig, jn - e0, eo);
+      if (issuer) G::issue(ring + s * G::STAGE, &bars[s], V, wig, jn - e0, eo);
     }
     if (++s == RB_NST) { s = 0; phase ^= 1; }
   }
@@ -554,6 +568,7 @@ __device__ __forceinline__ void rotate_back_bwd_group(const OpBufs<LMAX>& V, con
   constexpr int NC = (L_HI + 1) * (L_HI + 1) - L_LO * L_LO;
   const bool active = lane < CH / 4;
   const int c4 = active ? 4 * lane : 0;
+  const bool issuer = elect_one_();
   if (lane == 0) {
 #pragma unroll
     for (int s = 0; s < RB_NST; ++s) mbar_init_(&bars[s], 1);
@@ -566,7 +581,7 @@ __device__ __forceinline__ void rotate_back_bwd_group(const OpBufs<LMAX>& V, con
   for (int s = 0; s < RB_NST; ++s) {
     const int j = kb + s;
     const int eo = __shfl_sync(0xffffffffu, pv, s);
-    if (lane == 0 && j < ke) G::issue(ring + s * G::STAGE, &bars[s], V, wig, j - e0, eo);
+    if (issuer && j < ke) G::issue(ring + s * G::STAGE, &bars[s], V, wig, j - e0, eo);
   }
   float dy[NC][4];
   {
@@ -647,7 +662,7 @@ __device__ __forceinline__ void rotate_back_bwd_group(const OpBufs<LMAX>& V, con
         pv = (pbase + lane < ke) ? __ldg(perm + pbase + lane) : 0;
       }
       const int eo = __shfl_sync(0xffffffffu, pv, jn - pbase);
-      if (lane == 0) G::issue(ring + s * G::STAGE, &bars[s], V, wig, jn - e0, eo);
+      if (issuer) G::issue(ring + s * G::STAGE, &bars[s], V, wig, jn - e0, eo);
     }
     if (++s == RB_NST) { s = 0; phase ^= 1; }
   }
