@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(32 * WPB, 16 / WPB) rotate_in_bwd_node_kernel(
   static_assert(T::WSZ % 4 == 0, "Wigner rows are 16-byte padded");
   constexpr int CH = 2 * C;
   constexpr int NPAIR = (LMAX + 1) * (MMAX + 1) - MMAX * (MMAX + 1) / 2;  // (l, |m'|) pairs
-  __shared__ __align__(16) float sW[WPB][2][T::WSZ];
+  __shared__ __align__(16) float sW[WPB][2][2][T::WSZ];  // [warp][half][double buffer]
   __shared__ float sX[WPB][T::L][C];  // x of the warp's node (only d rad needs it): shared memory, not registers
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int half = lane >> 4, c = lane & 15;
@@ -192,13 +192,34 @@ __global__ void __launch_bounds__(32 * WPB, 16 / WPB) rotate_in_bwd_node_kernel(
     for (int i = lane; i < T::L * C; i += 32) (&sX[warp][0][0])[i] = __ldg(xp + i);
   }
   const float* x = &sX[warp][0][c];
-  float* sw = sW[warp][half];
+  // Software pipeline over the half-warp's edges: edge ids (segment position -> original id, two dependent loads) are
+  // fetched two iterations ahead and the Wigner rows one iteration ahead (cp.async into the other buffer), so only
+  // the d A / radial loads of the current edge are still exposed; before, the Wigner copy alone (load -> shared
+  // store behind the id chain) was 44 % of the stall samples (ncu r1k).
+  auto edge_pos = [&](int k) { return k < hi ? (seg_idx ? __ldg(seg_idx + k) : k) : -1; };
+  auto wig_async = [&](float* dst, int eo_) {
+    const float4* w4 = reinterpret_cast<const float4*>(wig + (size_t)eo_ * T::WSZ);
+    for (int i = c; i < T::WSZ / 4; i += 16)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst + 4 * i)),
+                   "l"(w4 + i)
+                   : "memory");
+  };
+  int pos_c = edge_pos(lo + half), pos_n = edge_pos(lo + 2 + half);
+  int eo_c = pos_c >= 0 ? __ldg(perm + pos_c) : 0, eo_n = pos_n >= 0 ? __ldg(perm + pos_n) : 0;
+  int buf = 0;
+  const uint32_t hmask = half ? 0xffff0000u : 0x0000ffffu;
+  if (pos_c >= 0) wig_async(sW[warp][half][0], eo_c);
+  asm volatile("cp.async.commit_group;" ::: "memory");
   for (int it = lo; it < hi; it += 2) {
-    const int k = it + half;
-    const bool act = k < hi;
-    const int pos = act ? (seg_idx ? seg_idx[k] : k) : 0;
+    const int pos_2 = edge_pos(it + 4 + half);
+    const int eo_2 = pos_2 >= 0 ? __ldg(perm + pos_2) : 0;
+    if (pos_n >= 0) wig_async(sW[warp][half][buf ^ 1], eo_n);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    const bool act = pos_c >= 0;
+    const int pos = act ? pos_c : 0;
     const int el = pos - e0;
-    const int eo = act ? perm[pos] : 0;
+    const int eo = eo_c;
+    float* sw = sW[warp][half][buf];
     // every global load of this edge is issued before the first store of the iteration (the d rad stores would
     // otherwise order the loads behind them): d A rows and radial values of the lane's channel into registers
     const float* rd = rad ? rad + (size_t)eo * rad_ld : nullptr;
@@ -222,12 +243,11 @@ __global__ void __launch_bounds__(32 * WPB, 16 / WPB) rotate_in_bwd_node_kernel(
         }
       }
     }
-    __syncwarp();
-    if (act) {
-      const float4* w4 = reinterpret_cast<const float4*>(wig + (size_t)eo * T::WSZ);
-      for (int i = c; i < T::WSZ / 4; i += 16) reinterpret_cast<float4*>(sw)[i] = __ldg(w4 + i);
-    }
-    __syncwarp();
+    asm volatile("cp.async.wait_group 1;" ::: "memory");  // this edge's Wigner rows have landed (next edge's may not)
+    __syncwarp(hmask);   // the two halves own separate buffers: synchronise per half-warp
+    pos_c = pos_n; pos_n = pos_2;
+    eo_c = eo_n; eo_n = eo_2;
+    buf ^= 1;
     if (!act) continue;
     int t = 0, s2 = 0;
 #pragma unroll
@@ -258,6 +278,7 @@ __global__ void __launch_bounds__(32 * WPB, 16 / WPB) rotate_in_bwd_node_kernel(
         if (rd) drd[rcol] = dr;
       }
     }
+    __syncwarp(hmask);   // every lane of the half is done with sw before the next iteration refills it
   }
 #pragma unroll
   for (int i = 0; i < T::L; ++i) {
@@ -825,14 +846,9 @@ extern "C" int efl_rotate_in_bwd_nodes(int lmax, int mmax, int C, int bf16_in, i
   EFL_REQUIRE(C == 16, "efl_rotate_in_bwd_nodes: sphere_channels must be 16");
   EFL_REQUIRE(side == 0 || seg_idx != nullptr, "efl_rotate_in_bwd_nodes: the source side needs the source grouping");
   cudaStream_t s = (cudaStream_t)stream;
-  // a warp owns a node; one warp per CTA lets the hardware backfill warp by warp (16 resident per SM at 128
-  // registers), which matters because a chunk has only ~1.5 waves of nodes with very different edge counts
-  static int wpb = 0;
-  if (!wpb) {
-    const char* e = getenv("EFL_ROTIN_WPB");
-    wpb = e ? atoi(e) : 1;
-    if (wpb != 1 && wpb != 2 && wpb != 4) wpb = 1;
-  }
+  // a warp owns a node, one warp per CTA: the hardware backfills warp by warp (16 resident per SM at 128 registers);
+  // 2 and 4 warps per CTA measured the same
+  constexpr int wpb = 1;
   dim3 grid((n1 - n0 + wpb - 1) / wpb), block(32 * wpb);
   const int coff = side == 0 ? C : 0;
 #define CALL_W(LM, MM, TIN, W)                                                                                   \
@@ -841,13 +857,7 @@ extern "C" int efl_rotate_in_bwd_nodes(int lmax, int mmax, int C, int bf16_in, i
 #define CALL(LM, MM)                                                                                             \
   {                                                                                                              \
     OpBufs<LM> o{{(void*)da0, (void*)da1, (void*)da2}};                                                          \
-    if (bf16_in) {                                                                                               \
-      if (wpb == 1) CALL_W(LM, MM, __nv_bfloat16, 1) else if (wpb == 2) CALL_W(LM, MM, __nv_bfloat16, 2)        \
-      else CALL_W(LM, MM, __nv_bfloat16, 4)                                                                      \
-    } else {                                                                                                     \
-      if (wpb == 1) CALL_W(LM, MM, float, 1) else if (wpb == 2) CALL_W(LM, MM, float, 2)                        \
-      else CALL_W(LM, MM, float, 4)                                                                              \
-    }                                                                                                            \
+    if (bf16_in) CALL_W(LM, MM, __nv_bfloat16, wpb) else CALL_W(LM, MM, float, wpb)                              \
   }
   DISPATCH_LM(lmax, mmax, CALL)
 #undef CALL
