@@ -43,14 +43,17 @@ __global__ void __launch_bounds__(128) rotate_in_fwd_kernel(
   using T = Tab<LMAX, MMAX>;
   static_assert(2 * C == 32, "lane = channel mapping needs 2C == 32");
   constexpr int CH = 2 * C;
-  __shared__ float sW[4][T::WSZ + 1];
+  static_assert(T::WSZ % 4 == 0, "Wigner rows are 16-byte padded");
+  // 16-byte aligned rows: the broadcast reads of a row compile to LDS.128 (the LSU pipe, at 77 % busy with scalar
+  // LDS, was the limiter of this kernel: ncu r1k)
+  __shared__ __align__(16) float sW[4][T::WSZ];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int el = blockIdx.x * 4 + warp;
   if (el >= Ec) return;
   const int e = e0 + el;
   const int eo = perm[e];
-  const float* w = wig + (size_t)eo * T::WSZ;
-  for (int i = lane; i < T::WSZ; i += 32) sW[warp][i] = w[i];
+  const float4* w4 = reinterpret_cast<const float4*>(wig + (size_t)eo * T::WSZ);
+  for (int i = lane; i < T::WSZ / 4; i += 32) reinterpret_cast<float4*>(sW[warp])[i] = __ldg(w4 + i);
   const int node = lane < C ? src[e] : dst[e];
   const float* xp = (lane < C ? x_src : x_dst) + (size_t)node * T::L * C + (lane & (C - 1));
   float x[T::L];
