@@ -222,6 +222,18 @@ int efl_radius_graph_fill(int N, int nbatch, float cs, int nx, int ny, int nz, f
 int efl_radius_graph_emit(const int* rowptr_full, const int* rowptr_cap, const int* col, int N, long long E,
                           long long* edge_index, int flow_target_to_source, void* stream);
 
+/* Destination-sorted CSR of a caller-supplied edge_index plus the source-side grouping (csrc/csr.cu).  The reference
+ * works on the raw edge list (gather EF_layers.py:326-328, index_add_ :342-351, softmax index :1180); every kernel of
+ * this library consumes edges grouped by destination instead.  src64/dst64: rows 0 and 1 of edge_index ([E] int64).
+ * Outputs (int32): perm [E] sorted position -> original edge id (stable), rowptr [num_dst+1], src_sorted/dst_sorted
+ * [E], dst_orig [E] (original order), src_ptr [num_src+1], src_idx [E] sorted positions grouped by source (stable).
+ * scratch 3*E ints; temp efl_csr_temp_bytes(E, max(num_src, num_dst)) bytes; *status (device int, zeroed by the
+ * caller) becomes 1 when an id is outside [0, num_src) / [0, num_dst). */
+long long efl_csr_temp_bytes(long long E, long long max_nodes);
+int efl_csr_from_edge_index(const long long* src64, const long long* dst64, int E, int num_src, int num_dst, int* perm,
+                            int* rowptr, int* src_sorted, int* dst_sorted, int* dst_orig, int* src_ptr, int* src_idx,
+                            int* scratch, void* temp, long long temp_bytes, int* status, void* stream);
+
 /* bf16 mode split of the same MLP: the hidden layers stay SIMT kernels, the 16 -> NO layer and its backward run as
  * K=16 / N=16 GEMMs of efl_tc_gemm_nt / efl_tc_gemm_tn.  hidden_fwd: x -> a2 [E,16] bf16 (input of the last Linear).
  * hidden_bwd: d a2 [E,16] fp32 -> dx [E,K0] and part [nblocks, efl_radial_hidden_part_size(K0)]:

@@ -439,3 +439,20 @@ def radius_graph_bruteforce(pos: torch.Tensor, r: float, batch: torch.Tensor = N
     src, dst = np.concatenate(src), np.concatenate(dst)
     order = np.lexsort((src, dst))
     return torch.from_numpy(np.stack((src[order], dst[order])).astype(np.int64))
+
+
+def csr_from_edge_index(edge_index: torch.Tensor, num_src: int, num_dst: int) -> dict:
+    """Destination-sorted view of an edge list as the reference's raw-edge-list ops imply it: `index_add_` over
+    edge_index[1] (EF_layers.py:342-351) sums a destination's edges, the softmax (:1180) normalises over the same
+    groups, the gather (:326-328) reads edge_index[0]/[1].  Checker for efl_csr_from_edge_index: numpy stable sorts
+    (ties keep ascending edge id)."""
+    import numpy as np
+    src = edge_index[0].cpu().numpy().astype(np.int64)
+    dst = edge_index[1].cpu().numpy().astype(np.int64)
+    perm = np.argsort(dst, kind="stable")
+    src_s, dst_s = src[perm], dst[perm]
+    rowptr = np.concatenate(([0], np.cumsum(np.bincount(dst, minlength=num_dst))))
+    src_idx = np.argsort(src_s, kind="stable")
+    src_ptr = np.concatenate(([0], np.cumsum(np.bincount(src, minlength=num_src))))
+    return dict(perm=perm, rowptr=rowptr, src_sorted=src_s, dst_sorted=dst_s, dst_orig=dst, src_ptr=src_ptr,
+                src_idx=src_idx)

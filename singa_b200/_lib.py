@@ -56,6 +56,7 @@ SIGNATURES = {
     "efl_radius_graph_count": "ppiipfiiifiippppppppl" "p",
     "efl_radius_graph_fill": "iifiiifippppp" "ip",
     "efl_radius_graph_emit": "pppilpip",
+    "efl_csr_from_edge_index": "ppiiipppppppp" "plpp",
     "efl_rmsnorm_sh_fwd": "iipppfpip",
     "efl_rmsnorm_sh_bwd": "iippfpppiip",
 }
@@ -89,6 +90,8 @@ def _load():
     lib.efl_radial_hidden_part_size.restype = _I
     lib.efl_radius_graph_temp_bytes.argtypes = [_L]
     lib.efl_radius_graph_temp_bytes.restype = _L
+    lib.efl_csr_temp_bytes.argtypes = [_L, _L]
+    lib.efl_csr_temp_bytes.restype = _L
     lib.efl_rotate_back_parts.argtypes = [_I, _I]
     lib.efl_rotate_back_parts.restype = _I
     return lib
@@ -112,7 +115,7 @@ def stream_ptr():
 
 
 # kernels launched per entry point (for the launch counter bench.py reports)
-_LAUNCHES = {"efl_embedding_grad": 2, "efl_gemm_tn_f32": 2, "efl_colsum": 2, "efl_tc_gemm_tn": 2, "efl_so3_linear_bwd_weight": 2}
+_LAUNCHES = {"efl_csr_from_edge_index": 12, "efl_embedding_grad": 2, "efl_gemm_tn_f32": 2, "efl_colsum": 2, "efl_tc_gemm_tn": 2, "efl_so3_linear_bwd_weight": 2}
 launch_count = 0
 _profile = None  # None, or a list receiving (name, work, start_event, end_event)
 

@@ -120,20 +120,24 @@ def build_csr(edge_index: torch.Tensor, num_src: int, num_dst: int, max_chunk_ed
     grouping used by the backward of the gather.  Row 0 = source, row 1 = target
     (aggregation is over row 1: EF_layers.py:143-145, 1180, 1197-1199)."""
     check_cuda(edge_index)
+    assert edge_index.dim() == 2 and edge_index.shape[0] == 2, "edge_index must be [2, E]"
     E = edge_index.shape[1]
-    src, dst = edge_index[0], edge_index[1]
-    dst_s, perm = torch.sort(dst, stable=True)
-    src_s = src[perm]
-    counts = torch.bincount(dst, minlength=num_dst)
-    rowptr = torch.zeros(num_dst + 1, dtype=torch.int64, device=dst.device)
-    rowptr[1:] = torch.cumsum(counts, 0)
-    _, src_idx = torch.sort(src_s, stable=True)
-    scount = torch.bincount(src, minlength=num_src)
-    src_ptr = torch.zeros(num_src + 1, dtype=torch.int64, device=dst.device)
-    src_ptr[1:] = torch.cumsum(scount, 0)
-    i32 = lambda t: t.to(torch.int32).contiguous()
-    csr = EdgeCSR(num_src, num_dst, E, i32(perm), i32(rowptr), i32(src_s), i32(dst_s), i32(dst), i32(src_ptr),
-                  i32(src_idx))
+    dev = edge_index.device
+    ei = edge_index.detach().to(torch.int64)
+    src, dst = ei[0].contiguous(), ei[1].contiguous()
+    i32 = lambda n: torch.empty(n, dtype=torch.int32, device=dev)
+    perm, src_s, dst_s, dst_o, src_idx = (i32(E) for _ in range(5))
+    rowptr, src_ptr = i32(num_dst + 1), i32(num_src + 1)
+    scratch = i32(3 * max(E, 1))
+    tbytes = int(LIB.efl_csr_temp_bytes(E, max(num_src, num_dst)))
+    temp = torch.empty(tbytes, dtype=torch.uint8, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    call("efl_csr_from_edge_index", ptr(src), ptr(dst), E, num_src, num_dst, ptr(perm), ptr(rowptr), ptr(src_s),
+         ptr(dst_s), ptr(dst_o), ptr(src_ptr), ptr(src_idx), ptr(scratch), ptr(temp), tbytes, ptr(status),
+         work=E * 60.0)
+    csr = EdgeCSR(num_src, num_dst, E, perm, rowptr, src_s, dst_s, dst_o, src_ptr, src_idx)
+    if int(status.item()) != 0:
+        raise IndexError(f"edge_index holds node ids outside [0, {num_src}) x [0, {num_dst})")
     csr.chunks = plan_chunks(rowptr.cpu().numpy(), max_chunk_edges or MAX_CHUNK_EDGES)
     return csr
 

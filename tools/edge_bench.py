@@ -77,6 +77,11 @@ def main():
             rate = d["work"] / iters / (ms * 1e-3) / (1e12 if tensor else 1e9)
             line.update({"achieved": round(rate, 1), "unit": "TFLOP/s" if tensor else "GB/s",
                          "frac_of_measured_peak": round(rate / (peaks["tensor"] if tensor else peaks["hbm"]), 3)})
+            if name in ("efl_s2act_tc_fwd", "efl_s2act_tc_bwd"):
+                # 70 FLOP/B, below the ridge (tensor peak / HBM peak ~ 207 FLOP/B): HBM is the binding roofline.
+                # bf16 rows in and out: fwd 2 x [M,H] x 2 B, bwd 3 x; work = {4,6} G M H per edge, so bytes = work / G
+                gbs = d["work"] / iters / 70.0 / (ms * 1e-3) / 1e9
+                line.update({"hbm_achieved": round(gbs, 1), "hbm_frac_of_measured_peak": round(gbs / peaks["hbm"], 3)})
         print(json.dumps(line))
     print(json.dumps({"summary": "entry points, one layer fwd+bwd", "ms": round(tot, 3),
                       "edges_per_s": round(E / (tot * 1e-3))}))
