@@ -172,7 +172,7 @@ def reference_arm(args):
     val = edges / sec
     cores = os.cpu_count() or 1
     sample = f"one synthetic complex (seed 0) cut to {n} protein + 24 ligand atoms, {edges} edges, 8 A radius graph"
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -181,12 +181,35 @@ def reference_arm(args):
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-    }))
+    })
 
 
 # ----------------------------------------------------------------------------------------------
+_RESULT_FD = None
+
+
+def _quiet_stdout():
+    """The contract is ONE JSON line on stdout: libraries that write to fd 1 (NCCL prints its version there when
+    NCCL_DEBUG is set on the box) are sent to stderr; the result line goes to the saved descriptor."""
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_RESULT_FD, data)
+
+
 def main():
     args = parse()
+    _quiet_stdout()
     if args.impl == "reference":
         reference_arm(args)
         return
@@ -317,7 +340,7 @@ def main():
                 "value": e / sec, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
                 "sample": f"one synthetic complex (seed 0) cut to {n} protein + 24 ligand atoms, {e} edges, fwd+bwd "
                           f"once, {sec:.1f} s"}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
