@@ -875,18 +875,42 @@ class SO2_Convolution(nn.Module):
 _CSR_CACHE = collections.OrderedDict()
 
 
+def _csr_key(edge_index: Tensor, num_src: int, num_dst: int):
+    return (id(edge_index), edge_index._version, num_src, num_dst)
+
+
+def _csr_store(key, edge_index, csr):
+    _CSR_CACHE[key] = (edge_index, csr)
+    while len(_CSR_CACHE) > 16:
+        _CSR_CACHE.popitem(last=False)
+
+
 def _edge_csr(edge_index: Tensor, num_src: int, num_dst: int):
     """Destination-sorted CSR of an edge list, cached on tensor identity (+ in-place version)."""
-    key = (id(edge_index), edge_index._version, num_src, num_dst)
+    key = _csr_key(edge_index, num_src, num_dst)
     hit = _CSR_CACHE.get(key)
     if hit is not None and hit[0] is edge_index:
         _CSR_CACHE.move_to_end(key)
         return hit[1]
     csr = _get_ops().build_csr(edge_index, num_src, num_dst)
-    _CSR_CACHE[key] = (edge_index, csr)
-    while len(_CSR_CACHE) > 16:
-        _CSR_CACHE.popitem(last=False)
+    _csr_store(key, edge_index, csr)
     return csr
+
+
+def prefetch_edge_csr(specs) -> None:
+    """Build the CSRs of several edge lists ``[(edge_index, num_src, num_dst), ...]`` ahead of their first use with
+    one device->host read for all of them (ops.build_csr_many); later ``_edge_csr`` calls hit the cache.  A caller
+    that knows every edge list of a step up front (EquivariantEmbedding.forward) uses this so that no pass stalls the
+    launch queue in the middle of the step."""
+    todo = []
+    for edge_index, num_src, num_dst in specs:
+        key = _csr_key(edge_index, num_src, num_dst)
+        hit = _CSR_CACHE.get(key)
+        if (hit is None or hit[0] is not edge_index) and all(k != key for k, _ in todo):
+            todo.append((key, (edge_index, num_src, num_dst)))
+    if todo:
+        for (key, spec), csr in zip(todo, _get_ops().build_csr_many([spec for _, spec in todo])):
+            _csr_store(key, spec[0], csr)
 
 
 def embedding_lookup(emb: nn.Embedding, ids: Tensor) -> Tensor:

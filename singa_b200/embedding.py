@@ -183,6 +183,10 @@ class EquivariantEmbedding(nn.Module):
         _ef.FRAME_CHECKS.flush(wait=True)  # frame checks of the previous call (long complete: no stall)
         zs = {PROTEIN: g['atomicnum'][PROTEIN], LIGAND: g['atomicnum'][LIGAND]}
         pos = {PROTEIN: g[PROTEIN]['pos'], LIGAND: g[LIGAND]['pos']}
+        if not gen_mode:  # all four edge lists are known here: one device->host read for their CSRs, none mid-step
+            n_p, n_l = len(zs[PROTEIN]), len(zs[LIGAND])
+            _ef.prefetch_edge_csr([(g[PP]['edge_index'], n_p, n_p), (g[LL]['edge_index'], n_l, n_l),
+                                   (g[LP]['edge_index'], n_l, n_p), (g[PL]['edge_index'], n_p, n_l)])
         x_dict[PROTEIN] = self._homo_pass(zs[PROTEIN], g[PROTEIN]['x'], pos[PROTEIN], g[PP]['edge_index'], frames, 'pp')
         if gen_mode:
             return x_dict

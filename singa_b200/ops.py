@@ -115,10 +115,8 @@ class EdgeCSR:
     chunks: list = field(default_factory=list)  # (n0, n1, e0, e1), edges of whole destinations
 
 
-def build_csr(edge_index: torch.Tensor, num_src: int, num_dst: int, max_chunk_edges: int = None) -> EdgeCSR:
-    """Stable sort of the edge list by destination (edge_index[1]) plus the source-side
-    grouping used by the backward of the gather.  Row 0 = source, row 1 = target
-    (aggregation is over row 1: EF_layers.py:143-145, 1180, 1197-1199)."""
+def _launch_csr(edge_index: torch.Tensor, num_src: int, num_dst: int):
+    """Queue the CSR kernels of one edge list; returns (csr without chunk plan, device status word)."""
     check_cuda(edge_index)
     assert edge_index.dim() == 2 and edge_index.shape[0] == 2, "edge_index must be [2, E]"
     E = edge_index.shape[1]
@@ -135,11 +133,33 @@ def build_csr(edge_index: torch.Tensor, num_src: int, num_dst: int, max_chunk_ed
     call("efl_csr_from_edge_index", ptr(src), ptr(dst), E, num_src, num_dst, ptr(perm), ptr(rowptr), ptr(src_s),
          ptr(dst_s), ptr(dst_o), ptr(src_ptr), ptr(src_idx), ptr(scratch), ptr(temp), tbytes, ptr(status),
          work=E * 60.0)
-    csr = EdgeCSR(num_src, num_dst, E, perm, rowptr, src_s, dst_s, dst_o, src_ptr, src_idx)
-    if int(status.item()) != 0:
-        raise IndexError(f"edge_index holds node ids outside [0, {num_src}) x [0, {num_dst})")
-    csr.chunks = plan_chunks(rowptr.cpu().numpy(), max_chunk_edges or MAX_CHUNK_EDGES)
-    return csr
+    return EdgeCSR(num_src, num_dst, E, perm, rowptr, src_s, dst_s, dst_o, src_ptr, src_idx), status
+
+
+def build_csr_many(specs, max_chunk_edges: int = None) -> list:
+    """``build_csr`` for several edge lists ``[(edge_index, num_src, num_dst), ...]`` with ONE device->host read
+    (status words + row pointers of all of them) instead of two per list: the chunk plan needs the row pointers on
+    the host, and every read drains the launch queue."""
+    if not specs:
+        return []
+    launched = [_launch_csr(*spec) for spec in specs]
+    host = torch.cat([t for csr, st in launched for t in (st, csr.rowptr)]).cpu().numpy()
+    out, o = [], 0
+    for (csr, _), (_, num_src, num_dst) in zip(launched, specs):
+        status, rowptr = int(host[o]), host[o + 1:o + 2 + num_dst]
+        o += 2 + num_dst
+        if status != 0:
+            raise IndexError(f"edge_index holds node ids outside [0, {num_src}) x [0, {num_dst})")
+        csr.chunks = plan_chunks(rowptr, max_chunk_edges or MAX_CHUNK_EDGES)
+        out.append(csr)
+    return out
+
+
+def build_csr(edge_index: torch.Tensor, num_src: int, num_dst: int, max_chunk_edges: int = None) -> EdgeCSR:
+    """Stable sort of the edge list by destination (edge_index[1]) plus the source-side
+    grouping used by the backward of the gather.  Row 0 = source, row 1 = target
+    (aggregation is over row 1: EF_layers.py:143-145, 1180, 1197-1199)."""
+    return build_csr_many([(edge_index, num_src, num_dst)], max_chunk_edges)[0]
 
 
 def plan_chunks(rowptr: np.ndarray, max_edges: int) -> list:

@@ -62,3 +62,29 @@ def test_out_of_range_ids_raise():
     ei = torch.tensor([[0, -1, 2], [0, 1, 1]], dtype=torch.int64, device=DEV)
     with pytest.raises(IndexError):
         ops.build_csr(ei, 3, 3)
+
+
+def test_batched_build_matches_single_builds_and_fills_the_cache():
+    """ops.build_csr_many / EF_layers.prefetch_edge_csr: one device->host read for several edge lists, same arrays and
+    chunk plans as one build per list; a bad list in the batch still raises."""
+    from singa_b200 import EF_layers as ef
+    from singa_b200 import ops
+    rs = np.random.RandomState(21)
+    shapes = [(40, 40, 500), (6, 40, 90), (40, 6, 90), (9, 9, 0)]
+    eis = [torch.from_numpy(np.stack((rs.randint(0, ns, size=E), rs.randint(0, nd, size=E))).astype(np.int64)).to(DEV)
+           for ns, nd, E in shapes]
+    specs = [(ei, ns, nd) for ei, (ns, nd, _) in zip(eis, shapes)]
+    many = ops.build_csr_many(specs, max_chunk_edges=64)
+    for csr, (ei, ns, nd) in zip(many, specs):
+        one = ops.build_csr(ei, ns, nd, max_chunk_edges=64)
+        assert all(torch.equal(getattr(csr, f), getattr(one, f)) for f in FIELDS)
+        assert csr.chunks == one.chunks
+    ef._CSR_CACHE.clear()
+    ef.prefetch_edge_csr(specs + specs[:1])
+    assert len(ef._CSR_CACHE) == len(specs)
+    for ei, ns, nd in specs:
+        hit = ef._edge_csr(ei, ns, nd)
+        assert hit is ef._CSR_CACHE[ef._csr_key(ei, ns, nd)][1]
+    bad = torch.tensor([[0, 1], [0, 7]], dtype=torch.int64, device=DEV)
+    with pytest.raises(IndexError):
+        ops.build_csr_many([specs[0], (bad, 3, 3)])
