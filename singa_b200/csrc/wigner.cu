@@ -7,122 +7,131 @@
 // kernel emits exactly those rows (235 values for lmax 6, mmax 2), each padded to 16 bytes: WSZ = 296 floats/edge.
 //
 // D^l = Z(alpha) J_l Z(beta) J_l Z(gamma) with Z(a)[m,m] = cos(m a), Z(a)[m,-m] = -sin(m a).
-// One warp per edge; lane j owns kept row j.
+//
+// One THREAD per edge, every (l, m') row fully unrolled.  The J matrices sit in __constant__ memory: with all lanes
+// of a warp on the same (l, m', i, k) the operand is a constant-bank immediate of the FFMA (no shared-memory load per
+// multiply), and J_l is 3/4 structural zeros (it only couples m-classes (sign, parity of l+|m|) in a fixed pairing), a
+// pattern known at compile time, so the skipped products never issue: 585 FFMA per edge for (6,2) instead of the
+// 2 253 of the dense row-times-matrix products.  (The earlier warp-per-edge kernel serialised the seven degrees of a
+// warp's rows through a switch and paid one LDS per FFMA: 2.8 ns/edge; see profiles/r1_radius_bench_v1.jsonl.)
 #include "efl_common.cuh"
 
 namespace efl {
 
-template <int l>
-__device__ __forceinline__ void wigner_row(int mp, const float* __restrict__ J, const float (*sc)[2],
-                                           const float (*scb)[2], const float (*scg)[2],
+constexpr int WIG_LMAX_BUILT = 8;
+__host__ __device__ constexpr int wig_joff(int l) { return l * (2 * l - 1) * (2 * l + 1) / 3; }  // sum_{k<l} (2k+1)^2
+// J_l blocks l = 0..8, row-major, concatenated: the table for a smaller lmax is a prefix of it
+__constant__ float cJ[wig_joff(WIG_LMAX_BUILT + 1)];
+
+// Structural non-zeros of J_l.  Class of order m: (s, q) = (m < 0, parity of l + |m|); J_l couples (1,1) and (0,0) to
+// themselves and (1,0) with (0,1).  (A superset of the numerical non-zeros; tests/test_constants.py checks it.)
+__host__ __device__ constexpr bool wig_jnz(int l, int i, int k) {
+  const int mi = i - l, mk = k - l;
+  const int si = mi < 0, sk = mk < 0;
+  const int qi = (l + (mi < 0 ? -mi : mi)) & 1, qk = (l + (mk < 0 ? -mk : mk)) & 1;
+  return (si == qi) ? (si == sk && qi == qk) : (si != sk && qi != qk);
+}
+
+template <int l, int mp, int NA>
+__device__ __forceinline__ void wigner_row(const float (&cA)[NA], const float (&sA)[NA], const float (&cB)[NA],
+                                           const float (&sB)[NA], const float (&cG)[NA], const float (&sG)[NA],
                                            float* __restrict__ out) {
-  constexpr int n = 2 * l + 1;
-  float r2[n], r3[n], r4[n];
-  const int am = mp < 0 ? -mp : mp;
-  // signed order: cos(m a) is even, sin(m a) odd
-  const float ca = sc[am][0];
-  const float sa = mp < 0 ? -sc[am][1] : sc[am][1];
+  constexpr int n = 2 * l + 1, jo = wig_joff(l), am = mp < 0 ? -mp : mp, rl = (n + 3) & ~3;
+  float r2[n], r3[n], r4[rl];
+  // row m' of Z(alpha) J: cos(m' a) J[m', :] - sin(m' a) J[-m', :]   (cos even, sin odd in m')
+  const float ca = cA[am];
+  const float sa = mp < 0 ? -sA[am] : sA[am];
 #pragma unroll
   for (int k = 0; k < n; ++k) {
-    float v = ca * J[(mp + l) * n + k];
-    if (mp != 0) v -= sa * J[(-mp + l) * n + k];
+    float v = 0.f;
+    if (wig_jnz(l, mp + l, k)) v = ca * cJ[jo + (mp + l) * n + k];
+    if (mp != 0 && wig_jnz(l, -mp + l, k)) v = fmaf(-sa, cJ[jo + (-mp + l) * n + k], v);
     r2[k] = v;
   }
+  // times Z(beta)
 #pragma unroll
   for (int k = 0; k < n; ++k) {
-    const int nn = k - l;
-    const int an = nn < 0 ? -nn : nn;
+    const int nn = k - l, an = nn < 0 ? -nn : nn;
     if (nn == 0) {
       r3[k] = r2[k];
     } else {
-      const float sb = nn < 0 ? -scb[an][1] : scb[an][1];
-      r3[k] = r2[k] * scb[an][0] + r2[n - 1 - k] * sb;
+      const float sb = nn < 0 ? -sB[an] : sB[an];
+      r3[k] = r2[k] * cB[an] + r2[n - 1 - k] * sb;
     }
   }
+  // times J (structural zeros skipped)
 #pragma unroll
   for (int k = 0; k < n; ++k) {
     float acc = 0.f;
 #pragma unroll
-    for (int i = 0; i < n; ++i) acc = fmaf(r3[i], J[i * n + k], acc);
+    for (int i = 0; i < n; ++i)
+      if (wig_jnz(l, i, k)) acc = fmaf(r3[i], cJ[jo + i * n + k], acc);
     r4[k] = acc;
   }
+  // times Z(gamma), rows padded to 16 bytes
+  float o[rl];
 #pragma unroll
-  for (int k = 0; k < n; ++k) {
-    const int nn = k - l;
-    const int an = nn < 0 ? -nn : nn;
-    if (nn == 0) {
-      out[k] = r4[k];
+  for (int k = 0; k < rl; ++k) {
+    const int nn = k - l, an = nn < 0 ? -nn : nn;
+    if (k >= n) {
+      o[k] = 0.f;
+    } else if (nn == 0) {
+      o[k] = r4[k];
     } else {
-      const float sg = nn < 0 ? -scg[an][1] : scg[an][1];
-      out[k] = r4[k] * scg[an][0] + r4[n - 1 - k] * sg;
+      const float sg = nn < 0 ? -sG[an] : sG[an];
+      o[k] = r4[k] * cG[an] + r4[n - 1 - k] * sg;
     }
+  }
+#pragma unroll
+  for (int q = 0; q < rl / 4; ++q)
+    *reinterpret_cast<float4*>(out + 4 * q) = make_float4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+}
+
+template <int LMAX, int MMAX, int l, int mp, int NA>
+__device__ __forceinline__ void wigner_rows(const float (&cA)[NA], const float (&sA)[NA], const float (&cB)[NA],
+                                            const float (&sB)[NA], const float (&cG)[NA], const float (&sG)[NA],
+                                            float* __restrict__ out) {
+  using T = Tab<LMAX, MMAX>;
+  if constexpr (l <= LMAX) {
+    if constexpr (l == 0) {
+      *reinterpret_cast<float4*>(out) = make_float4(1.0f * cJ[0] * cJ[0], 0.f, 0.f, 0.f);
+    } else {
+      wigner_row<l, mp>(cA, sA, cB, sB, cG, sG, out + T::wrow(l, mp));
+    }
+    if constexpr (mp < T::mm(l)) wigner_rows<LMAX, MMAX, l, mp + 1>(cA, sA, cB, sB, cG, sG, out);
+    else wigner_rows<LMAX, MMAX, l + 1, -T::mm(l + 1)>(cA, sA, cB, sB, cG, sG, out);
   }
 }
 
 template <int LMAX, int MMAX>
-__global__ void __launch_bounds__(128) wigner_kernel(const float* __restrict__ rot, const float* __restrict__ jd,
-                                                     float* __restrict__ wig, int E) {
+__global__ void __launch_bounds__(128) wigner_kernel(const float* __restrict__ rot, float* __restrict__ wig, int E) {
   using T = Tab<LMAX, MMAX>;
-  constexpr int JSZ = (LMAX + 1) * (2 * LMAX + 1) * (2 * LMAX + 3) / 3;  // sum (2l+1)^2
-  __shared__ float sJ[JSZ];
-  __shared__ float sSC[4][3][LMAX + 1][2];
-  for (int i = threadIdx.x; i < JSZ; i += blockDim.x) sJ[i] = jd[i];
-  __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int e = blockIdx.x * 4 + warp;
+  static_assert(T::WSZ % 4 == 0, "16-byte rows");
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= E) return;
   const float* R = rot + (size_t)e * 9;
+  const float R0 = R[0], R1 = R[1], R2 = R[2], R4 = R[4], R6 = R[6], R7 = R[7], R8 = R[8];
   // x = R @ (0,1,0): second column (EF_layers.py:509)
-  float x0 = R[1], x1 = R[4], x2 = R[7];
-  float nrm = fmaxf(sqrtf(x0 * x0 + x1 * x1 + x2 * x2), 1e-12f);
+  float x0 = R1, x1 = R4, x2 = R7;
+  const float nrm = fmaxf(sqrtf(x0 * x0 + x1 * x1 + x2 * x2), 1e-12f);
   x0 = fminf(fmaxf(x0 / nrm, -1.f), 1.f);
   x1 = fminf(fmaxf(x1 / nrm, -1.f), 1.f);
   x2 = fminf(fmaxf(x2 / nrm, -1.f), 1.f);
   const float beta = acosf(x1);
   const float alpha = atan2f(x0, x2);
   // first row of (Ry(alpha) Rx(beta))^T R  ->  gamma (EF_layers.py:511-517)
-  const float ca = cosf(alpha), sa = sinf(alpha);
-  const float r00 = ca * R[0] - sa * R[6];
-  const float r02 = ca * R[2] - sa * R[8];
+  const float ca1 = cosf(alpha), sa1 = sinf(alpha);
+  const float r00 = ca1 * R0 - sa1 * R6;
+  const float r02 = ca1 * R2 - sa1 * R8;
   const float gamma = atan2f(r02, r00);
-  if (lane < 3 * (LMAX + 1)) {
-    const int which = lane / (LMAX + 1), k = lane % (LMAX + 1);
-    const float ang = which == 0 ? alpha : (which == 1 ? beta : gamma);
-    const float a = (float)k * ang;
-    sSC[warp][which][k][0] = cosf(a);
-    sSC[warp][which][k][1] = sinf(a);
+  float cA[LMAX + 1], sA[LMAX + 1], cB[LMAX + 1], sB[LMAX + 1], cG[LMAX + 1], sG[LMAX + 1];
+#pragma unroll
+  for (int k = 0; k <= LMAX; ++k) {  // cos / sin of (k * angle), as the reference's _z_rot_mat forms them
+    sincosf((float)k * alpha, &sA[k], &cA[k]);
+    sincosf((float)k * beta, &sB[k], &cB[k]);
+    sincosf((float)k * gamma, &sG[k], &cG[k]);
   }
-  __syncwarp();
-  float* out = wig + (size_t)e * T::WSZ;
-  for (int j = lane; j < T::M; j += 32) {
-    // decode (l, m') of kept row j in l-primary order
-    int l = 0, base = 0;
-    while (base + T::nrows(l) <= j) {
-      base += T::nrows(l);
-      ++l;
-    }
-    const int mp = j - base - T::mm(l);
-    int joff = 0;
-    for (int k = 0; k < l; ++k) joff += (2 * k + 1) * (2 * k + 1);
-    const float* J = sJ + joff;
-    float* o = out + T::wrow(l, mp);
-    for (int k = 2 * l + 1; k < T::rowlen(l); ++k) o[k] = 0.f;  // row padding (16-byte rows)
-    const float(*sA)[2] = sSC[warp][0];
-    const float(*sB)[2] = sSC[warp][1];
-    const float(*sG)[2] = sSC[warp][2];
-    switch (l) {
-      case 0: o[0] = 1.0f * J[0] * J[0]; break;
-      case 1: wigner_row<1>(mp, J, sA, sB, sG, o); break;
-      case 2: wigner_row<2>(mp, J, sA, sB, sG, o); break;
-      case 3: if constexpr (LMAX >= 3) wigner_row<3>(mp, J, sA, sB, sG, o); break;
-      case 4: if constexpr (LMAX >= 4) wigner_row<4>(mp, J, sA, sB, sG, o); break;
-      case 5: if constexpr (LMAX >= 5) wigner_row<5>(mp, J, sA, sB, sG, o); break;
-      case 6: if constexpr (LMAX >= 6) wigner_row<6>(mp, J, sA, sB, sG, o); break;
-      case 7: if constexpr (LMAX >= 7) wigner_row<7>(mp, J, sA, sB, sG, o); break;
-      case 8: if constexpr (LMAX >= 8) wigner_row<8>(mp, J, sA, sB, sG, o); break;
-      default: break;
-    }
-  }
+  wigner_rows<LMAX, MMAX, 0, 0>(cA, sA, cB, sB, cG, sG, wig + (size_t)e * T::WSZ);
 }
 
 }  // namespace efl
@@ -131,14 +140,21 @@ extern "C" int efl_wigner_from_rotmat(int lmax, int mmax, const float* rot, cons
                                       void* stream) {
   if (E <= 0) return EFL_OK;
   cudaStream_t s = (cudaStream_t)stream;
-  dim3 grid((E + 3) / 4), block(128);
-  if (lmax == 6 && mmax == 2) efl::wigner_kernel<6, 2><<<grid, block, 0, s>>>(rot, jd, wig, E);
-  else if (lmax == 8 && mmax == 2) efl::wigner_kernel<8, 2><<<grid, block, 0, s>>>(rot, jd, wig, E);
-  else if (lmax == 4 && mmax == 2) efl::wigner_kernel<4, 2><<<grid, block, 0, s>>>(rot, jd, wig, E);
-  else {
+  if (!(mmax == 2 && (lmax == 4 || lmax == 6 || lmax == 8))) {
     efl_set_error("efl_wigner_from_rotmat: unsupported (lmax, mmax); built for (6,2), (8,2), (4,2)");
     return EFL_ERR_UNSUPPORTED;
   }
+  // J table -> constant bank, stream-ordered (a prefix of the lmax = 8 table; every caller writes the same values)
+  cudaError_t err = cudaMemcpyToSymbolAsync(efl::cJ, jd, sizeof(float) * efl::wig_joff(lmax + 1), 0,
+                                            cudaMemcpyDeviceToDevice, s);
+  if (err != cudaSuccess) {
+    efl_set_error(cudaGetErrorString(err));
+    return (int)err;
+  }
+  dim3 grid((E + 127) / 128), block(128);
+  if (lmax == 6) efl::wigner_kernel<6, 2><<<grid, block, 0, s>>>(rot, wig, E);
+  else if (lmax == 8) efl::wigner_kernel<8, 2><<<grid, block, 0, s>>>(rot, wig, E);
+  else efl::wigner_kernel<4, 2><<<grid, block, 0, s>>>(rot, wig, E);
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }

@@ -108,6 +108,17 @@ def j_matrix(l: int) -> np.ndarray:
 # coefficient index tables (CoefficientMappingModule, EF_layers.py:1421-1549)
 # ----------------------------------------------------------------------------
 @functools.lru_cache(maxsize=None)
+def j_structural_nonzero(l: int) -> np.ndarray:
+    """Boolean [2l+1, 2l+1]: entries of ``J_l`` that can be non-zero.  With the class of order m defined as
+    (s, q) = (m < 0, parity of l + |m|), J_l couples (1,1) and (0,0) to themselves and (1,0) with (0,1); every other
+    entry is exactly zero.  csrc/wigner.cu (``wig_jnz``) skips the zero products at compile time."""
+    m = np.arange(-l, l + 1)
+    s, q = (m < 0).astype(int), (l + np.abs(m)) % 2
+    same = (s[:, None] == s[None, :]) & (q[:, None] == q[None, :])
+    swap = (s[:, None] != s[None, :]) & (q[:, None] != q[None, :])
+    return np.where((s == q)[:, None], same, swap)
+
+
 def coefficient_tables(lmax: int, mmax: int) -> dict:
     """Index tables for one resolution.
 

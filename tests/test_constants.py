@@ -20,6 +20,14 @@ def test_j_matrices_are_symmetric_involutions():
 
 
 @pytest.mark.skipif(not rl.reference_available(), reason="needs /root/reference (build container only)")
+def test_j_matrix_zero_pattern_used_by_the_wigner_kernel():
+    """csrc/wigner.cu skips products with structurally zero J entries: the pattern must cover every non-zero."""
+    for l in range(0, 12):
+        J, nz = sc.j_matrix(l), sc.j_structural_nonzero(l)
+        assert float(np.abs(J[~nz]).max() if (~nz).any() else 0.0) < 1e-13, l
+        assert nz.sum() <= (2 * l + 1) ** 2 // 4 + l + 1
+
+
 def test_j_matrices_match_shipped_jd():
     jd = torch.load(os.path.join(rl.REFERENCE_ROOT, "model", "Jd.pt"), weights_only=False)
     for l in range(len(jd)):
