@@ -54,6 +54,22 @@ def pack_feature_bits(x: torch.Tensor) -> torch.Tensor:
     return (x[:, -15:].to(torch.long) * weights).sum(dim=1)
 
 
+def batch_vector_from_ptr(ptr: torch.Tensor, num_nodes: Optional[int] = None, device=None) -> torch.Tensor:
+    """Node -> complex id vector from the pyg ``ptr`` offsets: the vectorised form of the two Python loops of
+    ``SINGA.forward`` (GAN.py:48-55: ``batch.extend([i] * (ptr[i+1] - ptr[i]))``), which cost one device read per
+    complex.  ``num_nodes`` (= ``ptr[-1]``, known to the caller as ``len(x)``) avoids the one remaining read."""
+    counts = ptr[1:] - ptr[:-1]
+    ids = torch.arange(counts.numel(), dtype=torch.long, device=ptr.device)
+    out = torch.repeat_interleave(ids, counts, output_size=num_nodes)
+    return out if device is None else out.to(device)
+
+
+def stack_props(dic: Dict[str, torch.Tensor], props) -> torch.Tensor:
+    """``torch.tensor(list(zip(*[dic[p] for p in props])))`` (GAN.py:42) without the per-element host round trip:
+    [num_complexes, len(props)] float32."""
+    return torch.stack([dic[p].reshape(-1).to(torch.float32) for p in props], dim=1)
+
+
 class EquivariantEmbedding(nn.Module):
     def __init__(self, config, device: str = 'cuda', compute_dead_blocks: bool = False) -> None:
         super().__init__()

@@ -89,3 +89,22 @@ def test_synthetic_complex_shape():
     p1 = syn.portable_parameters([("a.weight", (3, 4)), ("b.bias", (5,))], 3)
     p2 = syn.portable_parameters([("b.bias", (5,)), ("a.weight", (3, 4))], 3)
     assert torch.equal(p1["a.weight"], p2["a.weight"]) and torch.equal(p1["b.bias"], p2["b.bias"])
+
+
+def test_batch_vector_and_props_equal_the_reference_loops():
+    """GAN.py:42, 48-55 restated literally (Python loops) against the vectorised helpers, including empty complexes."""
+    from singa_b200.embedding import batch_vector_from_ptr, stack_props
+    for ptr in ([0, 3, 3, 10, 11], [0, 5], [0, 0, 2]):
+        _batch = torch.tensor(ptr)
+        batch = []
+        for i in range(_batch.shape[0] - 1):
+            batch.extend([i] * (_batch[i + 1] - _batch[i]))
+        want = torch.tensor(batch, dtype=torch.long)
+        assert torch.equal(batch_vector_from_ptr(_batch), want)
+        assert torch.equal(batch_vector_from_ptr(_batch, num_nodes=ptr[-1]), want)
+    dic = {"vina_score": torch.tensor([1.0, 0.0, 1.0]), "qed": torch.tensor([0.0, 0.0, 1.0]),
+           "sas": torch.tensor([1.0, 1.0, 0.0])}
+    props = ["vina_score", "qed", "sas"]
+    want = torch.tensor(list(zip(*[dic[p] for p in props])))
+    got = stack_props(dic, props)
+    assert got.shape == (3, 3) and torch.equal(got, want.to(torch.float32))
