@@ -12,8 +12,13 @@
 // of a warp on the same (l, m', i, k) the operand is a constant-bank immediate of the FFMA (no shared-memory load per
 // multiply), and J_l is 3/4 structural zeros (it only couples m-classes (sign, parity of l+|m|) in a fixed pairing), a
 // pattern known at compile time, so the skipped products never issue: 585 FFMA per edge for (6,2) instead of the
-// 2 253 of the dense row-times-matrix products.  (The earlier warp-per-edge kernel serialised the seven degrees of a
+// 2 253 of the dense row-times-matrix products.  A thread's rows go to HBM through a per-warp shared-memory stage, one
+// degree block at a time: written directly, each 16-byte store of a warp lands in 32 different lines (edges are
+// 1 184 B apart) and the kernel is bound by L2 write requests (12.7 ms per 12 M edges, 0.18 of HBM); staged, a warp's
+// store instruction covers whole contiguous degree blocks (<= 400 B runs).  (The earlier warp-per-edge kernel serialised the seven degrees of a
 // warp's rows through a switch and paid one LDS per FFMA: 2.8 ns/edge; see profiles/r1_radius_bench_v1.jsonl.)
+#include <cstdlib>
+
 #include "efl_common.cuh"
 
 namespace efl {
@@ -87,28 +92,73 @@ __device__ __forceinline__ void wigner_row(const float (&cA)[NA], const float (&
     *reinterpret_cast<float4*>(out + 4 * q) = make_float4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
 }
 
-template <int LMAX, int MMAX, int l, int mp, int NA>
+// shared-memory row stride (floats) of a staged degree block of BL floats: an odd number of 16-byte units, so the
+// 128-bit stores of 8 consecutive lanes fall into distinct bank groups
+__host__ __device__ constexpr int wig_stride(int BL) { return ((BL / 4) & 1) ? BL : BL + 4; }
+template <int LMAX, int MMAX>
+__host__ __device__ constexpr int wig_stage_floats() {
+  int m = 0;
+  for (int l = 0; l <= LMAX; ++l) {
+    const int s = wig_stride(Tab<LMAX, MMAX>::nrows(l) * Tab<LMAX, MMAX>::rowlen(l));
+    m = s > m ? s : m;
+  }
+  return m;
+}
+
+// copy the staged block of degree l of the warp's 32 edges to the Wigner store, 16 bytes per lane and coalesced
+template <int LMAX, int MMAX, int l>
+__device__ __forceinline__ void wigner_flush(const float* __restrict__ stage, float* __restrict__ wig, int e0, int E,
+                                             int lane) {
+  using T = Tab<LMAX, MMAX>;
+  constexpr int BL = T::nrows(l) * T::rowlen(l), UPB = BL / 4, S = wig_stride(BL);
+  __syncwarp();
+#pragma unroll 5
+  for (int u = lane; u < 32 * UPB; u += 32) {
+    const int ed = u / UPB, q = u - ed * UPB;
+    if (e0 + ed < E) {
+      const float4 v = *reinterpret_cast<const float4*>(stage + ed * S + 4 * q);
+      *reinterpret_cast<float4*>(wig + (size_t)(e0 + ed) * T::WSZ + T::woff(l) + 4 * q) = v;
+    }
+  }
+  __syncwarp();
+}
+
+// STAGED: out = the warp's stage (each lane writes its edge's rows at lane * stride), flushed after every degree;
+// otherwise out = the edge's slot in the Wigner store.
+template <int LMAX, int MMAX, bool STAGED, int l, int mp, int NA>
 __device__ __forceinline__ void wigner_rows(const float (&cA)[NA], const float (&sA)[NA], const float (&cB)[NA],
                                             const float (&sB)[NA], const float (&cG)[NA], const float (&sG)[NA],
-                                            float* __restrict__ out) {
+                                            float* __restrict__ out, float* __restrict__ wig, int e0, int E, int lane) {
   using T = Tab<LMAX, MMAX>;
   if constexpr (l <= LMAX) {
+    constexpr int S = wig_stride(T::nrows(l) * T::rowlen(l));
+    float* row = STAGED ? out + lane * S + (mp + T::mm(l)) * T::rowlen(l) : out + T::wrow(l, mp);
     if constexpr (l == 0) {
-      *reinterpret_cast<float4*>(out) = make_float4(1.0f * cJ[0] * cJ[0], 0.f, 0.f, 0.f);
+      *reinterpret_cast<float4*>(row) = make_float4(1.0f * cJ[0] * cJ[0], 0.f, 0.f, 0.f);
     } else {
-      wigner_row<l, mp>(cA, sA, cB, sB, cG, sG, out + T::wrow(l, mp));
+      wigner_row<l, mp>(cA, sA, cB, sB, cG, sG, row);
     }
-    if constexpr (mp < T::mm(l)) wigner_rows<LMAX, MMAX, l, mp + 1>(cA, sA, cB, sB, cG, sG, out);
-    else wigner_rows<LMAX, MMAX, l + 1, -T::mm(l + 1)>(cA, sA, cB, sB, cG, sG, out);
+    if constexpr (mp < T::mm(l)) {
+      wigner_rows<LMAX, MMAX, STAGED, l, mp + 1>(cA, sA, cB, sB, cG, sG, out, wig, e0, E, lane);
+    } else {
+      if constexpr (STAGED) wigner_flush<LMAX, MMAX, l>(out, wig, e0, E, lane);
+      wigner_rows<LMAX, MMAX, STAGED, l + 1, -T::mm(l + 1)>(cA, sA, cB, sB, cG, sG, out, wig, e0, E, lane);
+    }
   }
 }
 
-template <int LMAX, int MMAX>
-__global__ void __launch_bounds__(128) wigner_kernel(const float* __restrict__ rot, float* __restrict__ wig, int E) {
+constexpr int WIG_WARPS = 2;
+
+template <int LMAX, int MMAX, bool STAGED>
+__global__ void __launch_bounds__(32 * WIG_WARPS) wigner_kernel(const float* __restrict__ rot, float* __restrict__ wig,
+                                                                int E) {
   using T = Tab<LMAX, MMAX>;
   static_assert(T::WSZ % 4 == 0, "16-byte rows");
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= E) return;
+  __shared__ __align__(16) float stage[STAGED ? WIG_WARPS * 32 * wig_stage_floats<LMAX, MMAX>() : 4];
+  const int e_raw = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (!STAGED && e_raw >= E) return;
+  const int e = e_raw < E ? e_raw : E - 1;  // staged: lanes past the end compute a duplicate and store nothing
   const float* R = rot + (size_t)e * 9;
   const float R0 = R[0], R1 = R[1], R2 = R[2], R4 = R[4], R6 = R[6], R7 = R[7], R8 = R[8];
   // x = R @ (0,1,0): second column (EF_layers.py:509)
@@ -131,7 +181,15 @@ __global__ void __launch_bounds__(128) wigner_kernel(const float* __restrict__ r
     sincosf((float)k * beta, &sB[k], &cB[k]);
     sincosf((float)k * gamma, &sG[k], &cG[k]);
   }
-  wigner_rows<LMAX, MMAX, 0, 0>(cA, sA, cB, sB, cG, sG, wig + (size_t)e * T::WSZ);
+  float* out = STAGED ? stage + warp * 32 * wig_stage_floats<LMAX, MMAX>() : wig + (size_t)e * T::WSZ;
+  wigner_rows<LMAX, MMAX, STAGED, 0, 0>(cA, sA, cB, sB, cG, sG, out, wig, e_raw - lane, E, lane);
+}
+
+template <int LMAX, int MMAX>
+static void wigner_launch(const float* rot, float* wig, int E, bool staged, cudaStream_t s) {
+  const int T = 32 * WIG_WARPS;
+  if (staged) wigner_kernel<LMAX, MMAX, true><<<(E + T - 1) / T, T, 0, s>>>(rot, wig, E);
+  else wigner_kernel<LMAX, MMAX, false><<<(E + T - 1) / T, T, 0, s>>>(rot, wig, E);
 }
 
 }  // namespace efl
@@ -151,10 +209,13 @@ extern "C" int efl_wigner_from_rotmat(int lmax, int mmax, const float* rot, cons
     efl_set_error(cudaGetErrorString(err));
     return (int)err;
   }
-  dim3 grid((E + 127) / 128), block(128);
-  if (lmax == 6) efl::wigner_kernel<6, 2><<<grid, block, 0, s>>>(rot, wig, E);
-  else if (lmax == 8) efl::wigner_kernel<8, 2><<<grid, block, 0, s>>>(rot, wig, E);
-  else efl::wigner_kernel<4, 2><<<grid, block, 0, s>>>(rot, wig, E);
+  static const bool staged = [] {  // EFL_WIGNER_DIRECT=1: per-thread stores straight to HBM (A/B switch)
+    const char* v = getenv("EFL_WIGNER_DIRECT");
+    return !(v && v[0] == '1');
+  }();
+  if (lmax == 6) efl::wigner_launch<6, 2>(rot, wig, E, staged, s);
+  else if (lmax == 8) efl::wigner_launch<8, 2>(rot, wig, E, staged, s);
+  else efl::wigner_launch<4, 2>(rot, wig, E, staged, s);
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }

@@ -40,6 +40,24 @@ def test_wigner_kernel_matches_reference_rows(lmax, key):
     assert off == wig.shape[1]
 
 
+@pytest.mark.parametrize("lmax", [6, 8])
+def test_wigner_kernel_ragged_edge_counts(lmax):
+    """Edge counts that are not a multiple of the warp / CTA size (the staged stores are warp-cooperative): every
+    prefix of the golden edge set gives bit-identical rows, and nothing is written past the last edge."""
+    from singa_b200 import ops
+    rot = load_golden("wigner_small.pt")["rot"].to(DEV)
+    rot = torch.cat([rot, rot.flip(0), rot], dim=0)  # 192 edges: several warps and CTAs
+    full = ops.wigner_from_rotmat(rot, lmax, 2)
+    for n in (1, 31, 32, 33, 63, 65, 127, 191):
+        part = ops.wigner_from_rotmat(rot[:n].contiguous(), lmax, 2)
+        assert part.shape == (n, full.shape[1])
+        assert torch.equal(part, full[:n]), n
+    from singa_b200._lib import call, ptr
+    guard = torch.full((35, full.shape[1]), 7.0, device=DEV)
+    call("efl_wigner_from_rotmat", lmax, 2, ptr(rot), ptr(ops.jd_device(lmax, rot.device)), ptr(guard), 33)
+    assert torch.equal(guard[:33], full[:33]) and bool((guard[33:] == 7.0).all())
+
+
 @pytest.mark.parametrize("name", ["homo", "hetero"])
 def test_transblock_fwd_bwd_matches_reference_golden(name):
     errs = run_attention_case(name, DEV, "fp32", return_all=True)

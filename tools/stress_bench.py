@@ -73,6 +73,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"])
+    ap.add_argument("--profile", action="store_true", help="CUDA-event time per entry point (rank 0)")
     args = ap.parse_args()
     import torch.distributed as dist
     world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
@@ -109,11 +110,14 @@ def main():
         dist.barrier()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n0 = _lib.launch_count
+    if args.profile:
+        _lib.start_profile()
     a.record()
     for _ in range(args.steps):
         loss = step()
     b.record()
     torch.cuda.synchronize()
+    prof = _lib.stop_profile() if args.profile else {}
     ms = torch.tensor([a.elapsed_time(b) / args.steps], device=dev)
     tot = torch.tensor([float(edges)], device=dev)
     if world > 1:
@@ -128,7 +132,9 @@ def main():
             "mean_degree": round(g["ei_pp"].shape[1] / g["z_p"].numel(), 2), "ms_per_step": round(float(ms), 3),
             "edges_per_s": round(float(tot) / (float(ms) * 1e-3)), "loss_finite": finite,
             "gpu_launches_per_step": (_lib.launch_count - n0) // args.steps,
-            "peak_mem_GB": round(torch.cuda.max_memory_allocated() / 2 ** 30, 2)}), flush=True)
+            "peak_mem_GB": round(torch.cuda.max_memory_allocated() / 2 ** 30, 2),
+            "kernel_ms_per_step": {k: round(v["ms"] / args.steps, 3)
+                                   for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}}), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
