@@ -29,6 +29,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 METRIC = "EF_layers fwd+bwd edges/sec"
+DOMINANT = "efl_tc_gemm_nt"  # entry point with the largest share of a step (checked against the full profile)
 UNIT = "edges/s"
 
 
@@ -277,7 +278,10 @@ def main():
     if rank == 0:
         sampler.start()
     launches0 = _lib.launch_count
-    _lib.start_profile()
+    # Event pairs in the timed region only around the dominant entry point (the roofline's kernel): pairs around all
+    # ~5 000 calls of a step cost enough host time to make the step host-bound on a slow box.  The per-entry-point
+    # breakdown comes from a second, fully profiled pass of the same K steps below (outside the timed region).
+    _lib.start_profile(only={DOMINANT})
     ms_dev = timed(lambda: step(resident), args.steps)
     prof = _lib.stop_profile()
     launches = _lib.launch_count - launches0
@@ -290,6 +294,9 @@ def main():
         e2e_step()
     ms_e2e = timed(e2e_step, args.steps)
     clocks = sampler.stop() if rank == 0 else None
+    _lib.start_profile()
+    ms_profiled = timed(lambda: step(resident), args.steps)
+    full = _lib.stop_profile()
 
     tot_edges = torch.tensor([float(edges)], device=dev)
     if world > 1:
@@ -299,6 +306,8 @@ def main():
     if rank == 0:
         pk = peaks()
         top = max(prof.items(), key=lambda kv: kv[1]["ms"]) if prof else (None, None)
+        if full and max(full.items(), key=lambda kv: kv[1]["ms"])[0] != DOMINANT:  # another entry point took over
+            top = max(full.items(), key=lambda kv: kv[1]["ms"])
         roofline = None
         if top[0] is not None:
             name, d = top
@@ -318,7 +327,7 @@ def main():
                         "algorithmic_per_launch": per_launch_work, "ms_per_launch": per_launch_s * 1e3,
                         "peak_source": pk["source"], "share_of_step": d["ms"] / (ms_dev * args.steps),
                         "launches": d["calls"]}
-        breakdown = {k: round(v["ms"] / args.steps, 3) for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}
+        breakdown = {k: round(v["ms"] / args.steps, 3) for k, v in sorted(full.items(), key=lambda kv: -kv[1]["ms"])}
         line = {
             "metric": METRIC, "value": tot_edges / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak",
@@ -331,6 +340,8 @@ def main():
             "e2e": {"value": tot_edges / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e},
             "gpu_launches": launches, "roofline": roofline, "clocks": clocks, "kernel_ms_per_step": breakdown,
+            "kernel_ms_per_step_source": f"second pass of {args.steps} steps with event pairs around every entry point "
+                                         f"({ms_profiled:.1f} ms/step under that profile)",
         }
         if world == 1 and not args.no_cpu_baseline:
             graph, n = cpu_sample_graph(args.cpu_budget_s)

@@ -118,18 +118,22 @@ def stream_ptr():
 _LAUNCHES = {"efl_csr_from_edge_index": 12, "efl_embedding_grad": 2, "efl_gemm_tn_f32": 2, "efl_colsum": 2, "efl_tc_gemm_tn": 2, "efl_so3_linear_bwd_weight": 2}
 launch_count = 0
 _profile = None  # None, or a list receiving (name, work, start_event, end_event)
+_profile_only = None  # None = every entry point, or the set of names (tags) that get event pairs
 
 
-def start_profile():
-    """Record a CUDA-event pair around every entry-point call (on the launching stream) until stop_profile()."""
-    global _profile
+def start_profile(only=None):
+    """Record a CUDA-event pair around entry-point calls (on the launching stream) until stop_profile().  ``only``
+    restricts the pairs to a set of entry-point names / tags: two event records per call are host time, and with
+    ~5 000 calls per step the full profile can make a GPU-bound step host-bound."""
+    global _profile, _profile_only
     _profile = []
+    _profile_only = set(only) if only else None
 
 
 def stop_profile():
     """-> {name: dict(ms=total ms, calls=n, work=sum of algorithmic work units passed by the caller)}"""
-    global _profile
-    rec, _profile = _profile or [], None
+    global _profile, _profile_only
+    rec, _profile, _profile_only = _profile or [], None, None
     torch.cuda.synchronize()
     out = {}
     for name, work, a, b in rec:
@@ -145,7 +149,7 @@ def call(name: str, *args, work: float = 0.0, tag: str = None):
     FLOPs (GEMMs) or bytes (HBM-bound kernels) of this call, used only by the profiler."""
     global launch_count
     launch_count += _LAUNCHES.get(name, 1)
-    if _profile is not None:
+    if _profile is not None and (_profile_only is None or (tag or name) in _profile_only):
         a = torch.cuda.Event(enable_timing=True)
         b = torch.cuda.Event(enable_timing=True)
         a.record()

@@ -596,6 +596,84 @@ class EdgeDegreeFunction(torch.autograd.Function):
 # ---------------------------------------------------------------------------
 # node-level separable S2 activation (FeedForwardNetwork)
 # ---------------------------------------------------------------------------
+# Node-level S2 activation on grids the fused tcgen05 kernel is not built for (lmax 8: 81 coefficients, 342 grid
+# points): the two projections are plain tensor-core GEMMs over all (node, channel) rows with the small grid matrix as
+# the B operand, and the [N*CH, G] grid values make one bf16 round trip through HBM (2.9 GB per layer at 8 000 nodes,
+# ~1 ms) instead of 90 ms in the fp32 SIMT kernel.  EFL_NODE_S2_GEMM=0 falls back to the SIMT kernel.
+_NODE_S2_GEMM = os.environ.get("EFL_NODE_S2_GEMM", "1") != "0"
+_GRID_OPERANDS: dict = {}
+
+
+def _grid_operands(to_g, from_g):
+    """bf16 B operands of the four GEMMs, zero-padded to multiples of 16: T [GP, LP], T^T [LP, GP], F [GP, LP],
+    F^T [LP, GP] (to_g / from_g are [G, L] fp32)."""
+    key = (to_g.data_ptr(), to_g._version, from_g.data_ptr(), from_g._version, tuple(to_g.shape))
+    hit = _GRID_OPERANDS.get(key)
+    if hit is None:
+        G, L = to_g.shape
+        GP, LP = _pad(G, 16), _pad(L, 16)
+
+        def padded(m, r, c):
+            out = torch.zeros(r, c, dtype=torch.bfloat16, device=m.device)
+            out[:m.shape[0], :m.shape[1]] = m
+            return out
+        hit = (padded(to_g, GP, LP), padded(to_g.t(), LP, GP), padded(from_g, GP, LP), padded(from_g.t(), LP, GP))
+        if len(_GRID_OPERANDS) > 32:
+            _GRID_OPERANDS.clear()
+        _GRID_OPERANDS[key] = hit
+    return hit
+
+
+def _rows_from_nodes(x, LP):
+    """[N, L, CH] -> bf16 [N*CH, LP] (coefficients contiguous per (node, channel) row, zero padded)."""
+    N, L, CH = x.shape
+    xt = torch.zeros(N, CH, LP, dtype=torch.bfloat16, device=x.device)
+    xt[:, :, :L] = x.transpose(1, 2)
+    return xt.view(N * CH, LP)
+
+
+def _nodes_from_rows(yt, N, L, CH):
+    return yt.view(N, CH, -1)[:, :, :L].transpose(1, 2).float().contiguous()
+
+
+def _bf16_gemm(A, B, M, N, K):
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=A.device)
+    _gemm_nt(0, A, B, None, out, N, None, 0, 0, M, N, K)
+    return out
+
+
+def _node_s2_gemm_forward(gate, x, to_g, from_g):
+    N, L, CH = x.shape
+    Tb, _, _, FbT = _grid_operands(to_g, from_g)
+    GP, LP = Tb.shape
+    R = N * CH
+    xt = _rows_from_nodes(x, LP)
+    grid = _bf16_gemm(xt, Tb, R, GP, LP)                         # to_grid
+    act = torch.nn.functional.silu(grid)
+    del grid
+    yt = _bf16_gemm(act, FbT, R, LP, GP)                         # from_grid
+    y = _nodes_from_rows(yt, N, L, CH)
+    y[:, 0, :] = torch.nn.functional.silu(gate)                  # l = 0 row <- SiLU(gate) (EF_layers.py:1765-1773)
+    return y, xt
+
+
+def _node_s2_gemm_backward(gate, xt, to_g, from_g, dy, shape):
+    N, L, CH = shape
+    Tb, TbT, Fb, _ = _grid_operands(to_g, from_g)
+    GP, LP = Tb.shape
+    R = N * CH
+    dy = dy.float()
+    dgate = torch.ops.aten.silu_backward(dy[:, 0, :].contiguous(), gate)
+    dyt = _rows_from_nodes(dy, LP)
+    dyt[:, 0] = 0                                                # the l = 0 output row does not come from the grid
+    grid = _bf16_gemm(xt, Tb, R, GP, LP)                         # recomputed, not saved
+    dact = _bf16_gemm(dyt, Fb, R, GP, LP)
+    dgrid = torch.ops.aten.silu_backward(dact, grid)
+    del grid, dact
+    dxt = _bf16_gemm(dgrid, TbT, R, LP, GP)
+    return dgate, _nodes_from_rows(dxt, N, L, CH)
+
+
 class NodeS2ActFunction(torch.autograd.Function):
     """(gate [N, CH], x [N, L, CH]) -> SeparableS2Activation output [N, L, CH] on the (lmax, lmax) grid.
     bf16 mode: tcgen05 kernel on bf16 copies (fp32 accumulation); fp32 mode: SIMT kernel."""
@@ -608,6 +686,12 @@ class NodeS2ActFunction(torch.autograd.Function):
         G = to_g.shape[0]
         tc = _PRECISION == "bf16" and CH % 128 == 0 and Lc <= 64 and G <= 224
         ctx.tc = tc
+        ctx.gemm = (not tc) and _PRECISION == "bf16" and CH % 8 == 0 and N > 0 and _NODE_S2_GEMM
+        if ctx.gemm:
+            y, xt = _node_s2_gemm_forward(gate, x, to_g, from_g)
+            ctx.save_for_backward(gate, xt, to_g, from_g)
+            ctx.shape = (N, Lc, CH)
+            return y
         if tc:
             xb = x.to(torch.bfloat16).contiguous()
             yb = torch.empty_like(xb)
@@ -626,6 +710,9 @@ class NodeS2ActFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         gate, x, to_g, from_g = ctx.saved_tensors
+        if ctx.gemm:
+            dgate, dx = _node_s2_gemm_backward(gate, x, to_g, from_g, dy, ctx.shape)
+            return dgate, dx, None, None
         N, Lc, CH = x.shape
         G = to_g.shape[0]
         if ctx.tc:

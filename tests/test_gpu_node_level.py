@@ -166,3 +166,34 @@ def test_bias_gradient_column_sum_bf16(rows, cols, pitch):
     out2 = torch.full((cols,), 3.0, device=DEV)
     ops._colsum(X, rows, cols, out2, True)
     assert torch.equal(out, out2)
+
+
+@pytest.mark.parametrize("n,ch", [(1, 128), (37, 512)])
+def test_node_s2_activation_lmax8_gemm_route_matches_fp32_kernel(n, ch):
+    """FeedForwardNetwork's S2 activation on the (8,8) grid (81 coefficients, 342 points; BASELINE config 5): the bf16
+    tensor-core GEMM route (ops._node_s2_gemm_*) against the fp32 SIMT kernel, outputs and gradients, at the stated
+    bf16 tolerance (2e-2 of the tensor's max)."""
+    from singa_b200 import ops
+    from singa_b200 import so3_constants as sc
+    to, fr = sc.s2_grid_matrices(8, 8)
+    G = to.shape[0] * to.shape[1]
+    to_g = torch.tensor(to.reshape(G, -1), dtype=torch.float32, device=DEV).contiguous()
+    from_g = torch.tensor(fr.reshape(G, -1), dtype=torch.float32, device=DEV).contiguous()
+    assert to_g.shape == (342, 81)
+    g = torch.Generator(device="cpu").manual_seed(n)
+    x0 = torch.randn(n, 81, ch, generator=g).to(DEV)
+    gate0 = torch.randn(n, ch, generator=g).to(DEV)
+    dy = torch.randn(n, 81, ch, generator=g).to(DEV)
+    res = {}
+    try:
+        for mode in ("fp32", "bf16"):
+            ops.set_precision(mode)
+            x, gate = x0.clone().requires_grad_(True), gate0.clone().requires_grad_(True)
+            y = ops.NodeS2ActFunction.apply(gate, x, to_g, from_g)
+            y.backward(dy)
+            res[mode] = (y.detach(), x.grad, gate.grad)
+    finally:
+        ops.set_precision("fp32")
+    for a, b, name in zip(res["fp32"], res["bf16"], ("y", "dx", "dgate")):
+        err = float((a - b).abs().max() / a.abs().max())
+        assert err < 2e-2, (name, err)
