@@ -35,7 +35,9 @@ const char* efl_last_error_string(void);
 int efl_device_cc(int device, int* major, int* minor);
 
 /* SO3_Rotation.set_wigner / RotationToWignerDMatrix / wigner_D / _z_rot_mat (:485-528, :2207-2229).
- * rot [E,3,3] fp32 edge frames, jd = concatenated J_l (l=0..lmax, row-major) -> wig [E, WSZ] kept rows. */
+ * rot [E,3,3] fp32 edge frames, jd = concatenated J_l (l=0..lmax, row-major; the Jd.pt matrices, a device pointer:
+ * copied stream-ordered into the kernel's constant bank on every call) -> wig [E, WSZ]: the rows |m'| <= mmax of every
+ * D^l, each padded to 16 bytes (WSZ = 296 floats for (6,2), 476 for (8,2)).  Built for mmax = 2, lmax in {4, 6, 8}. */
 int efl_wigner_from_rotmat(int lmax, int mmax, const float* rot, const float* jd, float* wig, int E, void* stream);
 
 /* Gather + rotate-in: SO3_Embedding.clone/_expand_edge + cat (:1110-1119), SO3_Rotation.rotate (:494-497),

@@ -9,3 +9,4 @@ timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --mas
 cat gpurun_out/${TAG}_bench.json | cut -c1-900; tail -3 gpurun_out/${TAG}_bench.err
 [ "${STRESS:-1}" = "1" ] && timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 tools/stress_bench.py > gpurun_out/${TAG}_stress.jsonl 2> gpurun_out/${TAG}_stress.err; echo "stress exit $? ($(( $(date +%s) - T0 )) s)"
 cat gpurun_out/${TAG}_stress.jsonl; tail -3 gpurun_out/${TAG}_stress.err
+exit 0
