@@ -1,0 +1,61 @@
+"""Next scope row, checker only: oracle/cpromg_oracle.py against the golden written by the unmodified
+reference ``MultiHeadAttention`` (oracle/make_golden_cpromg.py), forward and every gradient; the brute-force kNN graph
+restatement against its defining properties.  No CUDA path exists for this row yet."""
+import os
+
+import numpy as np
+import torch
+
+from oracle import cpromg_oracle as co
+from tests.parity_util import load_golden
+
+
+def test_message_passing_oracle_matches_reference_golden():
+    fx = load_golden("cpromg_attention.pt")
+    p = {k: v.clone().requires_grad_(v.dtype.is_floating_point) for k, v in fx["state_dict"].items()}
+    x = fx["node_attr"].clone().requires_grad_(True)
+    ea = fx["edge_attr"].clone().requires_grad_(True)
+    out = co.multi_head_attention(p, x, fx["edge_index"], ea, fx["dims"]["heads"])
+    rel = lambda a, b: float((a - b).abs().max() / b.abs().max())
+    assert rel(out.detach(), fx["out"]) < 1e-5
+    (out * fx["loss_weights"]).sum().backward()
+    assert rel(x.grad, fx["d_node_attr"]) < 1e-4
+    assert rel(ea.grad, fx["d_edge_attr"]) < 1e-4
+    for k, g in fx["d_params"].items():
+        # weight_k_lin.bias shifts every logit of a centre by the same q_i . b: its gradient is exactly zero and both
+        # sides hold rounding noise (~1e-7), hence the absolute floor
+        assert float((p[k].grad - g).abs().max()) < 1e-4 * float(g.abs().max()) + 2e-6, k
+
+
+def test_scatter_restatements_against_per_segment_loops():
+    rs = np.random.RandomState(3)
+    idx = torch.from_numpy(rs.randint(0, 9, size=200))        # segment 4 left empty below
+    idx[idx == 4] = 5
+    src = torch.from_numpy(rs.normal(size=(200, 4)).astype(np.float32))
+    sm, sums = co.scatter_softmax(src, idx, 9), co.scatter_sum(src, idx, 9)
+    for seg in range(9):
+        m = idx == seg
+        if m.any():
+            assert torch.allclose(sm[m], torch.softmax(src[m], dim=0), atol=1e-6)
+            assert torch.allclose(sums[seg], src[m].sum(0), atol=1e-5)
+        else:
+            assert float(sums[seg].abs().max()) == 0.0
+
+
+def test_knn_graph_restatement_properties():
+    fx = load_golden("cpromg_attention.pt")
+    pos, batch, k = fx["pos"], fx["batch"], fx["dims"]["knn"]
+    ei = co.knn_graph_bruteforce(pos, k, batch)
+    assert torch.equal(ei, fx["knn_directed"])
+    centre, nbr = ei
+    assert bool((centre != nbr).all()) and bool((batch[centre] == batch[nbr]).all())
+    assert torch.equal(torch.bincount(centre, minlength=len(pos)), torch.full((len(pos),), k))
+    d = (pos[centre] - pos[nbr]).norm(dim=1).view(len(pos), k)
+    assert bool((d[:, 1:] >= d[:, :-1]).all())                  # nearest first
+    for i in (0, 17, 39):                                        # the k-th neighbour bounds every excluded point
+        same = (batch == batch[i]).nonzero().flatten().tolist()
+        others = [j for j in same if j != i and j not in nbr[centre == i].tolist()]
+        if others:
+            assert float((pos[others] - pos[i]).norm(dim=1).min()) >= float(d[i, -1]) - 1e-6
+    small = co.knn_graph_bruteforce(pos[:4], 6, None)            # fewer than k candidates: every other point, once
+    assert small.shape[1] == 12
