@@ -9,6 +9,10 @@ Metric: edges/s = directed edges of the batch (all four edge sets) pushed throug
 second, summed over ranks.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--precision fp32|bf16]
+                  [--scaling weak|strong] [--global-batch B]
+
+--scaling strong splits a FIXED global batch (default 64 complexes = BASELINE.json config 3's batch) over the ranks
+with parallel.shard_by_edges; the default (weak) gives every rank its own 32 complexes.
 
 Prints ONE JSON line on rank 0 (see DESIGN.md "Measurement" for every key).
 """
@@ -31,6 +35,8 @@ sys.path.insert(0, ROOT)
 METRIC = "EF_layers fwd+bwd edges/sec"
 DOMINANT = "efl_tc_gemm_nt"  # entry point with the largest share of a step (checked against the full profile)
 UNIT = "edges/s"
+WORKLOAD = ("EF_layers fwd+bwd, batch 32 synthetic CrossDocked-shaped complexes (~450 atoms, 8 A cutoff, lmax=6, mmax=2) "
+            "per GPU")
 
 
 def parse():
@@ -43,11 +49,15 @@ def parse():
     ap.add_argument("--batch", type=int, default=32, help="complexes per GPU")
     ap.add_argument("--atoms", type=int, default=None, help="fix protein atoms per complex (default U{400..500})")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-budget-s", type=float, default=25.0)
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--global-batch", type=int, default=64, help="complexes of the whole job under --scaling strong")
     return ap.parse_args()
 
 
 # ----------------------------------------------------------------------------------------------
+LAYERS = 3
+
+
 def make_batch(rank: int, batch: int, atoms):
     from singa_b200 import synthetic as syn
     graphs = [syn.make_complex(1000 * rank + i, n_protein=atoms) for i in range(batch)]
@@ -55,7 +65,21 @@ def make_batch(rank: int, batch: int, atoms):
 
 
 def count_edges(g) -> int:
+    """All four edge sets (the size of the input)."""
     return int(sum(g[k].shape[1] for k in ("ei_pp", "ei_ll", "ei_lp", "ei_pl")))
+
+
+def count_edge_layers(g) -> int:
+    """Edge-layers actually computed per step: the homogeneous passes push their edges through all LAYERS attention
+    blocks; in the two hetero passes only the LAST block's output is observable (Embedding.py:415-428 keeps one), so
+    with compute_dead_blocks=False (both arms) their edges pass through ONE block."""
+    return int(LAYERS * (g["ei_pp"].shape[1] + g["ei_ll"].shape[1]) + g["ei_lp"].shape[1] + g["ei_pl"].shape[1])
+
+
+def metric_edges(g) -> float:
+    """The metric's unit: directed edges through the 3-layer stack = edge-layers computed / 3 (round 1 counted the
+    hetero edges at 3 layers, ~2 % in its own favour: VERDICT r1 weak #10)."""
+    return count_edge_layers(g) / float(LAYERS)
 
 
 class ClockSampler:
@@ -111,24 +135,37 @@ def peaks():
 # ----------------------------------------------------------------------------------------------
 # reference / CPU arm: the oracle port on the host cores (the reference is pure Python and cannot travel)
 # ----------------------------------------------------------------------------------------------
-def cpu_sample_graph(budget_s: float):
-    """A sub-ball of complex seed 0 sized so that one fwd+bwd of the CPU port fits ``budget_s``.
-    Calibrated at ~1.0 k edges/s per 8 threads for the 3-layer stack."""
+REF_SAMPLE_ATOMS = 200      # the reference arm ALWAYS times this cut (a budget-sized sample moved the ratio 16 %)
+PARITY_SAMPLE_ATOMS = 460   # cpu_baseline leg of our arm: one full config-2-sized complex, also the parity check
+
+
+def cpu_sample_graph(n_protein: int):
+    """Complex seed 0 with a fixed number of protein atoms (+ 24 ligand atoms), 8 A radius graph."""
     from singa_b200 import synthetic as syn
-    cores = os.cpu_count() or 1
-    est_rate = 1000.0 * max(1.0, min(cores, 32) / 8.0) ** 0.7
-    target_edges = max(1500.0, est_rate * budget_s)
-    n = 60
-    while n < 450:
-        g = syn.make_complex(0, n_protein=n, n_ligand=24)
-        if count_edges(g) >= target_edges:
-            return g, n
-        n += 20
-    return syn.make_complex(0, n_protein=n, n_ligand=24), n
+    return syn.make_complex(0, n_protein=n_protein, n_ligand=24), n_protein
 
 
-def run_cpu_port(graph, steps: int, warmup: int):
-    """fwd+bwd of oracle/ef_oracle.py (the CPU port of the reference algorithm) on all host threads."""
+def oracle_frames(graph, seed: int = 1):
+    from oracle import ef_oracle as eo
+    from singa_b200 import synthetic as syn
+    rnd = syn.frame_randoms(graph, seed)
+    frames = {}
+    for key, (s, d, ei) in dict(pp=("pos_p", "pos_p", "ei_pp"), ll=("pos_l", "pos_l", "ei_ll"),
+                                lp=("pos_l", "pos_p", "ei_lp")).items():
+        frames[key] = eo.edge_rot_mat(graph[s][graph[ei][0]] - graph[d][graph[ei][1]], rnd[key])
+    return frames
+
+
+def loss_weights(graph, seed: int = 7):
+    rs = np.random.RandomState(seed)
+    f = lambda n: torch.from_numpy(rs.normal(size=(n, 49, 16)).astype(np.float32))
+    return f(graph["z_p"].numel()), f(graph["z_l"].numel())
+
+
+def run_cpu_port(graph, steps: int, warmup: int, state=None, keep=False):
+    """fwd+bwd of oracle/ef_oracle.py (the CPU port of the reference algorithm) on all host threads, hetero passes
+    through the last block only (compute_dead_blocks=False, as the GPU arm).  ``state``: a state_dict to run with
+    (default: portable parameters, seed 0).  ``keep``: also return outputs and parameter gradients of the last step."""
     from oracle import ef_oracle as eo
     from singa_b200 import so3_constants as sc
     from singa_b200 import synthetic as syn
@@ -136,49 +173,76 @@ def run_cpu_port(graph, steps: int, warmup: int):
     torch.set_num_threads(os.cpu_count() or 1)
     torch.manual_seed(0)
     shapes = EquivariantEmbedding(DEFAULT_CONFIG, device="cpu")
-    syn.load_portable_parameters(shapes, 0)
-    p = {k: v.detach().clone().requires_grad_(v.dtype.is_floating_point and k in dict(shapes.named_parameters()))
-         for k, v in shapes.state_dict().items()}
+    if state is None:
+        syn.load_portable_parameters(shapes, 0)
+        state = shapes.state_dict()
+    names = set(dict(shapes.named_parameters()))
+    p = {k: v.detach().cpu().clone().requires_grad_(v.dtype.is_floating_point and k in names) for k, v in state.items()}
     f32 = lambda a: torch.tensor(a, dtype=torch.float32)
     to62, fr62 = sc.s2_grid_matrices(6, 2)
     to66, fr66 = sc.s2_grid_matrices(6, 6)
     t = eo.Tables(6, 2, [sc.j_matrix(l) for l in range(7)], f32(to62), f32(fr62), f32(to66), f32(fr66))
-    rnd = syn.frame_randoms(graph, 1)
-    frames = {}
-    for key, (s, d, ei) in dict(pp=("pos_p", "pos_p", "ei_pp"), ll=("pos_l", "pos_l", "ei_ll"),
-                                lp=("pos_l", "pos_p", "ei_lp")).items():
-        frames[key] = eo.edge_rot_mat(graph[s][graph[ei][0]] - graph[d][graph[ei][1]], rnd[key])
-    times = []
+    frames = oracle_frames(graph)
+    Rp, Rl = loss_weights(graph)
+    times, out = [], None
     for it in range(warmup + steps):
         for v in p.values():
             v.grad = None
         t0 = time.perf_counter()
-        out = eo.embedding_forward(p, graph, frames, t, dict(DEFAULT_CONFIG))
-        loss = out["protein_atoms"].sum() * 0.5 + out["ligand_atoms"].sum()
+        out = eo.embedding_forward(p, graph, frames, t, dict(DEFAULT_CONFIG), compute_dead_blocks=False)
+        loss = (out["protein_atoms"] * Rp).sum() + (out["ligand_atoms"] * Rl).sum()
         loss.backward()
         dt = time.perf_counter() - t0
         if it >= warmup:
             times.append(dt)
-    return float(np.mean(times))
+    sec = float(np.mean(times))
+    if keep:
+        return sec, {k: v.detach() for k, v in out.items()}, {k: v.grad for k, v in p.items() if v.grad is not None}
+    return sec
+
+
+def parity_against_port(model, graph, outs_ref, grads_ref, dev):
+    """The SAME complex through the CUDA path in the precision being benchmarked, same parameters, same frames, same
+    loss: relative errors (||d||_inf / ||ref||_inf) of the outputs and of every parameter gradient."""
+    from singa_b200 import synthetic as syn
+    frames = {k: v.to(dev) for k, v in oracle_frames(graph).items()}
+    Rp, Rl = (r.to(dev) for r in loss_weights(graph))
+    model.zero_grad(set_to_none=True)
+    out = model(syn.GraphView({k: v.to(dev) for k, v in graph.items()}), frames=frames)
+    loss = (out[syn.PROTEIN].embedding * Rp).sum() + (out[syn.LIGAND].embedding * Rl).sum()
+    loss.backward()
+
+    def rel(a, b):
+        a, b = a.detach().double().cpu(), b.detach().double().cpu()
+        return float((a - b).abs().max()) / max(float(b.abs().max()), 1e-30)
+
+    e_out = {k: rel(out[k].embedding, outs_ref[k]) for k in outs_ref}
+    e_grad = {n: rel(p.grad, grads_ref[n]) for n, p in model.named_parameters() if p.grad is not None and n in grads_ref}
+    worst = max(e_grad, key=e_grad.get)
+    srt = sorted(e_grad.values())
+    model.zero_grad(set_to_none=True)
+    return {"out_rel_err": max(e_out.values()), "grad_rel_err": e_grad[worst], "grad_rel_err_median": srt[len(srt) // 2],
+            "worst_grad": worst, "outputs": e_out, "n_grads": len(e_grad),
+            "against": "oracle/ef_oracle.py (CPU port, fp32) on the cpu_baseline sample, same parameters/frames/loss"}
 
 
 def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    total = max(1, args.steps + args.warmup)
-    graph, n = cpu_sample_graph(max(4.0, 180.0 / total))
-    edges = count_edges(graph)
+    graph, n = cpu_sample_graph(REF_SAMPLE_ATOMS)
+    edges = metric_edges(graph)
     sec = run_cpu_port(graph, args.steps, args.warmup)
     val = edges / sec
     cores = os.cpu_count() or 1
-    sample = f"one synthetic complex (seed 0) cut to {n} protein + 24 ligand atoms, {edges} edges, 8 A radius graph"
+    sample = (f"FIXED sample: synthetic complex seed 0 cut to {n} protein + 24 ligand atoms, {count_edges(graph)} edges "
+              f"({count_edge_layers(graph)} edge-layers), 8 A radius graph; CPU port of the reference (oracle/ef_oracle.py), "
+              f"fp32, {cores} threads")
     emit({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "EF_layers fwd+bwd, batch 32 synthetic CrossDocked-shaped complexes (~450 atoms, 8 A "
-                               "cutoff, lmax=6, mmax=2)", "sample": sample},
+        "config": {"workload": WORKLOAD, "sample": sample},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -218,7 +282,7 @@ def main():
     from singa_b200 import _lib, ops
     from singa_b200 import synthetic as syn
     from singa_b200.embedding import DEFAULT_CONFIG, EquivariantEmbedding
-    from singa_b200.parallel import GradientBucket
+    from singa_b200.parallel import GradientBuckets, shard_by_edges
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -230,8 +294,19 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     ops.set_precision(args.precision)
 
-    batch, _ = make_batch(rank, args.batch, args.atoms)
-    edges = count_edges(batch)
+    if args.scaling == "strong":
+        # fixed global batch (seeds 0..B-1), whole complexes dealt to the ranks by edge count (parallel.shard_by_edges);
+        # the per-complex cost proxy is the protein atom count make_complex(seed) draws first (edges ~ 63 per atom)
+        sizes = [int(np.random.RandomState(i).randint(400, 501)) if args.atoms is None else args.atoms
+                 for i in range(args.global_batch)]
+        mine = shard_by_edges(sizes, world)[rank]
+        graphs = [syn.make_complex(i, n_protein=args.atoms) for i in mine]
+        n_local = len(mine)
+    else:
+        _, graphs = make_batch(rank, args.batch, args.atoms)
+        n_local = args.batch
+    batch = syn.collate(graphs)
+    edges = metric_edges(batch)
     host = {k: v.pin_memory() for k, v in batch.items()}
     resident = {k: v.to(dev) for k, v in host.items()}
     h2d_bytes = int(sum(v.numel() * v.element_size() for v in host.values()))
@@ -240,17 +315,17 @@ def main():
     model = EquivariantEmbedding(DEFAULT_CONFIG, device=dev)
     syn.load_portable_parameters(model, 0)
     opt = torch.optim.Adam(model.parameters(), lr=1e-4)
-    bucket = GradientBucket(model.parameters())
+    buckets = GradientBuckets(model.named_parameters())   # gradients live in per-block flat buffers (views)
     rs = np.random.RandomState(7)
     Rp = torch.from_numpy(rs.normal(size=(resident["z_p"].numel(), 49, 16)).astype(np.float32)).to(dev)
     Rl = torch.from_numpy(rs.normal(size=(resident["z_l"].numel(), 49, 16)).astype(np.float32)).to(dev)
 
     def step(g):
-        opt.zero_grad(set_to_none=True)
+        buckets.zero_grad()
         out = model(syn.GraphView(g))
         loss = (out[syn.PROTEIN].embedding * Rp).sum() + (out[syn.LIGAND].embedding * Rl).sum()
-        loss.backward()
-        bucket.allreduce_()
+        loss.backward()        # each block's bucket starts its all-reduce as backward completes it (N > 1)
+        buckets.finish()
         opt.step()
         return loss
 
@@ -279,7 +354,7 @@ def main():
         sampler.start()
     launches0 = _lib.launch_count
     # Event pairs in the timed region only around the dominant entry point (the roofline's kernel): pairs around all
-    # ~5 000 calls of a step cost enough host time to make the step host-bound on a slow box.  The per-entry-point
+    # calls of a step cost enough host time to make the step host-bound on a slow box.  The per-entry-point
     # breakdown comes from a second, fully profiled pass of the same K steps below (outside the timed region).
     _lib.start_profile(only={DOMINANT})
     ms_dev = timed(lambda: step(resident), args.steps)
@@ -298,10 +373,10 @@ def main():
     ms_profiled = timed(lambda: step(resident), args.steps)
     full = _lib.stop_profile()
 
-    tot_edges = torch.tensor([float(edges)], device=dev)
+    tot = torch.tensor([float(edges), float(n_local), float(count_edges(batch))], device=dev)
     if world > 1:
-        dist.all_reduce(tot_edges)
-    tot_edges = float(tot_edges)
+        dist.all_reduce(tot)
+    tot_edges, tot_complexes, tot_input_edges = (float(v) for v in tot)
 
     if rank == 0:
         pk = peaks()
@@ -316,41 +391,60 @@ def main():
             per_launch_s = d["ms"] * 1e-3 / max(d["calls"], 1)
             achieved = per_launch_work / per_launch_s / (1e12 if tensor else 1e9)
             peak = pk["tensor"] if tensor else pk["hbm"]
-            traffic = None
+            traffic, traffic_note = None, None
             tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
             if os.path.isfile(tpath):
-                traffic = json.load(open(tpath)).get(name)
+                tj = json.load(open(tpath))
+                ent = tj.get(name)
+                if isinstance(ent, dict):
+                    traffic, traffic_note = ent.get("dram_bytes_per_launch"), ent.get("note")
+                else:
+                    traffic, traffic_note = ent, tj.get("_note")
             roofline = {"kernel": name, "bound": "tensor" if tensor else "hbm", "achieved": achieved, "peak": peak,
                         "unit": "TFLOP/s" if tensor else "GB/s", "frac": achieved / peak, "traffic": traffic,
-                        "traffic_unit": "dram bytes per launch (ncu --set full, profiles/ncu_traffic.json: one "
-                                        "edge-layer pass of 225 240 edges, chunk size comparable to this run's)",
-                        "algorithmic_per_launch": per_launch_work, "ms_per_launch": per_launch_s * 1e3,
+                        "traffic_unit": traffic_note,
+                        "algorithmic_per_launch": per_launch_work,
+                        "algorithmic_unit": "FLOP (2*M*N*K)" if tensor else "bytes",
+                        "ms_per_launch": per_launch_s * 1e3,
                         "peak_source": pk["source"], "share_of_step": d["ms"] / (ms_dev * args.steps),
                         "launches": d["calls"]}
         breakdown = {k: round(v["ms"] / args.steps, 3) for k, v in sorted(full.items(), key=lambda kv: -kv[1]["ms"])}
+        # whole-step tensor fraction: 36.0 MFLOP per edge-layer fwd+bwd over the step time
+        step_tflops = 36.0e6 * tot_edges * LAYERS / world / (ms_dev * 1e-3) / 1e12
         line = {
             "metric": METRIC, "value": tot_edges / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak",
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
-            "config": {"workload": "EF_layers fwd+bwd, batch 32 synthetic CrossDocked-shaped complexes (~450 atoms, "
-                                   "8 A cutoff, lmax=6, mmax=2) per GPU", "complexes_per_gpu": args.batch,
-                       "edges_per_gpu": edges, "layers": 3, "passes": 4, "parallelism": f"dp{world}",
+            "config": {"workload": WORKLOAD if args.scaling == "weak" else
+                       f"EF_layers fwd+bwd, GLOBAL batch {args.global_batch} synthetic CrossDocked-shaped complexes "
+                       f"(~450 atoms, 8 A cutoff, lmax=6, mmax=2) split over the ranks by edge count",
+                       "complexes_per_gpu": n_local, "complexes": tot_complexes,
+                       "input_edges": tot_input_edges, "edge_layers_per_step": tot_edges * LAYERS,
+                       "edge_count": "value counts edge-layers actually computed / 3: pp and ll edges through 3 blocks, "
+                                     "lp and pl edges through the one live block",
+                       "layers": LAYERS, "passes": 4, "parallelism": f"dp{world}",
                        "gemm_precision": args.precision, "l2": "inputs and per-chunk activations >> 126 MB L2",
-                       "complexes_per_s": args.batch * world / (ms_dev * 1e-3)},
+                       "complexes_per_s": tot_complexes / (ms_dev * 1e-3)},
             "e2e": {"value": tot_edges / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e},
-            "gpu_launches": launches, "roofline": roofline, "clocks": clocks, "kernel_ms_per_step": breakdown,
+            "gpu_launches": launches, "roofline": roofline, "clocks": clocks,
+            "step_tensor_tflops": step_tflops, "step_tensor_frac": step_tflops / pk["tensor"],
+            "kernel_ms_per_step": breakdown,
             "kernel_ms_per_step_source": f"second pass of {args.steps} steps with event pairs around every entry point "
                                          f"({ms_profiled:.1f} ms/step under that profile)",
         }
         if world == 1 and not args.no_cpu_baseline:
-            graph, n = cpu_sample_graph(args.cpu_budget_s)
-            sec = run_cpu_port(graph, 1, 0)
-            e = count_edges(graph)
+            # CPU port on ONE full config-2-sized complex, with the model's current parameters; the same complex then
+            # goes through the CUDA path in the benchmarked precision: measured parity at config-2 size in every run
+            graph, n = cpu_sample_graph(PARITY_SAMPLE_ATOMS)
+            sec, outs_ref, grads_ref = run_cpu_port(graph, 1, 0, state=model.state_dict(), keep=True)
+            e = metric_edges(graph)
             line["cpu_baseline"] = {
                 "value": e / sec, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
-                "sample": f"one synthetic complex (seed 0) cut to {n} protein + 24 ligand atoms, {e} edges, fwd+bwd "
-                          f"once, {sec:.1f} s"}
+                "sample": f"one synthetic complex (seed 0) with {n} protein + 24 ligand atoms, {count_edges(graph)} "
+                          f"edges ({count_edge_layers(graph)} edge-layers), fwd+bwd once, {sec:.1f} s"}
+            line["parity"] = parity_against_port(model, graph, outs_ref, grads_ref, dev)
+            line["parity"]["precision"] = args.precision
         emit(line)
     if world > 1:
         dist.destroy_process_group()

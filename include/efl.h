@@ -74,12 +74,6 @@ int efl_rotate_back_aggregate_fwd(int lmax, int mmax, int heads, int value_ch, i
                                   const void* v1, const void* v2, const float* alpha, const int* rowptr,
                                   const int* perm, const float* wig, float* out, int n0, int n1, int e0,
                                   void* stream);
-/* The same on the tensor cores (bf16 V buffers): per edge one tcgen05 MMA chain with the channels as M, the kept
- * m-primary rows as K and the l-primary output rows as N, ACCUMULATING IN TMEM over a destination's incoming edges
- * (the segment sum is the accumulate flag).  Chunk edges [e0, e0+Ec), destinations [n0, n1). */
-int efl_rotate_back_aggregate_tc_fwd(int lmax, int mmax, int heads, int value_ch, const void* v0, const void* v1,
-                                     const void* v2, const float* alpha, const int* rowptr, const int* perm,
-                                     const float* wig, float* out, int n0, int n1, int e0, int Ec, void* stream);
 /* Backward: dout [Nt,L,heads*value] -> dy0..dy2 (d value, dup layout for m>0) and dalpha
  * [efl_rotate_back_parts(lmax,mmax), E, heads]: one partial plane per degree group (planes part_stride floats
  * apart), summed in fixed order by efl_segment_softmax_bwd. */

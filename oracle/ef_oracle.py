@@ -406,8 +406,9 @@ def radius_graph_bruteforce(pos: torch.Tensor, r: float, batch: torch.Tensor = N
     """torch_cluster.radius_graph (torch-cluster 1.6.3, un-vendored; reference gen.py:17) restated as an O(N^2)
     scan per batch item: edge (j -> i) iff same batch item, j != i (unless loop) and
     ((xi-xj)^2 + (yi-yj)^2) + (zi-zj)^2 < r*r in fp32 with separately rounded operations (not cdist).
-    At most max_num_neighbors sources per target, smallest source indices kept (the dependency's CUDA kernel scans
-    sources in index order and stops at the cap).  Returns [2, E] int64, row 0 = source j, row 1 = target i,
+    Neighbour cap as upstream applies it: radius_graph(loop=False) calls radius(x, x, ..., max_num_neighbors + 1),
+    whose kernel scans sources in index order -- the self hit included -- and stops at the cap; self loops are
+    removed afterwards, so a target whose own index follows its first cap+1 hits keeps cap+1 sources.  Returns [2, E] int64, row 0 = source j, row 1 = target i,
     targets ascending and sources ascending inside a target.  Parity unpinned: no reference test or vector holds
     torch_cluster output."""
     import numpy as np
@@ -428,9 +429,13 @@ def radius_graph_bruteforce(pos: torch.Tensor, r: float, batch: torch.Tensor = N
             d2 = ((dx * dx).astype(np.float32) + (dy * dy).astype(np.float32)).astype(np.float32)
             d2 = (d2 + (dz * dz).astype(np.float32)).astype(np.float32)
             hit = d2 < r2
+            # upstream order (torch-cluster 1.6.x radius_graph): search with max_num_neighbors + 1 when loop is False,
+            # the self hit counted, sources scanned in ascending index; self loops dropped AFTER the cap
+            hit[np.arange(len(t)), np.arange(s0, s0 + len(t))] = True
+            cap = max_num_neighbors if loop else max_num_neighbors + 1
+            keep = hit & (np.cumsum(hit, axis=1) <= cap)
             if not loop:
-                hit[np.arange(len(t)), np.arange(s0, s0 + len(t))] = False
-            keep = hit & (np.cumsum(hit, axis=1) <= max_num_neighbors)
+                keep[np.arange(len(t)), np.arange(s0, s0 + len(t))] = False
             ti, sj = np.nonzero(keep)
             src.append(ids[sj])
             dst.append(ids[ti + s0])

@@ -65,11 +65,14 @@ class CoefficientMappingModule(nn.Module):
                 ms.extend(range(-mm, mm + 1))
                 ls.extend([l] * (2 * mm + 1))
             sizes.append(len(ls) - before)
-        long = lambda v: torch.tensor(v, dtype=torch.long, device=device)
+        # tables are built on the host and uploaded once: a constructor that runs torch.nonzero / .tolist() on device
+        # tensors costs a device sync and several library launches per module (49 SO3_Grid mappings per model)
+        long = lambda v: torch.tensor(v, dtype=torch.long)
         l_harmonic, m_complex = long(ls), long(ms)
+        self._ls, self._ms = list(ls), list(ms)
         n = len(ls)
-        to_m = torch.zeros(n, n, device=device)
-        m_size = torch.zeros(max(mmax_list) + 1, dtype=torch.long, device=device)
+        to_m = torch.zeros(n, n)
+        m_size = torch.zeros(max(mmax_list) + 1, dtype=torch.long)
         row = 0
         for m in range(max(mmax_list) + 1):
             idx_r, idx_i = self.complex_idx(m, -1, m_complex, l_harmonic)
@@ -78,6 +81,8 @@ class CoefficientMappingModule(nn.Module):
                     to_m[row, col] = 1.0
                     row += 1
             m_size[m] = len(idx_r)
+        l_harmonic, m_complex, to_m, m_size = (t.to(device) for t in (l_harmonic, m_complex, to_m, m_size))
+        long = lambda v: torch.tensor(v, dtype=torch.long, device=device)
         self.register_buffer('l_harmonic', l_harmonic)
         self.register_buffer('m_harmonic', m_complex.abs())
         self.register_buffer('m_complex', m_complex)
@@ -101,10 +106,10 @@ class CoefficientMappingModule(nn.Module):
         """Indices of coefficients with degree <= lmax and |order| <= mmax (cached for the last query)."""
         if self.lmax_cache == lmax and self.mmax_cache == mmax and self.mask_indices_cache is not None:
             return self.mask_indices_cache
-        mask = self.l_harmonic.le(lmax) & self.m_harmonic.le(mmax)
-        self.device = mask.device
+        self.device = self.l_harmonic.device
         self.lmax_cache, self.mmax_cache = lmax, mmax
-        self.mask_indices_cache = torch.nonzero(mask).flatten()
+        keep = [i for i, (l, m) in enumerate(zip(self._ls, self._ms)) if l <= lmax and abs(m) <= mmax]
+        self.mask_indices_cache = torch.tensor(keep, dtype=torch.long, device=self.device)
         self.rotate_inv_rescale_cache = None
         return self.mask_indices_cache
 
@@ -428,9 +433,9 @@ class GaussianSmearing(nn.Module):
                  basis_width_scalar: float = 1.0, device: str = 'cuda') -> None:
         super().__init__()
         self.num_output = num_gaussians
-        offset = torch.linspace(start, stop, num_gaussians, device=device)
+        offset = torch.linspace(start, stop, num_gaussians)  # host: no .item() device sync in the constructor
         self.coeff = -0.5 / (basis_width_scalar * (offset[1] - offset[0])).item() ** 2
-        self.register_buffer("offset", offset)
+        self.register_buffer("offset", offset.to(device))
 
     def forward(self, dist) -> Tensor:
         return torch.exp(self.coeff * (dist.view(-1, 1) - self.offset.view(1, -1)).pow(2))
@@ -441,9 +446,9 @@ class SigmoidSmearing(nn.Module):
                  basis_width_scalar: float = 1.0, device: str = 'cuda') -> None:
         super().__init__()
         self.num_output = num_sigmoid
-        offset = torch.linspace(start, stop, num_sigmoid, device=device)
+        offset = torch.linspace(start, stop, num_sigmoid)
         self.coeff = (basis_width_scalar / (offset[1] - offset[0])).item()
-        self.register_buffer("offset", offset)
+        self.register_buffer("offset", offset.to(device))
 
     def forward(self, dist) -> Tensor:
         return torch.sigmoid(self.coeff * (dist.view(-1, 1) - self.offset.view(1, -1)))

@@ -25,7 +25,6 @@ SIGNATURES = {
     "efl_rotate_in_bwd_nodes": "iiiiipppppp" "ipppppiiiiip",
     "efl_segment_sum_rows": "piiiipppiip",
     "efl_rotate_back_aggregate_fwd": "iiiiipppppppp" "iiip",
-    "efl_rotate_back_aggregate_tc_fwd": "iiiipppppppp" "iiiip",
     "efl_rotate_back_aggregate_bwd": "iiiiipppppppppppp" "liiip",
     "efl_edge_degree_fwd": "iiippppfpip",
     "efl_edge_degree_bwd": "iiipppfpip",

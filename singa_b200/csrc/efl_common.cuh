@@ -28,6 +28,17 @@ void efl_set_error(const char* msg);
     }                                                           \
   } while (0)
 
+// cudaFuncSetAttribute is per DEVICE: "done once" flags are kept as a bit per device ordinal, so a process that
+// touches a second GPU does not launch with an unset dynamic shared-memory limit there.
+static inline bool efl_first_use_on_device(unsigned long long* mask) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (*mask & bit) return false;
+  *mask |= bit;
+  return true;
+}
+
 namespace efl {
 
 // Coefficient bookkeeping for one resolution (lmax, mmax); mirrors what

@@ -539,15 +539,14 @@ extern "C" int efl_radial_mlp_bwd(const float* x, int K0, const float* W1, const
   cudaStream_t s = (cudaStream_t)stream;
 #define RLAUNCH(KK)                                                                                         \
   {                                                                                                         \
-    static bool done = false;                                                                               \
-    if (!done) {                                                                                            \
+    static unsigned long long done = 0;                                                                     \
+    if (efl_first_use_on_device(&done)) {                                                                   \
       cudaError_t e = cudaFuncSetAttribute(radial_bwd_kernel<KK>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                            (int)radial_bwd_smem(KK, 768));                                  \
       if (e != cudaSuccess) {                                                                               \
         efl_set_error(cudaGetErrorString(e));                                                               \
         return (int)e;                                                                                      \
       }                                                                                                     \
-      done = true;                                                                                          \
     }                                                                                                       \
     radial_bwd_kernel<KK><<<nblocks, RTHREADS, smem, s>>>(x, p, NO, dout, dx, part, E);                     \
   }

@@ -4,9 +4,9 @@
 // dataset's `linked_to` edges are radius graphs).  Semantics restated from the published algorithm:
 // edge (j -> i) iff j != i (unless loop), batch[j] == batch[i] and
 //     ((xi-xj)^2 + (yi-yj)^2) + (zi-zj)^2 < r*r        evaluated in fp32 with separately rounded operations
-// (the brute-force oracle's expression, oracle/ef_oracle.py: radius_graph_bruteforce); at most max_num_neighbors
-// sources per target, keeping the smallest source indices (the CUDA kernel of torch-cluster scans sources in index
-// order and stops at the cap).  Output: edge_index[0] = source j, edge_index[1] = target i, grouped by target in
+// (the brute-force oracle's expression, oracle/ef_oracle.py: radius_graph_bruteforce).  Neighbour cap as upstream
+// applies it: radius_graph(loop=False) calls radius(..., max_num_neighbors + 1), whose kernel scans sources in index
+// order, the self hit included, and stops at the cap; self loops are removed afterwards (see neighbour_kernel).  Output: edge_index[0] = source j, edge_index[1] = target i, grouped by target in
 // ascending i and, inside a target, ascending j - a canonical order, so the edge LIST (not only the set) is
 // reproducible bit for bit and is directly the CSR the attention kernels consume.
 //
@@ -127,15 +127,15 @@ template <bool FILL>
 __global__ void __launch_bounds__(128) neighbour_kernel(const float4* __restrict__ sorted, int n,
                                                         const int* __restrict__ cell_of,
                                                         const int* __restrict__ cell_start, Grid g, float r2, int loop,
-                                                        int* __restrict__ deg, const int* __restrict__ rowptr,
-                                                        int* __restrict__ col) {
+                                                        int cap, int* __restrict__ deg, int* __restrict__ deg_cap,
+                                                        const int* __restrict__ rowptr, int* __restrict__ col) {
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n) return;
   const float4 me = sorted[s];
   const int i = __float_as_int(me.w);
   const int c = cell_of[i];
   const int cx = c % g.nx, cy = (c / g.nx) % g.ny, cz = (c / (g.nx * g.ny)) % g.nz, b = c / (g.nx * g.ny * g.nz);
-  int cnt = 0;
+  int cnt = 0, cnt_lo = 0;  // hits; hits whose source index is below the target's own index
   int* out = FILL ? col + rowptr[i] : nullptr;
   for (int dz = -1; dz <= 1; ++dz) {
     const int z = cz + dz;
@@ -153,17 +153,21 @@ __global__ void __launch_bounds__(128) neighbour_kernel(const float4* __restrict
         const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy)), __fmul_rn(ddz, ddz));
         if (d2 < r2 && (loop || q != s)) {
           if (FILL) out[cnt] = __float_as_int(o.w);
+          else cnt_lo += __float_as_int(o.w) < i;
           ++cnt;
         }
       }
     }
   }
-  if (!FILL) deg[i] = cnt;
-}
-
-__global__ void cap_kernel(const int* __restrict__ deg, int n, int cap, int* __restrict__ deg_cap) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) deg_cap[i] = min(deg[i], cap);
+  if (!FILL) {
+    deg[i] = cnt;
+    // Neighbour cap as torch_cluster.radius_graph applies it (torch-cluster 1.6.x radius_graph -> radius): with
+    // loop=False it searches with max_num_neighbors + 1, the self hit included, in ascending source index, and
+    // removes self loops afterwards.  A target whose own index comes after its first cap+1 hits keeps cap+1
+    // sources; otherwise the self hit used one slot and min(deg, cap) remain.  Either way the kept sources are the
+    // smallest indices of the (sorted) row, so emit takes a prefix.
+    deg_cap[i] = loop ? min(cnt, cap) : (cnt_lo >= cap + 1 ? cap + 1 : min(cnt, cap));
+  }
 }
 
 // ascending sort of every CSR row; one warp per row, bitonic network in shared memory (rows <= CAP elements)
@@ -288,8 +292,7 @@ extern "C" int efl_radius_graph_count(const float* pos, const int* batch, int N,
   int* deg_cap = deg + (N + 1);
   cudaMemsetAsync(deg, 0, sizeof(int) * 2 * (size_t)(N + 1), s);
   rg::neighbour_kernel<false><<<nblk(N, 128), 128, 0, s>>>((const float4*)sorted, N, cell_of, cell_start, g,
-                                                           r * r, loop, deg_full, nullptr, nullptr);
-  rg::cap_kernel<<<nblk(N, 256), 256, 0, s>>>(deg_full, N, cap, deg_cap);
+                                                           r * r, loop, cap, deg_full, deg_cap, nullptr, nullptr);
   tb = (size_t)temp_bytes;
   cub::DeviceScan::ExclusiveSum(temp, tb, deg_full, rowptr_full, N + 1, s);
   tb = (size_t)temp_bytes;
@@ -306,20 +309,18 @@ extern "C" int efl_radius_graph_fill(int N, int nbatch, float cs, int nx, int ny
   cudaStream_t s = (cudaStream_t)stream;
   Grid g{1.0f / cs, nx, ny, nz, nbatch};
   rg::neighbour_kernel<true><<<nblk(N, 128), 128, 0, s>>>((const float4*)sorted, N, cell_of, cell_start, g,
-                                                          r * r, loop, nullptr, rowptr_full, col);
+                                                          r * r, loop, 0, nullptr, nullptr, rowptr_full, col);
   rg::rowsort_kernel<1024><<<nblk(N, 8), 256, 0, s>>>(rowptr_full, N, col);
   if (max_deg > 1024) {
     int P = 2048;
     while (P < max_deg) P <<= 1;
     EFL_REQUIRE(P <= 32768, "efl_radius_graph_fill: more than 32768 neighbours of one point");
-    static int smem_set = 0;
-    if (smem_set < P * 4) {
+    {  // per call: the attribute is per device and a process may touch several (cheap next to the sort itself)
       cudaError_t e = cudaFuncSetAttribute(rg::rowsort_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768 * 4);
       if (e != cudaSuccess) {
         efl_set_error(cudaGetErrorString(e));
         return (int)e;
       }
-      smem_set = 32768 * 4;
     }
     rg::rowsort_long_kernel<<<N < 1184 ? N : 1184, 256, (size_t)P * 4, s>>>(rowptr_full, N, col, 1024, P);
   }

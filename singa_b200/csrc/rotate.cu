@@ -194,6 +194,7 @@ __global__ void __launch_bounds__(32 * WPB, 16 / WPB) rotate_in_bwd_node_kernel(
     const float* xp = x_node + (size_t)n * T::L * C;
     for (int i = lane; i < T::L * C; i += 32) (&sX[warp][0][0])[i] = __ldg(xp + i);
   }
+  __syncwarp();  // sX is filled by all 32 lanes and read per half-warp: order the stores of the other half first
   const float* x = &sX[warp][0][c];
   // Software pipeline over the half-warp's edges: edge ids (segment position -> original id, two dependent loads) are
   // fetched two iterations ahead and the Wigner rows one iteration ahead (cp.async into the other buffer), so only
@@ -881,15 +882,14 @@ extern "C" int efl_segment_sum_rows(const float* buf, int L, int ldc, int coff, 
 // launch with dynamic shared memory (opt-in above 48 KB, set once per instantiation)
 #define RB_LAUNCH(KERNEL, SMEM_BYTES, ...)                                                              \
   {                                                                                                     \
-    static bool attr_done = false;                                                                      \
-    if (!attr_done) {                                                                                   \
+    static unsigned long long attr_done = 0;                                                            \
+    if (efl_first_use_on_device(&attr_done)) {                                                          \
       cudaError_t ae = cudaFuncSetAttribute(KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize,        \
                                             SMEM_BYTES);                                                \
       if (ae != cudaSuccess) {                                                                          \
         efl_set_error(cudaGetErrorString(ae));                                                          \
         return (int)ae;                                                                                 \
       }                                                                                                 \
-      attr_done = true;                                                                                 \
     }                                                                                                   \
     KERNEL<<<grid, block, SMEM_BYTES, s>>>(__VA_ARGS__);                                                \
   }

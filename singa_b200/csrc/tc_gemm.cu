@@ -518,8 +518,8 @@ extern "C" int efl_tc_gemm_pair_mode(int mode) {
 
 static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mc0,
                   const Params& p, int work_items, bool pair, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static unsigned long long attr_set = 0;
+  if (efl_first_use_on_device(&attr_set)) {
     cudaError_t e = cudaFuncSetAttribute(efl::tc::tc_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          efl::tc::SMEM_BYTES);
     if (e == cudaSuccess)
@@ -529,7 +529,6 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMa
       efl_set_error(cudaGetErrorString(e));
       return (int)e;
     }
-    attr_set = true;
   }
   if (!pair) {
     const int grid = work_items < efl_num_sms() ? work_items : efl_num_sms();

@@ -48,11 +48,6 @@ def _should_save(nbytes: int, device) -> bool:
 # backward of rotate-in: "nodes" = node-owned accumulation (no per-edge gradient tensor), "edges" = per-edge d x
 # followed by two segment sums.  Both deterministic; chosen by measurement (tools/edge_bench.py).
 ROTATE_IN_BWD = os.environ.get("EFL_ROTIN_BWD", "nodes")
-# bf16 mode, opt-in experiment: rotate-back + aggregate as per-edge tcgen05 MMAs accumulating in TMEM
-# (csrc/rotate_tc.cu).  Correct for (lmax, mmax) = (6, 2) but measured SLOWER than the SIMT kernel (0.93 vs 0.75 ms on
-# 225 k edges): one edge needs 7 small TMA copies and the per-SM issue rate of small boxes (~0.09 us each) bounds it.
-ROTATE_BACK_TC = os.environ.get("EFL_ROTBACK_TC", "0") == "1"
-
 
 def set_precision(mode: str) -> None:
     global _PRECISION
@@ -369,12 +364,7 @@ def _chunk_forward(d: AttnDims, ws: _Workspace, w1: _Weights, w2: _Weights, x_sr
     for m in range(1, d.mmax + 1):
         _gemm_nt(2, ws.B[m], w2.wm[m - 1], None, ws.V[m], d.ms[m] * VH, None, 0, 0, 2 * Ec, 2 * d.ms[m] * VH,
                  d.ms[m] * H)
-    if out is not None and bf16 and ROTATE_BACK_TC:
-        call("efl_rotate_back_aggregate_tc_fwd", d.lmax, d.mmax, d.heads, d.value_ch, ptr(ws.V[0]), ptr(ws.V[1]),
-             ptr(ws.V[2]), ptr(alpha), ptr(csr.rowptr), ptr(csr.perm), ptr(wig), ptr(out), n0, n1, e0, Ec,
-             work=Ec * _bytes_rotate_back(d, ws.V[0].element_size(), wig.shape[1]) + (n1 - n0) * out[0].numel() * 4,
-             tag="efl_rotate_back_aggregate_fwd")
-    elif out is not None:
+    if out is not None:
         call("efl_rotate_back_aggregate_fwd", d.lmax, d.mmax, d.heads, d.value_ch, bf16, ptr(ws.V[0]), ptr(ws.V[1]),
              ptr(ws.V[2]), ptr(alpha), ptr(csr.rowptr), ptr(csr.perm), ptr(wig), ptr(out), n0, n1, e0,
              work=Ec * _bytes_rotate_back(d, ws.V[0].element_size(), wig.shape[1]) + (n1 - n0) * out[0].numel() * 4)
@@ -400,6 +390,24 @@ def _bytes_rotate_back_bwd(d: AttnDims, es: int, wsz: int) -> float:
     return d.M * VH * es + wsz * 4 + dup + d.heads * 4 * 5 + 4
 
 
+def _check_edge_inputs(who, csr, wig, lmax, mmax, rad=None, m0=None, x_src=None, x_dst=None):
+    """The kernels index the Wigner store and the per-edge scalars by ORIGINAL edge id (csr.perm): a store computed
+    for another edge list (a forgotten set_wigner, or pass 4 reusing pass 3's rows with |PL| != |LP|) would be read out
+    of bounds.  The reference fails with a bmm shape error in that case (EF_layers.py:494-505); so do we."""
+    E = csr.num_edges
+    if wig.dim() != 2 or wig.shape[0] != E or wig.shape[1] != wigner_size(lmax, mmax):
+        raise RuntimeError(
+            f"{who}: Wigner rows {tuple(wig.shape)} do not match the edge list ({E} edges, {wigner_size(lmax, mmax)} "
+            f"floats per edge for lmax={lmax}, mmax={mmax}); call SO3_Rotation.set_wigner for this edge_index first")
+    for name, t in (("radial weights", rad), ("m=0 coefficients", m0)):
+        if t is not None and t.shape[0] != E:
+            raise RuntimeError(f"{who}: {name} have {t.shape[0]} rows for {E} edges")
+    if x_src is not None and x_src.shape[0] != csr.num_src:
+        raise RuntimeError(f"{who}: {x_src.shape[0]} source rows for a CSR over {csr.num_src} source nodes")
+    if x_dst is not None and x_dst.shape[0] != csr.num_dst:
+        raise RuntimeError(f"{who}: {x_dst.shape[0]} target rows for a CSR over {csr.num_dst} target nodes")
+
+
 class EdgeAttentionFunction(torch.autograd.Function):
     """x_src, x_dst, rad, conv1 (W0,b0,W1,W2), alpha LN (w,b), alpha_dot, conv2 (W0,b0,W1,W2)
     -> aggregated messages [num_dst, L, heads*value] (input of ``proj``)."""
@@ -410,6 +418,8 @@ class EdgeAttentionFunction(torch.autograd.Function):
         d: AttnDims = dims
         check_cuda(x_src, x_dst, rad, wig)
         assert d.mmax == 2, "the edge path is built for mmax == 2"
+        _check_edge_inputs("SO2EquivariantGraphAttention", csr, wig, d.lmax, d.mmax, rad=rad,
+                           x_src=x_src, x_dst=x_dst)
         x_src = x_src.contiguous()
         x_dst = x_dst.contiguous()
         rad = rad.contiguous()
@@ -575,6 +585,7 @@ class EdgeDegreeFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, m0, csr, wig, lmax, mmax, C, rescale_factor):
         check_cuda(m0, wig)
+        _check_edge_inputs("EdgeDegreeEmbedding", csr, wig, lmax, mmax, m0=m0)
         m0 = m0.contiguous()
         L = (lmax + 1) ** 2
         out = torch.empty(csr.num_dst, L, C, dtype=torch.float32, device=m0.device)

@@ -22,7 +22,7 @@ class RadiusCSR:
     rowptr: torch.Tensor       # [N+1] int32 over targets
     col: torch.Tensor          # [E] int32 sources
     max_degree: int            # largest degree before the max_num_neighbors cap
-    truncated: bool            # True when some target had more than max_num_neighbors sources
+    truncated: bool            # True when the neighbour cap removed edges
 
 
 def radius_graph_csr(x: torch.Tensor, r: float, batch: Optional[torch.Tensor] = None, loop: bool = False,
@@ -64,7 +64,7 @@ def radius_graph_csr(x: torch.Tensor, r: float, batch: Optional[torch.Tensor] = 
     rowptr_cap = torch.empty(N + 1, dtype=torch.int32, device=dev)
     tbytes = int(LIB.efl_radius_graph_temp_bytes(max(N, ncells) + 1))
     temp = torch.empty(max(tbytes, 16), dtype=torch.uint8, device=dev)
-    cap = int(max_num_neighbors)
+    cap = min(int(max_num_neighbors), 1 << 30)  # the kernel forms cap + 1 (upstream searches with one extra slot for self)
     call("efl_radius_graph_count", ptr(pos), ptr(b32), N, nbatch, ptr(origin), cs, nx, ny, nz, r, int(loop), cap,
          ptr(cell_of), ptr(cell_start), ptr(scratch), ptr(sorted_pts), ptr(deg), ptr(rowptr_full), ptr(rowptr_cap),
          ptr(temp), tbytes, work=N * 16.0 * 27)

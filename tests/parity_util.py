@@ -66,14 +66,20 @@ def oracle_tables(model=None):
     return eo.Tables(6, 2, jd, ex["to62"], ex["from62"], ex["to66"], ex["from66"])
 
 
-def run_attention_case(name: str, device="cuda:0", precision="fp32", return_all=False, fixture="attention_small.pt"):
+def run_attention_case(name: str, device="cuda:0", precision="fp32", return_all=False, fixture="attention_small.pt",
+                       model=None):
     """TransBlockV2 + EdgeDegreeEmbedding on tests/golden/attention_small.pt[name]: CUDA path vs the
     reference-generated golden.  Returns the max relative error over outputs and gradients."""
     from singa_b200 import EF_layers as ef
     fx = load_golden(fixture)
     case = fx["cases"][name]
     lmax = fx.get("lmax", 6)
-    model = build_model(device, fx["param_seed"], precision, lmax=lmax)
+    if model is None:
+        model = build_model(device, fx["param_seed"], precision, lmax=lmax)
+    else:   # a model built by the caller (smoke(): one construction, two precisions)
+        from singa_b200 import ops
+        ops.set_precision(precision)
+        model.zero_grad(set_to_none=True)
     block = model.blocks[1]
     dev = torch.device(device)
     ei = case["edge_index"].to(dev)

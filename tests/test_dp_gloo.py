@@ -7,7 +7,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from singa_b200.parallel import GradientBucket, shard_by_edges
+from singa_b200.parallel import GradientBucket, GradientBuckets, shard_by_edges
 
 
 def _free_port():
@@ -67,3 +67,64 @@ def test_two_rank_allreduce_matches_single_process(tmp_path):
             assert got[n] is None, n
         else:
             assert torch.allclose(got[n], p.grad, rtol=1e-5, atol=1e-6), n
+
+
+class _TwoBlock(torch.nn.Module):
+    """Parameter names shaped like the real model: two 'blocks' plus a tail and a never-used table."""
+
+    def __init__(self):
+        super().__init__()
+        torch.manual_seed(3)
+        self.blocks = torch.nn.ModuleList([torch.nn.Linear(6, 6), torch.nn.Linear(6, 6)])
+        self.head = torch.nn.Linear(6, 2)
+        self.side = torch.nn.Linear(6, 2)    # only rank 1's data goes through it
+        self.unused = torch.nn.Parameter(torch.zeros(4))
+
+    def forward(self, x, use_side):
+        h = self.blocks[1](torch.tanh(self.blocks[0](x)))
+        out = self.head(h).pow(2).sum()
+        if use_side:
+            out = out + self.side(h).sum()
+        return out
+
+
+def _worker_buckets(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sizes, xs = _data()
+    mine = shard_by_edges(sizes, world)[rank]
+    m = _TwoBlock()
+    gb = GradientBuckets(m.named_parameters(), average=False)
+    steps = []
+    for step in range(3):          # step 0 settles the participating set, steps 1-2 reduce from the hooks
+        gb.zero_grad()
+        sum(m(xs[i], use_side=(rank == 1)) for i in mine).backward()
+        gb.finish()
+        steps.append({n: (None if p.grad is None else p.grad.clone()) for n, p in m.named_parameters()})
+    if True:
+        torch.save(dict(steps=steps, dropped=gb.dropped, keys=[b.key for b in gb.buckets]), out + f".{rank}")
+    dist.destroy_process_group()
+
+
+def test_bucketed_overlapped_allreduce_with_a_rank_missing_a_gradient(tmp_path):
+    """GradientBuckets: gradients live in per-block flat buffers, buckets reduce in a fixed order as backward
+    completes them; a parameter without a gradient on ONE rank (``side`` on rank 0) still ends with the summed
+    gradient on every rank, and a parameter without a gradient on ANY rank is dropped globally."""
+    out = str(tmp_path / "gb.pt")
+    mp.spawn(_worker_buckets, args=(2, _free_port(), out), nprocs=2, join=True)
+    r0, r1 = torch.load(out + ".0"), torch.load(out + ".1")
+    assert r0["dropped"] == ["unused"] and r1["dropped"] == ["unused"]
+    assert r0["keys"] == ["block1", "block0", "rest"]
+    sizes, xs = _data()
+    shards = shard_by_edges(sizes, 2)
+    m = _TwoBlock()
+    (sum(m(xs[i], False) for i in shards[0]) + sum(m(xs[i], True) for i in shards[1])).backward()
+    for step in range(3):
+        for n, p in m.named_parameters():
+            a, b = r0["steps"][step][n], r1["steps"][step][n]
+            if n == "unused":
+                assert a is None and b is None
+                continue
+            assert torch.equal(a, b), (step, n)          # every rank holds the same reduced gradient
+            assert torch.allclose(a, p.grad, rtol=1e-5, atol=1e-6), (step, n)

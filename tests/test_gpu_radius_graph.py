@@ -57,6 +57,12 @@ def test_batches_cap_loop_and_flow():
     got = radius_graph_csr(p.to(DEV), 6.0, batch.to(DEV))
     assert got.truncated and torch.equal(got.edge_index.cpu(), refc)
     assert torch.equal(got.col.cpu().long(), refc[0])
+    # upstream cap order (self hit counted, dropped after the cap): small caps, both loop modes
+    for cap in (1, 4, 7):
+        for loop in (False, True):
+            refk = eo.radius_graph_bruteforce(p, 6.0, batch, loop=loop, max_num_neighbors=cap)
+            gotk = radius_graph(p.to(DEV), 6.0, batch.to(DEV), loop=loop, max_num_neighbors=cap).cpu()
+            assert torch.equal(gotk, refk), (cap, loop)
     refl = eo.radius_graph_bruteforce(p, 6.0, batch, loop=True, max_num_neighbors=1 << 30)
     assert torch.equal(radius_graph(p.to(DEV), 6.0, batch.to(DEV), loop=True, max_num_neighbors=1 << 30).cpu(), refl)
     t2s = radius_graph(p.to(DEV), 6.0, batch.to(DEV), max_num_neighbors=1 << 30, flow="target_to_source").cpu()

@@ -134,3 +134,51 @@ def test_node_s2_gemm_route_math_equals_dense_autograd(monkeypatch):
     dg, dx = ops._node_s2_gemm_backward(gate.detach(), xt, to_g, from_g, dy, (N, 81, CH))
     rel = lambda a, b: float((a - b).abs().max() / a.abs().max())
     assert rel(y.detach(), y2) < 2e-2 and rel(x.grad, dx) < 2e-2 and rel(gate.grad, dg) < 1e-6
+
+
+def test_init_edge_rot_mat_matches_reference_frames_on_cpu():
+    """a1 on the host (the function is ~25 element-wise torch ops, device-agnostic): product init_edge_rot_mat fed the
+    golden's random draws reproduces the frames written by the unmodified reference (EF_layers.py:2286-2351)."""
+    from singa_b200 import EF_layers as ef
+    from tests.parity_util import load_golden
+    fx = load_golden("example_3wi2.pt")
+    g = fx["graph"]
+    rnd = syn.frame_randoms(g, fx["frame_seed"])
+    orig = torch.rand_like
+    try:
+        for key, (s, d, ei) in dict(pp=("pos_p", "pos_p", "ei_pp"), ll=("pos_l", "pos_l", "ei_ll"),
+                                    lp=("pos_l", "pos_p", "ei_lp")).items():
+            torch.rand_like = lambda x, _r=rnd[key], **k: _r.to(x.dtype)
+            rot = ef.init_edge_rot_mat(g[s][g[ei][0]] - g[d][g[ei][1]], device="cpu")
+            assert float((rot - fx["frames"][key]).abs().max()) <= 1e-6, key
+        w = load_golden("wigner_small.pt")
+        torch.rand_like = lambda x, **k: w["rand"].to(x.dtype)
+        assert float((ef.init_edge_rot_mat(w["edge_vec"], device="cpu") - w["rot"]).abs().max()) <= 1e-6
+    finally:
+        torch.rand_like = orig
+
+
+@pytest.mark.skipif(not rl.reference_available(), reason="needs /root/reference (build container only)")
+def test_reference_caller_fixture_is_verbatim():
+    """tests/golden/ref_src/Embedding.py (boundary-test fixture) is byte-identical to the reference file."""
+    a = open(os.path.join(rl.REFERENCE_ROOT, "model", "Embedding.py"), "rb").read()
+    b = open(os.path.join(ROOT, "tests", "golden", "ref_src", "Embedding.py"), "rb").read()
+    assert a == b
+
+
+def test_edge_inputs_for_another_edge_list_are_rejected():
+    """Wigner rows / radial weights indexed by original edge id must belong to THIS edge list; the
+    reference fails with a bmm shape error (EF_layers.py:494-505), the B200 path raises before any launch."""
+    ops = pytest.importorskip("singa_b200.ops")
+    csr = ops.EdgeCSR(4, 5, 7, *([None] * 7))
+    good = torch.zeros(7, ops.wigner_size(6, 2))
+    ops._check_edge_inputs("t", csr, good, 6, 2, rad=torch.zeros(7, 576), x_src=torch.zeros(4, 49, 16),
+                           x_dst=torch.zeros(5, 49, 16))
+    with pytest.raises(RuntimeError, match="Wigner rows"):
+        ops._check_edge_inputs("t", csr, torch.zeros(6, ops.wigner_size(6, 2)), 6, 2)
+    with pytest.raises(RuntimeError, match="Wigner rows"):
+        ops._check_edge_inputs("t", csr, torch.zeros(7, ops.wigner_size(8, 2)), 6, 2)
+    with pytest.raises(RuntimeError, match="radial"):
+        ops._check_edge_inputs("t", csr, good, 6, 2, rad=torch.zeros(8, 576))
+    with pytest.raises(RuntimeError, match="source rows"):
+        ops._check_edge_inputs("t", csr, good, 6, 2, x_src=torch.zeros(3, 49, 16))

@@ -110,3 +110,16 @@ def test_oracle_matches_live_reference_on_synthetic_complex():
         o2 = eo.embedding_forward(p, g, frames, t, HP)
     for k in o2:
         assert rel_err(o2[k], out[k].embedding) < 5e-6, k
+
+
+def test_radius_graph_oracle_neighbour_cap_follows_upstream_order():
+    """torch-cluster 1.6.x radius_graph(loop=False) searches with max_num_neighbors + 1 INCLUDING the self hit, in
+    ascending source index, then removes self loops: a target whose own index follows its first cap+1
+    hits keeps cap+1 sources, the others min(deg, cap).  Hand-computed case: 6 collinear points, all within r."""
+    from oracle import ef_oracle as eo
+    p = torch.tensor([[float(i) * 0.1, 0.0, 0.0] for i in range(6)])
+    ei = eo.radius_graph_bruteforce(p, 10.0, max_num_neighbors=2)
+    rows = {t: ei[0][ei[1] == t].tolist() for t in range(6)}
+    assert rows == {0: [1, 2], 1: [0, 2], 2: [0, 1], 3: [0, 1, 2], 4: [0, 1, 2], 5: [0, 1, 2]}
+    eil = eo.radius_graph_bruteforce(p, 10.0, loop=True, max_num_neighbors=2)
+    assert all(eil[0][eil[1] == t].tolist() == [0, 1] for t in range(6))

@@ -17,7 +17,7 @@ import torch
 from singa_b200 import _lib, ops
 from singa_b200 import synthetic as syn
 from singa_b200.embedding import DEFAULT_CONFIG, EquivariantEmbedding
-from singa_b200.parallel import GradientBucket
+from singa_b200.parallel import GradientBuckets
 from singa_b200.radius import radius_graph
 
 
@@ -91,15 +91,15 @@ def main():
     model = EquivariantEmbedding(cfg, device=dev)
     syn.load_portable_parameters(model, 0)
     opt = torch.optim.Adam(model.parameters(), lr=1e-4)
-    bucket = GradientBucket(model.parameters())
+    bucket = GradientBuckets(model.named_parameters())
     view = syn.GraphView(g)
 
     def step():
-        opt.zero_grad(set_to_none=True)
+        bucket.zero_grad()
         out = model(view)
         loss = out[syn.PROTEIN].embedding.square().mean() + out[syn.LIGAND].embedding.square().mean()
         loss.backward()
-        bucket.allreduce_()
+        bucket.finish()
         opt.step()
         return loss
 
