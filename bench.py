@@ -49,6 +49,9 @@ def parse():
     ap.add_argument("--batch", type=int, default=32, help="complexes per GPU")
     ap.add_argument("--atoms", type=int, default=None, help="fix protein atoms per complex (default U{400..500})")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--config", type=int, default=2, choices=[2, 3],
+                    help="BASELINE.json configs index: 2 = EF_layers fwd+bwd (the metric's config, default), 3 = full "
+                         "SINGA train step (EquivariantEmbedding + CProMG transformer), global batch 64 over the ranks")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--global-batch", type=int, default=64, help="complexes of the whole job under --scaling strong")
     return ap.parse_args()
@@ -272,11 +275,97 @@ def emit(line: dict):
         os.write(_RESULT_FD, data)
 
 
+def config3(args):
+    """BASELINE.json configs[3]: full SINGA train step (EquivariantEmbedding + CProMG encoder/decoder, cross entropy,
+    Adam), GLOBAL batch 64, data parallel with the bucketed NCCL gradient all-reduce.  Every step takes its batch from
+    the CSR-carrying dataset format in pinned host memory (one H2D copy inside the timed region, loss read back at the
+    end of the run), so ``value`` IS end to end.  The dense transformer blocks run on PyTorch library ops (out of scope
+    for kernels, SURVEY.md 2 #5); the message passing, kNN graph and EF_layers run on libefl.so."""
+    import torch.distributed as dist
+    from singa_b200 import _lib, ops
+    from singa_b200 import dataset as ds
+    from singa_b200 import synthetic as syn
+    from singa_b200.gan import SINGA, default_config
+    from singa_b200.train import Trainer
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    ops.set_precision(args.precision)
+    gb = args.global_batch
+    assert gb % world == 0, "global batch must divide over the ranks"
+    data = ds.ComplexDataset(ds.synthetic_records(range(gb), n_protein=args.atoms))
+    torch.manual_seed(0)
+    model = SINGA(default_config(), device=dev)
+    syn.load_portable_parameters(model.embedding, 0)
+    syn.load_portable_parameters_fanin(model.model, 1)
+    tr = Trainer(model, data, batch_size_per_rank=gb // world, shuffle=False, prefetch=2, device=dev)
+    edges = sum(metric_edges({k: torch.empty(2, len(data[i][f"{k[3:]}_src"])) for k in ("ei_pp", "ei_ll", "ei_lp", "ei_pl")})
+                for i in tr.loader.indices)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        tr.step()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    n0 = _lib.launch_count
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(args.steps):
+        loss, _ = tr.step()
+    b.record()
+    barrier()
+    launches = _lib.launch_count - n0
+    clocks = sampler.stop() if rank == 0 else None
+    ms = torch.tensor([a.elapsed_time(b) / args.steps], device=dev)
+    tot = torch.tensor([float(edges)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot)
+    _lib.start_profile()
+    for _ in range(2):
+        tr.step()
+    full = _lib.stop_profile()
+    hb = next(tr.loader)
+    if rank == 0:
+        ms, tot = float(ms), float(tot)
+        emit({
+            "metric": METRIC, "value": tot / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+            "config": {"workload": f"BASELINE configs[3]: full SINGA train step (EF_layers embedding + CProMG "
+                                   f"encoder/decoder + cross entropy + Adam), GLOBAL batch {gb} synthetic complexes, dp{world}",
+                       "complexes_per_gpu": gb // world, "complexes_per_s": gb / (ms * 1e-3), "loss": float(loss),
+                       "dense_transformer": "PyTorch library ops (out of scope for kernels, SURVEY.md 2 #5)",
+                       "parameters": sum(p.numel() for p in model.parameters()),
+                       "edge_count": "EF_layers edges (edge-layers computed / 3) of the global batch"},
+            "e2e": {"value": tot / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": hb.nbytes, "d2h_bytes_per_step": 0,
+                    "note": "the timed step itself copies its pinned host batch (one buffer) to the device"},
+            "gpu_launches": launches, "clocks": clocks,
+            "kernel_ms_per_step": {k: round(v["ms"] / 2, 3) for k, v in sorted(full.items(), key=lambda kv: -kv[1]["ms"])},
+        })
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     args = parse()
     _quiet_stdout()
     if args.impl == "reference":
         reference_arm(args)
+        return
+    if args.config == 3:
+        config3(args)
         return
     import torch.distributed as dist
     from singa_b200 import _lib, ops

@@ -218,6 +218,16 @@ int efl_radius_graph_fill(int N, int nbatch, float cs, int nx, int ny, int nz, f
 int efl_radius_graph_emit(const int* rowptr_full, const int* rowptr_cap, const int* col, int N, long long E,
                           long long* edge_index, int flow_target_to_source, void* stream);
 
+/* knn_graph(pos, k, batch, flow='target_to_source') of torch-cluster 1.6.3 (un-vendored; reference call sites
+ * model/CProMG.py:293 and :330) on the same cell list: after efl_radius_graph_bbox, this bins/scans/scatters the points
+ * and finds, one warp per point, the k (<= 64) nearest OTHER points of the same batch item (fp32 ((dx^2+dy^2)+dz^2),
+ * ties to the smaller index), searching shells of cells until the k-th distance lies inside the covered radius.
+ * nbr [N*k] (ascending distance, -1 padded), cnt [N+1], rowptr_full [N+1] (= i*k), rowptr [N+1] = scan(cnt);
+ * efl_radius_graph_emit(rowptr_full, rowptr, nbr, N, rowptr[N], edge_index, flow) writes the int64 edge list. */
+int efl_knn_graph(const float* pos, const int* batch, int N, int nbatch, const float* origin, float cs, int nx, int ny,
+                  int nz, int K, int loop, int* cell_of, int* cell_start, int* scratch, void* sorted, int* nbr,
+                  int* cnt, int* rowptr_full, int* rowptr, void* temp, long long temp_bytes, void* stream);
+
 /* Destination-sorted CSR of a caller-supplied edge_index plus the source-side grouping (csrc/csr.cu).  The reference
  * works on the raw edge list (gather EF_layers.py:326-328, index_add_ :342-351, softmax index :1180); every kernel of
  * this library consumes edges grouped by destination instead.  src64/dst64: rows 0 and 1 of edge_index ([E] int64).

@@ -87,3 +87,57 @@ def knn_graph_bruteforce(pos: torch.Tensor, k: int, batch: torch.Tensor = None) 
     keep = torch.gather(d2, 1, order) < float("inf")
     centre = torch.arange(N).unsqueeze(1).expand_as(order)
     return torch.stack((centre[keep], order[keep]))
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# torch_geometric 2.3.1 utilities the encoders call around the attention (CProMG.py:293-300, 304, 307, 330-334),
+# restated from their published behaviour with plain loops (an independent route from the sort-based device code in
+# singa_b200/cpromg.py).  Un-vendored, no reference vector: "parity unpinned".
+# ---------------------------------------------------------------------------------------------------------------
+def to_undirected(edge_index, edge_attr=None, num_nodes=None, reduce="add"):
+    """Both directions of every edge; duplicate pairs merged, attribute = mean (reduce='mean') of the merged entries;
+    output sorted by (row, col)."""
+    assert reduce == "mean" and edge_attr is not None
+    acc = {}
+    for (r, c), a in zip(edge_index.t().tolist(), edge_attr.tolist()):
+        for key in ((r, c), (c, r)):
+            acc.setdefault(key, []).append(a)
+    keys = sorted(acc)
+    ei = torch.tensor(keys, dtype=torch.long).t().contiguous()
+    attr = torch.tensor([sum(acc[k]) / len(acc[k]) for k in keys], dtype=edge_attr.dtype)
+    return ei, attr
+
+
+def get_laplacian(edge_index, edge_weight=None, normalization=None, dtype=None, num_nodes=None):
+    """normalization=None: L = D - A.  Self loops removed, then one loop per node appended; weights cat(-w, deg) with
+    deg[i] = sum of w over the edges whose row is i.  Works for per-edge weight vectors [E, C] (CProMG.py:300)."""
+    assert normalization is None
+    keep = edge_index[0] != edge_index[1]
+    edge_index, edge_weight = edge_index[:, keep], edge_weight[keep]
+    n = int(edge_index.max()) + 1 if num_nodes is None else num_nodes
+    deg = torch.zeros((n,) + edge_weight.shape[1:], dtype=edge_weight.dtype).index_add_(0, edge_index[0], edge_weight)
+    loops = torch.arange(n, dtype=torch.long)
+    return torch.cat((edge_index, torch.stack((loops, loops))), dim=1), torch.cat((-edge_weight, deg), dim=0)
+
+
+def to_dense_batch(x, batch=None, fill_value=0.0, max_num_nodes=None, batch_size=None):
+    """[N, D] rows of a sorted batch vector -> ([B, Nmax, D], mask [B, Nmax])."""
+    B = int(batch.max()) + 1
+    counts = torch.bincount(batch, minlength=B)
+    nmax = int(counts.max())
+    out = x.new_full((B, nmax, x.shape[1]), fill_value)
+    mask = torch.zeros(B, nmax, dtype=torch.bool)
+    start = 0
+    for b in range(B):
+        c = int(counts[b])
+        out[b, :c] = x[start:start + c]
+        mask[b, :c] = True
+        start += c
+    return out, mask
+
+
+def knn_graph(x, k, batch=None, loop=False, flow="source_to_target", **kw):
+    """torch_geometric.nn.knn_graph signature over knn_graph_bruteforce."""
+    assert not loop
+    ei = knn_graph_bruteforce(x, k, batch)       # row 0 = centre, row 1 = neighbour
+    return ei if flow == "target_to_source" else ei.flip(0)

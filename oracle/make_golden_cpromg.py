@@ -59,8 +59,9 @@ def load_cpromg():
         mod("dgl")
         pyg = mod("torch_geometric")
         pyg.data = mod("torch_geometric.data", Data=object, HeteroData=object)
-        pyg.nn = mod("torch_geometric.nn", knn_graph=unused)
-        pyg.utils = mod("torch_geometric.utils", get_laplacian=unused, to_dense_batch=unused, to_undirected=unused)
+        pyg.nn = mod("torch_geometric.nn", knn_graph=co.knn_graph)
+        pyg.utils = mod("torch_geometric.utils", get_laplacian=co.get_laplacian, to_dense_batch=co.to_dense_batch,
+                        to_undirected=co.to_undirected)
         mod("torch_scatter", scatter_sum=_loop_scatter_sum, scatter_softmax=_loop_scatter_softmax)
         mod("torch_cluster")
         spec = importlib.util.spec_from_file_location("_ref_cpromg", os.path.join(rl.REFERENCE_ROOT, "model", "CProMG.py"))
@@ -106,5 +107,73 @@ def main():
     print(path, "edges", edge_index.shape[1], "out", tuple(out.shape), os.path.getsize(path), "bytes")
 
 
+class _Cfg(dict):
+    def __init__(self, d=None, **kw):
+        super().__init__()
+        for k, v in dict(d or {}, **kw).items():
+            self[k] = _Cfg(v) if isinstance(v, dict) else v
+    __getattr__ = dict.__getitem__
+
+
+def transformer_inputs(seed=5, tgt_len=12, vocab=116, pad=110):
+    """Two small complexes (27 + 33 'atoms', 7 + 9 'residue' nodes), portable numpy streams."""
+    rs = np.random.RandomState(seed)
+    n_p, n_l = [27, 33], [7, 9]
+    f32 = lambda a: torch.from_numpy(np.asarray(a, dtype=np.float32))
+    pos = f32(np.concatenate([rs.uniform(-5, 5, size=(n, 3)) + 40.0 * i for i, n in enumerate(n_p)]))
+    aa_pos = f32(np.concatenate([rs.uniform(-3, 3, size=(n, 3)) + 40.0 * i for i, n in enumerate(n_l)]))
+    batch = torch.from_numpy(np.repeat([0, 1], n_p))
+    aa_batch = torch.from_numpy(np.repeat([0, 1], n_l))
+    toks = rs.randint(1, vocab, size=(2, tgt_len))
+    toks[toks == pad] = 1
+    toks[0, 8:] = pad
+    return dict(node_attr=f32(rs.normal(size=(sum(n_p), 784)) * 0.3), pos=pos, batch=batch,
+                atom_laplacian=f32(rs.normal(size=(sum(n_p), 8)) * 0.3), smiles_index=torch.from_numpy(toks),
+                tgt_len=tgt_len, aa_node_attr=f32(rs.normal(size=(sum(n_l), 784)) * 0.3), aa_pos=aa_pos,
+                aa_batch=aa_batch, aa_laplacian=f32(rs.normal(size=(sum(n_l), 8)) * 0.3),
+                prop=f32(rs.randint(0, 2, size=(2, 3))))
+
+
+TRANSFORMER_CFG = dict(hidden_channels=256, featurizer_feat_dim=784,
+                       encoder=dict(hidden_channels=256, edge_channels=64, key_channels=128, num_heads=4,
+                                    num_interactions=6, cutoff=10.0, knn=6, lap_dim=8),
+                       decoder=dict(tgt_len=12, hidden_channels=256, key_channels=128, num_heads=4, num_interactions=6,
+                                    padding="right"))
+
+
+def main_transformer():
+    """The whole reference ``Transformer`` (CProMG.py:423-464: Encoder, Encoder2, Decoder) in eval mode on CPU."""
+    import yaml
+    ref = load_cpromg()
+    # keep the graph utilities bound after load_cpromg restored sys.modules: the reference module holds references
+    voc = yaml.safe_load(open(os.path.join(rl.REFERENCE_ROOT, "config", "train.yml")))["model"]["decoder"]["smiVoc"]
+    cfg = _Cfg(TRANSFORMER_CFG)
+    cfg.decoder["smiVoc"] = voc
+    from singa_b200 import synthetic as syn
+    torch.manual_seed(0)
+    model = ref.Transformer(cfg, 784, num_props=3, device="cpu").eval()
+    syn.load_portable_parameters_fanin(model, 5)      # parameters are regenerated from the seed, not stored
+    inp = transformer_inputs()
+    for k in ("node_attr", "aa_node_attr"):
+        inp[k].requires_grad_(True)
+    out = model(**inp)
+    rs = np.random.RandomState(9)
+    w = torch.from_numpy(rs.normal(size=tuple(out.shape)).astype(np.float32))
+    (out * w).sum().backward()
+    from oracle.make_golden import digest
+    fixture = dict(cfg=TRANSFORMER_CFG, vocab_size=len(voc), pad_index=voc.index("^"),
+                   param_seed=5, surface={k: [list(v.shape), str(v.dtype)] for k, v in model.state_dict().items()},
+                   inputs={k: (v.detach().clone() if torch.is_tensor(v) else v) for k, v in inp.items()},
+                   out=out.detach().clone(), loss_weights=w, d_node_attr=inp["node_attr"].grad.clone(),
+                   d_aa_node_attr=inp["aa_node_attr"].grad.clone(),
+                   d_params={k: digest(p.grad) for k, p in model.named_parameters() if p.grad is not None},
+                   params_without_grad=[k for k, p in model.named_parameters() if p.grad is None])
+    path = os.path.join(GOLDEN_DIR, "cpromg_transformer.pt")
+    torch.save(fixture, path)
+    print(path, "out", tuple(out.shape), os.path.getsize(path), "bytes; no grad:", fixture["params_without_grad"])
+
+
 if __name__ == "__main__":
-    main()
+    if "--attention" in sys.argv:
+        main()
+    main_transformer()

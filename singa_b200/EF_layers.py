@@ -902,6 +902,14 @@ def _edge_csr(edge_index: Tensor, num_src: int, num_dst: int):
     return csr
 
 
+def register_edge_csr(edge_index: Tensor, num_src: int, num_dst: int, csr) -> None:
+    """Attach a PREBUILT destination-sorted CSR (``ops.EdgeCSR`` with its chunk plan) to an edge_index tensor, so the
+    edge modules skip the sort and its device->host read: graphs that come out of ``radius.radius_graph_csr`` or out
+    of the CSR-carrying dataset format (singa_b200/dataset.py) are already grouped by destination."""
+    assert csr.num_edges == edge_index.shape[1] and csr.num_src == num_src and csr.num_dst == num_dst
+    _csr_store(_csr_key(edge_index, num_src, num_dst), edge_index, csr)
+
+
 def prefetch_edge_csr(specs) -> None:
     """Build the CSRs of several edge lists ``[(edge_index, num_src, num_dst), ...]`` ahead of their first use with
     one device->host read for all of them (ops.build_csr_many); later ``_edge_csr`` calls hit the cache.  A caller
@@ -1192,9 +1200,14 @@ class TransBlockV2(nn.Module):
         if isinstance(x, dict):
             source, target = source_target
             residual = x[target].embedding
-            x[source].embedding = self.norm_1(x[source].embedding)
-            x[target].embedding = self.norm_1(x[target].embedding)
+            # The caller keeps the two normalised tensors (the reference mutates its dict, :1356-1357) and the
+            # reference caller later adds to them IN PLACE (Embedding.py:457, 477-478).  The fused edge path saves its
+            # node inputs for backward, so it gets private tensors and the dict gets copies that are safe to mutate
+            # (found by tests/test_gpu_boundary.py: "modified by an inplace operation").
+            xs, xt = self.norm_1(x[source].embedding), self.norm_1(x[target].embedding)
+            x[source].embedding, x[target].embedding = xs, xt
             out = self.ga(x, atomic_numbers, edge_distance, edge_index, hetero, source_target)
+            x[source].embedding, x[target].embedding = xs.clone(), xt.clone()
         else:
             residual = x.embedding
             x.embedding = self.norm_1(x.embedding)

@@ -55,6 +55,7 @@ SIGNATURES = {
     "efl_radius_graph_count": "ppiipfiiifiippppppppl" "p",
     "efl_radius_graph_fill": "iifiiifippppp" "ip",
     "efl_radius_graph_emit": "pppilpip",
+    "efl_knn_graph": "ppiipfiiiiipppppppppl" "p",
     "efl_csr_from_edge_index": "ppiiipppppppp" "plpp",
     "efl_rmsnorm_sh_fwd": "iipppfpip",
     "efl_rmsnorm_sh_bwd": "iippfpppiip",

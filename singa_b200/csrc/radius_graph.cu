@@ -241,6 +241,126 @@ __global__ void emit_kernel(const int* __restrict__ rowptr_full, const int* __re
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// knn_graph on the same cell list (reference call sites model/CProMG.py:293, 330:
+// knn_graph(pos, k, batch=batch, flow='target_to_source'), torch-cluster 1.6.3, un-vendored).
+// One warp per query point.  The warp keeps its K best (distance, index) pairs as sorted 64-bit keys
+// (fp32 distance bits << 32 | source index: non-negative floats order like their bit patterns, ties go to the
+// smaller index) in shared memory, followed by a staging area for new candidates; when the staging area fills, the
+// whole buffer is bitonic-sorted and cut back to K.  Cells are visited in shells of growing Chebyshev radius around
+// the query's cell; after shell r every point closer than r * cs is known, so the search stops as soon as the K-th
+// best distance is inside that radius (or the shell has left the batch item's grid).  Distances use the radius
+// kernel's separately rounded fp32 expression.  Output nbr [N, K] (ascending distance, -1 padded) and cnt [N].
+// ---------------------------------------------------------------------------------------------------
+constexpr int KNN_BUF = 256;           // keys per warp: K best + staging (K <= 64)
+constexpr int KNN_WARPS = 4;
+
+__device__ __forceinline__ void knn_sort(unsigned long long* b, int lane) {
+  // bitonic sort of KNN_BUF keys by one warp
+  for (int k = 2; k <= KNN_BUF; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = lane; t < (KNN_BUF >> 1); t += 32) {
+        const int lo = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+        const int hi = lo | j;
+        const bool up = (lo & k) == 0;
+        const unsigned long long a = b[lo], c = b[hi];
+        if ((a > c) == up) { b[lo] = c; b[hi] = a; }
+      }
+      __syncwarp();
+    }
+  }
+}
+
+__global__ void __launch_bounds__(32 * KNN_WARPS) knn_kernel(const float4* __restrict__ sorted, int n,
+                                                             const int* __restrict__ cell_of,
+                                                             const int* __restrict__ cell_start, Grid g, float cs,
+                                                             int K, int loop, int* __restrict__ nbr,
+                                                             int* __restrict__ cnt) {
+  __shared__ unsigned long long buf[KNN_WARPS][KNN_BUF];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int s = blockIdx.x * KNN_WARPS + warp;
+  if (s >= n) return;
+  unsigned long long* b = buf[warp];
+  const unsigned long long EMPTY = ~0ull;
+  for (int t = lane; t < KNN_BUF; t += 32) b[t] = EMPTY;
+  __syncwarp();
+  const float4 me = sorted[s];
+  const int i = __float_as_int(me.w);
+  const int c = cell_of[i];
+  const int cx = c % g.nx, cy = (c / g.nx) % g.ny, cz = (c / (g.nx * g.ny)) % g.nz, bi = c / (g.nx * g.ny * g.nz);
+  int fill = K;                       // next free staging slot (warp-uniform)
+  unsigned long long kth = EMPTY;     // current K-th best key (warp-uniform): worse candidates are dropped at once
+  const int rmax = max(max(max(cx, g.nx - 1 - cx), max(cy, g.ny - 1 - cy)), max(cz, g.nz - 1 - cz));
+  for (int r = 0; r <= rmax; ++r) {
+    for (int dz = -r; dz <= r; ++dz) {
+      const int z = cz + dz;
+      if (z < 0 || z >= g.nz) continue;
+      for (int dy = -r; dy <= r; ++dy) {
+        const int y = cy + dy;
+        if (y < 0 || y >= g.ny) continue;
+        const bool face = (dz == -r || dz == r || dy == -r || dy == r);
+        // rows on the shell's faces take the whole x range; interior rows only the two end cells
+        for (int part = 0; part < (face || r == 0 ? 1 : 2); ++part) {
+          int x0, x1;
+          if (face || r == 0) { x0 = max(cx - r, 0); x1 = min(cx + r, g.nx - 1); }
+          else { x0 = x1 = part == 0 ? cx - r : cx + r; if (x0 < 0 || x0 >= g.nx) continue; }
+          const int base = ((bi * g.nz + z) * g.ny + y) * g.nx;
+          const int q0 = cell_start[base + x0], q1 = cell_start[base + x1 + 1];
+          for (int qb = q0; qb < q1; qb += 32) {
+            const int q = qb + lane;
+            unsigned long long key = EMPTY;
+            if (q < q1) {
+              const float4 o = __ldg(sorted + q);
+              const float ddx = __fsub_rn(me.x, o.x), ddy = __fsub_rn(me.y, o.y), ddz = __fsub_rn(me.z, o.z);
+              const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy)), __fmul_rn(ddz, ddz));
+              if (loop || q != s)
+                key = ((unsigned long long)__float_as_uint(d2) << 32) | (unsigned)__float_as_int(o.w);
+            }
+            const bool take = key < kth;
+            const unsigned m = __ballot_sync(0xffffffffu, take);
+            const int nnew = __popc(m);
+            if (nnew == 0) continue;
+            if (fill + nnew > KNN_BUF) {      // staging full: sort, keep the K best, refresh the threshold
+              knn_sort(b, lane);
+              for (int t = K + lane; t < KNN_BUF; t += 32) b[t] = EMPTY;
+              __syncwarp();
+              fill = K;
+              kth = b[K - 1];
+            }
+            if (take && key < kth) b[fill + __popc(m & ((1u << lane) - 1))] = key;
+            fill += nnew;                      // slots of candidates rejected by the refreshed threshold stay EMPTY
+            __syncwarp();
+          }
+        }
+      }
+    }
+    // shell r done: every point closer than r * cs has been seen
+    knn_sort(b, lane);
+    for (int t = K + lane; t < KNN_BUF; t += 32) b[t] = EMPTY;
+    __syncwarp();
+    fill = K;
+    kth = b[K - 1];
+    if (kth != EMPTY) {
+      const float covered = (float)r * cs * 0.999f;   // margin for the rounding of the cell assignment
+      const float d2k = __uint_as_float((unsigned)(kth >> 32));
+      if (d2k < covered * covered) break;
+    }
+  }
+  int have = 0;
+  for (int t = lane; t < K; t += 32) {
+    const unsigned long long key = b[t];
+    nbr[(size_t)i * K + t] = key == EMPTY ? -1 : (int)(unsigned)(key & 0xffffffffu);
+    have += key != EMPTY;
+  }
+  have = __reduce_add_sync(0xffffffffu, have);
+  if (lane == 0) cnt[i] = have;
+}
+
+__global__ void knn_rowptr_full_kernel(int n, int K, int* __restrict__ rowptr_full) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i <= n) rowptr_full[i] = i * K;
+}
+
 }  // namespace rg
 }  // namespace efl
 
@@ -334,6 +454,40 @@ extern "C" int efl_radius_graph_emit(const int* rowptr_full, const int* rowptr_c
   if (N <= 0 || E <= 0) return EFL_OK;
   rg::emit_kernel<<<nblk((long long)N * 32, 256), 256, 0, (cudaStream_t)stream>>>(rowptr_full, rowptr_cap, col, N, E,
                                                                                edge_index, flow_target_to_source);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+// knn_graph, steps after the bounding boxes (efl_radius_graph_bbox): bin + scan + scatter into the cell list, then
+// the K nearest neighbours of every point inside its batch item.  Buffers as efl_radius_graph_count plus
+// nbr [N*K] ints, cnt [N+1] ints (cnt[N] is set to 0), rowptr_full [N+1] (= i*K), rowptr [N+1] (exclusive scan of cnt).
+// efl_radius_graph_emit(rowptr_full, rowptr, nbr, N, E, edge_index, flow) then writes the int64 edge list.
+extern "C" int efl_knn_graph(const float* pos, const int* batch, int N, int nbatch, const float* origin, float cs,
+                             int nx, int ny, int nz, int K, int loop, int* cell_of, int* cell_start, int* scratch,
+                             void* sorted, int* nbr, int* cnt, int* rowptr_full, int* rowptr, void* temp,
+                             long long temp_bytes, void* stream) {
+  EFL_REQUIRE(N > 0 && nbatch > 0 && nx > 0 && ny > 0 && nz > 0, "efl_knn_graph: empty input");
+  EFL_REQUIRE(K >= 1 && K <= 64, "efl_knn_graph: k must be in [1, 64]");
+  EFL_REQUIRE(cs > 0.f, "efl_knn_graph: cell edge must be positive");
+  const long long ncells_ll = (long long)nbatch * nx * ny * nz;
+  EFL_REQUIRE(ncells_ll < (1ll << 30), "efl_knn_graph: too many cells");
+  EFL_REQUIRE((long long)N * K < (1ll << 31), "efl_knn_graph: N * k overflows int");
+  const int ncells = (int)ncells_ll;
+  cudaStream_t s = (cudaStream_t)stream;
+  Grid g{1.0f / cs, nx, ny, nz, nbatch};
+  int* cell_count = scratch;
+  int* cursor = scratch + (ncells + 1);
+  cudaMemsetAsync(scratch, 0, sizeof(int) * 2 * (size_t)(ncells + 1), s);
+  rg::bin_kernel<<<nblk(N, 256), 256, 0, s>>>(pos, batch, N, origin, g, cell_of, cell_count);
+  size_t tb = (size_t)temp_bytes;
+  cub::DeviceScan::ExclusiveSum(temp, tb, cell_count, cell_start, ncells + 1, s);
+  rg::scatter_kernel<<<nblk(N, 256), 256, 0, s>>>(pos, N, cell_of, cell_start, cursor, (float4*)sorted);
+  cudaMemsetAsync(cnt + N, 0, sizeof(int), s);
+  rg::knn_kernel<<<nblk(N, rg::KNN_WARPS), 32 * rg::KNN_WARPS, 0, s>>>((const float4*)sorted, N, cell_of, cell_start, g,
+                                                                     cs, K, loop, nbr, cnt);
+  rg::knn_rowptr_full_kernel<<<nblk(N + 1, 256), 256, 0, s>>>(N, K, rowptr_full);
+  tb = (size_t)temp_bytes;
+  cub::DeviceScan::ExclusiveSum(temp, tb, cnt, rowptr, N + 1, s);
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }

@@ -157,7 +157,9 @@ class EquivariantEmbedding(nn.Module):
 
     def _seed_nodes(self, z, feats):
         x = SO3_Embedding(len(z), self.lmax_list, self.sphere_channels, device=z.device, dtype=torch.long)
-        seed = self.sphere_embedding(z) + self.sphere_embedding_2(pack_feature_bits(feats))
+        # feats: the [N, 59] feature rows, or the already packed integer codes of the dataset format (dataset.py)
+        bits = feats if feats.dim() == 1 else pack_feature_bits(feats)
+        seed = self.sphere_embedding(z) + self.sphere_embedding_2(bits)
         x.embedding[:, self.offset_res, :] = seed  # float -> int64: truncation, no gradient (Embedding.py:262)
         return x
 

@@ -1,0 +1,86 @@
+"""``SINGA`` = EquivariantEmbedding + CProMG Transformer (reference model/GAN.py:12-81), B200 side.
+
+Same constructor and the same two children (``embedding``, ``model``), so a reference checkpoint loads unchanged.
+``forward`` differs from the reference where the reference stalls the device (each difference equal element for
+element to what it replaces, tests/test_host_logic.py):
+
+* property matrix: ``stack_props`` instead of ``torch.tensor(list(zip(...)))`` (GAN.py:42: one host round trip per
+  element);
+* node -> complex vectors: ``batch_vector_from_ptr`` instead of a Python ``extend`` per complex (GAN.py:48-55: one
+  device read per complex);
+* Laplacian positional encodings come with the batch (``lap_p`` / ``lap_l``, computed once per complex by the
+  dataset format) instead of a PyG->DGL conversion plus a CPU eigendecomposition of the batched graph on every
+  forward (GAN.py:70, 77; CProMG.py:562-571).  For one complex the two are the same quantity; for a batch the
+  reference decomposes the disjoint union, whose lowest modes are component indicators - per-complex encodings are
+  what the featuriser means.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from .cpromg import Transformer
+from .embedding import EquivariantEmbedding, batch_vector_from_ptr, stack_props
+from .synthetic import LIGAND, PROTEIN
+
+
+class _Cfg(dict):
+    def __init__(self, d=None, **kw):
+        super().__init__()
+        for k, v in dict(d or {}, **kw).items():
+            self[k] = _Cfg(v) if isinstance(v, dict) else v
+
+    def __getattr__(self, k):
+        try:
+            return self[k]
+        except KeyError as e:
+            raise AttributeError(k) from e
+
+
+def default_config() -> _Cfg:
+    """config/train.yml:27-103 without the vocabulary strings: 116 tokens, '^' (padding) at index 110."""
+    from .embedding import DEFAULT_CONFIG
+    enc = dict(name="cftfm", hidden_channels=256, edge_channels=64, key_channels=128, num_heads=4, num_interactions=6,
+               cutoff=10.0, knn=48, lap_dim=8)
+    dec = dict(tgt_len=200, hidden_channels=256, key_channels=128, num_heads=4, num_interactions=6, padding="right",
+               vocab_size=116, pad_index=110)
+    return _Cfg(embedding=dict(DEFAULT_CONFIG),
+                model=dict(name="SINGA", hidden_channels=256, featurizer_feat_dim=784, encoder=enc, decoder=dec),
+                train=dict(num_props=3, prop=["vina_score", "qed", "sas"], batch_size=64, max_grad_norm=float("inf"),
+                           optimizer=dict(type="adam", lr=1e-4, weight_decay=0, beta1=0.99, beta2=0.999)))
+
+
+class SINGA(nn.Module):
+    def __init__(self, config, device='cuda'):
+        super().__init__()
+        self.device = device
+        self.config = config if isinstance(config, _Cfg) else _Cfg(config)
+        self.embedding = EquivariantEmbedding(config=self.config.embedding, device=self.device)
+        self.model = Transformer(config=self.config.model, protein_atom_feature_dim=self.config.model.featurizer_feat_dim,
+                                 num_props=self.config.train.num_props, device=self.device)
+
+    def properties(self, lig) -> torch.Tensor:
+        """Binarised ligand properties in the configured order (GAN.py:27-44)."""
+        dic = {k: lig[k] for k in ("sas", "logP", "qed", "weight", "tpsa", "vina_score")}
+        dic["vina_score"] = torch.lt(dic["vina_score"], -7.5).float()
+        dic["qed"] = torch.gt(dic["qed"], 0.6).float()
+        dic["sas"] = torch.lt(dic["sas"], 4.0).float()
+        return stack_props(dic, self.config.train.prop)
+
+    def forward(self, g, sizes=None, frames=None):
+        """g: HeteroData-like (synthetic.GraphView over a collated batch).  ``sizes`` = dict(batch_size, max_atoms,
+        max_aa) from the collated batch's host metadata (avoids two device reads); ``frames`` as EquivariantEmbedding."""
+        lig = g["ligand_data"]
+        prop = self.properties(lig).to(self.device) if self.config.train.num_props else None
+        ptr_p, ptr_l = g[PROTEIN]["ptr"], g[LIGAND]["ptr"]
+        n_p, n_l = len(g[PROTEIN]["pos"]), len(g[LIGAND]["pos"])
+        batch = batch_vector_from_ptr(ptr_p, num_nodes=n_p, device=self.device)
+        batch_aa = batch_vector_from_ptr(ptr_l, num_nodes=n_l, device=self.device)
+        embed = self.embedding(g, frames=frames)
+        dim = self.config.model.featurizer_feat_dim
+        protein = embed[PROTEIN].embedding.view(-1, dim)
+        ligand = embed[LIGAND].embedding.view(-1, dim)
+        return self.model(node_attr=protein, pos=g[PROTEIN]["pos"], batch=batch, atom_laplacian=g[PROTEIN]["lap"],
+                          smiles_index=lig["smiIndices_input"], tgt_len=self.config.model.decoder.tgt_len,
+                          aa_node_attr=ligand, aa_pos=g[LIGAND]["pos"], aa_batch=batch_aa,
+                          aa_laplacian=g[LIGAND]["lap"], prop=prop, sizes=sizes)

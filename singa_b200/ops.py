@@ -30,6 +30,9 @@ _SAVE_POLICY = os.environ.get("EFL_SAVE_POLICY", "auto")
 _SAVE_FREE_FRACTION = float(os.environ.get("EFL_SAVE_FREE_FRACTION", "0.45"))
 
 
+STATS = {"save": 0, "recompute": 0}   # edge-attention forwards that kept / will recompute their edge activations
+
+
 def set_save_policy(mode: str) -> None:
     global _SAVE_POLICY
     if mode not in ("auto", "save", "recompute"):
@@ -108,6 +111,26 @@ class EdgeCSR:
     src_ptr: torch.Tensor     # int32 [num_src + 1]
     src_idx: torch.Tensor     # int32 [E]  sorted positions grouped by source (stable)
     chunks: list = field(default_factory=list)  # (n0, n1, e0, e1), edges of whole destinations
+    aux: dict = field(default_factory=dict)     # lazily derived index vectors (int64 copies, composite groupings)
+
+    def index(self, name: str) -> torch.Tensor:
+        """int64 index vectors for torch gathers: 'perm', 'dst_orig', 'src_orig' (original edge order) and
+        'src_group' (original edge ids grouped by source, aligned with src_ptr)."""
+        hit = self.aux.get(name)
+        if hit is None:
+            if name == "perm":
+                hit = self.perm.long()
+            elif name == "dst_orig":
+                hit = self.dst_orig.long()
+            elif name == "src_orig":
+                hit = torch.empty_like(self.index("perm"))
+                hit[self.index("perm")] = self.src_sorted.long()
+            elif name == "src_group":
+                hit = self.perm.index_select(0, self.src_idx.long()).contiguous()   # int32
+            else:
+                raise KeyError(name)
+            self.aux[name] = hit
+        return hit
 
 
 def _launch_csr(edge_index: torch.Tensor, num_src: int, num_dst: int):
@@ -434,6 +457,7 @@ class EdgeAttentionFunction(torch.autograd.Function):
         es = 4 if dtype == torch.float32 else 2
         save = (any(ctx.needs_input_grad) and E > 0
                 and _should_save(E * _Workspace.forward_bytes_per_edge(d, es), dev))
+        STATS["save" if save else "recompute"] += 1
         ws = None if save else _Workspace(d, maxE, dtype, dev)
         w1 = _Weights([c1w0, c1b0, c1w1, c1w2], dtype, need_t=False)
         w2 = _Weights([c2w0, c2b0, c2w1, c2w2], dtype, need_t=False)
@@ -1113,3 +1137,149 @@ class RMSNormSHFunction(torch.autograd.Function):
              work=3.0 * x.numel() * 4)
         tot = part.sum(dim=0)
         return dx, tot[:(lmax + 1) * C].view(lmax + 1, C), tot[(lmax + 1) * C:], None, None
+
+
+# ---------------------------------------------------------------------------
+# generic deterministic segment ops over an EdgeCSR (CProMG message passing)
+# ---------------------------------------------------------------------------
+class SegmentSoftmaxFunction(torch.autograd.Function):
+    """torch_scatter.scatter_softmax(src, index, dim=0) with index = the CSR's destination of every edge
+    (reference model/CProMG.py:69).  logits [E, H] in ORIGINAL edge order; one warp per destination over the sorted
+    CSR, no atomics (csrc/attention.cu).  The kernel's 1e-16 in the denominator (pyg's softmax, EF_layers.py:1180)
+    is below one ulp of a sum that is always >= 1, so the result equals scatter_softmax bit for bit."""
+
+    @staticmethod
+    def forward(ctx, logits, csr):
+        check_cuda(logits)
+        E, H = logits.shape
+        assert E == csr.num_edges, "logits rows must match the edge list"
+        perm = csr.index("perm")
+        ls = logits.detach().float().index_select(0, perm).contiguous()
+        alpha_s = torch.empty_like(ls)
+        if E > 0:
+            call("efl_segment_softmax_fwd", ptr(ls), H, ptr(csr.rowptr), ptr(alpha_s), 0, csr.num_dst,
+                 work=E * H * 8.0)
+        ctx.save_for_backward(alpha_s)
+        ctx.csr = csr
+        out = torch.empty_like(alpha_s)
+        out.index_copy_(0, perm, alpha_s)
+        return out
+
+    @staticmethod
+    def backward(ctx, dalpha):
+        (alpha_s,) = ctx.saved_tensors
+        csr = ctx.csr
+        E, H = alpha_s.shape
+        perm = csr.index("perm")
+        da_s = dalpha.float().index_select(0, perm).contiguous()
+        dl_s = torch.empty_like(da_s)
+        if E > 0:
+            call("efl_segment_softmax_bwd", ptr(alpha_s), ptr(da_s), 1, 0, H, ptr(csr.rowptr), ptr(dl_s), 0, csr.num_dst,
+                 work=E * H * 12.0)
+        out = torch.empty_like(dl_s)
+        out.index_copy_(0, perm, dl_s)
+        return out, None
+
+
+class SegmentSumFunction(torch.autograd.Function):
+    """torch_scatter.scatter_sum(src, index, dim=0, dim_size=N) (CProMG.py:76): values [E, D] in original edge order
+    -> [num_dst, D], fixed summation order per destination (efl_segment_sum_rows), zero rows for empty segments."""
+
+    @staticmethod
+    def forward(ctx, values, csr):
+        check_cuda(values)
+        values = values.contiguous().float()
+        E, D = values.shape
+        assert E == csr.num_edges, "value rows must match the edge list"
+        out = torch.empty(csr.num_dst, D, dtype=torch.float32, device=values.device)
+        call("efl_segment_sum_rows", ptr(values), 1, D, 0, D, ptr(csr.rowptr), ptr(csr.perm), ptr(out), csr.num_dst, 0,
+             work=(E + csr.num_dst) * D * 4.0)
+        ctx.csr = csr
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        return dout.index_select(0, ctx.csr.index("dst_orig")), None
+
+
+class GatherRowsFunction(torch.autograd.Function):
+    """h[index of every edge] with side = 'src' | 'dst' (CProMG.py:64-65: h_keys[col], h_queries[row]).  The backward
+    is the deterministic segment sum over that side's grouping instead of torch's atomic index_add_."""
+
+    @staticmethod
+    def forward(ctx, h, csr, side):
+        check_cuda(h)
+        assert side in ("src", "dst")
+        ctx.csr, ctx.side, ctx.rows = csr, side, h.shape[0]
+        return h.index_select(0, csr.index("src_orig" if side == "src" else "dst_orig"))
+
+    @staticmethod
+    def backward(ctx, dout):
+        csr, side = ctx.csr, ctx.side
+        dout = dout.contiguous().float()
+        E, D = dout.shape
+        dh = torch.empty(ctx.rows, D, dtype=torch.float32, device=dout.device)
+        if side == "dst":
+            seg, idx = csr.rowptr, csr.perm
+        else:
+            seg, idx = csr.src_ptr, csr.index("src_group")
+        call("efl_segment_sum_rows", ptr(dout), 1, D, 0, D, ptr(seg), ptr(idx), ptr(dh), ctx.rows, 0,
+             work=(E + ctx.rows) * D * 4.0)
+        return dh, None, None
+
+
+class LinearFunction(torch.autograd.Function):
+    """y = x W^T + b on the library's GEMMs: fp32 SIMT in accuracy mode, tcgen05 (bf16 operands, fp32 accumulate and
+    output) in bf16 mode; wgrad through the deterministic split-K TN GEMM.  x [M, K], W [N, K], b [N] or None."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        check_cuda(x, weight)
+        x = x.contiguous().float()
+        M, K = x.shape
+        N = weight.shape[0]
+        tc = _PRECISION != "fp32" and K % 8 == 0 and N % 16 == 0 and M > 0
+        dt = torch.bfloat16 if tc else torch.float32
+        xa = x.to(dt)
+        w = weight.detach().to(dt).contiguous()
+        b = None if bias is None else bias.detach().float().contiguous()
+        out = torch.empty(M, N, dtype=torch.float32, device=x.device)
+        if M > 0:
+            if tc:
+                _gemm_nt(1, xa, w, b, out, 8, out, N, N, M, N, K)
+            else:
+                _gemm_nt(0, xa, w, b, out, N, None, 0, 0, M, N, K)
+        ctx.save_for_backward(xa, w)
+        ctx.has_bias = bias is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        xa, w = ctx.saved_tensors
+        M, K = xa.shape
+        N = w.shape[0]
+        tc = xa.dtype == torch.bfloat16
+        dy = dout.contiguous().to(xa.dtype)
+        dx = dw = db = None
+        if M == 0:
+            return (torch.zeros(M, K, device=xa.device), torch.zeros(N, K, device=xa.device),
+                    torch.zeros(N, device=xa.device) if ctx.has_bias else None)
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(M, K, dtype=torch.float32, device=xa.device)
+            wt = w.t().contiguous()
+            if tc and K % 16 == 0 and N % 8 == 0:
+                _gemm_nt(1, dy, wt, None, dx, 8, dx, K, K, M, K, N)
+            elif tc:
+                _gemm_nt(0, dy.float(), wt.float(), None, dx, K, None, 0, 0, M, K, N)
+            else:
+                _gemm_nt(0, dy, wt, None, dx, K, None, 0, 0, M, K, N)
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty(N, K, dtype=torch.float32, device=xa.device)
+            if tc and K % 16 == 0:
+                _gemm_tn(dy, xa, dw, False, M, N, K)
+            else:
+                _gemm_tn(dy.float(), xa.float(), dw, False, M, N, K)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = torch.empty(N, dtype=torch.float32, device=xa.device)
+            _colsum(dy, M, N, db, False)
+        return dx, dw, db

@@ -58,6 +58,24 @@ def portable_parameters(named_shapes, seed: int = 0) -> dict:
     return out
 
 
+def load_portable_parameters_fanin(module: torch.nn.Module, seed: int = 0) -> None:
+    """Portable values for modules outside the EF_layers naming scheme (the CProMG transformer): >= 2-D tensors
+    ~ U(+-1/sqrt(fan_in)) with fan_in = prod(shape[1:]) (Linear, grouped Conv1d, Embedding), 1-D ``weight`` (norm
+    gains) ~ 1 + U(+-0.2), other 1-D tensors ~ U(+-0.1).  Buffers keep their constructor values."""
+    with torch.no_grad():
+        for name, p in module.named_parameters():
+            rs = np.random.RandomState((seed * 1000003 + zlib.crc32(name.encode())) % (2 ** 32))
+            shape = tuple(p.shape)
+            if len(shape) >= 2:
+                b = 1.0 / np.sqrt(float(np.prod(shape[1:])))
+                v = rs.uniform(-b, b, size=shape)
+            elif name.rsplit(".", 1)[-1] == "weight":
+                v = 1.0 + rs.uniform(-0.2, 0.2, size=shape)
+            else:
+                v = rs.uniform(-0.1, 0.1, size=shape)
+            p.copy_(torch.from_numpy(np.ascontiguousarray(v, dtype=np.float32)).to(p.device))
+
+
 def load_portable_parameters(module: torch.nn.Module, seed: int = 0) -> None:
     vals = portable_parameters(((n, p.shape) for n, p in module.named_parameters()), seed)
     with torch.no_grad():
@@ -171,10 +189,15 @@ class GraphView:
         g = self._g
         if key == "atomicnum":
             return {PROTEIN: g["z_p"], LIGAND: g["z_l"]}
-        if key == PROTEIN:
-            return {"x": g["x_p"], "pos": g["pos_p"]}
+        if key == PROTEIN:   # "x": feature rows, or their packed integer codes (dataset format)
+            return {"x": g["x_p"] if "x_p" in g else g["bits_p"], "pos": g["pos_p"], "ptr": g.get("ptr_p"),
+                    "lap": g.get("lap_p")}
         if key == LIGAND:
-            return {"x": g["x_l"], "pos": g["pos_l"]}
+            return {"x": g["x_l"] if "x_l" in g else g["bits_l"], "pos": g["pos_l"], "ptr": g.get("ptr_l"),
+                    "lap": g.get("lap_l")}
+        if key == "ligand_data":
+            return {"sas": g["sas"], "logP": g["logP"], "qed": g["qed"], "weight": g["weight"], "tpsa": g["tpsa"],
+                    "vina_score": g["vina_score"], "smiIndices_input": g["smi_in"], "smiIndices_tgt": g["smi_tgt"]}
         table = {PP: "ei_pp", LL: "ei_ll", LP: "ei_lp", PL: "ei_pl"}
         if key in table:
             return {"edge_index": g[table[key]]}

@@ -1,0 +1,133 @@
+"""CProMG side on the host: the mirror of model/CProMG.py in singa_b200/cpromg.py against the
+golden written by the UNMODIFIED reference ``Transformer`` (oracle/make_golden_cpromg.py -> cpromg_transformer.pt).
+
+The message-passing ops have no CPU path (they are CUDA kernels); here they are stood in for by the oracle
+(oracle/cpromg_oracle.py, test infrastructure) so that everything AROUND them -- module wiring, parameter names,
+graph assembly, masks, decoder -- is checked where no GPU exists.  tests/test_gpu_cpromg.py runs the same golden
+through the real kernels."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import cpromg_oracle as co
+from singa_b200 import cpromg as cp
+from singa_b200 import synthetic as syn
+from tests.parity_util import digest_err, load_golden, rel_err
+
+
+class _StubCSR:
+    def __init__(self, edge_index, n):
+        self.row, self.col, self.n = edge_index[0], edge_index[1], n
+
+
+@pytest.fixture
+def oracle_edge_ops(monkeypatch):
+    monkeypatch.setattr(cp, "_build_centre_csr", lambda ei, n: _StubCSR(ei, n))
+    monkeypatch.setattr(cp, "segment_softmax", lambda logits, csr: co.scatter_softmax(logits, csr.row, csr.n))
+    monkeypatch.setattr(cp, "segment_sum", lambda v, csr: co.scatter_sum(v, csr.row, csr.n))
+    monkeypatch.setattr(cp, "gather_rows", lambda h, csr, side: h[csr.col if side == "src" else csr.row])
+    monkeypatch.setattr(cp, "edge_linear", lambda x, lin: F.linear(x, lin.weight, lin.bias))
+    import singa_b200.radius as radius
+    monkeypatch.setattr(radius, "knn_graph", lambda x, k, batch=None, flow="source_to_target", **kw:
+                        co.knn_graph(x, k, batch=batch, flow=flow))
+    cp._CSR_CACHE.clear()
+    yield
+    cp._CSR_CACHE.clear()
+
+
+def _build(fx, device="cpu"):
+    cfg = cp_cfg(fx)
+    torch.manual_seed(0)
+    model = cp.Transformer(cfg, 784, num_props=3, device=device).eval()
+    syn.load_portable_parameters_fanin(model, fx["param_seed"])
+    return model
+
+
+def grad_errors(params, fx):
+    """Digest errors of every parameter gradient.  weight_k_lin.bias shifts all logits of a centre by the same amount
+    (q_i . b), which the per-centre softmax cancels: its gradient is zero up to rounding noise in the reference too,
+    so it is checked to be noise (<= 1e-6), not compared digit for digit."""
+    out = {}
+    for n, d in fx["d_params"].items():
+        if n.endswith("weight_k_lin.bias") or n.endswith("W_K.bias"):   # key biases: cancelled by the softmax
+            ref_max = float(d["full"].abs().max()) if "full" in d else float(d["sample"].abs().max())
+            assert ref_max < 1e-5, (n, ref_max)
+            out[n] = 0.0 if float(params[n].grad.abs().max()) < 1e-4 else 1.0
+        else:
+            out[n] = digest_err(params[n].grad, d)
+    return out
+
+
+def cp_cfg(fx):
+    from singa_b200.gan import _Cfg
+    cfg = _Cfg(fx["cfg"])
+    cfg.decoder["vocab_size"] = fx["vocab_size"]
+    cfg.decoder["pad_index"] = fx["pad_index"]
+    return cfg
+
+
+def test_state_dict_surface_matches_reference_transformer():
+    fx = load_golden("cpromg_transformer.pt")
+    sd = _build(fx).state_dict()
+    assert set(sd) == set(fx["surface"]), set(sd) ^ set(fx["surface"])
+    for k, (shape, dtype) in fx["surface"].items():
+        assert list(sd[k].shape) == shape and str(sd[k].dtype) == dtype, k
+
+
+def test_transformer_wiring_matches_reference_golden(oracle_edge_ops):
+    fx = load_golden("cpromg_transformer.pt")
+    model = _build(fx)
+    inp = {k: (v.clone() if torch.is_tensor(v) else v) for k, v in fx["inputs"].items()}
+    for k in ("node_attr", "aa_node_attr"):
+        inp[k].requires_grad_(True)
+    out = model(**inp)
+    assert rel_err(out, fx["out"]) < 2e-5, rel_err(out, fx["out"])
+    (out * fx["loss_weights"]).sum().backward()
+    assert rel_err(inp["node_attr"].grad, fx["d_node_attr"]) < 2e-4
+    assert rel_err(inp["aa_node_attr"].grad, fx["d_aa_node_attr"]) < 2e-4
+    params = dict(model.named_parameters())
+    bad = grad_errors(params, fx)
+    bad = {n: e for n, e in bad.items() if e > 5e-4}
+    assert not bad, bad
+    assert sorted(n for n, p in params.items() if p.grad is None) == sorted(fx["params_without_grad"])
+
+
+def test_graph_assembly_matches_the_loop_restatements():
+    """to_undirected(mean) / to_dense_batch: sort-based device code vs the loop restatements of the pyg utilities."""
+    rs = np.random.RandomState(3)
+    n = 23
+    pos = torch.from_numpy(rs.uniform(-4, 4, size=(n, 3)).astype(np.float32))
+    batch = torch.from_numpy(np.repeat([0, 1, 2], [9, 1, 13]))
+    di = co.knn_graph(pos, 4, batch=batch, flow="target_to_source")
+    length = (pos[di[0]] - pos[di[1]]).norm(dim=1)
+    ei_a, at_a = cp.to_undirected(di, length, n, reduce="mean")
+    ei_b, at_b = co.to_undirected(di, length, reduce="mean")
+    assert torch.equal(ei_a, ei_b) and torch.allclose(at_a, at_b, rtol=0, atol=1e-7)
+    x = torch.from_numpy(rs.normal(size=(n, 5)).astype(np.float32))
+    da, ma = cp.to_dense_batch(x, batch, 3, 13)
+    db, mb = co.to_dense_batch(x, batch)
+    assert torch.equal(da, db) and torch.equal(ma, mb)
+
+
+def test_laplacian_pe_is_an_eigenbasis_and_is_cached():
+    """dgl.lap_pe restated: columns are eigenvectors 1..k of I - D^-1/2 A D^-1/2 (up to sign), orthonormal; the cache
+    computes a complex once."""
+    g = syn.make_complex(3, n_protein=60, n_ligand=12)
+    ei = g["ei_pp"].numpy()
+    n = 60
+    cache = cp.LapPECache(8)
+    pe = cache.get(("c", 3), ei, n)
+    assert pe.shape == (n, 8) and cache.misses == 1
+    assert cache.get(("c", 3), ei, n) is pe and cache.hits == 1
+    A = np.zeros((n, n)); A[ei[1], ei[0]] = 1
+    d = np.clip(A.sum(1), 1, None) ** -0.5
+    L = np.eye(n) - d[:, None] * A * d[None, :]
+    val = np.sort(np.linalg.eigvalsh(L))
+    for j in range(8):
+        v = pe[:, j].astype(np.float64)
+        lam = v @ L @ v / (v @ v)
+        assert abs(lam - val[j + 1]) < 1e-5, (j, lam, val[j + 1])
+    assert np.allclose(pe.T @ pe, np.eye(8), atol=1e-4)
+    small = cp.laplacian_pe(np.array([[0, 1], [1, 0]]), 2, 8)       # fewer nodes than k: zero padded
+    assert small.shape == (2, 8) and np.all(small[:, 1:] == 0)

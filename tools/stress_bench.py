@@ -18,7 +18,7 @@ from singa_b200 import _lib, ops
 from singa_b200 import synthetic as syn
 from singa_b200.embedding import DEFAULT_CONFIG, EquivariantEmbedding
 from singa_b200.parallel import GradientBuckets
-from singa_b200.radius import radius_graph
+from singa_b200.radius import edge_csr_from_radius, radius_graph_csr
 
 
 def ball(rs, n, radius):
@@ -56,8 +56,11 @@ def make_batch(rank, complexes, atoms, dev, cutoff=8.0, contact=4.0, density=0.0
     g = {k: torch.from_numpy(v).to(dev) for k, v in g.items()}
     bpt = torch.from_numpy(np.concatenate(bp)).to(dev)
     blt = torch.from_numpy(np.concatenate(bl)).to(dev)
-    g["ei_pp"] = radius_graph(g["pos_p"], cutoff, bpt, max_num_neighbors=1 << 30)
-    g["ei_ll"] = radius_graph(g["pos_l"], cutoff, blt, max_num_neighbors=1 << 30)
+    # the cell-list kernel's destination-sorted CSR feeds the attention path directly (no sort on the step)
+    for key, pos, bt in (("ei_pp", g["pos_p"], bpt), ("ei_ll", g["pos_l"], blt)):
+        rc = radius_graph_csr(pos, cutoff, bt, max_num_neighbors=1 << 30)
+        edge_csr_from_radius(rc, pos.shape[0])
+        g[key] = rc.edge_index
     d = torch.cdist(g["pos_l"], g["pos_p"])
     li, pi = torch.nonzero((d <= contact) & (blt[:, None] == bpt[None, :]), as_tuple=True)
     g["ei_lp"] = torch.stack((li, pi))
