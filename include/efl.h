@@ -40,20 +40,30 @@ int efl_device_cc(int device, int* major, int* minor);
  * D^l, each padded to 16 bytes (WSZ = 296 floats for (6,2), 476 for (8,2)).  Built for mmax = 2, lmax in {4, 6, 8}. */
 int efl_wigner_from_rotmat(int lmax, int mmax, const float* rot, const float* jd, float* wig, int E, void* stream);
 
+/* Edge operand layout shared by the entry points below ("edge rows"): every edge of a chunk owns ONE row of
+ * `pitch` elements (fp32 or bf16); inside the row the kept coefficients are in m-primary order, the m = 0 block
+ * ((lmax+1) degrees x CH channels), then for m = 1, 2 the +m block followed by the -m block ((lmax+1-m) x CH each).
+ * The three pointers a0/a1/a2 (v0.., dy0..) address the start of the m = 0 / 1 / 2 blocks of the chunk's first edge.
+ * (+m | -m) adjacent makes an edge row the [x_re | x_im] operand of SO2_m_Convolution written as ONE real GEMM
+ * (:721-729: out_re = x_re Wr^T - x_im Wi^T, out_im = x_im Wr^T + x_re Wi^T  ==  [x_re | x_im] [[Wr,-Wi],[Wi,Wr]]^T),
+ * so forward, dgrad and wgrad of all six SO(2) linears are plain GEMMs over M = edges with no duplicated layout. */
+
 /* Gather + rotate-in: SO3_Embedding.clone/_expand_edge + cat (:1110-1119), SO3_Rotation.rotate (:494-497),
  * _m_primary (:354-355) and the radial multiply of SO2_Convolution (:820-850).
  * x_src [Ns,L,C], x_dst [Nt,L,C]; src/dst/perm int32 [E] (dst-sorted order; perm = original edge id);
- * wig [E,WSZ] and rad [E,rad_ld] in ORIGINAL edge order (rad may be NULL); a0..a2 operand buffers (fp32 or
- * bf16) for chunk edges [e0, e0+Ec). */
+ * wig [E,WSZ] and rad [E,rad_ld] in ORIGINAL edge order (rad may be NULL); a0..a2 + pitch: edge rows (CH = 2C)
+ * for chunk edges [e0, e0+Ec).  ones_pad > 0: the ones_pad columns in front of the m = 0 block are set to
+ * (1, 0, ..., 0): the bias column of the so2_conv_1 m = 0 GEMM (fc_m0.bias, :820-825). */
 int efl_rotate_in_fwd(int lmax, int mmax, int C, int bf16_out, const float* x_src, const float* x_dst,
                       const int* src, const int* dst, const int* perm, const float* wig, const float* rad,
-                      int rad_ld, void* a0, void* a1, void* a2, int e0, int Ec, void* stream);
-/* Backward of the above: da0..da2 (dgrad of so2_conv_1) -> drad [E,rad_ld] (original order) and per-edge
+                      int rad_ld, void* a0, void* a1, void* a2, long long pitch, int ones_pad, int e0, int Ec,
+                      void* stream);
+/* Backward of the above: da0..da2 (dgrad of so2_conv_1, edge rows) -> drad [E,rad_ld] (original order) and per-edge
  * d x [E, L, 2C] (sorted order; columns [0,C) source half, [C,2C) destination half). */
 int efl_rotate_in_bwd(int lmax, int mmax, int C, int bf16_in, const float* x_src, const float* x_dst,
                       const int* src, const int* dst, const int* perm, const float* wig, const float* rad,
-                      int rad_ld, const void* da0, const void* da1, const void* da2, float* drad, float* dxe,
-                      int e0, int Ec, void* stream);
+                      int rad_ld, const void* da0, const void* da1, const void* da2, long long pitch, float* drad,
+                      float* dxe, int e0, int Ec, void* stream);
 /* Node-owned variant: one warp per node sums d x over its edges in registers (fixed order) and writes
  * dx_out [N,L,C] once; the per-edge d x tensor never exists.  side 0 = destination half: seg_ptr = CSR rowptr,
  * seg_idx NULL, nodes [n0,n1) of the chunk.  side 1 = source half: seg_ptr/seg_idx = source grouping (sorted
@@ -61,7 +71,8 @@ int efl_rotate_in_bwd(int lmax, int mmax, int C, int bf16_in, const float* x_src
 int efl_rotate_in_bwd_nodes(int lmax, int mmax, int C, int bf16_in, int side, const float* x_node,
                             const int* seg_ptr, const int* seg_idx, const int* perm, const float* wig,
                             const float* rad, int rad_ld, const void* da0, const void* da1, const void* da2,
-                            float* drad, float* dx_out, int e0, int Ec, int n0, int n1, int accumulate, void* stream);
+                            long long pitch, float* drad, float* dx_out, int e0, int Ec, int n0, int n1,
+                            int accumulate, void* stream);
 /* Deterministic backward of the gather (:326-328): out[n,i,c] = sum_{k in [ptr[n],ptr[n+1])}
  * buf[idx?idx[k]:k, i, coff+c]; buf rows are L*ldc floats. */
 int efl_segment_sum_rows(const float* buf, int L, int ldc, int coff, int C, const int* ptr, const int* idx,
@@ -69,20 +80,21 @@ int efl_segment_sum_rows(const float* buf, int L, int ldc, int coff, int C, cons
 
 /* alpha*value (:1186-1190) + SO3_Rotation.rotate_inv with get_rotate_inv_rescale (:500-505, :1530-1549) +
  * SO3_Embedding._reduce_edge (:342-351) fused: out [Nt, L, heads*value] for destinations [n0,n1), one CTA per
- * destination, fixed summation order, no atomics.  alpha [E,heads] sorted order (NULL = 1). */
+ * destination, fixed summation order, no atomics.  v0..v2 + pitch: value edge rows (CH = heads*value);
+ * alpha [E,heads] sorted order (NULL = 1). */
 int efl_rotate_back_aggregate_fwd(int lmax, int mmax, int heads, int value_ch, int bf16_in, const void* v0,
-                                  const void* v1, const void* v2, const float* alpha, const int* rowptr,
-                                  const int* perm, const float* wig, float* out, int n0, int n1, int e0,
-                                  void* stream);
-/* Backward: dout [Nt,L,heads*value] -> dy0..dy2 (d value, dup layout for m>0) and dalpha
+                                  const void* v1, const void* v2, long long pitch, const float* alpha,
+                                  const int* rowptr, const int* perm, const float* wig, float* out, int n0, int n1,
+                                  int e0, void* stream);
+/* Backward: dout [Nt,L,heads*value] -> dy0..dy2 + dy_pitch (d value, edge rows like v) and dalpha
  * [efl_rotate_back_parts(lmax,mmax), E, heads]: one partial plane per degree group (planes part_stride floats
  * apart), summed in fixed order by efl_segment_softmax_bwd. */
 int efl_rotate_back_parts(int lmax, int mmax);
 int efl_rotate_back_aggregate_bwd(int lmax, int mmax, int heads, int value_ch, int bf16, const void* v0,
-                                  const void* v1, const void* v2, void* dy0, void* dy1, void* dy2,
-                                  const float* alpha, const int* rowptr, const int* perm, const float* wig,
-                                  const float* dout, float* dalpha, long long part_stride, int n0, int n1, int e0,
-                                  void* stream);
+                                  const void* v1, const void* v2, long long pitch, void* dy0, void* dy1, void* dy2,
+                                  long long dy_pitch, const float* alpha, const int* rowptr, const int* perm,
+                                  const float* wig, const float* dout, float* dalpha, long long part_stride, int n0,
+                                  int n1, int e0, void* stream);
 
 /* EdgeDegreeEmbedding tail (:116-147): m0 [E,(lmax+1)*C] (rad_func output, original order) -> out [Nt,L,C]. */
 int efl_edge_degree_fwd(int lmax, int mmax, int C, const float* m0, const int* rowptr, const int* perm,
@@ -149,13 +161,13 @@ int efl_tc_gemm_tn(const void* A, long long lda, const void* B, long long ldb, f
                    int accumulate, float* workspace, int Mred, int N1, int N2, void* stream);
 
 /* SeparableS2Activation of the edge path (:1757-1773) on the tensor cores, bf16 buffers: per edge two (fwd) or
- * three (bwd) tcgen05 MMAs with the channel axis as M; the grid values live only in TMEM.  h0..h2: hidden rows
- * (plain split buffers); fwd: out0..out2 plain split buffers; bwd: d0..d2 = d(out) rows, out0 = first hidden column
- * of the so2_conv_1 m=0 dY buffer (row pitch ld0), out1/out2 dup-layout buffers, dgate = its gate column.
+ * three (bwd) tcgen05 MMAs with the channel axis as M; the grid values live only in TMEM.  h: hidden edge rows
+ * [Ec, M, 128] (dense, m-primary); fwd: out + ld_out = output edge rows; bwd: d = d(out) rows (dense like h), out =
+ * first hidden column of the so2_conv_1 dY row and dgate = its gate column, both with row pitch ld_out.
  * T, F: to/from grid matrices [G, M] fp32 with m-primary columns. */
-int efl_s2act_tc(int bwd, int lmax, int mmax, int G, const void* h0, const void* h1, const void* h2, const void* d0,
-                 const void* d1, const void* d2, void* out0, void* out1, void* out2, long long ld0, void* dgate,
-                 const float* gate, long long gate_ld, const float* T, const float* F, int Ec, void* stream);
+int efl_s2act_tc(int bwd, int lmax, int mmax, int G, const void* h, const void* d, void* out, long long ld_out,
+                 void* dgate, const float* gate, long long gate_ld, const float* T, const float* F, int Ec,
+                 void* stream);
 
 /* Node-level variant for FeedForwardNetwork (:234-270): x [N, M, cht] bf16 (cht a multiple of 128), gate
  * [N, gate_ld] fp32, T/F [G, M] fp32; fwd: out [N, M, cht]; bwd: dy -> out = d x, dgate [N, cht] (bf16). */

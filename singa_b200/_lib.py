@@ -20,12 +20,12 @@ _CODES = {"p": _P, "i": _I, "l": _L, "f": _F}
 # name -> argument type codes (p pointer, i int, l long long, f float); every entry point returns int
 SIGNATURES = {
     "efl_wigner_from_rotmat": "iipppip",
-    "efl_rotate_in_fwd": "iiiipppppppipppiip",
-    "efl_rotate_in_bwd": "iiiipppppppippppp" "iip",
-    "efl_rotate_in_bwd_nodes": "iiiiipppppp" "ipppppiiiiip",
+    "efl_rotate_in_fwd": "iiiipppppppippp" "liiip",
+    "efl_rotate_in_bwd": "iiiipppppppippp" "lpp" "iip",
+    "efl_rotate_in_bwd_nodes": "iiiiipppppp" "ippp" "lpp" "iiiiip",
     "efl_segment_sum_rows": "piiiipppiip",
-    "efl_rotate_back_aggregate_fwd": "iiiiipppppppp" "iiip",
-    "efl_rotate_back_aggregate_bwd": "iiiiipppppppppppp" "liiip",
+    "efl_rotate_back_aggregate_fwd": "iiiiippp" "lppppp" "iiip",
+    "efl_rotate_back_aggregate_bwd": "iiiiippp" "lppp" "lpppppp" "liiip",
     "efl_edge_degree_fwd": "iiippppfpip",
     "efl_edge_degree_bwd": "iiipppfpip",
     "efl_alpha_logits_fwd": "piiippppip",
@@ -39,7 +39,7 @@ SIGNATURES = {
     "efl_colsum": "ipliipipp",
     "efl_tc_gemm_nt": "iplplpplpliiiip",
     "efl_tc_gemm_tn": "plplplipiiip",
-    "efl_s2act_tc": "iiii" "ppppppppp" "l" "p" "p" "l" "pp" "i" "p",
+    "efl_s2act_tc": "iiii" "ppp" "l" "pp" "l" "pp" "i" "p",
     "efl_s2act_tc_nodes": "iiii" "ppppp" "l" "pp" "i" "p",
     "efl_so3_linear_fwd": "ppppiiiip",
     "efl_so3_linear_bwd_data": "pppiiiip",

@@ -139,8 +139,11 @@ class MultiHeadAttention(nn.Module):
         N, H = node_attr.size(0), self.num_heads
         E = edge_index.size(1)
         csr = centre_csr(edge_index, N)            # "dst" side = centre (row), "src" side = neighbour (col)
-        x = node_attr.unsqueeze(-1)
-        h_k, h_q, h_v = self.k_lin(x).view(N, -1), self.q_lin(x).view(N, -1), self.v_lin(x).view(N, -1)
+        # grouped 1x1 convolutions as per-head matmuls: cuDNN's Conv1d would run them in TF32 (its default), which
+        # is a 1e-3 error on a path held to 1e-5; torch matmul stays fp32
+        xg = node_attr.view(N, H, -1)
+        proj = lambda conv: torch.einsum("ngi,goi->ngo", xg, conv.weight.view(H, -1, xg.size(2))).reshape(N, -1)
+        h_k, h_q, h_v = proj(self.k_lin), proj(self.q_lin), proj(self.v_lin)
         dk, dv = h_k.size(1) // H, h_v.size(1) // H
         w_k = self._edge_mlp(self.weight_k_net, edge_attr)                                      # [E, dk]
         k_j = gather_rows(h_k, csr, "src").view(E, H, dk) * w_k.unsqueeze(1)

@@ -11,8 +11,12 @@
 //                     no atomics; the [E, L, heads*value] tensor never exists.
 //  edge_degree      : EdgeDegreeEmbedding tail (EF_layers.py:116-147): only the m'=0 Wigner row.
 //
-// Per-edge operand layout ("m-primary, split by order"): for order m the buffer is dense
-// [rows_m * Ec, (LMAX+1-m) * CH] with rows_m = 1 (m=0) or 2 (row 2e = +m "real", 2e+1 = -m "imag").
+// Per-edge operand layout ("edge rows, m-primary"): every edge owns ONE row of `pitch` elements; inside the row the
+// kept coefficients sit in m-primary order, m = 0 block (LMAX+1 degrees), then for each order m > 0 the +m ("real")
+// block followed by the -m ("imag") block, each (LMAX+1-m) * CH wide.  The three base pointers address the start of
+// the m = 0, m = 1 and m = 2 blocks of edge 0 (they may carry a column offset: the m = 0 block of the rotate-in
+// output is preceded by the bias/ones pad of the SO(2) GEMM).  Because (+m | -m) are adjacent, one edge row is
+// directly the [x_re | x_im] operand of the SO(2) linear written as a real GEMM (ops.py: _Weights).
 #include "efl_common.cuh"
 
 namespace efl {
@@ -20,16 +24,15 @@ namespace efl {
 template <int LMAX>
 struct OpBufs {
   void* p[3];
+  long long pitch;   // elements between consecutive edges (the same for the three blocks: one row per edge)
 };
 
-// element (l, m') of local edge e, channel c in the split m-primary buffers
+// element (l, m') of local edge e, channel c
 template <int LMAX, typename T>
-__device__ __forceinline__ T* op_ptr(void* const* bufs, int e, int l, int mp, int CH, int c) {
+__device__ __forceinline__ T* op_ptr(const OpBufs<LMAX>& b, int e, int l, int mp, int CH, int c) {
   const int am = mp < 0 ? -mp : mp;
   const int K = (LMAX + 1 - am) * CH;
-  T* base = reinterpret_cast<T*>(bufs[am]);
-  if (am == 0) return base + (size_t)e * K + l * CH + c;
-  return base + ((size_t)e * 2 + (mp > 0 ? 0 : 1)) * K + (l - am) * CH + c;
+  return reinterpret_cast<T*>(b.p[am]) + (size_t)e * b.pitch + (mp < 0 ? K : 0) + (l - am) * CH + c;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -39,7 +42,7 @@ template <int LMAX, int MMAX, int C, typename TOut>
 __global__ void __launch_bounds__(128) rotate_in_fwd_kernel(
     const float* __restrict__ x_src, const float* __restrict__ x_dst, const int* __restrict__ src,
     const int* __restrict__ dst, const int* __restrict__ perm, const float* __restrict__ wig,
-    const float* __restrict__ rad, int rad_ld, OpBufs<LMAX> out, int e0, int Ec) {
+    const float* __restrict__ rad, int rad_ld, OpBufs<LMAX> out, int ones_pad, int e0, int Ec) {
   using T = Tab<LMAX, MMAX>;
   static_assert(2 * C == 32, "lane = channel mapping needs 2C == 32");
   constexpr int CH = 2 * C;
@@ -61,6 +64,10 @@ __global__ void __launch_bounds__(128) rotate_in_fwd_kernel(
   for (int i = 0; i < T::L; ++i) x[i] = __ldg(xp + i * C);
   __syncwarp();
   const float* rd = rad ? rad + (size_t)eo * rad_ld : nullptr;
+  // bias column of the SO(2) m = 0 GEMM: the ones_pad (<= 64) columns in front of the m = 0 block hold (1, 0, 0, ...),
+  // so the bias is a weight column forward and a row of the wgrad product backward (no bias epilogue, no column sum)
+  for (int t = lane; t < ones_pad; t += 32)
+    (reinterpret_cast<TOut*>(out.p[0]) + (size_t)el * out.pitch - ones_pad)[t] = from_f<TOut>(t == 0 ? 1.f : 0.f);
 #pragma unroll
   for (int l = 0; l <= LMAX; ++l) {
 #pragma unroll
@@ -77,7 +84,7 @@ __global__ void __launch_bounds__(128) rotate_in_fwd_kernel(
         for (int k = 0; k < am; ++k) roff += (LMAX + 1 - k) * CH;
         acc *= __ldg(rd + roff + (l - am) * CH + lane);
       }
-      *op_ptr<LMAX, TOut>(out.p, el, l, mp, CH, lane) = from_f<TOut>(acc);
+      *op_ptr<LMAX, TOut>(out, el, l, mp, CH, lane) = from_f<TOut>(acc);
     }
   }
 }
@@ -126,7 +133,7 @@ __global__ void __launch_bounds__(128) rotate_in_bwd_kernel(
       for (int sgn = 0; sgn < (am == 0 ? 1 : 2); ++sgn) {
         const int mp = sgn == 0 ? am : -am;
         const float* wr = &sW[warp][T::wrow(l, mp)];
-        const float da = to_f<TIn>(*op_ptr<LMAX, TIn>(dA.p, el, l, mp, CH, lane));
+        const float da = to_f<TIn>(*op_ptr<LMAX, TIn>(dA, el, l, mp, CH, lane));
         if (rd) {
           float xr = 0.f;
 #pragma unroll
@@ -242,7 +249,7 @@ __global__ void __launch_bounds__(32 * WPB, 16 / WPB) rotate_in_bwd_node_kernel(
 #pragma unroll
           for (int sgn = 0; sgn < (am == 0 ? 1 : 2); ++sgn) {
             const int mp = sgn == 0 ? am : -am;
-            da_r[t++] = act ? to_f<TIn>(*op_ptr<LMAX, TIn>(dA.p, el, l, mp, CH, coff + c)) : 0.f;
+            da_r[t++] = act ? to_f<TIn>(*op_ptr<LMAX, TIn>(dA, el, l, mp, CH, coff + c)) : 0.f;
           }
         }
       }
@@ -418,14 +425,14 @@ struct GroupCfg {
 #pragma unroll
     for (int am = 0; am <= MMAX; ++am) {
       if (nl(am) > 0) {
-        const TIn* base = reinterpret_cast<const TIn*>(V.p[am]);
+        const TIn* base = reinterpret_cast<const TIn*>(V.p[am]) + (size_t)el * V.pitch;
         if (am == 0) {
-          bulk_g2s(stage + seg_off(0, 0), base + ((size_t)el * (LMAX + 1) + la(0)) * CH, nl(0) * ROWB, bar);
+          bulk_g2s(stage + seg_off(0, 0), base + la(0) * CH, nl(0) * ROWB, bar);
         } else {
 #pragma unroll
           for (int neg = 0; neg < 2; ++neg)
-            bulk_g2s(stage + seg_off(am, neg),
-                     base + (((size_t)el * 2 + neg) * (LMAX + 1 - am) + (la(am) - am)) * CH, nl(am) * ROWB, bar);
+            bulk_g2s(stage + seg_off(am, neg), base + (neg * (LMAX + 1 - am) + (la(am) - am)) * CH, nl(am) * ROWB,
+                     bar);
         }
       }
     }
@@ -577,8 +584,7 @@ __global__ void __launch_bounds__(SPLIT ? 32 : 32 * Tab<LMAX, MMAX>::NG) rotate_
 #undef GROUP
 }
 
-// backward: d out[n] -> dV (written in the duplicated "dY" layout the SO(2) dgrad/wgrad GEMMs
-// consume: row 2e = [d re | d im], row 2e+1 = [d im | -d re], columns interleaved (re_q, im_q))
+// backward: d out[n] -> dV (same edge-row layout as V: the SO(2) dgrad/wgrad GEMMs consume it as it is)
 // and per-group partials of d alpha[e, h] = sum_{j, c in h} dva[j, c] * V[e, j, c]  (dalpha [NG, Etot, heads];
 // the segment-softmax backward sums the NG partials in fixed order).  Same ring as the forward.
 template <int LMAX, int MMAX, int CH, int VC, typename TIn, typename TOut, int L_LO, int L_HI>
@@ -656,21 +662,10 @@ __device__ __forceinline__ void rotate_back_bwd_group(const OpBufs<LMAX>& V, con
         }
       }
       if (active) {
-        store4(reinterpret_cast<TOut*>(dY.p[0]) + ((size_t)el * (LMAX + 1) + l) * CH + c4, dre[MMAX][0], dre[MMAX][1],
-               dre[MMAX][2], dre[MMAX][3]);
 #pragma unroll
-        for (int am = 1; am <= T::mm(l); ++am) {
-          const int half = (LMAX + 1 - am) * CH;
-          TOut* r0 = reinterpret_cast<TOut*>(dY.p[am]) + ((size_t)el * 2) * (2 * half) + 2 * ((l - am) * CH + c4);
-          float o0[8], o1[8];
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float gr = dre[MMAX + am][j], gi = dre[MMAX - am][j];
-            o0[2 * j] = gr; o0[2 * j + 1] = gi;
-            o1[2 * j] = gi; o1[2 * j + 1] = -gr;
-          }
-          store8(r0, o0);
-          store8(r0 + 2 * half, o1);
+        for (int mp = -T::mm(l); mp <= T::mm(l); ++mp) {
+          const float* g = dre[mp + MMAX];
+          store4(op_ptr<LMAX, TOut>(dY, el, l, mp, CH, c4), g[0], g[1], g[2], g[3]);
         }
       }
     }
@@ -792,21 +787,23 @@ using namespace efl;
 
 extern "C" int efl_rotate_in_fwd(int lmax, int mmax, int C, int bf16_out, const float* x_src, const float* x_dst,
                                  const int* src, const int* dst, const int* perm, const float* wig,
-                                 const float* rad, int rad_ld, void* a0, void* a1, void* a2, int e0, int Ec,
-                                 void* stream) {
+                                 const float* rad, int rad_ld, void* a0, void* a1, void* a2, long long pitch,
+                                 int ones_pad, int e0, int Ec, void* stream) {
   if (Ec <= 0) return EFL_OK;
   EFL_REQUIRE(C == 16, "efl_rotate_in_fwd: sphere_channels must be 16");
+  EFL_REQUIRE(ones_pad >= 0 && ones_pad <= 64, "efl_rotate_in_fwd: ones_pad must be in [0, 64]");
   cudaStream_t s = (cudaStream_t)stream;
   dim3 grid((Ec + 3) / 4), block(128);
 #define CALL(LM, MM)                                                                                          \
   {                                                                                                           \
-    OpBufs<LM> o{{a0, a1, a2}};                                                                               \
+    OpBufs<LM> o{{a0, a1, a2}, pitch};                                                                        \
     if (bf16_out)                                                                                             \
       rotate_in_fwd_kernel<LM, MM, 16, __nv_bfloat16><<<grid, block, 0, s>>>(x_src, x_dst, src, dst, perm,    \
-                                                                             wig, rad, rad_ld, o, e0, Ec);    \
+                                                                             wig, rad, rad_ld, o, ones_pad,   \
+                                                                             e0, Ec);                         \
     else                                                                                                      \
       rotate_in_fwd_kernel<LM, MM, 16, float><<<grid, block, 0, s>>>(x_src, x_dst, src, dst, perm, wig, rad,  \
-                                                                     rad_ld, o, e0, Ec);                      \
+                                                                     rad_ld, o, ones_pad, e0, Ec);            \
   }
   DISPATCH_LM(lmax, mmax, CALL)
 #undef CALL
@@ -817,14 +814,14 @@ extern "C" int efl_rotate_in_fwd(int lmax, int mmax, int C, int bf16_out, const 
 extern "C" int efl_rotate_in_bwd(int lmax, int mmax, int C, int bf16_in, const float* x_src, const float* x_dst,
                                  const int* src, const int* dst, const int* perm, const float* wig,
                                  const float* rad, int rad_ld, const void* da0, const void* da1, const void* da2,
-                                 float* drad, float* dxe, int e0, int Ec, void* stream) {
+                                 long long pitch, float* drad, float* dxe, int e0, int Ec, void* stream) {
   if (Ec <= 0) return EFL_OK;
   EFL_REQUIRE(C == 16, "efl_rotate_in_bwd: sphere_channels must be 16");
   cudaStream_t s = (cudaStream_t)stream;
   dim3 grid((Ec + 3) / 4), block(128);
 #define CALL(LM, MM)                                                                                           \
   {                                                                                                            \
-    OpBufs<LM> o{{(void*)da0, (void*)da1, (void*)da2}};                                                        \
+    OpBufs<LM> o{{(void*)da0, (void*)da1, (void*)da2}, pitch};                                                 \
     if (bf16_in)                                                                                               \
       rotate_in_bwd_kernel<LM, MM, 16, __nv_bfloat16><<<grid, block, 0, s>>>(x_src, x_dst, src, dst, perm,     \
                                                                              wig, rad, rad_ld, o, drad, dxe,   \
@@ -844,8 +841,8 @@ extern "C" int efl_rotate_in_bwd(int lmax, int mmax, int C, int bf16_in, const f
 extern "C" int efl_rotate_in_bwd_nodes(int lmax, int mmax, int C, int bf16_in, int side, const float* x_node,
                                        const int* seg_ptr, const int* seg_idx, const int* perm, const float* wig,
                                        const float* rad, int rad_ld, const void* da0, const void* da1,
-                                       const void* da2, float* drad, float* dx_out, int e0, int Ec, int n0, int n1,
-                                       int accumulate, void* stream) {
+                                       const void* da2, long long pitch, float* drad, float* dx_out, int e0, int Ec,
+                                       int n0, int n1, int accumulate, void* stream) {
   if (n1 <= n0) return EFL_OK;
   EFL_REQUIRE(C == 16, "efl_rotate_in_bwd_nodes: sphere_channels must be 16");
   EFL_REQUIRE(side == 0 || seg_idx != nullptr, "efl_rotate_in_bwd_nodes: the source side needs the source grouping");
@@ -860,7 +857,7 @@ extern "C" int efl_rotate_in_bwd_nodes(int lmax, int mmax, int C, int bf16_in, i
       x_node, seg_ptr, seg_idx, perm, wig, rad, rad_ld, o, drad, dx_out, coff, e0, Ec, n0, n1, accumulate);
 #define CALL(LM, MM)                                                                                             \
   {                                                                                                              \
-    OpBufs<LM> o{{(void*)da0, (void*)da1, (void*)da2}};                                                          \
+    OpBufs<LM> o{{(void*)da0, (void*)da1, (void*)da2}, pitch};                                                   \
     if (bf16_in) CALL_W(LM, MM, __nv_bfloat16, wpb) else CALL_W(LM, MM, float, wpb)                              \
   }
   DISPATCH_LM(lmax, mmax, CALL)
@@ -910,9 +907,9 @@ extern "C" int efl_rotate_back_parts(int lmax, int mmax) {
 }
 
 extern "C" int efl_rotate_back_aggregate_fwd(int lmax, int mmax, int heads, int value_ch, int bf16_in,
-                                             const void* v0, const void* v1, const void* v2, const float* alpha,
-                                             const int* rowptr, const int* perm, const float* wig, float* out,
-                                             int n0, int n1, int e0, void* stream) {
+                                             const void* v0, const void* v1, const void* v2, long long pitch,
+                                             const float* alpha, const int* rowptr, const int* perm,
+                                             const float* wig, float* out, int n0, int n1, int e0, void* stream) {
   if (n1 <= n0) return EFL_OK;
   EFL_REQUIRE(heads * value_ch == 112 && value_ch == 16, "efl_rotate_back_aggregate_fwd: needs heads*value == 112, value == 16");
   cudaStream_t s = (cudaStream_t)stream;
@@ -922,7 +919,7 @@ extern "C" int efl_rotate_back_aggregate_fwd(int lmax, int mmax, int heads, int 
             heads, rowptr, perm, wig, out, n0, e0)
 #define CALL(LM, MM)                                                                                           \
   {                                                                                                            \
-    OpBufs<LM> o{{(void*)v0, (void*)v1, (void*)v2}};                                                           \
+    OpBufs<LM> o{{(void*)v0, (void*)v1, (void*)v2}, pitch};                                                    \
     dim3 grid(n1 - n0, split ? Tab<LM, MM>::NG : 1), block(split ? 32 : 32 * Tab<LM, MM>::NG);                 \
     if (bf16_in) {                                                                                             \
       if (split) FWD(LM, MM, __nv_bfloat16, true, SMEM_SPLIT) else FWD(LM, MM, __nv_bfloat16, false, SMEM)     \
@@ -938,8 +935,9 @@ extern "C" int efl_rotate_back_aggregate_fwd(int lmax, int mmax, int heads, int 
 }
 
 extern "C" int efl_rotate_back_aggregate_bwd(int lmax, int mmax, int heads, int value_ch, int bf16,
-                                             const void* v0, const void* v1, const void* v2, void* dy0, void* dy1,
-                                             void* dy2, const float* alpha, const int* rowptr, const int* perm,
+                                             const void* v0, const void* v1, const void* v2, long long pitch,
+                                             void* dy0, void* dy1, void* dy2, long long dy_pitch, const float* alpha,
+                                             const int* rowptr, const int* perm,
                                              const float* wig, const float* dout, float* dalpha,
                                              long long part_stride, int n0, int n1, int e0, void* stream) {
   if (n1 <= n0) return EFL_OK;
@@ -951,8 +949,8 @@ extern "C" int efl_rotate_back_aggregate_bwd(int lmax, int mmax, int heads, int 
             dyo, alpha, heads, rowptr, perm, wig, dout, dalpha, part_stride, n0, e0)
 #define CALL(LM, MM)                                                                                           \
   {                                                                                                            \
-    OpBufs<LM> vi{{(void*)v0, (void*)v1, (void*)v2}};                                                          \
-    OpBufs<LM> dyo{{dy0, dy1, dy2}};                                                                           \
+    OpBufs<LM> vi{{(void*)v0, (void*)v1, (void*)v2}, pitch};                                                   \
+    OpBufs<LM> dyo{{dy0, dy1, dy2}, dy_pitch};                                                                 \
     dim3 grid(n1 - n0, split ? Tab<LM, MM>::NG : 1), block(split ? 32 : 32 * Tab<LM, MM>::NG);                 \
     if (bf16) {                                                                                                \
       if (split) BWD(LM, MM, __nv_bfloat16, true, SMEM_SPLIT) else BWD(LM, MM, __nv_bfloat16, false, SMEM)     \

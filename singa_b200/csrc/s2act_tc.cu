@@ -48,7 +48,8 @@ struct Params {
   const float* gate;       // [Ec, gate_ld]
   long long gate_ld;
   __nv_bfloat16* out[3];   // fwd: plain split buffers; bwd: dup-layout buffers (out[0] already offset to hidden cols)
-  long long ld0;           // row pitch (elements) of out[0] per edge
+  long long ld0;           // pitch (elements) between consecutive items of dgate
+  long long ld_out;        // pitch (elements) between consecutive items of out[0] (plain output path)
   __nv_bfloat16* dgate;    // bwd: [Ec, ld0] view, already offset
   const __nv_bfloat16* dy0;  // bwd: order-0 rows of dY (row 0 feeds d gate)
   int dbg;                   // timing experiment (EFL_S2_DBG=1): load only the first channel half
@@ -386,7 +387,7 @@ s2act_tc_kernel(const __grid_constant__ CUtensorMap mapH0, const __grid_constant
       if (!DUP) {
         if (!BWD) yv[0] = __float_as_uint(y0);
         else p.dgate[(size_t)e * p.ld0 + cc] = __float2bfloat16_rn(y0);
-        __nv_bfloat16* o0 = p.out[0] + (size_t)e * R0 * cht + cc;
+        __nv_bfloat16* o0 = p.out[0] + (size_t)e * (size_t)p.ld_out + cc;
         __nv_bfloat16* o1 = p.out[1] + (size_t)e * R1 * cht + cc;
         __nv_bfloat16* o2 = p.out[2] + (size_t)e * R2 * cht + cc;
 #pragma unroll
@@ -443,7 +444,7 @@ static int s2_launch(efl::s2tc::Params& p, const void* const* hs, const void* co
   p.gstride = p.bwd ? 2 * p.GP : p.GP;
   p.NG = TMEM_COLS / p.gstride;
   // worker groups: forward of the (6,2) edge shape runs 6 (896 threads, <= 73 registers); everything else <= 4
-  const int ngcap = (!p.bwd && p.ms[0] == 7 && p.ms[1] == 6 && p.GP == 80) ? MAX_GROUPS : 4;
+  const int ngcap = (!p.bwd && p.M == 29 && p.GP == 80) ? MAX_GROUPS : 4;
   if (p.NG > ngcap) p.NG = ngcap;
   if (p.KP > 48 && p.NG > 2) p.NG = 2;
   // operand ring: as deep as shared memory allows (<= MAX_STAGES; EFL_S2_STAGES caps it for timing experiments)
@@ -478,11 +479,11 @@ static int s2_launch(efl::s2tc::Params& p, const void* const* hs, const void* co
       kern<<<grid, threads, smem, st>>>(mh[0], mh[1], mh[2], md[0], md[1], md[2], p);                            \
     }                                                                                                            \
   }
-  if (p.ms[0] == 7 && p.ms[1] == 6 && p.ms[2] == 5 && p.GP == 80) S2_LAUNCH(7, 6, 5, 80, MAX_THREADS, 512)
-  else if (p.ms[0] == 9 && p.ms[1] == 8 && p.ms[2] == 7 && p.GP == 96) S2_LAUNCH(9, 8, 7, 96, 640, 640)
+  if (p.ms[0] == 29 && p.ms[1] == 0 && p.GP == 80) S2_LAUNCH(29, 0, 0, 80, MAX_THREADS, 512)
+  else if (p.ms[0] == 39 && p.ms[1] == 0 && p.GP == 96) S2_LAUNCH(39, 0, 0, 96, 640, 640)
   else if (p.ms[0] == 49 && p.ms[1] == 0 && p.GP == 224) S2_LAUNCH(49, 0, 0, 224, 384, 384)
   else {
-    efl_set_error("efl_s2act_tc: built for (lmax,mmax,G) = (6,2,70), (8,2,90) and node blocks (49 rows, G=210)");
+    efl_set_error("efl_s2act_tc: built for edge rows of (lmax,mmax,G) = (6,2,70), (8,2,90) and node blocks (49 rows, G=210)");
     return EFL_ERR_UNSUPPORTED;
   }
 #undef S2_LAUNCH
@@ -490,31 +491,32 @@ static int s2_launch(efl::s2tc::Params& p, const void* const* hs, const void* co
   return EFL_OK;
 }
 
-// fwd: h0..h2 hidden rows (plain split buffers, bf16) -> out0..out2 (plain split buffers); gate [Ec, gate_ld] fp32.
-// bwd: additionally d0..d2 = d(out) rows; out0 = &dY1_0[0][hidden column], out1/out2 dup-layout buffers, ld0 = row
-//      pitch of dY1_0, dgate = &dY1_0[0][gate column].  T/F: to/from grid [G, M] fp32 with m-primary columns.
-extern "C" int efl_s2act_tc(int bwd, int lmax, int mmax, int G, const void* h0, const void* h1, const void* h2,
-                            const void* d0, const void* d1, const void* d2, void* out0, void* out1, void* out2,
-                            long long ld0, void* dgate, const float* gate, long long gate_ld, const float* T,
+// Edge path.  h: hidden rows [Ec, M, 128] bf16 (one row of M*128 per edge, m-primary coefficient order, dense);
+// fwd: out[e] = &out[e * ld_out], M*128 values; gate [Ec, gate_ld] fp32.
+// bwd: additionally d = d(out) rows, dense like h; out = &dY1[0][hidden column], dgate = &dY1[0][gate column],
+//      both with item pitch ld_out (the row pitch of dY1).  T/F: to/from grid [G, M] fp32 with m-primary columns.
+extern "C" int efl_s2act_tc(int bwd, int lmax, int mmax, int G, const void* h, const void* d, void* out,
+                            long long ld_out, void* dgate, const float* gate, long long gate_ld, const float* T,
                             const float* F, int Ec, void* stream) {
   using namespace efl::s2tc;
   if (Ec <= 0) return EFL_OK;
   EFL_REQUIRE(mmax == 2, "efl_s2act_tc: built for mmax == 2");
   Params p{};
   p.bwd = bwd;
-  p.ms[0] = lmax + 1; p.ms[1] = lmax; p.ms[2] = lmax - 1;
-  p.rows[0] = p.ms[0]; p.rows[1] = 2 * p.ms[1]; p.rows[2] = 2 * p.ms[2];
-  p.first[0] = 0; p.first[1] = p.rows[0]; p.first[2] = p.rows[0] + p.rows[1];
-  p.M = p.rows[0] + p.rows[1] + p.rows[2];
+  p.M = (lmax + 1) + 2 * lmax + 2 * (lmax - 1);
+  p.ms[0] = p.M; p.ms[1] = 0; p.ms[2] = 0;
+  p.rows[0] = p.M; p.rows[1] = 0; p.rows[2] = 0;
+  p.first[0] = 0; p.first[1] = p.M; p.first[2] = p.M;
   p.KP = (p.M + 15) / 16 * 16;
   p.G = G; p.GP = (G + 15) / 16 * 16;
   EFL_REQUIRE(p.KP <= 64 && p.GP <= 224, "efl_s2act_tc: coefficient / grid size out of range");
-  p.Ec = Ec; p.ncb = 1; p.cht = CH; p.dup = 1;
+  EFL_REQUIRE(ld_out >= (long long)p.M * CH, "efl_s2act_tc: output pitch smaller than one item");
+  p.Ec = Ec; p.ncb = 1; p.cht = CH; p.dup = 0;
   p.T = T; p.F = F; p.gate = gate; p.gate_ld = gate_ld;
-  p.out[0] = (__nv_bfloat16*)out0; p.out[1] = (__nv_bfloat16*)out1; p.out[2] = (__nv_bfloat16*)out2;
-  p.ld0 = ld0; p.dgate = (__nv_bfloat16*)dgate; p.dy0 = (const __nv_bfloat16*)d0;
-  const void* hs[3] = {h0, h1, h2};
-  const void* ds[3] = {d0, d1, d2};
+  p.out[0] = p.out[1] = p.out[2] = (__nv_bfloat16*)out;
+  p.ld0 = ld_out; p.ld_out = ld_out; p.dgate = (__nv_bfloat16*)dgate; p.dy0 = (const __nv_bfloat16*)d;
+  const void* hs[3] = {h, h, h};
+  const void* ds[3] = {d, d, d};
   return s2_launch(p, hs, ds, Ec, (cudaStream_t)stream);
 }
 
@@ -539,7 +541,7 @@ extern "C" int efl_s2act_tc_nodes(int bwd, int M, int G, int cht, const void* x,
   p.Ec = N; p.ncb = cht / CH; p.cht = cht; p.dup = 0;
   p.T = T; p.F = F; p.gate = gate; p.gate_ld = gate_ld;
   p.out[0] = p.out[1] = p.out[2] = (__nv_bfloat16*)out;
-  p.ld0 = cht; p.dgate = (__nv_bfloat16*)dgate; p.dy0 = (const __nv_bfloat16*)dy;
+  p.ld0 = cht; p.ld_out = (long long)M * cht; p.dgate = (__nv_bfloat16*)dgate; p.dy0 = (const __nv_bfloat16*)dy;
   const void* hs[3] = {x, x, x};
   const void* ds[3] = {dy, dy, dy};
   return s2_launch(p, hs, ds, N, (cudaStream_t)stream);

@@ -12,8 +12,10 @@ A *record* here is a flat dict of numpy arrays per complex, written once by ``pa
                               (``embedding.pack_feature_bits``: same truncation of the charge column)
   pos_p, pos_l        float32
   for each of the four edge lists (pp, ll, lp, pl):
-    {k}_src, {k}_dst  int32   edges in DESTINATION-SORTED order (stable in the original edge id)
-    {k}_perm          int32   sorted position -> original edge id (per-edge inputs stored in original order map back)
+    {k}_src, {k}_dst  int32   the stored edge list: DESTINATION-SORTED (stable) for pp / ll, with {k}_orig = stored
+                              position -> input edge id; input order for lp / pl (their pairing is semantic: pass 4
+                              reuses pass 3's Wigner matrices edge for edge), with {k}_perm = sorted position ->
+                              stored id and the sorted copies {k}_ssrc / {k}_sdst
     {k}_rowptr        int32   CSR over destinations
     {k}_srcptr/_srcidx int32  the source-side grouping the backward of the gather needs
   lap_p, lap_l        float32 [n, 8] Laplacian positional encodings (cpromg.laplacian_pe), computed once
@@ -40,7 +42,14 @@ _NODE_OF = {"pp": ("p", "p"), "ll": ("l", "l"), "lp": ("l", "p"), "pl": ("p", "l
 LIGAND_SCALARS = ("sas", "logP", "qed", "weight", "tpsa", "vina_score")
 
 
-def _csr_fields(edge_index: np.ndarray, n_src: int, n_dst: int) -> Dict[str, np.ndarray]:
+SORTED_KEYS = ("pp", "ll")   # stored destination-sorted (the bulk of the edges); lp / pl keep their input order
+
+
+def _csr_fields(edge_index: np.ndarray, n_src: int, n_dst: int, store_sorted: bool) -> Dict[str, np.ndarray]:
+    """CSR of one edge list.  ``store_sorted``: the list itself is stored destination-sorted (``perm`` = identity,
+    ``orig`` maps a stored position to the input edge id).  Otherwise the list is stored as given and ``perm`` maps a
+    sorted position to the stored edge id: the two interaction lists must keep their pairing, because pass 4 of the
+    caller reuses, edge for edge, the Wigner matrices of pass 3 (Embedding.py:437-471)."""
     src, dst = edge_index[0].astype(np.int64), edge_index[1].astype(np.int64)
     perm = np.argsort(dst, kind="stable")
     src_s, dst_s = src[perm], dst[perm]
@@ -48,8 +57,12 @@ def _csr_fields(edge_index: np.ndarray, n_src: int, n_dst: int) -> Dict[str, np.
     srcidx = np.argsort(src_s, kind="stable")
     srcptr = np.concatenate(([0], np.cumsum(np.bincount(src, minlength=n_src))))
     i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
-    return dict(src=i32(src_s), dst=i32(dst_s), perm=i32(perm), rowptr=i32(rowptr), srcptr=i32(srcptr),
-                srcidx=i32(srcidx))
+    out = dict(rowptr=i32(rowptr), srcptr=i32(srcptr), srcidx=i32(srcidx))
+    if store_sorted:
+        out.update(src=i32(src_s), dst=i32(dst_s), orig=i32(perm))
+    else:
+        out.update(src=i32(src), dst=i32(dst), perm=i32(perm), ssrc=i32(src_s), sdst=i32(dst_s))
+    return out
 
 
 def pack_bits(x: np.ndarray) -> np.ndarray:
@@ -69,7 +82,7 @@ def pack_complex(g: Dict[str, torch.Tensor], ligand_data: Optional[Dict] = None,
                bits_l=pack_bits(npy["x_l"]), pos_p=npy["pos_p"].astype(np.float32), pos_l=npy["pos_l"].astype(np.float32))
     for k in EDGE_KEYS:
         s, d = _NODE_OF[k]
-        for name, arr in _csr_fields(npy["ei_" + k], n[s], n[d]).items():
+        for name, arr in _csr_fields(npy["ei_" + k], n[s], n[d], k in SORTED_KEYS).items():
             rec[f"{k}_{name}"] = arr
     cache = lap_cache or LapPECache(lap_k)
     rec["lap_p"] = cache.get((key, "p"), npy["ei_pp"], n["p"])
@@ -186,8 +199,12 @@ class DeviceBatch:
                 s, d = _NODE_OF[k]
                 ei = torch.stack((t[f"{k}_src"], t[f"{k}_dst"])).long()
                 E = ei.shape[1]
-                perm = torch.arange(E, dtype=torch.int32, device=ei.device)   # the stored order IS the sorted order
-                csr = ops.EdgeCSR(n[s], n[d], E, perm, t[f"{k}_rowptr"], t[f"{k}_src"], t[f"{k}_dst"], t[f"{k}_dst"],
+                if k in SORTED_KEYS:   # the stored order IS the sorted order
+                    perm = torch.arange(E, dtype=torch.int32, device=ei.device)
+                    ssrc, sdst = t[f"{k}_src"], t[f"{k}_dst"]
+                else:
+                    perm, ssrc, sdst = t[f"{k}_perm"], t[f"{k}_ssrc"], t[f"{k}_sdst"]
+                csr = ops.EdgeCSR(n[s], n[d], E, perm, t[f"{k}_rowptr"], ssrc, sdst, t[f"{k}_dst"],
                                   t[f"{k}_srcptr"], t[f"{k}_srcidx"])
                 csr.chunks = ops.plan_chunks(m[f"{k}_rowptr_host"], ops.MAX_CHUNK_EDGES)
                 ef.register_edge_csr(ei, n[s], n[d], csr)
@@ -221,6 +238,10 @@ def collate_records(recs: List[Dict[str, np.ndarray]], pin: bool = True) -> Host
         a.add(f"{k}_rowptr", rowptr.astype(np.int32))
         a.add(f"{k}_srcptr", srcptr.astype(np.int32))
         a.add(f"{k}_srcidx", np.concatenate([r[f"{k}_srcidx"] + eoff[i] for i, r in enumerate(recs)]).astype(np.int32))
+        if k not in SORTED_KEYS:
+            a.add(f"{k}_perm", np.concatenate([r[f"{k}_perm"] + eoff[i] for i, r in enumerate(recs)]).astype(np.int32))
+            a.add(f"{k}_ssrc", np.concatenate([r[f"{k}_ssrc"] + off[s][i] for i, r in enumerate(recs)]).astype(np.int32))
+            a.add(f"{k}_sdst", np.concatenate([r[f"{k}_sdst"] + off[d][i] for i, r in enumerate(recs)]).astype(np.int32))
         meta[f"{k}_rowptr_host"] = rowptr.astype(np.int64)
         meta["edges"][k] = int(eoff[-1])
     if "smi_in" in recs[0]:

@@ -40,12 +40,32 @@ def set_save_policy(mode: str) -> None:
     _SAVE_POLICY = mode
 
 
+_SAVED_BYTES = {}   # device index -> bytes of edge activations currently kept for backward
+
+
+class _SavedChunks(list):
+    """The kept workspaces of one layer; the running total follows the object's lifetime (released by backward, or
+    with the autograd graph when backward never runs)."""
+
+    def __init__(self, dev_index: int, nbytes: int):
+        super().__init__()
+        self.dev_index, self.nbytes = dev_index, nbytes
+        _SAVED_BYTES[dev_index] = _SAVED_BYTES.get(dev_index, 0) + nbytes
+
+    def __del__(self):
+        _SAVED_BYTES[self.dev_index] = max(0, _SAVED_BYTES.get(self.dev_index, 0) - self.nbytes)
+
+
 def _should_save(nbytes: int, device) -> bool:
+    """Keep this layer's edge activations?  Two limits: the layer must fit a fraction of what is free NOW, and
+    everything kept so far in this step plus this layer must fit the same fraction of the DEVICE (layers decide one
+    after the other: without the running total, batch 64 kept saving until the last layers had no memory left)."""
     if _SAVE_POLICY != "auto":
         return _SAVE_POLICY == "save"
-    free, _ = torch.cuda.mem_get_info(device)
+    free, total = torch.cuda.mem_get_info(device)
     cached = torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device)
-    return nbytes < _SAVE_FREE_FRACTION * (free + cached)
+    kept = _SAVED_BYTES.get(torch.device(device).index or 0, 0)
+    return nbytes < _SAVE_FREE_FRACTION * (free + cached) and kept + nbytes < _SAVE_FREE_FRACTION * total
 
 
 # backward of rotate-in: "nodes" = node-owned accumulation (no per-edge gradient tensor), "edges" = per-edge d x
@@ -199,21 +219,8 @@ def plan_chunks(rowptr: np.ndarray, max_edges: int) -> list:
 # ---------------------------------------------------------------------------
 # helpers
 # ---------------------------------------------------------------------------
-def _interleave_rows(w: torch.Tensor) -> torch.Tensor:
-    """SO2_m_Convolution weight [2*half, K] (rows: real block then imag block, EF_layers.py:723-724)
-    -> rows interleaved (real_q, imag_q) so the complex combine is local to a column pair."""
-    half = w.shape[0] // 2
-    return torch.stack((w[:half], w[half:]), dim=1).reshape(2 * half, w.shape[1]).contiguous()
-
-
-def _deinterleave_rows(w: torch.Tensor) -> torch.Tensor:
-    half = w.shape[0] // 2
-    v = w.view(half, 2, w.shape[1])
-    return torch.cat((v[:, 0], v[:, 1]), dim=0).contiguous()
-
-
 class _Ptrs:
-    """Keeps ctypes arrays alive for the row-map arguments of the S2 kernels."""
+    """Keeps ctypes arrays alive for the row-map arguments of the SIMT S2 kernels."""
 
     def __init__(self, bases, strides, first):
         n = len(bases)
@@ -283,70 +290,110 @@ class AttnDims:
         return f
 
 
+def _pick_bn(n: int) -> int:
+    """Largest multiple of 16 that divides n and is <= 256 (csrc/tc_gemm.cu pick_bn): the MMA N of an n-wide output."""
+    return next((bn for bn in range(256, 15, -16) if n % bn == 0), 0)
+
+
+class _Layout:
+    """Column offsets of the per-edge rows (include/efl.h "edge rows"): inside a row the orders follow each other,
+    m = 0 | (+1 | -1) | (+2 | -2); the A row is preceded by the ones pad of the m = 0 GEMM's bias column."""
+
+    def __init__(self, d: AttnDims):
+        C2, H, VH = 2 * d.C, d.H, d.heads * d.value_ch
+        k0 = d.ms[0] * C2
+        # smallest pad that leaves the padded m = 0 K extent a decent MMA N for the dgrad / wgrad GEMMs
+        self.pad = next((p for p in (16, 32, 48, 64) if _pick_bn(k0 + p) >= 128), 16)
+        self.extra_w = d.heads * d.alpha_ch + H
+
+        def offs(CH, lead):
+            o, w = [lead], lead + d.ms[0] * CH
+            for m in range(1, d.mmax + 1):
+                o.append(w)
+                w += 2 * d.ms[m] * CH
+            return o, w
+        self.offA, self.wA = offs(C2, self.pad)         # A / dA rows: [pad | m0 | m1 | m2]
+        self.offH, self.wH = offs(H, 0)                 # hidden (Hb, B, dB) rows
+        self.offV, self.wV = offs(VH, 0)                # value (V, dY2) rows
+        self.wY1 = self.extra_w + self.wH               # dY1 rows: [d alpha_in | d gate | d hidden]
+        self.k0e = self.pad + k0                        # K of the so2_conv_1 m = 0 GEMM incl. the bias column
+        self.blkA = [d.ms[0] * C2] + [2 * d.ms[m] * C2 for m in range(1, d.mmax + 1)]
+        self.blkH = [d.ms[0] * H] + [2 * d.ms[m] * H for m in range(1, d.mmax + 1)]
+        self.blkV = [d.ms[0] * VH] + [2 * d.ms[m] * VH for m in range(1, d.mmax + 1)]
+
+
 class _Workspace:
-    """Chunk-sized edge buffers.  Operand layout per order m: dense [rows_m*Ec, ms[m]*CH].
-    ``forward`` buffers: A (rotate-in output), extra (alpha/gate columns), Hb (so2_conv_1 hidden), B (S2 output),
-    V (so2_conv_2 values); ``backward`` buffers: the matching gradients."""
+    """Chunk-sized edge buffers, one row per edge.  ``forward`` buffers: A (rotate-in output), extra (alpha/gate
+    columns, fp32), Hb (so2_conv_1 hidden), B (S2 output), V (so2_conv_2 values); ``backward`` buffers: the gradients."""
 
     def __init__(self, d: AttnDims, Ec: int, dtype, device, forward: bool = True, backward: bool = False):
-        C2, H, VH = 2 * d.C, d.H, d.heads * d.value_ch
-        self.extra_w = d.heads * d.alpha_ch + H
-        e = lambda r, c, dt=dtype: torch.empty(max(r, 1), c, dtype=dt, device=device)
-        rows = [Ec] + [2 * Ec] * d.mmax
+        L = self.L = _Layout(d)
+        e = lambda c, dt=dtype: torch.empty(max(Ec, 1), c, dtype=dt, device=device)
         if forward:
-            self.A = [e(rows[m], d.ms[m] * C2) for m in range(d.mmax + 1)]
-            self.extra = e(Ec, self.extra_w, torch.float32)
-            self.Hb = [e(rows[m], d.ms[m] * H) for m in range(d.mmax + 1)]
-            self.B = [e(rows[m], d.ms[m] * H) for m in range(d.mmax + 1)]
-            self.V = [e(rows[m], d.ms[m] * VH) for m in range(d.mmax + 1)]
+            self.A, self.extra, self.Hb, self.B, self.V = e(L.wA), e(L.extra_w, torch.float32), e(L.wH), e(L.wH), e(L.wV)
         if backward:
-            self.dY2 = [e(Ec, d.ms[0] * VH)] + [e(2 * Ec, 2 * d.ms[m] * VH) for m in range(1, d.mmax + 1)]
-            self.dB = [e(rows[m], d.ms[m] * H) for m in range(d.mmax + 1)]
-            self.dY1 = [e(Ec, self.extra_w + d.ms[0] * H)] + [e(2 * Ec, 2 * d.ms[m] * H) for m in range(1, d.mmax + 1)]
-            self.dA = [e(rows[m], d.ms[m] * C2) for m in range(d.mmax + 1)]
+            self.dY2, self.dB, self.dY1, self.dA = e(L.wV), e(L.wH), e(L.wY1), e(L.wA)
 
     @staticmethod
     def forward_bytes_per_edge(d: AttnDims, es: int) -> int:
-        return d.M * (2 * d.C + 2 * d.H + d.heads * d.value_ch) * es + (d.heads * d.alpha_ch + d.H) * 4
+        L = _Layout(d)
+        return (L.wA + 2 * L.wH + L.wV) * es + L.extra_w * 4
 
 
-def _rowmap_plain(bufs, d: AttnDims, CH, esz_offset=0, col_offset0=0, ld0=None):
-    """Row map over plain split buffers: m0 | +1 | -1 | +2 | -2."""
-    bases, strides = [], []
-    es = bufs[0].element_size()
-    ld0 = ld0 if ld0 is not None else d.ms[0] * CH
-    bases.append(bufs[0].data_ptr() + col_offset0 * es)
-    strides.append(ld0)
-    for m in range(1, d.mmax + 1):
-        K = d.ms[m] * CH
-        bases += [bufs[m].data_ptr(), bufs[m].data_ptr() + K * es]
-        strides += [2 * K, 2 * K]
-    return _Ptrs(bases, strides, d.first)
-
-
-def _rowmap_dup(bufs, d: AttnDims, CH, col_offset0, ld0):
-    bases, strides = [], []
-    es = bufs[0].element_size()
-    bases.append(bufs[0].data_ptr() + col_offset0 * es)
-    strides.append(ld0)
-    for m in range(1, d.mmax + 1):
-        K2 = 2 * d.ms[m] * CH
-        bases += [bufs[m].data_ptr(), 0]
-        strides += [2 * K2, 0]
-    return _Ptrs(bases, strides, d.first)
+def _blk_ptrs(buf, offs):
+    """Base pointers of the m = 0 / 1 / 2 blocks of an edge-row buffer."""
+    es = buf.element_size()
+    return [buf.data_ptr() + o * es for o in offs]
 
 
 class _Weights:
-    """GEMM-ready derived copies of the SO(2) convolution weights (never the stored parameters)."""
+    """GEMM-ready derived copies of one SO2_Convolution's weights (never the stored parameters), cached on the
+    parameters' versions: the four passes of a step and its backward share them.
 
-    def __init__(self, conv_w, dtype, need_t: bool):
-        # conv_w: [W_m0, b_m0, W_m1, W_m2, ...]
-        self.w0 = conv_w[0].detach().to(dtype).contiguous()
-        self.b0 = conv_w[1].detach().to(torch.float32).contiguous()
-        self.wm = [_interleave_rows(w.detach()).to(dtype) for w in conv_w[2:]]
-        if need_t:
-            self.w0t = self.w0.t().contiguous()
-            self.wmt = [w.t().contiguous() for w in self.wm]
+    m = 0: ``w0`` [N0, K0 (+pad)]; with ``pad`` the bias is column 0 of the pad (the A operand carries a ones column).
+    m > 0: SO2_m_Convolution as ONE real GEMM over [x_re | x_im] rows (EF_layers.py:721-729):
+        [out_re | out_im] = [x_re | x_im] @ Wf^T,   Wf = [[Wr, -Wi], [Wi, Wr]]      (Wr / Wi = the fc weight's two halves)
+    ``t`` variants are the transposes the dgrad GEMMs take as their B operand."""
+
+    _CACHE: dict = {}
+
+    def __init__(self, conv_w, dtype, pad: int):
+        W0, b0 = conv_w[0].detach(), conv_w[1].detach()
+        if pad:
+            w0 = torch.zeros(W0.shape[0], pad + W0.shape[1], dtype=torch.float32, device=W0.device)
+            w0[:, 0], w0[:, pad:] = b0, W0
+            self.b0 = None
+        else:
+            w0 = W0
+            self.b0 = b0.to(torch.float32).contiguous()
+        self.w0 = w0.to(dtype).contiguous()
+        self.wf = []
+        for w in conv_w[2:]:
+            h = w.shape[0] // 2
+            wr, wi = w.detach()[:h], w.detach()[h:]
+            self.wf.append(torch.cat((torch.cat((wr, -wi), 1), torch.cat((wi, wr), 1)), 0).to(dtype).contiguous())
+        self._t = None
+
+    def transposed(self):
+        if self._t is None:
+            self._t = (self.w0.t().contiguous(), [w.t().contiguous() for w in self.wf])
+        return self._t
+
+    @classmethod
+    def get(cls, conv_w, dtype, pad: int):
+        key = tuple((w.data_ptr(), w._version) for w in conv_w) + (dtype, pad)
+        hit = cls._CACHE.get(key)
+        if hit is None:
+            if len(cls._CACHE) > 64:
+                cls._CACHE.clear()
+            hit = cls._CACHE[key] = cls(conv_w, dtype, pad)
+        return hit
+
+
+def _combine_complex_wgrad(P):
+    """wgrad of the real-GEMM form back to the fc weight's layout: P = d Wf [2h, 2K] -> [d Wr ; d Wi] [2h, K]."""
+    h, K = P.shape[0] // 2, P.shape[1] // 2
+    return torch.cat((P[:h, :K] + P[h:, K:], P[h:, :K] - P[:h, K:]), 0)
 
 
 def _chunk_forward(d: AttnDims, ws: _Workspace, w1: _Weights, w2: _Weights, x_src, x_dst, rad, csr: EdgeCSR, wig,
@@ -357,40 +404,41 @@ def _chunk_forward(d: AttnDims, ws: _Workspace, w1: _Weights, w2: _Weights, x_sr
         if out is not None:
             out[n0:n1].zero_()
         return
-    C2, H, VH = 2 * d.C, d.H, d.heads * d.value_ch
-    bf16 = int(ws.A[0].dtype == torch.bfloat16)
+    L = ws.L
+    bf16 = int(ws.A.dtype == torch.bfloat16)
+    pa = _blk_ptrs(ws.A, L.offA)
     call("efl_rotate_in_fwd", d.lmax, d.mmax, d.C, bf16, ptr(x_src), ptr(x_dst), ptr(csr.src_sorted),
-         ptr(csr.dst_sorted), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.A[0]), ptr(ws.A[1]),
-         ptr(ws.A[2]), e0, Ec, work=Ec * _bytes_rotate_in(d, ws.A[0].element_size(), wig.shape[1]))
-    # so2_conv_1 (EF_layers.py:807-875)
-    _gemm_nt(1, ws.A[0], w1.w0, w1.b0, ws.Hb[0], d.ms[0] * H, ws.extra, ws.extra_w, ws.extra_w, Ec,
-             ws.extra_w + d.ms[0] * H, d.ms[0] * C2)
+         ptr(csr.dst_sorted), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], pa[0], pa[1], pa[2], L.wA, L.pad, e0, Ec,
+         work=Ec * _bytes_rotate_in(d, ws.A.element_size(), wig.shape[1]))
+    # so2_conv_1 (EF_layers.py:807-875): m = 0 with the bias column and the alpha/gate columns split off in fp32
+    _gemm_nt(1, ws.A[:, :L.k0e], w1.w0, None, ws.Hb, L.wH, ws.extra, L.extra_w, L.extra_w, Ec,
+             L.extra_w + L.blkH[0], L.k0e)
     for m in range(1, d.mmax + 1):
-        _gemm_nt(2, ws.A[m], w1.wm[m - 1], None, ws.Hb[m], d.ms[m] * H, None, 0, 0, 2 * Ec, 2 * d.ms[m] * H,
-                 d.ms[m] * C2)
-    call("efl_alpha_logits_fwd", ptr(ws.extra), ws.extra_w, d.heads, d.alpha_ch, ptr(ln_w), ptr(ln_b), ptr(adot),
+        _gemm_nt(0, ws.A[:, L.offA[m]:L.offA[m] + L.blkA[m]], w1.wf[m - 1], None, ws.Hb[:, L.offH[m]:], L.wH, None, 0, 0,
+                 Ec, L.blkH[m], L.blkA[m])
+    call("efl_alpha_logits_fwd", ptr(ws.extra), L.extra_w, d.heads, d.alpha_ch, ptr(ln_w), ptr(ln_b), ptr(adot),
          logits.data_ptr() + e0 * d.heads * 4, Ec, work=Ec * d.heads * (d.alpha_ch + 1) * 4.0)
     call("efl_segment_softmax_fwd", ptr(logits), d.heads, ptr(csr.rowptr), ptr(alpha), n0, n1)
     to_g, from_g, G = grids
     gate_ptr = ws.extra.data_ptr() + d.heads * d.alpha_ch * 4
     if bf16:
-        call("efl_s2act_tc", 0, d.lmax, d.mmax, G, ptr(ws.Hb[0]), ptr(ws.Hb[1]), ptr(ws.Hb[2]), None, None, None,
-             ptr(ws.B[0]), ptr(ws.B[1]), ptr(ws.B[2]), d.ms[0] * H, None, gate_ptr, ws.extra_w, ptr(to_g), ptr(from_g),
-             Ec, work=Ec * 4.0 * G * d.M * H, tag="efl_s2act_tc_fwd")
+        call("efl_s2act_tc", 0, d.lmax, d.mmax, G, ptr(ws.Hb), None, ptr(ws.B), L.wH, None, gate_ptr, L.extra_w,
+             ptr(to_g), ptr(from_g), Ec, work=Ec * 4.0 * G * d.M * d.H, tag="efl_s2act_tc_fwd")
     else:
-        rin = _rowmap_plain(ws.Hb, d, H)
-        rout = _rowmap_plain(ws.B, d, H)
-        call("efl_s2act_fwd", d.M, G, H, bf16, bf16, *rin.args(), *rout.args(), gate_ptr, ws.extra_w, ptr(to_g),
+        rin = _Ptrs([ws.Hb.data_ptr()], [L.wH], [0, d.M])
+        rout = _Ptrs([ws.B.data_ptr()], [L.wH], [0, d.M])
+        call("efl_s2act_fwd", d.M, G, d.H, 0, 0, *rin.args(), *rout.args(), gate_ptr, L.extra_w, ptr(to_g),
              ptr(from_g), Ec)
     # so2_conv_2
-    _gemm_nt(0, ws.B[0], w2.w0, w2.b0, ws.V[0], d.ms[0] * VH, None, 0, 0, Ec, d.ms[0] * VH, d.ms[0] * H)
+    _gemm_nt(0, ws.B[:, :L.blkH[0]], w2.w0, w2.b0, ws.V, L.wV, None, 0, 0, Ec, L.blkV[0], L.blkH[0])
     for m in range(1, d.mmax + 1):
-        _gemm_nt(2, ws.B[m], w2.wm[m - 1], None, ws.V[m], d.ms[m] * VH, None, 0, 0, 2 * Ec, 2 * d.ms[m] * VH,
-                 d.ms[m] * H)
+        _gemm_nt(0, ws.B[:, L.offH[m]:L.offH[m] + L.blkH[m]], w2.wf[m - 1], None, ws.V[:, L.offV[m]:], L.wV, None, 0, 0,
+                 Ec, L.blkV[m], L.blkH[m])
     if out is not None:
-        call("efl_rotate_back_aggregate_fwd", d.lmax, d.mmax, d.heads, d.value_ch, bf16, ptr(ws.V[0]), ptr(ws.V[1]),
-             ptr(ws.V[2]), ptr(alpha), ptr(csr.rowptr), ptr(csr.perm), ptr(wig), ptr(out), n0, n1, e0,
-             work=Ec * _bytes_rotate_back(d, ws.V[0].element_size(), wig.shape[1]) + (n1 - n0) * out[0].numel() * 4)
+        pv = _blk_ptrs(ws.V, L.offV)
+        call("efl_rotate_back_aggregate_fwd", d.lmax, d.mmax, d.heads, d.value_ch, bf16, pv[0], pv[1], pv[2], L.wV,
+             ptr(alpha), ptr(csr.rowptr), ptr(csr.perm), ptr(wig), ptr(out), n0, n1, e0,
+             work=Ec * _bytes_rotate_back(d, ws.V.element_size(), wig.shape[1]) + (n1 - n0) * out[0].numel() * 4)
 
 
 def _bytes_rotate_in(d: AttnDims, es: int, wsz: int) -> float:
@@ -406,11 +454,9 @@ def _bytes_rotate_back(d: AttnDims, es: int, wsz: int) -> float:
 
 
 def _bytes_rotate_back_bwd(d: AttnDims, es: int, wsz: int) -> float:
-    """Backward: value rows and Wigner rows read, d value written in the dup layout (m=0 rows once, m>0 rows
-    as two interleaved rows of double width), d alpha partials."""
+    """Backward: value rows and Wigner rows read, d value rows written (same layout), d alpha partials."""
     VH = d.heads * d.value_ch
-    dup = (d.ms[0] + 4 * sum(d.ms[1:])) * VH * es
-    return d.M * VH * es + wsz * 4 + dup + d.heads * 4 * 5 + 4
+    return 2 * d.M * VH * es + wsz * 4 + d.heads * 4 * 5 + 4
 
 
 def _check_edge_inputs(who, csr, wig, lmax, mmax, rad=None, m0=None, x_src=None, x_dst=None):
@@ -449,8 +495,8 @@ class EdgeAttentionFunction(torch.autograd.Function):
         dev = x_dst.device
         dtype = torch.float32 if _PRECISION == "fp32" else torch.bfloat16
         E = csr.num_edges
-        L = (d.lmax + 1) ** 2
-        out = torch.empty(csr.num_dst, L, d.heads * d.value_ch, dtype=torch.float32, device=dev)
+        Lc = (d.lmax + 1) ** 2
+        out = torch.empty(csr.num_dst, Lc, d.heads * d.value_ch, dtype=torch.float32, device=dev)
         logits = torch.empty(max(E, 1), d.heads, dtype=torch.float32, device=dev)
         alpha = torch.empty(max(E, 1), d.heads, dtype=torch.float32, device=dev)
         maxE = max((c[3] - c[2] for c in csr.chunks), default=0)
@@ -459,10 +505,11 @@ class EdgeAttentionFunction(torch.autograd.Function):
                 and _should_save(E * _Workspace.forward_bytes_per_edge(d, es), dev))
         STATS["save" if save else "recompute"] += 1
         ws = None if save else _Workspace(d, maxE, dtype, dev)
-        w1 = _Weights([c1w0, c1b0, c1w1, c1w2], dtype, need_t=False)
-        w2 = _Weights([c2w0, c2b0, c2w1, c2w2], dtype, need_t=False)
+        pad = _Layout(d).pad
+        w1 = _Weights.get([c1w0, c1b0, c1w1, c1w2], dtype, pad)
+        w2 = _Weights.get([c2w0, c2b0, c2w1, c2w2], dtype, 0)
         lw, lb, ad = ln_w.detach().contiguous(), ln_b.detach().contiguous(), adot.detach().contiguous()
-        saved = []
+        saved = _SavedChunks(dev.index or 0, E * _Workspace.forward_bytes_per_edge(d, es)) if save else None
         for chunk in csr.chunks:
             if save:
                 ws = _Workspace(d, chunk[3] - chunk[2], dtype, dev)
@@ -482,21 +529,25 @@ class EdgeAttentionFunction(torch.autograd.Function):
         dev = x_dst.device
         dout = dout.contiguous().to(torch.float32)
         E = csr.num_edges
-        L = (d.lmax + 1) ** 2
-        C2, H, VH = 2 * d.C, d.H, d.heads * d.value_ch
+        Lc = (d.lmax + 1) ** 2
+        C2 = 2 * d.C
         bf16 = int(dtype == torch.bfloat16)
         maxE = max((c[3] - c[2] for c in csr.chunks), default=0)
         saved_ws = ctx.saved_ws
         ctx.saved_ws = None
         wsr = _Workspace(d, maxE, dtype, dev, forward=saved_ws is None, backward=True)
-        w1 = _Weights([c1w0, c1b0, c1w1, c1w2], dtype, need_t=True)
-        w2 = _Weights([c2w0, c2b0, c2w1, c2w2], dtype, need_t=True)
+        L = wsr.L
+        w1 = _Weights.get([c1w0, c1b0, c1w1, c1w2], dtype, L.pad)
+        w2 = _Weights.get([c2w0, c2b0, c2w1, c2w2], dtype, 0)
+        w1_0t, w1_ft = w1.transposed()
+        w2_0t, w2_ft = w2.transposed()
         lw, lb, ad = ln_w.detach().contiguous(), ln_b.detach().contiguous(), adot.detach().contiguous()
         f32 = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
-        g_c1w0, g_c1b0 = f32(*c1w0.shape), f32(*c1b0.shape)
-        g_c1wm = [f32(*c1w1.shape), f32(*c1w2.shape)]       # interleaved row order until the end
+        n01 = L.extra_w + L.blkH[0]
+        g_c1w0e = f32(n01, L.k0e)                                         # [d W0 | pad | bias column]
+        P1 = [f32(L.blkH[m], L.blkA[m]) for m in range(1, d.mmax + 1)]    # d Wf of so2_conv_1, m > 0
         g_c2w0, g_c2b0 = f32(*c2w0.shape), f32(*c2b0.shape)
-        g_c2wm = [f32(*c2w1.shape), f32(*c2w2.shape)]
+        P2 = [f32(L.blkV[m], L.blkH[m]) for m in range(1, d.mmax + 1)]
         drad = torch.empty_like(rad)   # every column of every edge is written by the rotate-in backward
         dx_dst = torch.zeros_like(x_dst)
         dx_src = torch.zeros_like(x_src)
@@ -509,6 +560,7 @@ class EdgeAttentionFunction(torch.autograd.Function):
         part_all = f32(stride)
         part = torch.empty(nblk, stride, dtype=torch.float32, device=dev)
         to_g, from_g, G = grids
+        ha = d.heads * d.alpha_ch
         first = True
         for ci, chunk in enumerate(csr.chunks):
             n0, n1, e0, e1 = chunk
@@ -523,81 +575,81 @@ class EdgeAttentionFunction(torch.autograd.Function):
                 ws = saved_ws[ci]
                 saved_ws[ci] = None     # release the chunk's activations as soon as its gradients are done
                 ws.dY2, ws.dB, ws.dY1, ws.dA = wsr.dY2, wsr.dB, wsr.dY1, wsr.dA
-            # ---- rotate-back + aggregate backward -> dV (dup layout), d alpha
-            call("efl_rotate_back_aggregate_bwd", d.lmax, d.mmax, d.heads, d.value_ch, bf16, ptr(ws.V[0]),
-                 ptr(ws.V[1]), ptr(ws.V[2]), ptr(ws.dY2[0]), ptr(ws.dY2[1]), ptr(ws.dY2[2]), ptr(alpha),
-                 ptr(csr.rowptr), ptr(csr.perm), ptr(wig), ptr(dout), ptr(dalpha), dalpha.stride(0), n0, n1, e0,
-                 work=Ec * _bytes_rotate_back_bwd(d, ws.V[0].element_size(), wig.shape[1]))
-            # ---- so2_conv_2 backward
+            es = ws.dY1.element_size()
+            # ---- rotate-back + aggregate backward -> dV (edge rows), d alpha
+            pv, pdy = _blk_ptrs(ws.V, L.offV), _blk_ptrs(ws.dY2, L.offV)
+            call("efl_rotate_back_aggregate_bwd", d.lmax, d.mmax, d.heads, d.value_ch, bf16, pv[0], pv[1], pv[2], L.wV,
+                 pdy[0], pdy[1], pdy[2], L.wV, ptr(alpha), ptr(csr.rowptr), ptr(csr.perm), ptr(wig), ptr(dout),
+                 ptr(dalpha), dalpha.stride(0), n0, n1, e0,
+                 work=Ec * _bytes_rotate_back_bwd(d, ws.V.element_size(), wig.shape[1]))
+            # ---- so2_conv_2 backward (plain GEMMs over M = edges: wgrad TN, dgrad NT)
             acc = not first
-            _gemm_tn(ws.dY2[0], ws.B[0], g_c2w0, acc, Ec, d.ms[0] * VH, d.ms[0] * H)
-            _colsum(ws.dY2[0], Ec, d.ms[0] * VH, g_c2b0, acc)
-            _gemm_nt(0, ws.dY2[0], w2.w0t, None, ws.dB[0], d.ms[0] * H, None, 0, 0, Ec, d.ms[0] * H, d.ms[0] * VH)
+            dy20 = ws.dY2[:Ec, :L.blkV[0]]
+            _gemm_tn(dy20, ws.B[:, :L.blkH[0]], g_c2w0, acc, Ec, L.blkV[0], L.blkH[0])
+            _colsum(dy20, Ec, L.blkV[0], g_c2b0, acc)
+            _gemm_nt(0, dy20, w2_0t, None, ws.dB, L.wH, None, 0, 0, Ec, L.blkH[0], L.blkV[0])
             for m in range(1, d.mmax + 1):
-                _gemm_tn(ws.dY2[m], ws.B[m], g_c2wm[m - 1], acc, 2 * Ec, 2 * d.ms[m] * VH, d.ms[m] * H)
-                _gemm_nt(0, ws.dY2[m], w2.wmt[m - 1], None, ws.dB[m], d.ms[m] * H, None, 0, 0, 2 * Ec, d.ms[m] * H,
-                         2 * d.ms[m] * VH)
-            # ---- S2 activation backward -> dY1 (m0: [d alpha_in | d gate | d hidden rows]; m>0 dup layout)
-            ld1 = ws.extra_w + d.ms[0] * H
-            es = ws.dY1[0].element_size()
-            gate_ptr = ws.extra.data_ptr() + d.heads * d.alpha_ch * 4
-            dgate_ptr = ws.dY1[0].data_ptr() + d.heads * d.alpha_ch * es
+                dy2m = ws.dY2[:Ec, L.offV[m]:L.offV[m] + L.blkV[m]]
+                _gemm_tn(dy2m, ws.B[:, L.offH[m]:L.offH[m] + L.blkH[m]], P2[m - 1], acc, Ec, L.blkV[m], L.blkH[m])
+                _gemm_nt(0, dy2m, w2_ft[m - 1], None, ws.dB[:, L.offH[m]:], L.wH, None, 0, 0, Ec, L.blkH[m], L.blkV[m])
+            # ---- S2 activation backward -> dY1 row = [d alpha_in | d gate | d hidden rows]
+            gate_ptr = ws.extra.data_ptr() + ha * 4
+            dgate_ptr = ws.dY1.data_ptr() + ha * es
+            dhid_ptr = ws.dY1.data_ptr() + L.extra_w * es
             if bf16:
-                call("efl_s2act_tc", 1, d.lmax, d.mmax, G, ptr(ws.Hb[0]), ptr(ws.Hb[1]), ptr(ws.Hb[2]), ptr(ws.dB[0]),
-                     ptr(ws.dB[1]), ptr(ws.dB[2]), ws.dY1[0].data_ptr() + ws.extra_w * es, ptr(ws.dY1[1]),
-                     ptr(ws.dY1[2]), ld1, dgate_ptr, gate_ptr, ws.extra_w, ptr(to_g), ptr(from_g), Ec,
-                     work=Ec * 6.0 * G * d.M * H, tag="efl_s2act_tc_bwd")
+                call("efl_s2act_tc", 1, d.lmax, d.mmax, G, ptr(ws.Hb), ptr(ws.dB), dhid_ptr, L.wY1, dgate_ptr, gate_ptr,
+                     L.extra_w, ptr(to_g), ptr(from_g), Ec, work=Ec * 6.0 * G * d.M * d.H, tag="efl_s2act_tc_bwd")
             else:
-                rin = _rowmap_plain(ws.Hb, d, H)
-                rdin = _rowmap_plain(ws.dB, d, H)
-                rdout = _rowmap_dup(ws.dY1, d, H, ws.extra_w, ld1)
-                call("efl_s2act_bwd", d.M, G, H, bf16, bf16, *rin.args(), *rdin.args(), *rdout.args(), 1, gate_ptr,
-                     ws.extra_w, dgate_ptr, ld1, ptr(to_g), ptr(from_g), Ec)
-            # ---- softmax + alpha-logit backward -> first heads*alpha columns of dY1[0]
+                rin = _Ptrs([ws.Hb.data_ptr()], [L.wH], [0, d.M])
+                rdin = _Ptrs([ws.dB.data_ptr()], [L.wH], [0, d.M])
+                rdout = _Ptrs([dhid_ptr], [L.wY1], [0, d.M])
+                call("efl_s2act_bwd", d.M, G, d.H, 0, 0, *rin.args(), *rdin.args(), *rdout.args(), 0, gate_ptr,
+                     L.extra_w, dgate_ptr, L.wY1, ptr(to_g), ptr(from_g), Ec)
+            # ---- softmax + alpha-logit backward -> first heads*alpha columns of the dY1 rows
             call("efl_segment_softmax_bwd", ptr(alpha), ptr(dalpha), nparts, dalpha.stride(0), d.heads, ptr(csr.rowptr),
                  ptr(dlogits), n0, n1)
-            call("efl_alpha_logits_bwd", ptr(ws.extra), ws.extra_w, d.heads, d.alpha_ch, ptr(lw), ptr(lb), ptr(ad),
-                 dlogits.data_ptr() + e0 * d.heads * 4, ptr(ws.dY1[0]), ld1, bf16, ptr(part), nblk, Ec,
-                 work=Ec * d.heads * ((d.alpha_ch + 1) * 4.0 + d.alpha_ch * ws.dY1[0].element_size()))
+            call("efl_alpha_logits_bwd", ptr(ws.extra), L.extra_w, d.heads, d.alpha_ch, ptr(lw), ptr(lb), ptr(ad),
+                 dlogits.data_ptr() + e0 * d.heads * 4, ptr(ws.dY1), L.wY1, bf16, ptr(part), nblk, Ec,
+                 work=Ec * d.heads * ((d.alpha_ch + 1) * 4.0 + d.alpha_ch * es))
             part_all += part.sum(dim=0)
-            # ---- so2_conv_1 backward
-            _gemm_tn(ws.dY1[0], ws.A[0], g_c1w0, acc, Ec, ld1, d.ms[0] * C2)
-            _colsum(ws.dY1[0], Ec, ld1, g_c1b0, acc)
-            _gemm_nt(0, ws.dY1[0], w1.w0t, None, ws.dA[0], d.ms[0] * C2, None, 0, 0, Ec, d.ms[0] * C2, ld1)
+            # ---- so2_conv_1 backward; the bias gradient is the ones-column row of the m = 0 wgrad product
+            dy10 = ws.dY1[:Ec, :n01]
+            _gemm_tn(dy10, ws.A[:, :L.k0e], g_c1w0e, acc, Ec, n01, L.k0e)
+            _gemm_nt(0, dy10, w1_0t, None, ws.dA, L.wA, None, 0, 0, Ec, L.k0e, n01)
             for m in range(1, d.mmax + 1):
-                _gemm_tn(ws.dY1[m], ws.A[m], g_c1wm[m - 1], acc, 2 * Ec, 2 * d.ms[m] * H, d.ms[m] * C2)
-                _gemm_nt(0, ws.dY1[m], w1.wmt[m - 1], None, ws.dA[m], d.ms[m] * C2, None, 0, 0, 2 * Ec,
-                         d.ms[m] * C2, 2 * d.ms[m] * H)
+                o = L.extra_w + L.offH[m]
+                dy1m = ws.dY1[:Ec, o:o + L.blkH[m]]
+                _gemm_tn(dy1m, ws.A[:, L.offA[m]:L.offA[m] + L.blkA[m]], P1[m - 1], acc, Ec, L.blkH[m], L.blkA[m])
+                _gemm_nt(0, dy1m, w1_ft[m - 1], None, ws.dA[:, L.offA[m]:], L.wA, None, 0, 0, Ec, L.blkA[m], L.blkH[m])
             # ---- rotate-in backward -> d rad and d x
+            pda = _blk_ptrs(ws.dA, L.offA)
             if ROTATE_IN_BWD == "nodes":  # node-owned: no per-edge gradient tensor
-                wrk = Ec * (_bytes_rotate_in(d, ws.dA[0].element_size(), wig.shape[1]) + d.M * C2 * 4) / 2
+                wrk = Ec * (_bytes_rotate_in(d, ws.dA.element_size(), wig.shape[1]) + d.M * C2 * 4) / 2
                 call("efl_rotate_in_bwd_nodes", d.lmax, d.mmax, d.C, bf16, 0, ptr(x_dst), ptr(csr.rowptr), None,
-                     ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.dA[0]), ptr(ws.dA[1]), ptr(ws.dA[2]),
+                     ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], pda[0], pda[1], pda[2], L.wA,
                      ptr(drad), ptr(dx_dst), e0, Ec, n0, n1, 0, work=wrk, tag="efl_rotate_in_bwd_dst")
                 call("efl_rotate_in_bwd_nodes", d.lmax, d.mmax, d.C, bf16, 1, ptr(x_src), ptr(csr.src_ptr),
-                     ptr(csr.src_idx), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.dA[0]),
-                     ptr(ws.dA[1]), ptr(ws.dA[2]), ptr(drad), ptr(dx_src), e0, Ec, 0, csr.num_src, 1, work=wrk,
-                     tag="efl_rotate_in_bwd_src")
+                     ptr(csr.src_idx), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], pda[0], pda[1], pda[2], L.wA,
+                     ptr(drad), ptr(dx_src), e0, Ec, 0, csr.num_src, 1, work=wrk, tag="efl_rotate_in_bwd_src")
             else:  # edge-owned: per-edge d x [E, L, 2C] + two deterministic segment sums after the loop
                 if dxe is None:
-                    dxe = torch.empty(max(E, 1), L, C2, dtype=torch.float32, device=dev)
+                    dxe = torch.empty(max(E, 1), Lc, C2, dtype=torch.float32, device=dev)
                 call("efl_rotate_in_bwd", d.lmax, d.mmax, d.C, bf16, ptr(x_src), ptr(x_dst), ptr(csr.src_sorted),
-                     ptr(csr.dst_sorted), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], ptr(ws.dA[0]),
-                     ptr(ws.dA[1]), ptr(ws.dA[2]), ptr(drad), ptr(dxe), e0, Ec,
-                     work=Ec * (_bytes_rotate_in(d, ws.dA[0].element_size(), wig.shape[1]) + d.M * C2 * 4 + L * C2 * 4))
+                     ptr(csr.dst_sorted), ptr(csr.perm), ptr(wig), ptr(rad), rad.shape[1], pda[0], pda[1], pda[2],
+                     L.wA, ptr(drad), ptr(dxe), e0, Ec,
+                     work=Ec * (_bytes_rotate_in(d, ws.dA.element_size(), wig.shape[1]) + d.M * C2 * 4 + Lc * C2 * 4))
             first = False
         if dxe is not None:
-            call("efl_segment_sum_rows", ptr(dxe), L, C2, d.C, d.C, ptr(csr.rowptr), None, ptr(dx_dst), csr.num_dst, 0,
-                 work=(E + csr.num_dst) * L * d.C * 4.0)
-            call("efl_segment_sum_rows", ptr(dxe), L, C2, 0, d.C, ptr(csr.src_ptr), ptr(csr.src_idx), ptr(dx_src),
-                 csr.num_src, 0, work=(E + csr.num_src) * L * d.C * 4.0 + E * 4.0)
-        ha = d.heads * d.alpha_ch
+            call("efl_segment_sum_rows", ptr(dxe), Lc, C2, d.C, d.C, ptr(csr.rowptr), None, ptr(dx_dst), csr.num_dst, 0,
+                 work=(E + csr.num_dst) * Lc * d.C * 4.0)
+            call("efl_segment_sum_rows", ptr(dxe), Lc, C2, 0, d.C, ptr(csr.src_ptr), ptr(csr.src_idx), ptr(dx_src),
+                 csr.num_src, 0, work=(E + csr.num_src) * Lc * d.C * 4.0 + E * 4.0)
         g_adot = part_all[:ha].view(d.heads, d.alpha_ch)
         g_lnw = part_all[ha:ha + d.alpha_ch]
         g_lnb = part_all[ha + d.alpha_ch:]
-        return (dx_src, dx_dst, drad, g_c1w0, g_c1b0, _deinterleave_rows(g_c1wm[0]), _deinterleave_rows(g_c1wm[1]),
-                g_lnw, g_lnb, g_adot, g_c2w0, g_c2b0, _deinterleave_rows(g_c2wm[0]), _deinterleave_rows(g_c2wm[1]),
-                None, None, None, None)
+        return (dx_src, dx_dst, drad, g_c1w0e[:, L.pad:].contiguous(), g_c1w0e[:, 0].contiguous(),
+                _combine_complex_wgrad(P1[0]), _combine_complex_wgrad(P1[1]), g_lnw, g_lnb, g_adot, g_c2w0, g_c2b0,
+                _combine_complex_wgrad(P2[0]), _combine_complex_wgrad(P2[1]), None, None, None, None)
 
 
 # ---------------------------------------------------------------------------

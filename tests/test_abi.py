@@ -36,3 +36,22 @@ def test_ops_refuse_cpu_tensors():
     from singa_b200 import _lib, ops
     with pytest.raises(_lib.EflError):
         ops.wigner_from_rotmat(torch.eye(3).repeat(4, 1, 1), 6, 2)
+
+
+def test_python_signatures_match_the_header_prototypes():
+    """ctypes argument codes of singa_b200/_lib.py against the C prototypes of include/efl.h, argument by argument
+    (pointer / int / long long / float): a drifted binding corrupts the call stack instead of failing loudly."""
+    from singa_b200 import _lib
+    text = open(os.path.join(ROOT, "include", "efl.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    checked = 0
+    for m in re.finditer(r"int\s+(efl_\w+)\s*\(([^;]*?)\)\s*;", text, flags=re.S):
+        name, args = m.group(1), m.group(2)
+        if name not in _lib.SIGNATURES:
+            continue
+        codes = ""
+        for a in (x.strip() for x in args.split(",")):
+            codes += "p" if "*" in a else ("l" if a.startswith("long long") else ("f" if a.startswith("float") else "i"))
+        assert codes == _lib.SIGNATURES[name], (name, codes, _lib.SIGNATURES[name])
+        checked += 1
+    assert checked >= 35

@@ -21,8 +21,13 @@ def test_record_fields_match_the_oracle_csr_and_bit_packing(tmp_path):
     for k, (s, d) in ds._NODE_OF.items():
         n = {"p": len(g["z_p"]), "l": len(g["z_l"])}
         ref = eo.csr_from_edge_index(g["ei_" + k], n[s], n[d])
-        assert np.array_equal(rec[f"{k}_perm"], ref["perm"]) and np.array_equal(rec[f"{k}_rowptr"], ref["rowptr"])
-        assert np.array_equal(rec[f"{k}_src"], ref["src_sorted"]) and np.array_equal(rec[f"{k}_dst"], ref["dst_sorted"])
+        assert np.array_equal(rec[f"{k}_rowptr"], ref["rowptr"])
+        if k in ds.SORTED_KEYS:
+            assert np.array_equal(rec[f"{k}_orig"], ref["perm"])
+            assert np.array_equal(rec[f"{k}_src"], ref["src_sorted"]) and np.array_equal(rec[f"{k}_dst"], ref["dst_sorted"])
+        else:   # interaction lists keep their input order (Wigner reuse pairs lp and pl edge for edge)
+            assert np.array_equal(rec[f"{k}_src"], g["ei_" + k][0].numpy()) and np.array_equal(rec[f"{k}_perm"], ref["perm"])
+            assert np.array_equal(rec[f"{k}_ssrc"], ref["src_sorted"]) and np.array_equal(rec[f"{k}_sdst"], ref["dst_sorted"])
         assert np.array_equal(rec[f"{k}_srcptr"], ref["src_ptr"]) and np.array_equal(rec[f"{k}_srcidx"], ref["src_idx"])
     assert np.array_equal(rec["bits_p"], pack_feature_bits(g["x_p"]).numpy())
     assert rec["lap_p"].shape == (len(g["z_p"]), 8) and rec["lap_l"].shape == (len(g["z_l"]), 8)
@@ -44,8 +49,12 @@ def test_collation_is_a_sorted_disjoint_union_without_a_sort():
     assert np.array_equal(t["ptr_p"].numpy(), big["ptr_p"].numpy())
     for k, (s, d) in ds._NODE_OF.items():
         ref = eo.csr_from_edge_index(big["ei_" + k], n[s], n[d])      # the sort the loader avoids
-        assert np.array_equal(t[f"{k}_src"].numpy(), ref["src_sorted"]), k
-        assert np.array_equal(t[f"{k}_dst"].numpy(), ref["dst_sorted"]), k
+        sk = ("src", "dst") if k in ds.SORTED_KEYS else ("ssrc", "sdst")
+        assert np.array_equal(t[f"{k}_{sk[0]}"].numpy(), ref["src_sorted"]), k
+        assert np.array_equal(t[f"{k}_{sk[1]}"].numpy(), ref["dst_sorted"]), k
+        if k not in ds.SORTED_KEYS:
+            assert np.array_equal(t[f"{k}_perm"].numpy(), ref["perm"]), k
+            assert np.array_equal(t[f"{k}_src"].numpy(), big["ei_" + k][0].numpy()), k
         assert np.array_equal(t[f"{k}_rowptr"].numpy(), ref["rowptr"]), k
         assert np.array_equal(t[f"{k}_srcptr"].numpy(), ref["src_ptr"]), k
         assert np.array_equal(t[f"{k}_srcidx"].numpy(), ref["src_idx"]), k

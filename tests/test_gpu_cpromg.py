@@ -181,11 +181,12 @@ def test_prebuilt_csr_batch_equals_the_sorting_path():
         frames[key] = ef.init_edge_rot_mat(big[sp][e[0]] - big[dp][e[1]], device=DEV)
     with torch.no_grad():
         a = model(syn.GraphView(big), frames=frames)
-        # the record stores edges destination-sorted: permute the frames the same way
-        perm = {k: torch.cat([torch.from_numpy(r[f"{k}_perm"].astype(np.int64)) + off for r, off in
+        # the record stores the pp / ll edges destination-sorted: permute their frames the same way
+        perm = {k: torch.cat([torch.from_numpy(r[f"{k}_orig"].astype(np.int64)) + off for r, off in
                               zip(recs, np.cumsum([0] + [len(r[f"{k}_src"]) for r in recs])[:-1])]).to(DEV)
-                for k in ("pp", "ll", "lp")}
-        b = model(syn.GraphView(g1), frames={k: frames[k][perm[k]] for k in frames})
+                for k in ("pp", "ll")}
+        b = model(syn.GraphView(g1), frames=dict(pp=frames["pp"][perm["pp"]], ll=frames["ll"][perm["ll"]],
+                                                 lp=frames["lp"]))
     for k in ("protein_atoms", "ligand_atoms"):
         assert torch.equal(a[k].embedding, b[k].embedding), k
 

@@ -68,12 +68,42 @@ def test_chunk_plan_covers_all_destinations():
     assert plan_chunks(np.array([0, 0, 0]), 10) == [(0, 2, 0, 0)]
 
 
-def test_weight_interleave_roundtrip():
-    from singa_b200.ops import _deinterleave_rows, _interleave_rows
-    w = torch.arange(24.0).view(6, 4)
-    wi = _interleave_rows(w)
-    assert torch.equal(wi[0], w[0]) and torch.equal(wi[1], w[3]) and torch.equal(wi[2], w[1])
-    assert torch.equal(_deinterleave_rows(wi), w)
+def test_so2_m_convolution_as_one_real_gemm():
+    """ops._Weights writes SO2_m_Convolution (EF_layers.py:721-729) as ONE real GEMM over [x_re | x_im] edge rows:
+    forward, and the weight gradient mapped back to the fc weight's layout, against the module itself."""
+    from singa_b200 import EF_layers as ef
+    from singa_b200.ops import _Weights, _combine_complex_wgrad
+    torch.manual_seed(0)
+    conv = ef.SO2_m_Convolution(1, 32, 128, [6], [2], device="cpu")
+    E, K = 11, conv.fc.in_features
+    x = torch.randn(E, 2, K)
+    out = conv(x)                                          # [E, 2, half]
+    w0, b0 = torch.randn(8, 4), torch.randn(8)
+    w = _Weights([w0, b0, conv.fc.weight], torch.float32, 0)
+    got = x.reshape(E, 2 * K) @ w.wf[0].t()
+    assert torch.allclose(got, out.reshape(E, -1), atol=1e-5)
+    r = torch.randn_like(out)
+    (out * r).sum().backward()
+    P = r.reshape(E, -1).t() @ x.reshape(E, 2 * K)          # wgrad of the real-GEMM form
+    assert torch.allclose(_combine_complex_wgrad(P), conv.fc.weight.grad, atol=1e-4)
+    # m = 0 with the bias folded into a padded column
+    wp = _Weights([w0, b0, conv.fc.weight], torch.float32, 16)
+    assert wp.w0.shape == (8, 20) and torch.equal(wp.w0[:, 0], b0) and torch.equal(wp.w0[:, 16:], w0)
+    assert float(wp.w0[:, 1:16].abs().max()) == 0.0 and wp.b0 is None
+    w0t, wft = w.transposed()
+    assert torch.equal(w0t, w.w0.t()) and torch.equal(wft[0], w.wf[0].t())
+    assert _Weights.get([w0, b0, conv.fc.weight], torch.float32, 0) is _Weights.get([w0, b0, conv.fc.weight], torch.float32, 0)
+
+
+def test_edge_row_layout_offsets():
+    from singa_b200.ops import AttnDims, _Layout
+    L6 = _Layout(AttnDims(6, 2, 16, 128, 7, 32, 16))
+    assert (L6.pad, L6.k0e, L6.wA, L6.offA) == (16, 240, 944, [16, 240, 624])
+    assert (L6.wH, L6.offH, L6.wV, L6.offV, L6.wY1) == (3712, [0, 896, 2432], 3248, [0, 784, 2128], 4064)
+    L8 = _Layout(AttnDims(8, 2, 16, 128, 7, 32, 16))
+    assert (L8.pad, L8.k0e, L8.wA) == (32, 320, 32 + 39 * 32)      # 288 + 16 = 304 = 16 * 19 would be an N = 16 MMA
+    for L in (L6, L8):   # every block starts 16-byte aligned in bf16 (TMA / bulk-copy requirement)
+        assert all(o % 8 == 0 for o in L.offA + L.offH + L.offV) and L.wA % 8 == 0 and L.wY1 % 8 == 0
 
 
 def test_synthetic_complex_shape():

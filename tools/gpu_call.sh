@@ -1,7 +1,7 @@
 #!/bin/bash
 # One parameterised GPU call (replaces the round-1 gpu_*.sh scratch scripts).  Usage on the box, through gpurun:
 #   gpurun --timeout 1500 -- 'bash tools/gpu_call.sh TAG [steps...]'
-# steps (default "test smoke bench"): test smoke bench edge kernel radius stress ref ncu_edge ncu_launch ncu_src prof
+# steps (default "test smoke bench"): test testall smoke bench config3 edge kernel radius stress ref probe ncu_edge ncu_launch ncu_src prof
 # Every step writes gpurun_out/${TAG}_<step>.*; a number printed under ncu is never a bench value.
 set -u
 mkdir -p gpurun_out
@@ -55,6 +55,12 @@ ncu_src)    # source-level capture of one kernel: NCU_KERNEL=regex NCU_CMD="pyth
   el "ncu src exit $?"
   ncu -i /tmp/${TAG}_src.ncu-rep --page source --csv --print-source sass > gpurun_out/${TAG}_src_sass.csv 2>/dev/null
   ncu -i /tmp/${TAG}_src.ncu-rep --page raw --csv > gpurun_out/${TAG}_src_raw.csv 2>/dev/null ;;
+probe)
+  timeout 300 python tools/e2e_probe.py > gpurun_out/${TAG}_e2e_probe.txt 2>&1; el "e2e_probe exit $?"
+  cat gpurun_out/${TAG}_e2e_probe.txt | tail -6 ;;
+config3)
+  timeout 600 python bench.py --config 3 --steps ${BENCH_STEPS:-5} --warmup 3 > gpurun_out/${TAG}_bench_config3.json 2> gpurun_out/${TAG}_bench_config3.err; el "bench config 3 exit $?"
+  cat gpurun_out/${TAG}_bench_config3.json; tail -5 gpurun_out/${TAG}_bench_config3.err ;;
 prof)
   timeout 200 python tools/profile_step.py > gpurun_out/${TAG}_torch_profile.txt 2>&1; el "profile_step exit $?"
   timeout 120 python tools/cpu_profile_step.py > gpurun_out/${TAG}_cpu_profile.txt 2>&1; el "cpu_profile_step exit $?"
