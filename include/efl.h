@@ -160,6 +160,13 @@ int efl_tc_gemm_pair_mode(int mode);
 int efl_tc_gemm_tn(const void* A, long long lda, const void* B, long long ldb, float* C, long long ldc,
                    int accumulate, float* workspace, int Mred, int N1, int N2, void* stream);
 
+/* bf16x3 operand preparation (accurate tensor-core mode): fp32 x [rows, cols] -> three bf16 copies (hi, hi, lo) for an
+ * A operand or (hi, lo, hi) for a B operand (second = 1), side by side along the columns (stack = 0, NT GEMMs) or one
+ * under the other (stack = 1, TN GEMMs), so that ONE efl_tc_gemm_* launch with a 3x longer reduction computes
+ * a_hi b_hi + a_hi b_lo + a_lo b_hi in fp32 (csrc/split3.cu). */
+int efl_split3(const float* x, long long ld, long long rows, int cols, void* out, long long ldo, int stack, int second,
+               void* stream);
+
 /* SeparableS2Activation of the edge path (:1757-1773) on the tensor cores, bf16 buffers: per edge two (fwd) or
  * three (bwd) tcgen05 MMAs with the channel axis as M; the grid values live only in TMEM.  h: hidden edge rows
  * [Ec, M, 128] (dense, m-primary); fwd: out + ld_out = output edge rows; bwd: d = d(out) rows (dense like h), out =

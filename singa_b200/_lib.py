@@ -37,6 +37,7 @@ SIGNATURES = {
     "efl_gemm_nt_f32": "iplplpplpliiiip",
     "efl_gemm_tn_f32": "plplplipiiip",
     "efl_colsum": "ipliipipp",
+    "efl_split3": "plliplii" "p",
     "efl_tc_gemm_nt": "iplplpplpliiiip",
     "efl_tc_gemm_tn": "plplplipiiip",
     "efl_s2act_tc": "iiii" "ppp" "l" "pp" "l" "pp" "i" "p",
@@ -110,7 +111,14 @@ def ptr(t):
     return t.data_ptr()
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream_ptr():
+    """Raw handle of torch's current stream on the current device.  ``torch.cuda.current_stream()`` builds a Stream
+    object per call (16 us: 13 ms of host time per step over ~830 entry-point calls); the raw getter is ~50x cheaper."""
+    if _raw_stream is not None:
+        return _raw_stream(torch.cuda.current_device())
     return torch.cuda.current_stream().cuda_stream
 
 

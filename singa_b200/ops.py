@@ -19,8 +19,12 @@ import torch
 from . import so3_constants as sc
 from ._lib import LIB, call, check_cuda, ptr
 
-# GEMM operand precision of the SO(2) linear maps: "fp32" (SIMT, parity mode) or
-# "bf16" (tcgen05 tensor cores, fp32 accumulate).  Set through set_precision().
+# GEMM operand precision of the SO(2) linear maps, set through set_precision():
+#   "fp32"    SIMT fp32 (parity mode, 1e-5 / 1e-4)
+#   "bf16"    tcgen05 tensor cores, bf16 operands and edge activations, fp32 accumulate (the benchmarked mode)
+#   "bf16x3"  tcgen05 tensor cores on error-compensated operands: fp32 activations, every GEMM operand split into
+#             bf16 (hi, lo) and a*b taken as a_hi b_hi + a_hi b_lo + a_lo b_hi in ONE launch with a 3x longer
+#             reduction (csrc/split3.cu); everything else as in "fp32".  The accurate tensor-core mode of SURVEY.md 7.1.
 _PRECISION = "fp32"
 MAX_CHUNK_EDGES = 262144
 # Saved-for-backward policy (SURVEY.md 8a note): keep the chunk's edge activations (A, extra, hidden, S2 output,
@@ -74,8 +78,8 @@ ROTATE_IN_BWD = os.environ.get("EFL_ROTIN_BWD", "nodes")
 
 def set_precision(mode: str) -> None:
     global _PRECISION
-    if mode not in ("fp32", "bf16"):
-        raise ValueError("precision must be 'fp32' or 'bf16'")
+    if mode not in ("fp32", "bf16", "bf16x3"):
+        raise ValueError("precision must be 'fp32', 'bf16' or 'bf16x3'")
     _PRECISION = mode
 
 
@@ -234,8 +238,44 @@ class _Ptrs:
                 ctypes.cast(self.f, ctypes.c_void_p))
 
 
+def _split3(x, rows, cols, stack: bool, second: bool):
+    """fp32 [rows, cols] (any row pitch) -> bf16 (hi, hi, lo) / (hi, lo, hi) copies for the bf16x3 GEMMs."""
+    out = torch.empty((3 * rows, cols) if stack else (rows, 3 * cols), dtype=torch.bfloat16, device=x.device)
+    call("efl_split3", ptr(x), x.stride(0), rows, cols, ptr(out), out.stride(0), int(stack), int(second),
+         work=float(rows) * cols * 10.0)
+    return out
+
+
+def _x3_ok(*dims) -> bool:
+    return _PRECISION == "bf16x3" and all(v % 16 == 0 for v in dims)
+
+
+def _weight_x3(B, N, K):
+    """(hi | lo | hi) copy of a derived weight, cached on the tensor object (the _Weights cache keeps it alive)."""
+    hit = getattr(B, "_efl_x3", None)
+    if hit is None:
+        hit = _split3(B, N, K, False, True)
+        try:
+            B._efl_x3 = hit
+        except AttributeError:
+            pass
+    return hit
+
+
 def _gemm_nt(epi, A, B, bias, C, ldc, C0, ldc0, nsplit, M, N, K):
     if A.dtype == torch.float32:
+        if _x3_ok(N, K) and epi in (0, 1) and M > 0:   # accurate tensor-core mode: fp32 in, fp32 out, 3x K
+            from . import tc_gemm
+            A3, B3 = _split3(A, M, K, False, False), _weight_x3(B, N, K)
+            if epi == 0:
+                tc_gemm.gemm_nt(1, A3, B3, bias, C, 8, C, ldc, N, M, N, 3 * K)
+            else:   # split epilogue: both parts are fp32 here, two launches over the two column ranges
+                tc_gemm.gemm_nt(1, A3, B3[:nsplit], None if bias is None else bias[:nsplit], C0, 8, C0, ldc0, nsplit, M,
+                                nsplit, 3 * K)
+                if N > nsplit:
+                    tc_gemm.gemm_nt(1, A3, B3[nsplit:], None if bias is None else bias[nsplit:], C, 8, C, ldc,
+                                    N - nsplit, M, N - nsplit, 3 * K)
+            return
         call("efl_gemm_nt_f32", epi, ptr(A), A.stride(0), ptr(B), B.stride(0), ptr(bias), ptr(C), ldc, ptr(C0), ldc0,
              nsplit, M, N, K, work=2.0 * M * N * K)
     else:
@@ -245,6 +285,11 @@ def _gemm_nt(epi, A, B, bias, C, ldc, C0, ldc0, nsplit, M, N, K):
 
 def _gemm_tn(A, B, C, accumulate, Mred, N1, N2):
     if A.dtype == torch.float32:
+        if _x3_ok(N1, N2) and Mred > 0 and C.stride(0) == N2:
+            from . import tc_gemm
+            tc_gemm.gemm_tn(_split3(A, Mred, N1, True, False), _split3(B, Mred, N2, True, True), C, accumulate, 3 * Mred,
+                            N1, N2)
+            return
         splits = LIB.efl_gemm_tn_splits(Mred)
         ws = torch.empty(splits * N1 * N2, dtype=torch.float32, device=A.device)
         call("efl_gemm_tn_f32", ptr(A), A.stride(0), ptr(B), B.stride(0), ptr(C), C.stride(0), int(accumulate), ptr(ws),
@@ -493,7 +538,7 @@ class EdgeAttentionFunction(torch.autograd.Function):
         x_dst = x_dst.contiguous()
         rad = rad.contiguous()
         dev = x_dst.device
-        dtype = torch.float32 if _PRECISION == "fp32" else torch.bfloat16
+        dtype = torch.bfloat16 if _PRECISION == "bf16" else torch.float32
         E = csr.num_edges
         Lc = (d.lmax + 1) ** 2
         out = torch.empty(csr.num_dst, Lc, d.heads * d.value_ch, dtype=torch.float32, device=dev)
@@ -1290,7 +1335,7 @@ class LinearFunction(torch.autograd.Function):
         x = x.contiguous().float()
         M, K = x.shape
         N = weight.shape[0]
-        tc = _PRECISION != "fp32" and K % 8 == 0 and N % 16 == 0 and M > 0
+        tc = _PRECISION == "bf16" and K % 8 == 0 and N % 16 == 0 and M > 0
         dt = torch.bfloat16 if tc else torch.float32
         xa = x.to(dt)
         w = weight.detach().to(dt).contiguous()

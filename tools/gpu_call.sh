@@ -24,6 +24,12 @@ smoke)
 bench)
   timeout 600 python bench.py --steps ${BENCH_STEPS:-10} --warmup 3 ${BENCH_ARGS:-} > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err; el "bench exit $?"
   cat gpurun_out/${TAG}_bench.json; tail -3 gpurun_out/${TAG}_bench.err ;;
+bench_x3)
+  timeout 600 python bench.py --steps 3 --warmup 3 --precision bf16x3 > gpurun_out/${TAG}_bench_bf16x3.json 2> gpurun_out/${TAG}_bench_bf16x3.err; el "bench bf16x3 exit $?"
+  cat gpurun_out/${TAG}_bench_bf16x3.json | cut -c1-1500; tail -3 gpurun_out/${TAG}_bench_bf16x3.err ;;
+bench_fp32)
+  timeout 900 python bench.py --steps 2 --warmup 3 --precision fp32 --no-cpu-baseline > gpurun_out/${TAG}_bench_fp32.json 2> gpurun_out/${TAG}_bench_fp32.err; el "bench fp32 exit $?"
+  cat gpurun_out/${TAG}_bench_fp32.json | cut -c1-1500; tail -3 gpurun_out/${TAG}_bench_fp32.err ;;
 ref)
   timeout 400 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${TAG}_bench_ref.json 2> gpurun_out/${TAG}_bench_ref.err; el "reference arm exit $?"
   cut -c1-500 gpurun_out/${TAG}_bench_ref.json ;;

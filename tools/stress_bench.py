@@ -78,6 +78,13 @@ def main():
     ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"])
     ap.add_argument("--profile", action="store_true", help="CUDA-event time per entry point (rank 0)")
     args = ap.parse_args()
+    line = run(args)
+    if line is not None:
+        print(json.dumps(line), flush=True)
+
+
+def run(args):
+    """The measurement itself (also behind ``bench.py --config 5``); returns the result dict on rank 0."""
     import torch.distributed as dist
     world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
     torch.cuda.set_device(local)
@@ -127,8 +134,9 @@ def main():
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot)
     finite = bool(torch.isfinite(loss))
+    line = None
     if rank == 0:
-        print(json.dumps({
+        line = ({
             "workload": f"config 5 stress: {args.complexes} x {args.atoms}-atom complexes per GPU, lmax {args.lmax}, "
                         f"mmax 2, 8 A radius graph from the cell-list kernel, fwd+bwd+Adam, {args.precision}",
             "n_gpus": world, "edges_total": int(tot), "edges_per_gpu": edges, "nodes_per_gpu": int(g["z_p"].numel()),
@@ -137,9 +145,10 @@ def main():
             "gpu_launches_per_step": (_lib.launch_count - n0) // args.steps,
             "peak_mem_GB": round(torch.cuda.max_memory_allocated() / 2 ** 30, 2),
             "kernel_ms_per_step": {k: round(v["ms"] / args.steps, 3)
-                                   for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}}), flush=True)
+                                   for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}})
     if world > 1:
         dist.destroy_process_group()
+    return line
 
 
 if __name__ == "__main__":
