@@ -157,8 +157,20 @@ int efl_tc_gemm_tn_splits(int Mred, int N1, int N2);
 /* CTA-pair (cta_group::2, 256-row tiles) variant of efl_tc_gemm_nt: 0 off (default), 1 large problems, 2 always.
  * Returns the previous mode; a mode outside 0..2 only queries. */
 int efl_tc_gemm_pair_mode(int mode);
+/* Operand ring size of the tcgen05 GEMM CTAs in KB (96..192, default 192 or EFL_GEMM_RING_KB): a smaller ring leaves
+ * shared memory for HBM-bound kernels of another stream to co-reside with the persistent GEMM.  Returns the previous value. */
+int efl_tc_gemm_ring_kb(int kb);
 int efl_tc_gemm_tn(const void* A, long long lda, const void* B, long long ldb, float* C, long long ldc,
                    int accumulate, float* workspace, int Mred, int N1, int N2, void* stream);
+
+/* Operand kernels of the node-level S2 activation on grids outside the fused tcgen05 node kernel (lmax = 8, config 5;
+ * FeedForwardNetwork :234-270 with SeparableS2Activation :1757-1773 as two plain GEMMs over (node, channel) rows):
+ * pack x [N,L,CH] fp32 -> bf16 rows [(n,c), LP] (zero padded, optionally l = 0 zeroed); unpack back to fp32 with the
+ * l = 0 row replaced by SiLU(gate [N,CH]) when gate != NULL; efl_bf16_silu: a <- SiLU(a) (mode 0) or
+ * a <- a * SiLU'(b) (mode 1) in place on bf16 arrays. */
+int efl_node_rows_pack(const float* x, int N, int L, int CH, int LP, int zero_row0, void* out, void* stream);
+int efl_node_rows_unpack(const void* yt, int N, int L, int CH, int LP, const float* gate, float* y, void* stream);
+int efl_bf16_silu(void* a, const void* b, long long n, int mode, void* stream);
 
 /* bf16x3 operand preparation (accurate tensor-core mode): fp32 x [rows, cols] -> three bf16 copies (hi, hi, lo) for an
  * A operand or (hi, lo, hi) for a B operand (second = 1), side by side along the columns (stack = 0, NT GEMMs) or one

@@ -38,6 +38,9 @@ SIGNATURES = {
     "efl_gemm_tn_f32": "plplplipiiip",
     "efl_colsum": "ipliipipp",
     "efl_split3": "plliplii" "p",
+    "efl_node_rows_pack": "piiiiipp",
+    "efl_node_rows_unpack": "piiiippp",
+    "efl_bf16_silu": "pplip",
     "efl_tc_gemm_nt": "iplplpplpliiiip",
     "efl_tc_gemm_tn": "plplplipiiip",
     "efl_s2act_tc": "iiii" "ppp" "l" "pp" "l" "pp" "i" "p",
@@ -85,6 +88,8 @@ def _load():
     lib.efl_tc_gemm_tn_splits.restype = _I
     lib.efl_tc_gemm_pair_mode.argtypes = [_I]
     lib.efl_tc_gemm_pair_mode.restype = _I
+    lib.efl_tc_gemm_ring_kb.argtypes = [_I]
+    lib.efl_tc_gemm_ring_kb.restype = _I
     lib.efl_radial_mlp_part_size.argtypes = [_I, _I]
     lib.efl_radial_mlp_part_size.restype = _I
     lib.efl_radial_hidden_part_size.argtypes = [_I]

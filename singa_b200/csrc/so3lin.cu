@@ -108,3 +108,114 @@ extern "C" int efl_so3_select(const float* ye, long long ld, const float* bias, 
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Operand kernels of the node-level S2 activation on grids the fused tcgen05 node kernel is not built for (lmax = 8:
+// 81 coefficients x 342 grid points, BASELINE.json config 5).  The two projections run as plain tcgen05 GEMMs over
+// all (node, channel) rows (ops._node_s2_gemm_*); these kernels replace the torch transposes / casts / SiLU calls
+// around them (about 20 full passes over [N, L, CH] per layer, 65 ms of a 292 ms step in round 1):
+//   pack      x [N, L, CH] fp32 -> bf16 rows [(n, c), LP] (coefficients contiguous, zero padded; optionally l = 0 zeroed)
+//   unpack    bf16 rows -> y [N, L, CH] fp32, with the l = 0 row replaced by SiLU(gate) when a gate is given
+//   silu      grid <- SiLU(grid) in place (bf16)
+//   dsilu_mul dact <- dact * SiLU'(grid) in place (bf16)
+// All HBM-bound; pack / unpack transpose through a padded shared-memory tile so both sides stay coalesced.
+// ---------------------------------------------------------------------------------------------------
+namespace efl {
+
+constexpr int NS2_TC = 32;   // channels per tile
+
+__global__ void __launch_bounds__(256) node_rows_pack_kernel(const float* __restrict__ x, int L, int CH, int LP,
+                                                             int zero_row0, __nv_bfloat16* __restrict__ out) {
+  extern __shared__ float tile[];   // [L][NS2_TC + 1]
+  const int n = blockIdx.x, c0 = blockIdx.y * NS2_TC;
+  const float* xn = x + (size_t)n * L * CH;
+  for (int i = threadIdx.x; i < L * NS2_TC; i += blockDim.x) {
+    const int l = i / NS2_TC, c = i % NS2_TC;
+    tile[l * (NS2_TC + 1) + c] = (c0 + c < CH) ? xn[(size_t)l * CH + c0 + c] : 0.f;
+  }
+  __syncthreads();
+  __nv_bfloat16* o = out + ((size_t)n * CH + c0) * LP;
+  for (int i = threadIdx.x; i < NS2_TC * LP; i += blockDim.x) {
+    const int c = i / LP, l = i % LP;
+    if (c0 + c < CH) {
+      const float v = (l < L && !(zero_row0 && l == 0)) ? tile[l * (NS2_TC + 1) + c] : 0.f;
+      o[(size_t)c * LP + l] = __float2bfloat16_rn(v);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) node_rows_unpack_kernel(const __nv_bfloat16* __restrict__ yt, int L, int CH,
+                                                               int LP, const float* __restrict__ gate,
+                                                               float* __restrict__ y) {
+  extern __shared__ float tile[];   // [L][NS2_TC + 1]
+  const int n = blockIdx.x, c0 = blockIdx.y * NS2_TC;
+  const __nv_bfloat16* src = yt + ((size_t)n * CH + c0) * LP;
+  for (int i = threadIdx.x; i < NS2_TC * LP; i += blockDim.x) {
+    const int c = i / LP, l = i % LP;
+    if (l < L && c0 + c < CH) tile[l * (NS2_TC + 1) + c] = __bfloat162float(src[(size_t)c * LP + l]);
+  }
+  __syncthreads();
+  float* yn = y + (size_t)n * L * CH;
+  for (int i = threadIdx.x; i < L * NS2_TC; i += blockDim.x) {
+    const int l = i / NS2_TC, c = i % NS2_TC;
+    if (c0 + c < CH) {
+      float v = tile[l * (NS2_TC + 1) + c];
+      if (gate && l == 0) v = siluf_(gate[(size_t)n * CH + c0 + c]);
+      yn[(size_t)l * CH + c0 + c] = v;
+    }
+  }
+}
+
+// mode 0: a <- SiLU(a);  mode 1: a <- a * SiLU'(b)
+__global__ void __launch_bounds__(256) bf16_silu_kernel(__nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
+                                                        long long n8, int mode) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    uint4 va = reinterpret_cast<uint4*>(a)[i];
+    uint4 vb = mode ? reinterpret_cast<const uint4*>(b)[i] : va;
+    __nv_bfloat16* pa = reinterpret_cast<__nv_bfloat16*>(&va);
+    const __nv_bfloat16* pb = reinterpret_cast<const __nv_bfloat16*>(&vb);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float x = __bfloat162float(pa[j]);
+      pa[j] = __float2bfloat16_rn(mode ? x * dsiluf_(__bfloat162float(pb[j])) : siluf_(x));
+    }
+    reinterpret_cast<uint4*>(a)[i] = va;
+  }
+}
+
+}  // namespace efl
+
+extern "C" int efl_node_rows_pack(const float* x, int N, int L, int CH, int LP, int zero_row0, void* out,
+                                  void* stream) {
+  if (N <= 0) return EFL_OK;
+  EFL_REQUIRE(LP >= L && L <= 128, "efl_node_rows_pack: LP >= L, L <= 128");
+  dim3 grid(N, (CH + efl::NS2_TC - 1) / efl::NS2_TC);
+  efl::node_rows_pack_kernel<<<grid, 256, sizeof(float) * L * (efl::NS2_TC + 1), (cudaStream_t)stream>>>(
+      x, L, CH, LP, zero_row0, (__nv_bfloat16*)out);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+extern "C" int efl_node_rows_unpack(const void* yt, int N, int L, int CH, int LP, const float* gate, float* y,
+                                    void* stream) {
+  if (N <= 0) return EFL_OK;
+  EFL_REQUIRE(LP >= L && L <= 128, "efl_node_rows_unpack: LP >= L, L <= 128");
+  dim3 grid(N, (CH + efl::NS2_TC - 1) / efl::NS2_TC);
+  efl::node_rows_unpack_kernel<<<grid, 256, sizeof(float) * L * (efl::NS2_TC + 1), (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)yt, L, CH, LP, gate, y);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}
+
+// a, b: bf16 arrays of n elements (n % 8 == 0, 16-byte aligned).  mode 0: a <- SiLU(a); mode 1: a <- a * SiLU'(b).
+extern "C" int efl_bf16_silu(void* a, const void* b, long long n, int mode, void* stream) {
+  if (n <= 0) return EFL_OK;
+  EFL_REQUIRE(n % 8 == 0 && ((uintptr_t)a & 15) == 0 && (mode == 0 || ((uintptr_t)b & 15) == 0),
+              "efl_bf16_silu: n % 8 == 0 and 16-byte aligned arrays");
+  long long blocks = (n / 8 + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  efl::bf16_silu_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)a, (const __nv_bfloat16*)b,
+                                                                          n / 8, mode);
+  EFL_CHECK_LAUNCH();
+  return EFL_OK;
+}

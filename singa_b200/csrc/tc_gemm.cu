@@ -47,6 +47,8 @@ struct Params {
   int splits;
   int kb_per_split;
   int tma_c, tma_c0;  // output tensor maps valid: full-width blocks leave through TMA stores
+  int ring_bytes;     // operand ring size (<= STAGES * STAGE_BYTES): a smaller ring leaves shared memory for the
+                      // HBM-bound kernels of another stream to co-reside with the persistent GEMM CTAs
 };
 
 // PAIR: the two CTAs of a (2,1,1) cluster work on one 256-row tile with cta_group::2 MMAs: each CTA stages its own
@@ -58,7 +60,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                const __grid_constant__ CUtensorMap mapC, const __grid_constant__ CUtensorMap mapC0, const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.ring_bytes);
   uint64_t* full = bars;                     // [MAX_STAGES]
   uint64_t* empty = bars + MAX_STAGES;       // [MAX_STAGES]
   uint64_t* tfull = bars + 2 * MAX_STAGES;   // [2]
@@ -111,7 +113,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   // is as deep as the 192 KB operand region allows: the operand loads are latency-bound (~2500 cycles from "stage
   // free" to "stage full" under load, ncu r1i), so bytes in flight, not stage count, set the pace.
   const int stage_bytes = tn ? (2 + b_blocks) * 64 * 128 : A_BYTES + bn_cta * 128;
-  const int nstage = min(MAX_STAGES, (STAGES * STAGE_BYTES) / stage_bytes);
+  const int nstage = min(MAX_STAGES, p.ring_bytes / stage_bytes);
   const uint32_t stage_tx = (uint32_t)stage_bytes * (PAIR ? 2u : 1u);
 
   if (warp == 0) {
@@ -213,7 +215,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     // instruction and made the LSU, not the tensor pipe, the limiter of the short-K shapes.
     const int q = warp & 3;
     const int eh = (warp - 4) >> 2;
-    uint8_t* stg = smem + STAGES * STAGE_BYTES + 1024 + (warp - 4) * STG_BYTES;
+    uint8_t* stg = smem + p.ring_bytes + 1024 + (warp - 4) * STG_BYTES;
     const uint32_t stg_w = smem_u32(stg) + (uint32_t)lane * 128u;   // this lane's row (write phase)
     const int swz = lane & 7;
     // Full-width blocks (128 bytes per row) leave through ONE TMA store of the staging tile (the XOR swizzle above
@@ -516,8 +518,28 @@ extern "C" int efl_tc_gemm_pair_mode(int mode) {
   return prev;
 }
 
+// Operand ring budget: EFL_GEMM_RING_KB (default 192 = 4 x 48 KB) or efl_tc_gemm_ring_kb(); multiples of 48 KB keep
+// every stage shape whole.  144 leaves ~45 KB of shared memory per SM for co-resident kernels of another stream.
+static int g_ring_kb = -1;
+static int ring_bytes() {
+  if (g_ring_kb < 0) {
+    const char* e = getenv("EFL_GEMM_RING_KB");
+    g_ring_kb = e ? atoi(e) : 192;
+    if (g_ring_kb < 96 || g_ring_kb > 192) g_ring_kb = 192;
+  }
+  return g_ring_kb * 1024;
+}
+extern "C" int efl_tc_gemm_ring_kb(int kb) {
+  const int prev = ring_bytes() / 1024;
+  if (kb >= 96 && kb <= 192) g_ring_kb = kb;
+  return prev;
+}
+
 static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& mc0,
-                  const Params& p, int work_items, bool pair, cudaStream_t s) {
+                  const Params& p_in, int work_items, bool pair, cudaStream_t s) {
+  Params p = p_in;
+  p.ring_bytes = ring_bytes();
+  const int smem_bytes = p.ring_bytes + 1024 + 1024 + 8 * efl::tc::STG_BYTES;
   static unsigned long long attr_set = 0;
   if (efl_first_use_on_device(&attr_set)) {
     cudaError_t e = cudaFuncSetAttribute(efl::tc::tc_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -532,7 +554,7 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMa
   }
   if (!pair) {
     const int grid = work_items < efl_num_sms() ? work_items : efl_num_sms();
-    efl::tc::tc_gemm_kernel<false><<<grid, efl::tc::NUM_THREADS, efl::tc::SMEM_BYTES, s>>>(ma, mb, mc, mc0, p);
+    efl::tc::tc_gemm_kernel<false><<<grid, efl::tc::NUM_THREADS, smem_bytes, s>>>(ma, mb, mc, mc0, p);
     EFL_CHECK_LAUNCH();
     return EFL_OK;
   }
@@ -542,7 +564,7 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMa
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(2 * pairs));
   cfg.blockDim = dim3(efl::tc::NUM_THREADS);
-  cfg.dynamicSmemBytes = efl::tc::SMEM_BYTES;
+  cfg.dynamicSmemBytes = smem_bytes;
   cfg.stream = s;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;

@@ -756,16 +756,20 @@ def _grid_operands(to_g, from_g):
     return hit
 
 
-def _rows_from_nodes(x, LP):
-    """[N, L, CH] -> bf16 [N*CH, LP] (coefficients contiguous per (node, channel) row, zero padded)."""
+def _rows_from_nodes(x, LP, zero_row0=False):
+    """[N, L, CH] fp32 -> bf16 [N*CH, LP] (coefficients contiguous per (node, channel) row, zero padded)."""
     N, L, CH = x.shape
-    xt = torch.zeros(N, CH, LP, dtype=torch.bfloat16, device=x.device)
-    xt[:, :, :L] = x.transpose(1, 2)
-    return xt.view(N * CH, LP)
+    xt = torch.empty(N * CH, LP, dtype=torch.bfloat16, device=x.device)
+    call("efl_node_rows_pack", ptr(x), N, L, CH, LP, int(zero_row0), ptr(xt), work=N * L * CH * 4.0 + N * CH * LP * 2.0)
+    return xt
 
 
-def _nodes_from_rows(yt, N, L, CH):
-    return yt.view(N, CH, -1)[:, :, :L].transpose(1, 2).float().contiguous()
+def _nodes_from_rows(yt, N, L, CH, gate=None):
+    """bf16 [N*CH, LP] -> fp32 [N, L, CH]; with ``gate`` the l = 0 row is SiLU(gate) (EF_layers.py:1765-1773)."""
+    y = torch.empty(N, L, CH, dtype=torch.float32, device=yt.device)
+    call("efl_node_rows_unpack", ptr(yt), N, L, CH, yt.shape[1], ptr(gate), ptr(y),
+         work=N * L * CH * 4.0 + N * CH * yt.shape[1] * 2.0)
+    return y
 
 
 def _bf16_gemm(A, B, M, N, K):
@@ -779,14 +783,12 @@ def _node_s2_gemm_forward(gate, x, to_g, from_g):
     Tb, _, _, FbT = _grid_operands(to_g, from_g)
     GP, LP = Tb.shape
     R = N * CH
-    xt = _rows_from_nodes(x, LP)
+    xt = _rows_from_nodes(x.contiguous().float(), LP)
     grid = _bf16_gemm(xt, Tb, R, GP, LP)                         # to_grid
-    act = torch.nn.functional.silu(grid)
+    call("efl_bf16_silu", ptr(grid), None, grid.numel(), 0, work=grid.numel() * 4.0)
+    yt = _bf16_gemm(grid, FbT, R, LP, GP)                        # from_grid
     del grid
-    yt = _bf16_gemm(act, FbT, R, LP, GP)                         # from_grid
-    y = _nodes_from_rows(yt, N, L, CH)
-    y[:, 0, :] = torch.nn.functional.silu(gate)                  # l = 0 row <- SiLU(gate) (EF_layers.py:1765-1773)
-    return y, xt
+    return _nodes_from_rows(yt, N, L, CH, gate), xt
 
 
 def _node_s2_gemm_backward(gate, xt, to_g, from_g, dy, shape):
@@ -794,15 +796,14 @@ def _node_s2_gemm_backward(gate, xt, to_g, from_g, dy, shape):
     Tb, TbT, Fb, _ = _grid_operands(to_g, from_g)
     GP, LP = Tb.shape
     R = N * CH
-    dy = dy.float()
+    dy = dy.contiguous().float()
     dgate = torch.ops.aten.silu_backward(dy[:, 0, :].contiguous(), gate)
-    dyt = _rows_from_nodes(dy, LP)
-    dyt[:, 0] = 0                                                # the l = 0 output row does not come from the grid
+    dyt = _rows_from_nodes(dy, LP, zero_row0=True)               # the l = 0 output row does not come from the grid
     grid = _bf16_gemm(xt, Tb, R, GP, LP)                         # recomputed, not saved
     dact = _bf16_gemm(dyt, Fb, R, GP, LP)
-    dgrid = torch.ops.aten.silu_backward(dact, grid)
-    del grid, dact
-    dxt = _bf16_gemm(dgrid, TbT, R, LP, GP)
+    call("efl_bf16_silu", ptr(dact), ptr(grid), dact.numel(), 1, work=dact.numel() * 6.0)   # d grid, in place
+    del grid
+    dxt = _bf16_gemm(dact, TbT, R, LP, GP)
     return dgate, _nodes_from_rows(dxt, N, L, CH)
 
 

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
 def test_python_binding_covers_header():
     from singa_b200 import _lib
     bound = set(_lib.SIGNATURES) | {"efl_version", "efl_last_error_string", "efl_gemm_tn_splits", "efl_device_cc",
-                                    "efl_tc_gemm_tn_splits", "efl_tc_gemm_pair_mode", "efl_rotate_back_parts", "efl_radial_mlp_part_size", "efl_radius_graph_temp_bytes", "efl_csr_temp_bytes", "efl_radial_hidden_part_size"}
+                                    "efl_tc_gemm_tn_splits", "efl_tc_gemm_pair_mode", "efl_tc_gemm_ring_kb", "efl_rotate_back_parts", "efl_radial_mlp_part_size", "efl_radius_graph_temp_bytes", "efl_csr_temp_bytes", "efl_radial_hidden_part_size"}
     assert set(declared_symbols()) <= bound, set(declared_symbols()) - bound
     assert _lib.LIB.efl_version() >= 100
 

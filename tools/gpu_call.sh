@@ -30,6 +30,12 @@ bench_x3)
 bench_fp32)
   timeout 900 python bench.py --steps 2 --warmup 3 --precision fp32 --no-cpu-baseline > gpurun_out/${TAG}_bench_fp32.json 2> gpurun_out/${TAG}_bench_fp32.err; el "bench fp32 exit $?"
   cat gpurun_out/${TAG}_bench_fp32.json | cut -c1-1500; tail -3 gpurun_out/${TAG}_bench_fp32.err ;;
+bench2)
+  timeout 600 python bench.py --steps ${BENCH_STEPS:-10} --warmup 5 --no-cpu-baseline > gpurun_out/${TAG}_bench_run2.json 2> gpurun_out/${TAG}_bench_run2.err; el "bench (second run) exit $?"
+  python -c "import json;b=json.load(open('gpurun_out/${TAG}_bench_run2.json'));print('run2 ms/step',b['ms_per_step'],'e2e',b['e2e']['ms_per_step'],b['allocator'],b['clocks'])" ;;
+config5)
+  timeout 600 python bench.py --config 5 --steps 3 --warmup 2 > gpurun_out/${TAG}_bench_config5.json 2> gpurun_out/${TAG}_bench_config5.err; el "bench config 5 exit $?"
+  cut -c1-1800 gpurun_out/${TAG}_bench_config5.json; tail -3 gpurun_out/${TAG}_bench_config5.err ;;
 ref)
   timeout 400 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${TAG}_bench_ref.json 2> gpurun_out/${TAG}_bench_ref.err; el "reference arm exit $?"
   cut -c1-500 gpurun_out/${TAG}_bench_ref.json ;;
@@ -61,6 +67,9 @@ ncu_src)    # source-level capture of one kernel: NCU_KERNEL=regex NCU_CMD="pyth
   el "ncu src exit $?"
   ncu -i /tmp/${TAG}_src.ncu-rep --page source --csv --print-source sass > gpurun_out/${TAG}_src_sass.csv 2>/dev/null
   ncu -i /tmp/${TAG}_src.ncu-rep --page raw --csv > gpurun_out/${TAG}_src_raw.csv 2>/dev/null ;;
+overlap)
+  timeout 300 python tools/overlap_probe.py > gpurun_out/${TAG}_overlap_probe.jsonl 2>&1; el "overlap_probe exit $?"
+  cat gpurun_out/${TAG}_overlap_probe.jsonl | tail -5 ;;
 probe)
   timeout 300 python tools/e2e_probe.py > gpurun_out/${TAG}_e2e_probe.txt 2>&1; el "e2e_probe exit $?"
   cat gpurun_out/${TAG}_e2e_probe.txt | tail -6 ;;
