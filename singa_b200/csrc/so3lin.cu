@@ -122,8 +122,15 @@ extern "C" int efl_so3_select(const float* ye, long long ld, const float* bias, 
 // ---------------------------------------------------------------------------------------------------
 namespace efl {
 
-constexpr int NS2_TC = 32;   // channels per tile
+constexpr int NS2_TC = 64;   // channels per tile
 
+__device__ __forceinline__ float silu_fast_(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float dsilu_fast_(float x) {
+  const float s = __fdividef(1.0f, 1.0f + __expf(-x));
+  return s * fmaf(x, 1.0f - s, 1.0f);
+}
+
+// LP is even; a thread writes / reads two adjacent coefficients of one (node, channel) row as one bf16x2 word
 __global__ void __launch_bounds__(256) node_rows_pack_kernel(const float* __restrict__ x, int L, int CH, int LP,
                                                              int zero_row0, __nv_bfloat16* __restrict__ out) {
   extern __shared__ float tile[];   // [L][NS2_TC + 1]
@@ -134,12 +141,15 @@ __global__ void __launch_bounds__(256) node_rows_pack_kernel(const float* __rest
     tile[l * (NS2_TC + 1) + c] = (c0 + c < CH) ? xn[(size_t)l * CH + c0 + c] : 0.f;
   }
   __syncthreads();
-  __nv_bfloat16* o = out + ((size_t)n * CH + c0) * LP;
-  for (int i = threadIdx.x; i < NS2_TC * LP; i += blockDim.x) {
-    const int c = i / LP, l = i % LP;
+  const int half = LP >> 1;
+  uint32_t* o = reinterpret_cast<uint32_t*>(out + ((size_t)n * CH + c0) * LP);
+  for (int i = threadIdx.x; i < NS2_TC * half; i += blockDim.x) {
+    const int c = i / half, l = (i % half) << 1;
     if (c0 + c < CH) {
-      const float v = (l < L && !(zero_row0 && l == 0)) ? tile[l * (NS2_TC + 1) + c] : 0.f;
-      o[(size_t)c * LP + l] = __float2bfloat16_rn(v);
+      const float v0 = (l < L && !(zero_row0 && l == 0)) ? tile[l * (NS2_TC + 1) + c] : 0.f;
+      const float v1 = (l + 1 < L) ? tile[(l + 1) * (NS2_TC + 1) + c] : 0.f;
+      __nv_bfloat162 h = __floats2bfloat162_rn(v0, v1);
+      o[(size_t)c * half + (l >> 1)] = *reinterpret_cast<uint32_t*>(&h);
     }
   }
 }
@@ -147,12 +157,17 @@ __global__ void __launch_bounds__(256) node_rows_pack_kernel(const float* __rest
 __global__ void __launch_bounds__(256) node_rows_unpack_kernel(const __nv_bfloat16* __restrict__ yt, int L, int CH,
                                                                int LP, const float* __restrict__ gate,
                                                                float* __restrict__ y) {
-  extern __shared__ float tile[];   // [L][NS2_TC + 1]
+  extern __shared__ float tile[];   // [L + 1][NS2_TC + 1]
   const int n = blockIdx.x, c0 = blockIdx.y * NS2_TC;
-  const __nv_bfloat16* src = yt + ((size_t)n * CH + c0) * LP;
-  for (int i = threadIdx.x; i < NS2_TC * LP; i += blockDim.x) {
-    const int c = i / LP, l = i % LP;
-    if (l < L && c0 + c < CH) tile[l * (NS2_TC + 1) + c] = __bfloat162float(src[(size_t)c * LP + l]);
+  const int half = LP >> 1;
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(yt + ((size_t)n * CH + c0) * LP);
+  for (int i = threadIdx.x; i < NS2_TC * half; i += blockDim.x) {
+    const int c = i / half, l = (i % half) << 1;
+    if (l < L && c0 + c < CH) {
+      const uint32_t w = src[(size_t)c * half + (l >> 1)];
+      tile[l * (NS2_TC + 1) + c] = __uint_as_float(w << 16);
+      tile[(l + 1) * (NS2_TC + 1) + c] = __uint_as_float(w & 0xffff0000u);   // row L is scratch when L is odd
+    }
   }
   __syncthreads();
   float* yn = y + (size_t)n * L * CH;
@@ -160,7 +175,7 @@ __global__ void __launch_bounds__(256) node_rows_unpack_kernel(const __nv_bfloat
     const int l = i / NS2_TC, c = i % NS2_TC;
     if (c0 + c < CH) {
       float v = tile[l * (NS2_TC + 1) + c];
-      if (gate && l == 0) v = siluf_(gate[(size_t)n * CH + c0 + c]);
+      if (gate && l == 0) v = silu_fast_(gate[(size_t)n * CH + c0 + c]);
       yn[(size_t)l * CH + c0 + c] = v;
     }
   }
@@ -177,7 +192,7 @@ __global__ void __launch_bounds__(256) bf16_silu_kernel(__nv_bfloat16* __restric
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float x = __bfloat162float(pa[j]);
-      pa[j] = __float2bfloat16_rn(mode ? x * dsiluf_(__bfloat162float(pb[j])) : siluf_(x));
+      pa[j] = __float2bfloat16_rn(mode ? x * dsilu_fast_(__bfloat162float(pb[j])) : silu_fast_(x));
     }
     reinterpret_cast<uint4*>(a)[i] = va;
   }
@@ -188,7 +203,7 @@ __global__ void __launch_bounds__(256) bf16_silu_kernel(__nv_bfloat16* __restric
 extern "C" int efl_node_rows_pack(const float* x, int N, int L, int CH, int LP, int zero_row0, void* out,
                                   void* stream) {
   if (N <= 0) return EFL_OK;
-  EFL_REQUIRE(LP >= L && L <= 128, "efl_node_rows_pack: LP >= L, L <= 128");
+  EFL_REQUIRE(LP >= L && L <= 128 && LP % 2 == 0, "efl_node_rows_pack: LP >= L, LP even, L <= 128");
   dim3 grid(N, (CH + efl::NS2_TC - 1) / efl::NS2_TC);
   efl::node_rows_pack_kernel<<<grid, 256, sizeof(float) * L * (efl::NS2_TC + 1), (cudaStream_t)stream>>>(
       x, L, CH, LP, zero_row0, (__nv_bfloat16*)out);
@@ -199,9 +214,9 @@ extern "C" int efl_node_rows_pack(const float* x, int N, int L, int CH, int LP, 
 extern "C" int efl_node_rows_unpack(const void* yt, int N, int L, int CH, int LP, const float* gate, float* y,
                                     void* stream) {
   if (N <= 0) return EFL_OK;
-  EFL_REQUIRE(LP >= L && L <= 128, "efl_node_rows_unpack: LP >= L, L <= 128");
+  EFL_REQUIRE(LP >= L && L <= 128 && LP % 2 == 0, "efl_node_rows_unpack: LP >= L, LP even, L <= 128");
   dim3 grid(N, (CH + efl::NS2_TC - 1) / efl::NS2_TC);
-  efl::node_rows_unpack_kernel<<<grid, 256, sizeof(float) * L * (efl::NS2_TC + 1), (cudaStream_t)stream>>>(
+  efl::node_rows_unpack_kernel<<<grid, 256, sizeof(float) * (L + 1) * (efl::NS2_TC + 1), (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)yt, L, CH, LP, gate, y);
   EFL_CHECK_LAUNCH();
   return EFL_OK;

@@ -7,7 +7,8 @@
 //   NT : C[i, n] = sum_k A[i, k] B[n, k]     both operands K-major      (forward, dgrad)
 //   TN : P[z][n1, n2] = sum_{i in split z} A[i, n1] B[i, n2]   both operands MN-major (wgrad, split over edges,
 //        partials reduced in fixed order by splitk_reduce)
-// NT epilogues as in gemm_simt.cu (0 plain, 1 split, 2 complex combine); outputs bf16 (fp32 for the split part).
+// NT epilogues as in gemm_simt.cu (0 plain, 1 split, 2 complex combine) plus 3 = plain with SiLU; outputs bf16 (fp32
+// for the split part).
 //
 // Replaces the cuBLAS mm calls under SO2_Convolution / SO2_m_Convolution (reference EF_layers.py:721-729, 807-875).
 #include <string.h>
@@ -289,6 +290,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 } else {
 #pragma unroll
                   for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
+                }
+                if (p.epi == 3) {   // SiLU before the bf16 store (node-level S2 to_grid GEMM, ops._node_s2_gemm_forward)
+#pragma unroll
+                  for (int j = 0; j < 16; ++j) f[j] = __fdividef(f[j], 1.0f + __expf(-f[j]));
                 }
                 if (kind == 1) {
 #pragma unroll
@@ -589,7 +594,7 @@ extern "C" int efl_tc_gemm_nt(int epilogue, const void* A, long long lda, const 
   if (M <= 0 || N <= 0) return EFL_OK;
   const int bn = pick_bn(N);
   EFL_REQUIRE(bn > 0, "efl_tc_gemm_nt: N must be a multiple of 16");
-  EFL_REQUIRE(epilogue >= 0 && epilogue <= 2, "efl_tc_gemm_nt: unknown epilogue");
+  EFL_REQUIRE(epilogue >= 0 && epilogue <= 3, "efl_tc_gemm_nt: unknown epilogue");
   EFL_REQUIRE(epilogue != 2 || (M % 2 == 0), "efl_tc_gemm_nt: complex epilogue needs even M");
   EFL_REQUIRE(epilogue != 1 || (nsplit % 16 == 0), "efl_tc_gemm_nt: nsplit must be a multiple of 16");
   EFL_REQUIRE((ldc % 8) == 0 && ((uintptr_t)C & 15) == 0, "efl_tc_gemm_nt: C must be 16-byte aligned with ldc % 8 == 0");

@@ -784,8 +784,8 @@ def _node_s2_gemm_forward(gate, x, to_g, from_g):
     GP, LP = Tb.shape
     R = N * CH
     xt = _rows_from_nodes(x.contiguous().float(), LP)
-    grid = _bf16_gemm(xt, Tb, R, GP, LP)                         # to_grid
-    call("efl_bf16_silu", ptr(grid), None, grid.numel(), 0, work=grid.numel() * 4.0)
+    grid = torch.empty(R, GP, dtype=torch.bfloat16, device=x.device)
+    _gemm_nt(3, xt, Tb, None, grid, GP, None, 0, 0, R, GP, LP)   # to_grid with SiLU in the GEMM epilogue
     yt = _bf16_gemm(grid, FbT, R, LP, GP)                        # from_grid
     del grid
     return _nodes_from_rows(yt, N, L, CH, gate), xt
