@@ -535,6 +535,8 @@ def main():
                         "traffic_unit": traffic_note,
                         "algorithmic_per_launch": per_launch_work,
                         "algorithmic_unit": "FLOP (2*M*N*K)" if tensor else "bytes",
+                        "algorithmic_bytes_per_launch": (d.get("bytes", 0.0) / max(d["calls"], 1)) if tensor
+                        else per_launch_work,
                         "ms_per_launch": per_launch_s * 1e3,
                         "peak_source": pk["source"], "share_of_step": d["ms"] / (ms_dev * args.steps),
                         "launches": d["calls"]}

@@ -144,22 +144,24 @@ def start_profile(only=None):
 
 
 def stop_profile():
-    """-> {name: dict(ms=total ms, calls=n, work=sum of algorithmic work units passed by the caller)}"""
+    """-> {name: dict(ms=total ms, calls=n, work=sum of algorithmic work units, bytes=sum of algorithmic bytes)}"""
     global _profile, _profile_only
     rec, _profile, _profile_only = _profile or [], None, None
     torch.cuda.synchronize()
     out = {}
-    for name, work, a, b in rec:
-        d = out.setdefault(name, dict(ms=0.0, calls=0, work=0.0))
+    for name, work, nbytes, a, b in rec:
+        d = out.setdefault(name, dict(ms=0.0, calls=0, work=0.0, bytes=0.0))
         d["ms"] += a.elapsed_time(b)
         d["calls"] += 1
         d["work"] += work
+        d["bytes"] += nbytes
     return out
 
 
-def call(name: str, *args, work: float = 0.0, tag: str = None):
+def call(name: str, *args, work: float = 0.0, nbytes: float = 0.0, tag: str = None):
     """Invoke an entry point; the trailing stream argument is appended here.  ``work`` is the algorithmic
-    FLOPs (GEMMs) or bytes (HBM-bound kernels) of this call, used only by the profiler."""
+    FLOPs (GEMMs) or bytes (HBM-bound kernels) of this call and ``nbytes`` the algorithmic operand + result bytes of a
+    GEMM (so its measured DRAM traffic has something to be set against); both used only by the profiler."""
     global launch_count
     launch_count += _LAUNCHES.get(name, 1)
     if _profile is not None and (_profile_only is None or (tag or name) in _profile_only):
@@ -168,7 +170,7 @@ def call(name: str, *args, work: float = 0.0, tag: str = None):
         a.record()
         rc = getattr(LIB, name)(*args, stream_ptr())
         b.record()
-        _profile.append((tag or name, work, a, b))
+        _profile.append((tag or name, work, nbytes, a, b))
     else:
         rc = getattr(LIB, name)(*args, stream_ptr())
     if rc != 0:

@@ -252,6 +252,32 @@ class LapPECache:
         return pe
 
 
+_LAP_CACHE = LapPECache(8)
+
+
+def lap_pe(data, node_type: str):
+    """Signature of the reference's ``lap_pe(data, node_type)`` (CProMG.py:562-571), for ``GAN.py`` running on this
+    module: the encodings carried by the batch (``data[node_type]['lap']``, dataset format) when present; otherwise
+    computed per complex on the host from ``ptr`` and the ``linked_to`` edges and cached on the complexes' positions
+    (the reference decomposes the whole batched graph on every call: DESIGN.md section 8, f-3)."""
+    assert node_type in ('protein_atoms', 'ligand_atoms'), "Node type not accepted"
+    store = data[node_type]
+    have = store.get('lap') if hasattr(store, 'get') else None
+    if have is not None:
+        return have
+    pos = store['pos']
+    ei = data[(node_type, 'linked_to', node_type)]['edge_index'].cpu().numpy()
+    ptr = store.get('ptr') if hasattr(store, 'get') else None
+    bounds = [0, pos.shape[0]] if ptr is None else [int(v) for v in ptr.cpu().tolist()]
+    pos_h = pos.detach().cpu().numpy()
+    out = []
+    for a, b in zip(bounds[:-1], bounds[1:]):
+        m = (ei[1] >= a) & (ei[1] < b)
+        key = (node_type, b - a, pos_h[a:b].tobytes())
+        out.append(_LAP_CACHE.get(key, ei[:, m] - a, b - a))
+    return torch.from_numpy(np.concatenate(out, axis=0)).to(pos.device)
+
+
 # ---------------------------------------------------------------------------------------------------------------
 # dense transformer blocks (PyTorch library ops; out of scope for kernels, SURVEY.md 2 #5)
 # ---------------------------------------------------------------------------------------------------------------

@@ -64,10 +64,12 @@ __global__ void __launch_bounds__(128) rotate_in_fwd_kernel(
   for (int i = 0; i < T::L; ++i) x[i] = __ldg(xp + i * C);
   __syncwarp();
   const float* rd = rad ? rad + (size_t)eo * rad_ld : nullptr;
-  // bias column of the SO(2) m = 0 GEMM: the ones_pad (<= 64) columns in front of the m = 0 block hold (1, 0, 0, ...),
-  // so the bias is a weight column forward and a row of the wgrad product backward (no bias epilogue, no column sum)
-  for (int t = lane; t < ones_pad; t += 32)
-    (reinterpret_cast<TOut*>(out.p[0]) + (size_t)el * out.pitch - ones_pad)[t] = from_f<TOut>(t == 0 ? 1.f : 0.f);
+  // this edge's row: one 64-bit multiply here, compile-time offsets below (per-store 64-bit address arithmetic cost
+  // 33 registers and 30 % of this kernel's speed: ncu r2f)
+  const size_t roff_e = (size_t)el * (size_t)out.pitch;
+  TOut* const row[3] = {reinterpret_cast<TOut*>(out.p[0]) + roff_e + lane,
+                        reinterpret_cast<TOut*>(out.p[MMAX >= 1 ? 1 : 0]) + roff_e + lane,
+                        reinterpret_cast<TOut*>(out.p[MMAX >= 2 ? 2 : 0]) + roff_e + lane};
 #pragma unroll
   for (int l = 0; l <= LMAX; ++l) {
 #pragma unroll
@@ -76,17 +78,20 @@ __global__ void __launch_bounds__(128) rotate_in_fwd_kernel(
       float acc = 0.f;
 #pragma unroll
       for (int n = 0; n < 2 * l + 1; ++n) acc = fmaf(wr[n], x[l * l + n], acc);
+      const int am = mp < 0 ? -mp : mp;
       if (rd) {
-        const int am = mp < 0 ? -mp : mp;
         // radial layout: [m=0 | m=1 | m=2 ...], each (LMAX+1-m)*CH wide (EF_layers.py:823,848)
         int roff = 0;
 #pragma unroll
         for (int k = 0; k < am; ++k) roff += (LMAX + 1 - k) * CH;
         acc *= __ldg(rd + roff + (l - am) * CH + lane);
       }
-      *op_ptr<LMAX, TOut>(out, el, l, mp, CH, lane) = from_f<TOut>(acc);
+      row[am][(mp < 0 ? (LMAX + 1 - am) * CH : 0) + (l - am) * CH] = from_f<TOut>(acc);
     }
   }
+  // bias column of the SO(2) m = 0 GEMM: the ones_pad (<= 64) columns in front of the m = 0 block hold (1, 0, 0, ...),
+  // so the bias is a weight column forward and a row of the wgrad product backward (no bias epilogue, no column sum)
+  for (int t = lane; t < ones_pad; t += 32) (row[0] - lane - ones_pad)[t] = from_f<TOut>(t == 0 ? 1.f : 0.f);
 }
 
 // ------------------------------------------------------------------------------------------

@@ -131,3 +131,18 @@ def test_laplacian_pe_is_an_eigenbasis_and_is_cached():
     assert np.allclose(pe.T @ pe, np.eye(8), atol=1e-4)
     small = cp.laplacian_pe(np.array([[0, 1], [1, 0]]), 2, 8)       # fewer nodes than k: zero padded
     assert small.shape == (2, 8) and np.all(small[:, 1:] == 0)
+
+
+def test_lap_pe_reference_signature_uses_batch_encodings_or_caches_per_complex():
+    g1, g2 = syn.make_complex(1, n_protein=30, n_ligand=8), syn.make_complex(2, n_protein=25, n_ligand=9)
+    b = syn.collate([g1, g2])
+    view = syn.GraphView(b)
+    pe = cp.lap_pe(view, "protein_atoms")
+    assert pe.shape == (55, 8)
+    one = cp.laplacian_pe(g2["ei_pp"].numpy(), 25, 8)
+    # per complex (not the batched graph), up to the cached random signs
+    assert np.allclose(np.abs(pe[30:].numpy()), np.abs(one), atol=1e-5)
+    misses = cp._LAP_CACHE.misses
+    assert torch.equal(cp.lap_pe(view, "protein_atoms"), pe) and cp._LAP_CACHE.misses == misses
+    carried = dict(b, lap_p=torch.zeros(55, 8))
+    assert cp.lap_pe(syn.GraphView(carried), "protein_atoms") is carried["lap_p"]
