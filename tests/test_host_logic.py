@@ -140,32 +140,6 @@ def test_batch_vector_and_props_equal_the_reference_loops():
     assert got.shape == (3, 3) and torch.equal(got, want.to(torch.float32))
 
 
-def test_node_s2_gemm_route_math_equals_dense_autograd(monkeypatch):
-    """ops._node_s2_gemm_forward/backward (the lmax-8 FeedForwardNetwork S2 activation as GEMMs over (node, channel)
-    rows): operand padding, transposes and the hand-written backward, with the tensor-core GEMM replaced by a torch
-    matmul of the same bf16 operands (no CUDA call), against autograd of the dense einsum formulation
-    (EF_layers.py:1736-1773)."""
-    from singa_b200 import ops
-    from singa_b200 import so3_constants as sc
-    monkeypatch.setattr(ops, "_bf16_gemm", lambda A, B, M, N, K: (A.float() @ B.float().t()).to(torch.bfloat16))
-    to, fr = sc.s2_grid_matrices(8, 8)
-    to_g = torch.tensor(to.reshape(342, 81), dtype=torch.float32)
-    from_g = torch.tensor(fr.reshape(342, 81), dtype=torch.float32)
-    N, CH = 4, 16
-    torch.manual_seed(0)
-    x = torch.randn(N, 81, CH, requires_grad=True)
-    gate = torch.randn(N, CH, requires_grad=True)
-    dy = torch.randn(N, 81, CH)
-    grid = torch.einsum('gl,nlc->ngc', to_g, x)
-    y = torch.einsum('gl,ngc->nlc', from_g, torch.nn.functional.silu(grid))
-    y = torch.cat((torch.nn.functional.silu(gate).unsqueeze(1), y[:, 1:]), dim=1)
-    y.backward(dy)
-    y2, xt = ops._node_s2_gemm_forward(gate.detach(), x.detach(), to_g, from_g)
-    dg, dx = ops._node_s2_gemm_backward(gate.detach(), xt, to_g, from_g, dy, (N, 81, CH))
-    rel = lambda a, b: float((a - b).abs().max() / a.abs().max())
-    assert rel(y.detach(), y2) < 2e-2 and rel(x.grad, dx) < 2e-2 and rel(gate.grad, dg) < 1e-6
-
-
 def test_init_edge_rot_mat_matches_reference_frames_on_cpu():
     """a1 on the host (the function is ~25 element-wise torch ops, device-agnostic): product init_edge_rot_mat fed the
     golden's random draws reproduces the frames written by the unmodified reference (EF_layers.py:2286-2351)."""
