@@ -26,7 +26,7 @@ from ._lib import LIB, call, check_cuda, ptr
 #             bf16 (hi, lo) and a*b taken as a_hi b_hi + a_hi b_lo + a_lo b_hi in ONE launch with a 3x longer
 #             reduction (csrc/split3.cu); everything else as in "fp32".  The accurate tensor-core mode of SURVEY.md 7.1.
 _PRECISION = "fp32"
-MAX_CHUNK_EDGES = 262144
+MAX_CHUNK_EDGES = int(os.environ.get("EFL_MAX_CHUNK_EDGES", "262144"))
 # Saved-for-backward policy (SURVEY.md 8a note): keep the chunk's edge activations (A, extra, hidden, S2 output,
 # values: ~25 KB/edge in bf16) when they fit a fraction of the free HBM, otherwise recompute them in backward.
 # "auto" | "save" | "recompute"
@@ -45,6 +45,7 @@ def set_save_policy(mode: str) -> None:
 
 
 _SAVED_BYTES = {}   # device index -> bytes of edge activations currently kept for backward
+_MEMINFO = {}       # device index -> (timestamp, free, total) of the last cudaMemGetInfo
 
 
 class _SavedChunks(list):
@@ -66,7 +67,15 @@ def _should_save(nbytes: int, device) -> bool:
     after the other: without the running total, batch 64 kept saving until the last layers had no memory left)."""
     if _SAVE_POLICY != "auto":
         return _SAVE_POLICY == "save"
-    free, total = torch.cuda.mem_get_info(device)
+    # cudaMemGetInfo costs ~0.6 ms of host time per call (5 ms per step over the 24 layer passes): ask the driver at
+    # most every 100 ms, the allocator's own counters (cheap) are read every time
+    import time
+    now = time.monotonic()
+    idx = torch.device(device).index or 0
+    hit = _MEMINFO.get(idx)
+    if hit is None or now - hit[0] > 0.1:
+        hit = _MEMINFO[idx] = (now,) + tuple(torch.cuda.mem_get_info(device))
+    free, total = hit[1], hit[2]
     cached = torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device)
     kept = _SAVED_BYTES.get(torch.device(device).index or 0, 0)
     return nbytes < _SAVE_FREE_FRACTION * (free + cached) and kept + nbytes < _SAVE_FREE_FRACTION * total
