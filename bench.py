@@ -457,17 +457,23 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, n):
+    per_step = {}
+
+    def timed(fn, n, tag=None):
+        """K steps between two events on the launching stream (the reported time); with ``tag`` an event after every
+        step as well, so that the spread of the individual steps is on record (transients show up there)."""
         barrier()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        for _ in range(n):
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(n + 1)]
+        evs[0].record()
+        for i in range(n):
             fn()
-        b.record()
+            evs[i + 1].record()
         barrier()
-        ms = torch.tensor([a.elapsed_time(b)], device=dev)
+        ms = torch.tensor([evs[0].elapsed_time(evs[n])], device=dev)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        if tag:
+            per_step[tag] = [round(evs[i].elapsed_time(evs[i + 1]), 2) for i in range(n)]
         return float(ms) / n
 
     for _ in range(max(args.warmup, 3)):
@@ -481,7 +487,7 @@ def main():
     # calls of a step cost enough host time to make the step host-bound on a slow box.  The per-entry-point
     # breakdown comes from a second, fully profiled pass of the same K steps below (outside the timed region).
     _lib.start_profile(only={DOMINANT})
-    ms_dev = timed(lambda: step(resident), args.steps)
+    ms_dev = timed(lambda: step(resident), args.steps, "device")
     prof = _lib.stop_profile()
     launches = _lib.launch_count - launches0
     mem1 = torch.cuda.memory_stats(dev)
@@ -497,7 +503,7 @@ def main():
 
     for _ in range(3):   # fresh input tensors every step: let the caching allocator and the CSR cache reach steady state
         e2e_step()
-    ms_e2e = timed(e2e_step, args.steps)
+    ms_e2e = timed(e2e_step, args.steps, "e2e")
     clocks = sampler.stop() if rank == 0 else None
     _lib.start_profile()
     ms_profiled = timed(lambda: step(resident), args.steps)
@@ -562,6 +568,7 @@ def main():
                     "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e},
             "gpu_launches": launches, "roofline": roofline, "clocks": clocks, "allocator": allocator,
             "step_tensor_tflops": step_tflops, "step_tensor_frac": step_tflops / pk["tensor"],
+            "step_ms_rank0": per_step,
             "kernel_ms_per_step": breakdown,
             "kernel_ms_per_step_source": f"second pass of {args.steps} steps with event pairs around every entry point "
                                          f"({ms_profiled:.1f} ms/step under that profile)",
