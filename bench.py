@@ -98,7 +98,11 @@ class ClockSampler:
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
-        self.index, self.proc, self.lines = index, None, []
+        self.index, self.proc, self.lines, self.first = index, None, [], 0
+
+    def mark(self):
+        """Samples from here on count (the sampler is started before the warm-up)."""
+        self.first = len(self.lines)
 
     def start(self):
         try:
@@ -117,7 +121,7 @@ class ClockSampler:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
         sm, mx, reasons = [], [], set()
-        for ln in self.lines:
+        for ln in self.lines[self.first:]:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -309,6 +313,7 @@ def config3(args):
     model = SINGA(default_config(), device=dev)
     syn.load_portable_parameters(model.embedding, 0)
     syn.load_portable_parameters_fanin(model.model, 1)
+    ops.reserve_workspace(0.6, dev)
     tr = Trainer(model, data, batch_size_per_rank=gb // world, shuffle=False, prefetch=2, device=dev)
     edges = sum(metric_edges({k: torch.empty(2, len(data[i][f"{k[3:]}_src"])) for k in ("ei_pp", "ei_ll", "ei_lp", "ei_pl")})
                 for i in tr.loader.indices)
@@ -476,11 +481,26 @@ def main():
             per_step[tag] = [round(evs[i].elapsed_time(evs[i + 1]), 2) for i in range(n)]
         return float(ms) / n
 
-    for _ in range(max(args.warmup, 3)):
-        step(resident)
     sampler = ClockSampler(local)
     if rank == 0:
-        sampler.start()
+        sampler.start()   # before the warm-up: nvidia-smi's own start-up (NVML init) must not land in the timed region
+    ops.reserve_workspace(0.6, dev)   # pool sized once, so that no step extends it (see ops.reserve_workspace)
+
+    def settle(fn, lo, hi=12):
+        """``lo`` warm-up steps, then more (at most ``hi``) until a step runs without a cudaMalloc: the timed region
+        starts from a steady memory footprint."""
+        done = 0
+        while done < lo + hi:
+            n0 = torch.cuda.memory_stats(dev).get("num_device_alloc", 0)
+            fn()
+            done += 1
+            if done >= lo and torch.cuda.memory_stats(dev).get("num_device_alloc", 0) == n0:
+                break
+        return done
+
+    warm_done = settle(lambda: step(resident), max(args.warmup, 3))
+    if rank == 0:
+        sampler.mark()
     launches0 = _lib.launch_count
     mem0 = torch.cuda.memory_stats(dev)
     # Event pairs in the timed region only around the dominant entry point (the roofline's kernel): pairs around all
@@ -501,8 +521,7 @@ def main():
         g = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
         return float(step(g).item())
 
-    for _ in range(3):   # fresh input tensors every step: let the caching allocator and the CSR cache reach steady state
-        e2e_step()
+    settle(e2e_step, 5)   # fresh input tensors every step: the caching allocator and the CSR cache reach steady state
     ms_e2e = timed(e2e_step, args.steps, "e2e")
     clocks = sampler.stop() if rank == 0 else None
     _lib.start_profile()
@@ -551,7 +570,7 @@ def main():
         step_tflops = 36.0e6 * tot_edges * LAYERS / world / (ms_dev * 1e-3) / 1e12
         line = {
             "metric": METRIC, "value": tot_edges / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True, "scaling": args.scaling,
+            "warmup": warm_done, "ms_per_step": ms_dev, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": {"bf16": "bf16", "bf16x3": "bf16x3 (error-compensated bf16 operands, fp32 storage)"}.get(
                 args.precision, "f32"), "data": "synthetic",
             "config": {"workload": WORKLOAD if args.scaling == "weak" else

@@ -37,6 +37,21 @@ _SAVE_FREE_FRACTION = float(os.environ.get("EFL_SAVE_FREE_FRACTION", "0.45"))
 STATS = {"save": 0, "recompute": 0}   # edge-attention forwards that kept / will recompute their edge activations
 
 
+def reserve_workspace(fraction: float = 0.6, device=None) -> int:
+    """Pre-size the caching allocator's pool: allocate ``fraction`` of the currently free device memory once and
+    release it to the pool.  The chunk workspaces of a step (tens of GB at config 2) are then carved out of memory
+    the process already owns, instead of the pool being extended while a step is running (each extension is a
+    device-wide host stall of 0.5-0.9 s on the B200 boxes: tools/step_trace.py).  Returns the bytes reserved."""
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    free, _ = torch.cuda.mem_get_info(device)
+    want = int(free * fraction) - (torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device))
+    if want <= 0:
+        return 0
+    block = torch.empty(want, dtype=torch.uint8, device=device)
+    del block
+    return want
+
+
 def set_save_policy(mode: str) -> None:
     global _SAVE_POLICY
     if mode not in ("auto", "save", "recompute"):
@@ -435,13 +450,18 @@ class _Weights:
 
     @classmethod
     def get(cls, conv_w, dtype, pad: int):
-        key = tuple((w.data_ptr(), w._version) for w in conv_w) + (dtype, pad)
+        # one slot per (parameter storage, dtype, pad); a new parameter version REPLACES the slot, so the cache (and
+        # with it the step's memory footprint) does not grow from step to step: a footprint that creeps makes the
+        # caching allocator extend its pool in the middle of a step, a 0.5-0.9 s host stall on this box
+        # (tools/step_trace.py)
+        key = tuple(w.data_ptr() for w in conv_w) + (dtype, pad)
+        ver = tuple(w._version for w in conv_w)
         hit = cls._CACHE.get(key)
-        if hit is None:
+        if hit is None or hit[0] != ver:
             if len(cls._CACHE) > 64:
                 cls._CACHE.clear()
-            hit = cls._CACHE[key] = cls(conv_w, dtype, pad)
-        return hit
+            hit = cls._CACHE[key] = (ver, cls(conv_w, dtype, pad))
+        return hit[1]
 
 
 def _combine_complex_wgrad(P):

@@ -92,7 +92,12 @@ def test_so2_m_convolution_as_one_real_gemm():
     assert float(wp.w0[:, 1:16].abs().max()) == 0.0 and wp.b0 is None
     w0t, wft = w.transposed()
     assert torch.equal(w0t, w.w0.t()) and torch.equal(wft[0], w.wf[0].t())
-    assert _Weights.get([w0, b0, conv.fc.weight], torch.float32, 0) is _Weights.get([w0, b0, conv.fc.weight], torch.float32, 0)
+    first = _Weights.get([w0, b0, conv.fc.weight], torch.float32, 0)
+    assert _Weights.get([w0, b0, conv.fc.weight], torch.float32, 0) is first
+    n = len(_Weights._CACHE)
+    w0.add_(1.0)                                  # an optimiser step: new version, same storage -> the slot is replaced
+    again = _Weights.get([w0, b0, conv.fc.weight], torch.float32, 0)
+    assert again is not first and torch.equal(again.w0, w0) and len(_Weights._CACHE) == n
 
 
 def test_edge_row_layout_offsets():
