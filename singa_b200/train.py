@@ -22,7 +22,7 @@ from .parallel import GradientBuckets, shard_by_edges
 class Trainer:
     def __init__(self, model, dataset: ComplexDataset, batch_size_per_rank: int, lr: float = 1e-4, betas=(0.99, 0.999),
                  weight_decay: float = 0.0, max_grad_norm: float = math.inf, seed: int = 0, device=None,
-                 shuffle: bool = True, prefetch: int = 0):
+                 shuffle: bool = True, prefetch: int = 0, reserve_fraction: float = 0.0):
         self.model = model
         self.device = device or next(model.parameters()).device
         world = dist.get_world_size() if dist.is_initialized() else 1
@@ -35,6 +35,9 @@ class Trainer:
         self.buckets = GradientBuckets(model.named_parameters())
         self.max_grad_norm = max_grad_norm
         self.it = 0
+        if reserve_fraction > 0:   # size the allocator pool once: no pool extension (a host stall) inside a step
+            from . import ops
+            ops.reserve_workspace(reserve_fraction, self.device)
 
     def step(self, host_batch: Optional[HostBatch] = None):
         """zero_grad -> H2D -> forward -> cross entropy -> backward (+ overlapped all-reduce) -> clip -> Adam
