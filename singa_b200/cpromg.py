@@ -397,10 +397,52 @@ class EncoderLayer2(nn.Module):
         return self.pos_ffn(msa)
 
 
+def encoder_graph_host(pos: np.ndarray, k: int) -> Dict[str, np.ndarray]:
+    """The encoder's message-passing graph of ONE complex, built on the host once (dataset format): the
+    structure of ``knn_graph(pos, k) -> to_undirected -> get_laplacian`` (CProMG.py:293-300, 330-334) depends only on the
+    positions, yet the reference (and the device path above) rebuilds it on every forward, which on the GPU costs a
+    neighbour search, a sort and eight device->host reads per encoder per step.  Same arithmetic as the kernel:
+    fp32 ((dx^2+dy^2)+dz^2), neighbours by increasing distance, ties to the smaller index.
+    Returns ``und`` [2, E] (undirected pairs sorted by (row, col)) and ``und_rowptr`` [n+1] over rows."""
+    p = pos.astype(np.float32)
+    n = p.shape[0]
+    d2 = np.zeros((n, n), dtype=np.float32)
+    for a in range(3):
+        diff = (p[:, None, a] - p[None, :, a]).astype(np.float32)
+        sq = (diff * diff).astype(np.float32)
+        d2 = sq if a == 0 else (d2 + sq).astype(np.float32)
+    np.fill_diagonal(d2, np.inf)
+    kk = min(k, n - 1)
+    nbr = np.argsort(d2, axis=1, kind="stable")[:, :kk] if kk > 0 else np.zeros((n, 0), dtype=np.int64)
+    row = np.repeat(np.arange(n), kk)
+    col = nbr.reshape(-1)
+    key = np.unique(np.concatenate((row * n + col, col * n + row)))        # both directions, duplicates merged, sorted
+    und = np.stack((key // n, key % n)).astype(np.int32)
+    rowptr = np.concatenate(([0], np.cumsum(np.bincount(und[0], minlength=n)))).astype(np.int32)
+    return dict(und=und, und_rowptr=rowptr)
+
+
+class PrebuiltGraph:
+    """Device-side encoder graph of a batch assembled from host-built per-complex graphs: ``edge_index`` [2, E + N]
+    (undirected pairs, then one loop per node: the order get_laplacian produces), the number of non-loop edges, the
+    CSR of the undirected part (row degrees) and the centre-sorted CSR of the whole list (registered for the
+    attention layers).  No search, sort or host read on the step."""
+
+    def __init__(self, edge_index, num_und: int, und_csr, lap_csr):
+        self.edge_index, self.num_und, self.und_csr, self.lap_csr = edge_index, num_und, und_csr, lap_csr
+        _CSR_CACHE[(id(edge_index), edge_index._version, lap_csr.num_dst)] = (edge_index, lap_csr)
+
+
 class _GraphEncoderBase(nn.Module):
-    def _graph(self, pos, batch, k):
-        from .radius import knn_graph
+    def _graph(self, pos, batch, k, prebuilt: Optional[PrebuiltGraph] = None):
         n = pos.size(0)
+        if prebuilt is not None:
+            ei = prebuilt.edge_index
+            row, col = ei[0, :prebuilt.num_und], ei[1, :prebuilt.num_und]
+            w = self.distance_expansion(torch.norm(pos[row] - pos[col], dim=1))
+            deg = segment_sum(w, prebuilt.und_csr)
+            return ei, torch.cat((-w, deg), dim=0)
+        from .radius import knn_graph
         directed = knn_graph(pos, k, batch=batch, flow='target_to_source')
         length = torch.norm(pos[directed[0]] - pos[directed[1]], dim=1)
         edge_index, length = to_undirected(directed, length, n, reduce='mean')
@@ -421,9 +463,9 @@ class Encoder(_GraphEncoderBase):
         self.out = nn.Linear(config.hidden_channels, config.hidden_channels, device=device)
         self.layer_norm = nn.LayerNorm(config.hidden_channels, device=device)
 
-    def forward(self, protein_atom_feature, pos, batch, atom_laplacian, sizes):
+    def forward(self, protein_atom_feature, pos, batch, atom_laplacian, sizes, prebuilt=None):
         node_attr = self.protein_atom_emb(protein_atom_feature) + self.laplacian_emb(atom_laplacian)
-        edge_index, edge_attr = self._graph(pos, batch, self.config.knn)
+        edge_index, edge_attr = self._graph(pos, batch, self.config.knn, prebuilt)
         msa_dense = []
         for layer in self.layers:
             msa, node_attr = layer(node_attr, edge_index, edge_attr)
@@ -446,9 +488,9 @@ class Encoder2(_GraphEncoderBase):
         self.out = nn.Linear(config.hidden_channels, config.hidden_channels, device=device)
         self.layer_norm = nn.LayerNorm(config.hidden_channels, device=device)
 
-    def forward(self, aa_feature, aa_pos, aa_batch, aa_laplacian, atom_mask, atom_msa_outputs, sizes):
+    def forward(self, aa_feature, aa_pos, aa_batch, aa_laplacian, atom_mask, atom_msa_outputs, sizes, prebuilt=None):
         node_attr = self.aa_emb(aa_feature) + self.laplacian_emb(aa_laplacian)
-        edge_index, edge_attr = self._graph(aa_pos, aa_batch, 30)
+        edge_index, edge_attr = self._graph(aa_pos, aa_batch, 30, prebuilt)
         for idx, layer in enumerate(self.layers):
             node_attr = layer(node_attr, edge_index, edge_attr, idx, atom_msa_outputs, atom_mask, aa_batch, sizes)
         enc, mask = to_dense_batch(node_attr, aa_batch, *sizes)
@@ -511,8 +553,9 @@ class Decoder(nn.Module):
 
 
 class Transformer(nn.Module):
-    """Encoder + Encoder2 + Decoder + vocabulary projection (CProMG.py:423-464).  Extra argument ``sizes`` =
-    dict(batch_size, max_atoms, max_aa): the dense-batch extents, known to the caller from the collated batch."""
+    """Encoder + Encoder2 + Decoder + vocabulary projection (CProMG.py:423-464).  Extra arguments: ``sizes`` =
+    dict(batch_size, max_atoms, max_aa), the dense-batch extents, known to the caller from the collated batch; ``graphs``
+    = dict(atom=PrebuiltGraph, aa=PrebuiltGraph), the encoders' message-passing graphs when the dataset carries them."""
 
     def __init__(self, config, protein_atom_feature_dim, num_props=None, device='cuda'):
         super().__init__()
@@ -523,14 +566,15 @@ class Transformer(nn.Module):
         self.projection = nn.Linear(config.hidden_channels, self.decoder.vocab_size, bias=False, device=device)
 
     def forward(self, node_attr, pos, batch, atom_laplacian, smiles_index, tgt_len, aa_node_attr, aa_pos, aa_batch,
-                aa_laplacian, prop=None, sizes=None):
+                aa_laplacian, prop=None, sizes=None, graphs=None):
+        graphs = graphs or {}
         if sizes is None:   # the reference's behaviour: read the extents back from the device
             B = int(batch.max()) + 1
             sizes = dict(batch_size=B, max_atoms=int(torch.bincount(batch, minlength=B).max()),
                          max_aa=int(torch.bincount(aa_batch, minlength=B).max()))
         s1, s2 = (sizes["batch_size"], sizes["max_atoms"]), (sizes["batch_size"], sizes["max_aa"])
-        enc1, mask1, msa = self.encoder(node_attr, pos, batch, atom_laplacian, s1)
-        enc2, mask2 = self.encoder2(aa_node_attr, aa_pos, aa_batch, aa_laplacian, mask1, msa, s2)
+        enc1, mask1, msa = self.encoder(node_attr, pos, batch, atom_laplacian, s1, graphs.get("atom"))
+        enc2, mask2 = self.encoder2(aa_node_attr, aa_pos, aa_batch, aa_laplacian, mask1, msa, s2, graphs.get("aa"))
         dec = self.decoder(smiles_index, torch.cat([enc1, enc2], dim=1), torch.cat([mask1, mask2], dim=2), tgt_len, prop)
         logits = self.projection(dec)[:, (1 if self.num_props else 0):, :]
         return logits.reshape(-1, logits.size(-1))

@@ -72,8 +72,25 @@ def pack_bits(x: np.ndarray) -> np.ndarray:
     return (x[:, -15:].astype(np.int64) * w).sum(axis=1).astype(np.int32)
 
 
+def _encoder_graph_fields(pos: np.ndarray, k: int) -> Dict[str, np.ndarray]:
+    """Host-built message-passing graph of one encoder for one complex (cpromg.encoder_graph_host) with the CSR of its
+    Laplacian edge list [undirected pairs..., one loop per node] grouped by centre (row 0)."""
+    from .cpromg import encoder_graph_host
+    n = pos.shape[0]
+    g = encoder_graph_host(pos, k)
+    und = g["und"]
+    loops = np.arange(n, dtype=np.int32)
+    lap = np.concatenate((und, np.stack((loops, loops))), axis=1)
+    f = _csr_fields(lap[::-1], n, n, store_sorted=False)      # destination = centre = row 0, source = neighbour = row 1
+    return dict(und=und, und_rowptr=g["und_rowptr"], perm=f["perm"], rowptr=f["rowptr"], ssrc=f["ssrc"], sdst=f["sdst"],
+                srcptr=f["srcptr"], srcidx=f["srcidx"])
+
+
+ENCODER_GRAPHS = (("ga", "p", 48), ("gl", "l", 30))   # (record prefix, node side, k): CProMG.py:293 (config knn), :330
+
+
 def pack_complex(g: Dict[str, torch.Tensor], ligand_data: Optional[Dict] = None, lap_k: int = 8, key=None,
-                 lap_cache=None) -> Dict[str, np.ndarray]:
+                 lap_cache=None, encoder_graphs: bool = True) -> Dict[str, np.ndarray]:
     """One complex in the flat-dict form of ``synthetic.make_complex`` (z_*, x_*, pos_*, ei_*) -> record."""
     from .cpromg import LapPECache
     npy = {k: (v.numpy() if isinstance(v, torch.Tensor) else np.asarray(v)) for k, v in g.items()}
@@ -87,6 +104,10 @@ def pack_complex(g: Dict[str, torch.Tensor], ligand_data: Optional[Dict] = None,
     cache = lap_cache or LapPECache(lap_k)
     rec["lap_p"] = cache.get((key, "p"), npy["ei_pp"], n["p"])
     rec["lap_l"] = cache.get((key, "l"), npy["ei_ll"], n["l"])
+    if encoder_graphs:
+        for prefix, side, k in ENCODER_GRAPHS:
+            for name, arr in _encoder_graph_fields(rec["pos_" + side], k).items():
+                rec[f"{prefix}_{name}"] = arr
     if ligand_data is not None:
         for name in LIGAND_SCALARS:
             rec[name] = np.float32(ligand_data[name])
@@ -212,6 +233,21 @@ class DeviceBatch:
             for name in LIGAND_SCALARS + ("smi_in", "smi_tgt"):
                 if name in t:
                     g[name] = t[name]
+            enc = {}
+            for (prefix, side, _k), role in zip(ENCODER_GRAPHS, ("atom", "aa")):
+                if f"{prefix}_ei" not in t:
+                    continue
+                from .cpromg import PrebuiltGraph
+                N, E = n[side], m[f"{prefix}_und_edges"]
+                ei32 = t[f"{prefix}_ei"]
+                ei = ei32.long()
+                ident = torch.arange(E, dtype=torch.int32, device=ei.device)
+                und = ops.EdgeCSR(N, N, E, ident, t[f"{prefix}_und_rowptr"], ei32[1, :E].contiguous(),
+                                  ei32[0, :E].contiguous(), ei32[0, :E].contiguous(), t[f"{prefix}_und_rowptr"], ident)
+                lap = ops.EdgeCSR(N, N, E + N, t[f"{prefix}_perm"], t[f"{prefix}_rowptr"], t[f"{prefix}_ssrc"],
+                                  t[f"{prefix}_sdst"], ei32[0].contiguous(), t[f"{prefix}_srcptr"], t[f"{prefix}_srcidx"])
+                enc[role] = PrebuiltGraph(ei, E, und, lap)
+            g["enc_graphs"] = enc
             self._graph = g
         return self._graph
 
@@ -244,6 +280,30 @@ def collate_records(recs: List[Dict[str, np.ndarray]], pin: bool = True) -> Host
             a.add(f"{k}_sdst", np.concatenate([r[f"{k}_sdst"] + off[d][i] for i, r in enumerate(recs)]).astype(np.int32))
         meta[f"{k}_rowptr_host"] = rowptr.astype(np.int64)
         meta["edges"][k] = int(eoff[-1])
+    for prefix, side, _k in ENCODER_GRAPHS:
+        if f"{prefix}_und" not in recs[0]:
+            continue
+        ne = np.array([r[f"{prefix}_und"].shape[1] for r in recs])
+        eoff = np.concatenate(([0], np.cumsum(ne)))
+        E, N = int(eoff[-1]), int(off[side][-1])
+        soff = eoff[:-1] + off[side][:-1]                       # offset of a complex in sorted-position space
+        und = np.concatenate([r[f"{prefix}_und"] + off[side][i] for i, r in enumerate(recs)], axis=1)
+        loops = np.arange(N, dtype=np.int64)
+        a.add(f"{prefix}_ei", np.concatenate((und, np.stack((loops, loops))), axis=1).astype(np.int32))
+        a.add(f"{prefix}_und_rowptr", np.concatenate([r[f"{prefix}_und_rowptr"][:-1] + eoff[i] for i, r in enumerate(recs)]
+                                                     + [eoff[-1:]]).astype(np.int32))
+        perm = []
+        for i, r in enumerate(recs):   # stored ids: undirected pairs first (all complexes), then the loops
+            pc = r[f"{prefix}_perm"].astype(np.int64)
+            perm.append(np.where(pc < ne[i], pc + eoff[i], pc - ne[i] + E + off[side][i]))
+        a.add(f"{prefix}_perm", np.concatenate(perm).astype(np.int32))
+        for name in ("rowptr", "srcptr"):
+            a.add(f"{prefix}_{name}", np.concatenate([r[f"{prefix}_{name}"][:-1] + soff[i] for i, r in enumerate(recs)]
+                                                     + [np.array([E + N])]).astype(np.int32))
+        a.add(f"{prefix}_srcidx", np.concatenate([r[f"{prefix}_srcidx"] + soff[i] for i, r in enumerate(recs)]).astype(np.int32))
+        for name in ("ssrc", "sdst"):
+            a.add(f"{prefix}_{name}", np.concatenate([r[f"{prefix}_{name}"] + off[side][i] for i, r in enumerate(recs)]).astype(np.int32))
+        meta[f"{prefix}_und_edges"] = E
     if "smi_in" in recs[0]:
         for name in LIGAND_SCALARS:
             a.add(name, np.array([r[name] for r in recs], dtype=np.float32))

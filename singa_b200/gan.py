@@ -67,9 +67,10 @@ class SINGA(nn.Module):
         dic["sas"] = torch.lt(dic["sas"], 4.0).float()
         return stack_props(dic, self.config.train.prop)
 
-    def forward(self, g, sizes=None, frames=None):
+    def forward(self, g, sizes=None, frames=None, graphs=None):
         """g: HeteroData-like (synthetic.GraphView over a collated batch).  ``sizes`` = dict(batch_size, max_atoms,
-        max_aa) from the collated batch's host metadata (avoids two device reads); ``frames`` as EquivariantEmbedding."""
+        max_aa) from the collated batch's host metadata (avoids two device reads); ``frames`` as EquivariantEmbedding;
+        ``graphs`` = the encoders' prebuilt message-passing graphs when the batch carries them (dataset format)."""
         lig = g["ligand_data"]
         prop = self.properties(lig).to(self.device) if self.config.train.num_props else None
         ptr_p, ptr_l = g[PROTEIN]["ptr"], g[LIGAND]["ptr"]
@@ -83,4 +84,4 @@ class SINGA(nn.Module):
         return self.model(node_attr=protein, pos=g[PROTEIN]["pos"], batch=batch, atom_laplacian=g[PROTEIN]["lap"],
                           smiles_index=lig["smiIndices_input"], tgt_len=self.config.model.decoder.tgt_len,
                           aa_node_attr=ligand, aa_pos=g[LIGAND]["pos"], aa_batch=batch_aa,
-                          aa_laplacian=g[LIGAND]["lap"], prop=prop, sizes=sizes)
+                          aa_laplacian=g[LIGAND]["lap"], prop=prop, sizes=sizes, graphs=graphs)

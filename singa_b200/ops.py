@@ -26,7 +26,9 @@ from ._lib import LIB, call, check_cuda, ptr
 #             bf16 (hi, lo) and a*b taken as a_hi b_hi + a_hi b_lo + a_lo b_hi in ONE launch with a 3x longer
 #             reduction (csrc/split3.cu); everything else as in "fp32".  The accurate tensor-core mode of SURVEY.md 7.1.
 _PRECISION = "fp32"
-MAX_CHUNK_EDGES = int(os.environ.get("EFL_MAX_CHUNK_EDGES", "262144"))
+# edges per chunk of the edge path (whole destinations): 524 288 measured 2 % faster per step than 262 144 (fewer
+# launches, longer persistent-GEMM runs; tools/ab_knobs.sh), 1 048 576 no better and twice the backward workspace
+MAX_CHUNK_EDGES = int(os.environ.get("EFL_MAX_CHUNK_EDGES", "524288"))
 # Saved-for-backward policy (SURVEY.md 8a note): keep the chunk's edge activations (A, extra, hidden, S2 output,
 # values: ~25 KB/edge in bf16) when they fit a fraction of the free HBM, otherwise recompute them in backward.
 # "auto" | "save" | "recompute"

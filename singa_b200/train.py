@@ -48,7 +48,7 @@ class Trainer:
         db = hb.to(self.device)
         g = db.graph()
         sizes = dict(batch_size=hb.meta["batch_size"], max_atoms=hb.meta["max_p"], max_aa=hb.meta["max_l"])
-        logits = self.model(syn.GraphView(g), sizes=sizes)
+        logits = self.model(syn.GraphView(g), sizes=sizes, graphs=g.get("enc_graphs"))
         loss = self.criterion(logits, g["smi_tgt"].contiguous().view(-1))
         loss.backward()
         self.buckets.finish()

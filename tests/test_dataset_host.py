@@ -41,7 +41,7 @@ def test_record_fields_match_the_oracle_csr_and_bit_packing(tmp_path):
 
 def test_collation_is_a_sorted_disjoint_union_without_a_sort():
     graphs = _graphs()
-    recs = [ds.pack_complex(g, key=i) for i, g in enumerate(graphs)]
+    recs = [ds.pack_complex(g, key=i, encoder_graphs=False) for i, g in enumerate(graphs)]
     hb = ds.collate_records(recs, pin=False)
     t = hb.arena.views(hb.host)
     big = syn.collate(graphs)
@@ -73,3 +73,30 @@ def test_batch_loader_keeps_its_iterator_and_shards():
     t = hb.arena.views(hb.host)
     assert t["smi_in"].shape == (2, 10) and t["smi_tgt"].shape == (2, 10) and t["vina_score"].shape == (2,)
     assert int(t["smi_in"].max()) < 116
+
+
+def test_encoder_graphs_in_the_record_equal_the_on_the_fly_construction():
+    """The CProMG encoders' graphs (knn_graph -> to_undirected -> get_laplacian, CProMG.py:293-300, 330-334) depend only
+    on positions; the record carries them, built on the host.  The collated batch graph and its centre-sorted CSR must
+    equal what the loop restatements of the pyg / torch-cluster functions give on the batched positions."""
+    from oracle import cpromg_oracle as co
+    graphs = [syn.make_complex(s, n_protein=40 + 5 * s, n_ligand=7 + s) for s in range(3)]
+    recs = [ds.pack_complex(g, key=i) for i, g in enumerate(graphs)]
+    hb = ds.collate_records(recs, pin=False)
+    t = hb.arena.views(hb.host)
+    big = syn.collate(graphs)
+    for prefix, side, k in ds.ENCODER_GRAPHS:
+        pos = big["pos_" + side]
+        n = pos.shape[0]
+        batch = torch.repeat_interleave(torch.arange(3), torch.tensor([len(g["z_" + side]) for g in graphs]))
+        di = co.knn_graph(pos, k, batch=batch, flow="target_to_source")
+        ei, attr = co.to_undirected(di, (pos[di[0]] - pos[di[1]]).norm(dim=1), reduce="mean")
+        lap_ei, _ = co.get_laplacian(ei, attr.unsqueeze(1), num_nodes=n)
+        assert torch.equal(t[prefix + "_ei"].long(), lap_ei), prefix
+        assert hb.meta[prefix + "_und_edges"] == ei.shape[1]
+        ref = eo.csr_from_edge_index(lap_ei.flip(0), n, n)
+        for a, b in (("perm", "perm"), ("rowptr", "rowptr"), ("ssrc", "src_sorted"), ("sdst", "dst_sorted"),
+                     ("srcptr", "src_ptr"), ("srcidx", "src_idx")):
+            assert np.array_equal(t[f"{prefix}_{a}"].numpy(), ref[b]), (prefix, a)
+        und_rowptr = np.concatenate(([0], np.cumsum(np.bincount(ei[0].numpy(), minlength=n))))
+        assert np.array_equal(t[prefix + "_und_rowptr"].numpy(), und_rowptr)

@@ -191,6 +191,40 @@ def test_prebuilt_csr_batch_equals_the_sorting_path():
         assert torch.equal(a[k].embedding, b[k].embedding), k
 
 
+def test_prebuilt_encoder_graphs_give_the_same_transformer_output():
+    """Encoder graphs carried by the dataset batch (host-built once) against the on-the-fly device construction
+    (knn kernel + sort-based to_undirected + get_laplacian): identical edge lists, identical logits."""
+    from singa_b200 import cpromg as cp
+    from singa_b200 import dataset as ds
+    from singa_b200 import synthetic as syn
+    from singa_b200.embedding import batch_vector_from_ptr
+    from singa_b200.gan import default_config
+    recs = ds.synthetic_records(range(3), n_protein=70, tgt_len=12)
+    hb = ds.collate_records(recs)
+    g = hb.to(DEV).graph()
+    cfg = default_config().model
+    cfg.decoder["tgt_len"] = 12
+    torch.manual_seed(0)
+    model = cp.Transformer(cfg, 784, num_props=3, device=DEV).eval()
+    syn.load_portable_parameters_fanin(model, 2)
+    rs = np.random.RandomState(0)
+    f = lambda n: torch.from_numpy(rs.normal(size=(n, 784)).astype(np.float32) * 0.3).to(DEV)
+    n_p, n_l = g["pos_p"].shape[0], g["pos_l"].shape[0]
+    args = dict(node_attr=f(n_p), pos=g["pos_p"], batch=batch_vector_from_ptr(g["ptr_p"], n_p), atom_laplacian=g["lap_p"],
+                smiles_index=g["smi_in"], tgt_len=12, aa_node_attr=f(n_l), aa_pos=g["pos_l"],
+                aa_batch=batch_vector_from_ptr(g["ptr_l"], n_l), aa_laplacian=g["lap_l"],
+                prop=torch.ones(3, 3, device=DEV),
+                sizes=dict(batch_size=3, max_atoms=hb.meta["max_p"], max_aa=hb.meta["max_l"]))
+    with torch.no_grad():
+        a = model(**args)
+        b = model(**args, graphs=g["enc_graphs"])
+        for role, (pos, bt, k) in dict(atom=(g["pos_p"], args["batch"], cfg.encoder.knn),
+                                       aa=(g["pos_l"], args["aa_batch"], 30)).items():
+            ei, _ = model.encoder._graph(pos, bt, k)
+            assert torch.equal(ei, g["enc_graphs"][role].edge_index), role
+    assert torch.equal(a, b)
+
+
 def test_singa_train_step_runs_and_is_reproducible():
     """BASELINE.json config 3 in miniature: SINGA (EquivariantEmbedding + CProMG transformer) through Trainer.step on
     dataset-format batches; finite loss, every trainable parameter that can receive a gradient gets one, and two

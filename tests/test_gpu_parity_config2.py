@@ -1,7 +1,7 @@
 """Parity at BASELINE.json config-2 SIZE: one full ~460-atom / 30 k-edge complex through all four
 passes, forward AND backward, CUDA path vs the CPU oracle, in both precisions, with the MEASURED errors written to
 gpurun_out/r2_parity_config2.json (copied to profiles/); and a batch that crosses a 262 144-edge chunk boundary,
-checked against the oracle on the complex that straddles the boundary.
+checked against the oracle on the complex that straddles the boundary (ops.MAX_CHUNK_EDGES = 524 288).
 
 Stated bounds (||d||_inf / ||ref||_inf per tensor): fp32 mode outputs <= 2e-5, parameter gradients <= 2e-4 (sums over
 ~3e4 edges x 3 layers); bf16x3 accurate tensor-core mode outputs <= 1e-3, gradients <= 5e-3; bf16 tcgen05 mode
@@ -62,7 +62,7 @@ def test_full_size_complex_fwd_bwd_matches_oracle(precision):
 
 
 def test_batch_across_a_chunk_boundary_matches_oracle_on_the_straddling_complex():
-    """10 complexes = ~285 k protein-protein edges: the second chunk starts inside one complex's destination range
+    """20 complexes = ~575 k protein-protein edges: the second chunk starts inside one complex's destination range
     (chunks hold whole destinations, ops.plan_chunks).  That complex's outputs, computed inside the batch, against the
     oracle run on the complex alone (complexes share no edges)."""
     import bench
@@ -70,11 +70,11 @@ def test_batch_across_a_chunk_boundary_matches_oracle_on_the_straddling_complex(
     from singa_b200 import ops
     from singa_b200 import synthetic as syn
     from singa_b200.embedding import DEFAULT_CONFIG
-    graphs = [syn.make_complex(i) for i in range(10)]
+    graphs = [syn.make_complex(i) for i in range(20)]
     batch = syn.collate(graphs)
     cum = np.cumsum([0] + [g["ei_pp"].shape[1] for g in graphs])
     assert cum[-1] > ops.MAX_CHUNK_EDGES, "batch must span two chunks"
-    k = int(np.searchsorted(cum, ops.MAX_CHUNK_EDGES, side="right")) - 1   # complex holding edge no. 262 144
+    k = int(np.searchsorted(cum, ops.MAX_CHUNK_EDGES, side="right")) - 1   # complex holding the boundary edge
     assert cum[k] < ops.MAX_CHUNK_EDGES < cum[k + 1]
     per = [bench.oracle_frames(g, seed=20 + i) for i, g in enumerate(graphs)]
     frames = {key: torch.cat([p[key] for p in per]).to(DEV) for key in ("pp", "ll", "lp")}
