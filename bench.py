@@ -20,6 +20,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import datetime
 import os
 import subprocess
 import sys
@@ -285,6 +286,26 @@ def emit(line: dict):
         os.write(_RESULT_FD, data)
 
 
+def settle_steps(fn, lo, hi, alloc_count, any_rank=None):
+    """``lo`` warm-up steps, then more (at most ``hi``) until a step runs without a cudaMalloc: the timed region starts
+    from a steady memory footprint.  ``fn`` contains collectives when N > 1 (the gradient all-reduce), so every rank
+    must run the SAME number of steps: the stop decision goes through ``any_rank`` (a MAX all-reduce of the local
+    flag, called once per step on every rank).  A rank-local decision deadlocks the job as soon as two ranks settle
+    after a different number of steps (seen at N = 8: six ranks in the barrier of the timed region, two still in the
+    warm-up's all-reduce)."""
+    done = 0
+    while done < lo + hi:
+        n0 = alloc_count()
+        fn()
+        done += 1
+        grew = alloc_count() != n0
+        if any_rank is not None:
+            grew = any_rank(grew)
+        if done >= lo and not grew:
+            break
+    return done
+
+
 def config3(args):
     """BASELINE.json configs[3]: full SINGA train step (EquivariantEmbedding + CProMG encoder/decoder, cross entropy,
     Adam), GLOBAL batch 64, data parallel with the bucketed NCCL gradient all-reduce.  Every step takes its batch from
@@ -304,7 +325,7 @@ def config3(args):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=300))
     ops.set_precision(args.precision)
     gb = args.global_batch
     assert gb % world == 0, "global batch must divide over the ranks"
@@ -419,7 +440,7 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=300))
     ops.set_precision(args.precision)
 
     if args.scaling == "strong":
@@ -486,17 +507,16 @@ def main():
         sampler.start()   # before the warm-up: nvidia-smi's own start-up (NVML init) must not land in the timed region
     ops.reserve_workspace(0.6, dev)   # pool sized once, so that no step extends it (see ops.reserve_workspace)
 
+    def any_rank(flag):
+        """True on every rank when ``flag`` is true on at least one: keeps rank-local decisions collective."""
+        if world == 1:
+            return flag
+        t = torch.tensor([1.0 if flag else 0.0], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return bool(t.item() > 0)
+
     def settle(fn, lo, hi=12):
-        """``lo`` warm-up steps, then more (at most ``hi``) until a step runs without a cudaMalloc: the timed region
-        starts from a steady memory footprint."""
-        done = 0
-        while done < lo + hi:
-            n0 = torch.cuda.memory_stats(dev).get("num_device_alloc", 0)
-            fn()
-            done += 1
-            if done >= lo and torch.cuda.memory_stats(dev).get("num_device_alloc", 0) == n0:
-                break
-        return done
+        return settle_steps(fn, lo, hi, lambda: torch.cuda.memory_stats(dev).get("num_device_alloc", 0), any_rank)
 
     warm_done = settle(lambda: step(resident), max(args.warmup, 3))
     if rank == 0:

@@ -128,3 +128,49 @@ def test_bucketed_overlapped_allreduce_with_a_rank_missing_a_gradient(tmp_path):
                 continue
             assert torch.equal(a, b), (step, n)          # every rank holds the same reduced gradient
             assert torch.allclose(a, p.grad, rtol=1e-5, atol=1e-6), (step, n)
+
+
+def _settle_worker(rank, world, port, out):
+    """bench.settle_steps with a step that contains a collective and allocation counters that settle after a
+    DIFFERENT number of steps on the two ranks (rank 0: 5 steps, rank 1: 2)."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world, timeout=__import__("datetime").timedelta(seconds=60))
+    grows_until = 5 if rank == 0 else 2
+    state = {"steps": 0, "allocs": 0}
+
+    def fn():
+        state["steps"] += 1
+        if state["steps"] <= grows_until:
+            state["allocs"] += 1
+        t = torch.ones(3)
+        dist.all_reduce(t)            # the gradient all-reduce of a step
+        assert float(t[0]) == world
+
+    def any_rank(flag):
+        t = torch.tensor([1.0 if flag else 0.0])
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return bool(t.item() > 0)
+
+    done = bench.settle_steps(fn, 3, 12, lambda: state["allocs"], any_rank)
+    dist.barrier()                    # what the timed region does next: must not meet a stray all-reduce
+    torch.save(done, f"{out}.{rank}")
+    dist.destroy_process_group()
+
+
+def test_warmup_until_steady_runs_the_same_number_of_steps_on_every_rank(tmp_path):
+    """Regression: the bench's settle loop stopped per rank; at N = 8 two ranks were still in a warm-up step's
+    all-reduce while six sat in the timed region's barrier (NCCL watchdog timeout after 600 s)."""
+    out = str(tmp_path / "done")
+    mp.spawn(_settle_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    d0, d1 = torch.load(out + ".0"), torch.load(out + ".1")
+    assert d0 == d1 == 6              # rank 0's last growing step is 5: step 6 is the first steady one everywhere
+    import bench
+    state = {"n": 0}
+    assert bench.settle_steps(lambda: None, 3, 12, lambda: state["n"]) == 3      # single rank, steady from the start
+    def grow():
+        state["n"] += 1
+    assert bench.settle_steps(grow, 3, 4, lambda: state["n"]) == 7               # never steady: bounded by lo + hi

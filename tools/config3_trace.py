@@ -39,6 +39,18 @@ for _ in range(3):
 prof = _lib.stop_profile()
 tot = sum(v["ms"] for v in prof.values()) / 3
 print("libefl kernels ms/step", round(tot, 1), "launches/step", sum(v["calls"] for v in prof.values()) / 3)
+if os.environ.get("CPROFILE", "0") == "1":
+    import cProfile, pstats
+    pr = cProfile.Profile()
+    pr.enable()
+    for _ in range(5):
+        tr.step()
+    pr.disable()
+    torch.cuda.synchronize()
+    st = pstats.Stats(pr)
+    st.sort_stats("tottime").print_stats(45)
+    st.sort_stats("cumulative").print_stats(70)
+    sys.exit(0)
 from torch.profiler import profile, ProfilerActivity
 with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as p:
     for _ in range(3):

@@ -1,5 +1,6 @@
 """Per-rank phase times of the end-to-end step under torchrun (weak batches): where does e2e lose against the
 resident-input step at N > 1?  Each phase is followed by a device synchronise (diagnosis, not a benchmark)."""
+import datetime
 import os, sys, time
 os.environ.setdefault("PYTORCH_CUDA_ALLOC_CONF", "expandable_segments:True")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -15,7 +16,7 @@ torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
 if world > 1:
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-    dist.init_process_group("nccl", device_id=dev)
+    dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=300))
 ops.set_precision("bf16")
 batch, _ = bench.make_batch(rank, 32, None)
 host = {k: v.pin_memory() for k, v in batch.items()}

@@ -10,9 +10,9 @@ el() { echo "[$(( $(date +%s) - T0 )) s] $*"; }
 run() {  # run NAME ARGS...
   local name=$1; shift
   if [ "$N" = "1" ]; then
-    timeout 900 python bench.py --gpus 1 "$@" > gpurun_out/${TAG}_${name}.json 2> gpurun_out/${TAG}_${name}.err
+    timeout 420 python bench.py --gpus 1 "$@" > gpurun_out/${TAG}_${name}.json 2> gpurun_out/${TAG}_${name}.err
   else
-    timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
+    timeout 420 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
       bench.py --gpus $N "$@" > gpurun_out/${TAG}_${name}.json 2> gpurun_out/${TAG}_${name}.err
   fi
   el "$name exit $?"

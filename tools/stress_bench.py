@@ -7,6 +7,7 @@ batch is sharded by whole complex, SURVEY.md 8e) and gradients are all-reduced; 
 """
 import argparse
 import json
+import datetime
 import os
 import sys
 
@@ -91,7 +92,7 @@ def run(args):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=300))
     ops.set_precision(args.precision)
     g = make_batch(rank, args.complexes, args.atoms, dev)
     edges = int(sum(g[k].shape[1] for k in ("ei_pp", "ei_ll", "ei_lp", "ei_pl")))
