@@ -60,6 +60,16 @@ def edge_linear(x, lin: nn.Linear):
 
 
 _CSR_CACHE: Dict = {}
+_CSR_CACHE_SLOTS = 8     # two encoder graphs per batch x (current + prefetched batches); oldest entries leave first
+
+
+def _csr_cache_put(key, edge_index, csr) -> None:
+    """Bounded, insertion-ordered: an entry pins its edge list and CSR in device memory, so a cache that only ever
+    grows (one pair of encoder graphs per training step) is a leak."""
+    _CSR_CACHE.pop(key, None)
+    _CSR_CACHE[key] = (edge_index, csr)
+    while len(_CSR_CACHE) > _CSR_CACHE_SLOTS:
+        _CSR_CACHE.pop(next(iter(_CSR_CACHE)))
 
 
 def _build_centre_csr(edge_index: torch.Tensor, num_nodes: int):
@@ -75,9 +85,7 @@ def centre_csr(edge_index: torch.Tensor, num_nodes: int):
     if hit is not None and hit[0] is edge_index:
         return hit[1]
     csr = _build_centre_csr(edge_index, num_nodes)
-    if len(_CSR_CACHE) > 8:
-        _CSR_CACHE.clear()
-    _CSR_CACHE[key] = (edge_index, csr)
+    _csr_cache_put(key, edge_index, csr)
     return csr
 
 
@@ -430,7 +438,7 @@ class PrebuiltGraph:
 
     def __init__(self, edge_index, num_und: int, und_csr, lap_csr):
         self.edge_index, self.num_und, self.und_csr, self.lap_csr = edge_index, num_und, und_csr, lap_csr
-        _CSR_CACHE[(id(edge_index), edge_index._version, lap_csr.num_dst)] = (edge_index, lap_csr)
+        _csr_cache_put((id(edge_index), edge_index._version, lap_csr.num_dst), edge_index, lap_csr)
 
 
 class _GraphEncoderBase(nn.Module):

@@ -146,3 +146,23 @@ def test_lap_pe_reference_signature_uses_batch_encodings_or_caches_per_complex()
     assert torch.equal(cp.lap_pe(view, "protein_atoms"), pe) and cp._LAP_CACHE.misses == misses
     carried = dict(b, lap_p=torch.zeros(55, 8))
     assert cp.lap_pe(syn.GraphView(carried), "protein_atoms") is carried["lap_p"]
+
+
+def test_centre_csr_cache_is_bounded_and_evicts_oldest_first():
+    """Every training step registers the batch's two prebuilt encoder graphs; the cache must not grow with the steps
+    (each entry pins an edge list and its CSR in device memory)."""
+    from singa_b200 import cpromg as cp
+    saved = dict(cp._CSR_CACHE)
+    cp._CSR_CACHE.clear()
+    try:
+        eis = [torch.zeros(2, 3, dtype=torch.int64) for _ in range(3 * cp._CSR_CACHE_SLOTS)]
+        for i, ei in enumerate(eis):
+            cp._csr_cache_put((id(ei), ei._version, 5), ei, f"csr{i}")
+            assert len(cp._CSR_CACHE) <= cp._CSR_CACHE_SLOTS
+        kept = [v[1] for v in cp._CSR_CACHE.values()]
+        assert kept == [f"csr{i}" for i in range(len(eis) - cp._CSR_CACHE_SLOTS, len(eis))]
+        last = eis[-1]
+        assert cp._CSR_CACHE[(id(last), last._version, 5)][0] is last
+    finally:
+        cp._CSR_CACHE.clear()
+        cp._CSR_CACHE.update(saved)
