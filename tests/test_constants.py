@@ -85,3 +85,23 @@ def test_coefficient_tables():
     assert len(t["keep"]) == 29 and list(t["m_size"]) == [7, 6, 5]
     assert sorted(t["to_m_perm"].tolist()) == list(range(29))
     assert abs(t["rescale"][6] - math.sqrt(13 / 5)) < 1e-15 and t["rescale"][2] == 1.0
+
+
+def test_real_spherical_harmonics_match_scipy():
+    """Independent anchor for the e3nn-convention real harmonics (e3nn itself is not vendored: the grid constants are
+    otherwise pinned only through the reference's buffers built on a shim).  scipy's complex Y_l^m (Condon-Shortley
+    phase, polar angle from the y axis, azimuth atan2(x, z)) -> real form without the phase: m > 0 carries
+    sqrt(2) (-1)^m Re Y_l^m, m < 0 carries sqrt(2) (-1)^m Im Y_l^|m|."""
+    sp = pytest.importorskip("scipy.special")
+    if not hasattr(sp, "sph_harm_y"):
+        pytest.skip("scipy without sph_harm_y")
+    rs = np.random.RandomState(0)
+    xyz = rs.normal(size=(200, 3))
+    xyz /= np.linalg.norm(xyz, axis=1, keepdims=True)
+    beta, alpha = np.arccos(xyz[:, 1]), np.arctan2(xyz[:, 0], xyz[:, 2])
+    ours = sc.real_sph_harm(8, xyz)
+    for l in range(9):
+        for m in range(-l, l + 1):
+            Y = sp.sph_harm_y(l, abs(m), beta, alpha)
+            ref = Y.real if m == 0 else np.sqrt(2.0) * (-1) ** m * (Y.real if m > 0 else Y.imag)
+            assert np.abs(ref - ours[:, l * l + l + m]).max() < 1e-12, (l, m)
