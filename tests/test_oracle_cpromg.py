@@ -1,9 +1,10 @@
 """Next scope row, checker only: oracle/cpromg_oracle.py against the golden written by the unmodified
 reference ``MultiHeadAttention`` (oracle/make_golden_cpromg.py), forward and every gradient; the brute-force kNN graph
-restatement against its defining properties.  No CUDA path exists for this row yet."""
+restatement against its defining properties.  The CUDA path is tested in tests/test_gpu_cpromg.py."""
 import os
 
 import numpy as np
+import pytest
 import torch
 
 from oracle import cpromg_oracle as co
@@ -59,3 +60,30 @@ def test_knn_graph_restatement_properties():
             assert float((pos[others] - pos[i]).norm(dim=1).min()) >= float(d[i, -1]) - 1e-6
     small = co.knn_graph_bruteforce(pos[:4], 6, None)            # fewer than k candidates: every other point, once
     assert small.shape[1] == 12
+
+
+def test_neighbour_graph_oracles_agree_with_scikit_learn():
+    """torch-cluster is not vendored, so the kNN / radius-graph oracles (which the CUDA kernels are compared with bit
+    for bit) are "parity unpinned" against upstream; this anchors their neighbour SETS and ORDER on an independent
+    third-party implementation (float64 brute force of scikit-learn) for points without distance ties."""
+    neighbors = pytest.importorskip("sklearn.neighbors")
+    from oracle import ef_oracle as eo
+    rs = np.random.RandomState(3)
+    pos = rs.uniform(0, 30, size=(400, 3)).astype(np.float32)
+    batch = np.repeat(np.arange(4), 100)
+    k, r = 12, 8.0
+    ei = co.knn_graph_bruteforce(torch.from_numpy(pos), k, torch.from_numpy(batch))
+    e = eo.radius_graph_bruteforce(torch.from_numpy(pos), r, torch.from_numpy(batch), max_num_neighbors=10 ** 6)
+    adj = np.zeros((400, 400), dtype=bool)
+    adj[e[1].numpy(), e[0].numpy()] = True
+    ref = np.zeros((400, 400), dtype=bool)
+    for b in range(4):
+        ids = np.nonzero(batch == b)[0]
+        p64 = pos[ids].astype(np.float64)
+        _, idx = neighbors.NearestNeighbors(n_neighbors=k + 1, algorithm="brute").fit(p64).kneighbors(p64)
+        for li, i in enumerate(ids):
+            mine = ei[1][ei[0] == i].tolist()
+            assert mine == [ids[j] for j in idx[li] if ids[j] != i][:k], i
+        ref[np.ix_(ids, ids)] = neighbors.radius_neighbors_graph(p64, r, mode="connectivity",
+                                                                 include_self=False).toarray() > 0
+    assert (adj == ref).all() and adj.sum() > 1000
