@@ -147,6 +147,20 @@ int efl_gemm_tn_f32(const float* A, long long lda, const float* B, long long ldb
 /* Bias gradients: out[c] (+)= sum_r X[r,c]; workspace (rows/512 + 2) * cols floats. */
 int efl_colsum(int bf16, const void* X, long long ld, int rows, int cols, float* out, int accumulate,
                float* workspace, void* stream);
+/* efl_colsum without the workspace argument, for callers that are not able to allocate device memory: a process whose
+ * memory pool is sized once and then closed, a plugin working inside buffers its host program gave it, or code inside
+ * a stream capture, where cudaMalloc fails.  No counterpart in the reference (there every op allocates freely through
+ * torch); it exists only because of how this library is embedded.  The partial sums go to an array that is part of
+ * libefl.so itself: EFL_COLSUM_STATIC_MAX_FLOATS floats (4 MiB) held on every GPU that loads the library, until the
+ * process exits.  Shapes with (ceil(rows/512) + 1) * cols above that limit return EFL_ERR_ARG (message in
+ * efl_last_error_string()); nothing is allocated or freed by this call.  Results are bit-identical to efl_colsum.
+ * The first call on a device resolves the array's address on that device: make it with that device current and
+ * before any stream capture starts.  `stream` must be a stream of the current device.  All calls on a GPU share the
+ * array, which keeps the previous call's contents (every slot that is read is rewritten first, so no clearing is
+ * needed); calls that can overlap on the GPU race on it -- keep them on one stream or order them with events. */
+#define EFL_COLSUM_STATIC_MAX_FLOATS (1 << 20)
+int efl_colsum_static(int bf16, const void* X, long long ld, int rows, int cols, float* out, int accumulate,
+                      void* stream);
 
 /* The same linear maps on the 5th-generation tensor cores: bf16 operands, fp32 accumulation in TMEM
  * (tcgen05.mma), operands staged by TMA, persistent warp-specialised CTAs.  Same epilogues as

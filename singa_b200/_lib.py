@@ -37,6 +37,7 @@ SIGNATURES = {
     "efl_gemm_nt_f32": "iplplpplpliiiip",
     "efl_gemm_tn_f32": "plplplipiiip",
     "efl_colsum": "ipliipipp",
+    "efl_colsum_static": "ipliipip",
     "efl_split3": "plliplii" "p",
     "efl_node_rows_pack": "piiiiipp",
     "efl_node_rows_unpack": "piiiippp",
@@ -128,7 +129,7 @@ def stream_ptr():
 
 
 # kernels launched per entry point (for the launch counter bench.py reports)
-_LAUNCHES = {"efl_csr_from_edge_index": 12, "efl_embedding_grad": 2, "efl_gemm_tn_f32": 2, "efl_colsum": 2, "efl_tc_gemm_tn": 2, "efl_so3_linear_bwd_weight": 2}
+_LAUNCHES = {"efl_csr_from_edge_index": 12, "efl_embedding_grad": 2, "efl_gemm_tn_f32": 2, "efl_colsum": 2, "efl_colsum_static": 2, "efl_tc_gemm_tn": 2, "efl_so3_linear_bwd_weight": 2}
 launch_count = 0
 _profile = None  # None, or a list receiving (name, work, start_event, end_event)
 _profile_only = None  # None = every entry point, or the set of names (tags) that get event pairs

@@ -364,3 +364,79 @@ extern "C" int efl_colsum(int bf16, const void* X, long long ld, int rows, int c
   EFL_CHECK_LAUNCH();
   return EFL_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Column sum for callers that cannot allocate device memory.
+//
+// efl_colsum needs (ceil(rows / 512) + 1) * cols floats of scratch for its per-block partial sums, and the caller has
+// to bring them.  Some callers have nowhere to get them from: code running inside a memory pool that is already
+// sized and frozen (a serving process after start-up, a plugin that was handed fixed buffers by its host program), or
+// code between cudaStreamBeginCapture and cudaStreamEndCapture, where cudaMalloc is an error.  For those the partial
+// sums live in the fixed array below, which is part of the library image: every GPU that loads libefl.so gives up
+// EFL_COLSUM_STATIC_MAX_FLOATS * 4 bytes (4 MiB) for it from module load until the process exits.
+//
+// `g_colsum_static` as written in HOST code is only the host-side handle of the symbol.  It is not a device address,
+// so it must never be handed to a kernel; the device address differs per GPU and is looked up with
+// cudaGetSymbolAddress while that GPU is current (colsum_static_scratch below), once per device.
+#include <cstdio>
+#include <mutex>
+
+constexpr long long kColsumStaticFloats = 1ll << 20;
+static __device__ __align__(256) float g_colsum_static[kColsumStaticFloats];
+
+// Device address of g_colsum_static on the CURRENT device.  The first call on a device asks the runtime for it and
+// keeps the answer; later calls only read the table.
+static int colsum_static_scratch(float** out) {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static float* addr[kMaxDevices] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    efl_set_error(cudaGetErrorString(e));
+    return (int)e;
+  }
+  EFL_REQUIRE(dev >= 0 && dev < kMaxDevices, "efl_colsum_static: device ordinal outside [0, 64)");
+  std::lock_guard<std::mutex> lock(mu);
+  if (addr[dev] == nullptr) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_colsum_static);
+    if (e != cudaSuccess || p == nullptr) {
+      efl_set_error(e != cudaSuccess ? cudaGetErrorString(e) : "efl_colsum_static: null address for the scratch symbol");
+      return e != cudaSuccess ? (int)e : EFL_ERR_ARG;
+    }
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return EFL_OK;
+}
+
+// Same result as efl_colsum (same kernels, same summation order, so bit-identical), without a workspace argument and
+// without any allocation: no cudaMalloc / cudaFree / allocating library call on this path.
+//   * Limit: (ceil(rows / 512) + 1) * cols <= EFL_COLSUM_STATIC_MAX_FLOATS (2^20); anything larger is refused with
+//     EFL_ERR_ARG and a message that names both numbers -- use efl_colsum with your own workspace then.
+//   * The first call on each device looks up the array's device address (a runtime query, not an allocation).  Make
+//     that first call with the right device current and before any stream capture begins.
+//   * `stream` must belong to the current device.
+//   * All calls on one GPU share the one array and it keeps whatever the last call left there.  The partial-sum
+//     kernel overwrites every slot the reduction reads, so nothing has to be cleared in between; but two calls whose
+//     kernels can run at the same time (different streams without an ordering between them) race on it.
+extern "C" int efl_colsum_static(int bf16, const void* X, long long ld, int rows, int cols, float* out,
+                                 int accumulate, void* stream) {
+  EFL_REQUIRE(rows >= 0 && cols >= 0, "efl_colsum_static: negative shape");
+  if (cols == 0) return EFL_OK;
+  const long long need = ((long long)(rows + 511) / 512 + 1) * (long long)cols;
+  if (need > kColsumStaticFloats) {
+    char msg[192];
+    snprintf(msg, sizeof msg,
+             "efl_colsum_static: needs %lld scratch floats, the built-in array holds %lld; call efl_colsum with a "
+             "caller-supplied workspace instead",
+             need, kColsumStaticFloats);
+    efl_set_error(msg);
+    return EFL_ERR_ARG;
+  }
+  float* scratch = nullptr;
+  const int rc = colsum_static_scratch(&scratch);
+  if (rc != EFL_OK) return rc;
+  return efl_colsum(bf16, X, ld, rows, cols, out, accumulate, scratch, stream);
+}
