@@ -11,6 +11,7 @@ from __future__ import annotations
 
 import ctypes
 import os
+import weakref
 from dataclasses import dataclass, field
 
 import numpy as np
@@ -427,6 +428,7 @@ class _Weights:
     ``t`` variants are the transposes the dgrad GEMMs take as their B operand."""
 
     _CACHE: dict = {}
+    BUILDS = 0  # derived-weight constructions so far (tests count cache misses with it)
 
     def __init__(self, conv_w, dtype, pad: int):
         W0, b0 = conv_w[0].detach(), conv_w[1].detach()
@@ -456,14 +458,30 @@ class _Weights:
         # with it the step's memory footprint) does not grow from step to step: a footprint that creeps makes the
         # caching allocator extend its pool in the middle of a step, a 0.5-0.9 s host stall on this box
         # (tools/step_trace.py)
+        #
+        # A slot is only valid for the very tensor objects it was derived from: it keeps weak references to them and a
+        # hit needs `ref() is w` for every one (plus equal version counters).  Address + version alone is NOT an
+        # identity: when a model is freed and the next one is built, the caching allocator hands the same blocks back
+        # and the same constructor sequence gives the same versions, so the new model would silently run with the old
+        # model's SO(2) weights (round-2 review; tests/test_host_logic.py::test_derived_weight_cache_*).  The reference
+        # reads its weights fresh on every call (EF_layers.py:807-875).  Writes through `p.data` do not bump
+        # `_version`; call ops.clear_derived_caches() after such a write.
         key = tuple(w.data_ptr() for w in conv_w) + (dtype, pad)
         ver = tuple(w._version for w in conv_w)
         hit = cls._CACHE.get(key)
-        if hit is None or hit[0] != ver:
+        if hit is None or hit[0] != ver or len(hit[2]) != len(conv_w) or any(r() is not w for r, w in zip(hit[2], conv_w)):
             if len(cls._CACHE) > 64:
                 cls._CACHE.clear()
-            hit = cls._CACHE[key] = (ver, cls(conv_w, dtype, pad))
+            cls.BUILDS += 1
+            hit = cls._CACHE[key] = (ver, cls(conv_w, dtype, pad), tuple(weakref.ref(w) for w in conv_w))
         return hit[1]
+
+
+def clear_derived_caches():
+    """Drop every derived-operand cache (GEMM-ready SO(2) weights, bf16 grid matrices).  Needed only after parameters
+    were overwritten behind autograd's back (``p.data.copy_``), which leaves the version counters unchanged."""
+    _Weights._CACHE.clear()
+    _GRID_OPERANDS.clear()
 
 
 def _combine_complex_wgrad(P):
@@ -772,6 +790,8 @@ def _grid_operands(to_g, from_g):
     F^T [LP, GP] (to_g / from_g are [G, L] fp32)."""
     key = (to_g.data_ptr(), to_g._version, from_g.data_ptr(), from_g._version, tuple(to_g.shape))
     hit = _GRID_OPERANDS.get(key)
+    if hit is not None and (hit[4]() is not to_g or hit[5]() is not from_g):
+        hit = None  # same address and version, another tensor: a freed model's block handed out again (see _Weights.get)
     if hit is None:
         G, L = to_g.shape
         GP, LP = _pad(G, 16), _pad(L, 16)
@@ -780,7 +800,8 @@ def _grid_operands(to_g, from_g):
             out = torch.zeros(r, c, dtype=torch.bfloat16, device=m.device)
             out[:m.shape[0], :m.shape[1]] = m
             return out
-        hit = (padded(to_g, GP, LP), padded(to_g.t(), LP, GP), padded(from_g, GP, LP), padded(from_g.t(), LP, GP))
+        hit = (padded(to_g, GP, LP), padded(to_g.t(), LP, GP), padded(from_g, GP, LP), padded(from_g.t(), LP, GP),
+               weakref.ref(to_g), weakref.ref(from_g))
         if len(_GRID_OPERANDS) > 32:
             _GRID_OPERANDS.clear()
         _GRID_OPERANDS[key] = hit
@@ -811,7 +832,7 @@ def _bf16_gemm(A, B, M, N, K):
 
 def _node_s2_gemm_forward(gate, x, to_g, from_g):
     N, L, CH = x.shape
-    Tb, _, _, FbT = _grid_operands(to_g, from_g)
+    Tb, _, _, FbT = _grid_operands(to_g, from_g)[:4]
     GP, LP = Tb.shape
     R = N * CH
     xt = _rows_from_nodes(x.contiguous().float(), LP)
@@ -824,7 +845,7 @@ def _node_s2_gemm_forward(gate, x, to_g, from_g):
 
 def _node_s2_gemm_backward(gate, xt, to_g, from_g, dy, shape):
     N, L, CH = shape
-    Tb, TbT, Fb, _ = _grid_operands(to_g, from_g)
+    Tb, TbT, Fb, _ = _grid_operands(to_g, from_g)[:4]
     GP, LP = Tb.shape
     R = N * CH
     dy = dy.contiguous().float()

@@ -173,6 +173,38 @@ def test_oracle_and_cuda_agree_on_synthetic_radius_graph():
         assert rel_err(out[k].embedding, ref[k]) < 2e-5, (k, rel_err(out[k].embedding, ref[k]))
 
 
+def test_second_model_in_one_process_uses_its_own_weights():
+    """Round-2 review, weak #1: model(seed A) runs and is freed, model(seed B) is built in the blocks the allocator
+    hands back and must run with ITS weights: both compared with the CPU oracle on their own state_dict, and the two
+    outputs must differ.  The reference reads its weights on every call (EF_layers.py:807-875)."""
+    import gc
+    from oracle import ef_oracle as eo
+    from singa_b200 import synthetic as syn
+    from singa_b200.embedding import DEFAULT_CONFIG
+    g = syn.make_complex(5, n_protein=40, n_ligand=9, cutoff=8.0)
+    rnd = syn.frame_randoms(g, 7)
+    frames = {}
+    for key, (s, d, ei) in dict(pp=("pos_p", "pos_p", "ei_pp"), ll=("pos_l", "pos_l", "ei_ll"),
+                                lp=("pos_l", "pos_p", "ei_lp")).items():
+        frames[key] = eo.edge_rot_mat(g[s][g[ei][0]] - g[d][g[ei][1]], rnd[key])
+    gd = {k: v.to(DEV) for k, v in g.items()}
+    fd = {k: v.to(DEV) for k, v in frames.items()}
+    outs = []
+    for seed in (3, 3, 8):
+        model = build_model(DEV, seed, "fp32")
+        out = model(syn.GraphView(gd), frames=fd)
+        p = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+        with torch.no_grad():
+            ref = eo.embedding_forward(p, g, frames, oracle_tables(), dict(DEFAULT_CONFIG))
+        for k in ref:
+            assert rel_err(out[k].embedding, ref[k]) < 2e-5, (seed, k, rel_err(out[k].embedding, ref[k]))
+        outs.append({k: v.embedding.detach().clone() for k, v in out.items()})
+        del model, out
+        gc.collect()
+    k0 = sorted(outs[0])[0]
+    assert rel_err(outs[0][k0], outs[1][k0]) < 1e-6 and rel_err(outs[2][k0], outs[1][k0]) > 1e-2
+
+
 TOL_OUT_BF16, TOL_GRAD_BF16 = 2e-2, 6e-2
 
 
