@@ -56,15 +56,25 @@ class GradientBuckets:
     optimiser's), forward, backward (buckets reduce as they complete), ``gb.finish()`` (waits; gradients are then
     the sum - or mean - over ranks on EVERY rank, also for a parameter this rank's shard gave no gradient), step.
 
-    Parameters that receive no gradient on any rank (``sphere_embedding*``: the int64 seed quirk, Embedding.py:262)
-    are found once, globally, after the first step and dropped from the buckets (``.grad`` None again), so every
-    rank agrees on the participating set.
+    Parameters that receive no gradient on any rank in the first step (``sphere_embedding*``: the int64 seed quirk,
+    Embedding.py:262) are found once, globally, and moved to a bucket of their own, ``idle``, which is reduced LAST and
+    only from ``finish()``, never from a hook.  They stay reduced every step (a few KB of zeros), so a parameter that
+    wakes up later on some rank (a data-dependent branch, a hetero edge set that was empty in step 1, an unfrozen
+    layer) is summed over the ranks like any other and the ranks cannot drift apart.  Their ``.grad`` is a view of
+    zeros rather than ``None``: with Adam and ``weight_decay=0`` (config/train.yml:207) the update of such a parameter
+    is exactly zero, as in the reference where the optimiser skips it; with weight decay it would decay.
+
+    One ``backward()`` per step is assumed when ``overlap`` is on: a bucket is reduced the moment its last gradient
+    arrives, and a gradient arriving for a bucket that was already reduced raises.  For gradient accumulation (several
+    backward passes per step) build with ``overlap=False``: everything is then reduced in ``finish()``.
     """
 
     def __init__(self, named_params: Iterable[Tuple[str, torch.nn.Parameter]], group=None, average: bool = True,
-                 bucket_of: Callable[[str], str] = _default_bucket_of):
+                 bucket_of: Callable[[str], str] = _default_bucket_of, overlap: bool = True):
         self.group = group
         self.average = average
+        self.overlap = overlap
+        self.idle: List[str] = []
         self._bucket_of = bucket_of
         self._named = [(n, p) for n, p in named_params if p.requires_grad]
         self._touched: Dict[int, bool] = {id(p): False for _, p in self._named}
@@ -101,7 +111,7 @@ class GradientBuckets:
         # backward completes them in: last block first, everything else last), never in completion order
         def rank_of(b):
             m = re.match(r"block(\d+)$", b.key)
-            return (0, -int(m.group(1))) if m else (1, 0)
+            return (0, -int(m.group(1))) if m else ((2, 0) if b.key == "idle" else (1, 0))
         self.buckets.sort(key=rank_of)
         self._next = 0
 
@@ -128,14 +138,18 @@ class GradientBuckets:
         b = self._owner.get(id(p))
         if b is None:
             return
+        if b.launched:
+            raise RuntimeError(
+                f"GradientBuckets: a gradient arrived for bucket '{b.key}' after its all-reduce was launched (a second "
+                "backward() in one step?).  Build GradientBuckets(..., overlap=False) to reduce everything in finish().")
         b.ready += 1
-        if self._settled:
+        if self._settled and self.overlap:
             self._launch_ready()
 
     def _launch_ready(self, force: bool = False) -> None:
         while self._next < len(self.buckets):
             b = self.buckets[self._next]
-            if not force and b.ready < len(b.named):
+            if not force and (b.ready != len(b.named) or b.key == "idle"):
                 return
             self._launch(b)
             self._next += 1
@@ -164,19 +178,21 @@ class GradientBuckets:
         if self._distributed():
             dist.all_reduce(flags, op=dist.ReduceOp.MAX, group=self.group)
         live = flags.cpu().tolist()
-        keep = [(n, p) for (n, p), f in zip(self._named, live) if f > 0]
-        dead = [(n, p) for (n, p), f in zip(self._named, live) if f <= 0]
+        dead = {id(p) for (n, p), f in zip(self._named, live) if f <= 0}
         self._settled = True
+        self.idle = [n for n, p in self._named if id(p) in dead]
         if dead:
-            saved = {id(p): p.grad.clone() for _, p in keep}
-            for _, p in dead:
-                p.grad = None
-            self._build(keep)
-            for _, p in keep:   # this step's (already reduced) gradients move to the rebuilt buckets
+            saved = {id(p): p.grad.clone() for _, p in self._named}
+            inner = self._bucket_of
+            self._bucket_of = lambda name, _idle=set(self.idle): "idle" if name in _idle else inner(name)
+            self._build(self._named)
+            for _, p in self._named:   # this step's (already reduced) gradients move to the rebuilt buckets
                 p.grad.copy_(saved[id(p)])
-            self.dropped = [n for n, _ in dead]
-        else:
-            self.dropped = []
+
+    @property
+    def dropped(self) -> List[str]:
+        """Round-2 name of ``idle`` (the parameters are no longer dropped from the reduction)."""
+        return self.idle
 
     # round-1 name, kept for callers that reduce after backward in one go
     def allreduce_(self) -> None:
@@ -194,6 +210,8 @@ class GradientBucket(GradientBuckets):
     def allreduce_(self, group=None, average: Optional[bool] = None) -> None:
         if average is not None:
             self.average = average
+        if group is not None:
+            self.group = group
         # callers of this interface may have replaced or dropped the gradient views (zero_grad(set_to_none=True)):
         # bring whatever is in p.grad into the bucket, zeros where this rank has no gradient
         for b in self.buckets:

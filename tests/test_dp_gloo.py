@@ -63,8 +63,8 @@ def test_two_rank_allreduce_matches_single_process(tmp_path):
     m = _model()
     sum(m(x).pow(2).sum() for x in xs).backward()
     for n, p in m.named_parameters():
-        if p.grad is None:
-            assert got[n] is None, n
+        if p.grad is None:   # never used anywhere: stays in the reduction as zeros (parallel.GradientBuckets, "idle")
+            assert not got[n].any(), n
         else:
             assert torch.allclose(got[n], p.grad, rtol=1e-5, atol=1e-6), n
 
@@ -110,12 +110,13 @@ def _worker_buckets(rank, world, port, out):
 def test_bucketed_overlapped_allreduce_with_a_rank_missing_a_gradient(tmp_path):
     """GradientBuckets: gradients live in per-block flat buffers, buckets reduce in a fixed order as backward
     completes them; a parameter without a gradient on ONE rank (``side`` on rank 0) still ends with the summed
-    gradient on every rank, and a parameter without a gradient on ANY rank is dropped globally."""
+    gradient on every rank, and a parameter without a gradient on ANY rank moves to the ``idle`` bucket,
+    reduced last, with a zero gradient on every rank (it is no longer dropped from the reduction)."""
     out = str(tmp_path / "gb.pt")
     mp.spawn(_worker_buckets, args=(2, _free_port(), out), nprocs=2, join=True)
     r0, r1 = torch.load(out + ".0"), torch.load(out + ".1")
     assert r0["dropped"] == ["unused"] and r1["dropped"] == ["unused"]
-    assert r0["keys"] == ["block1", "block0", "rest"]
+    assert r0["keys"] == ["block1", "block0", "rest", "idle"]
     sizes, xs = _data()
     shards = shard_by_edges(sizes, 2)
     m = _TwoBlock()
@@ -124,10 +125,80 @@ def test_bucketed_overlapped_allreduce_with_a_rank_missing_a_gradient(tmp_path):
         for n, p in m.named_parameters():
             a, b = r0["steps"][step][n], r1["steps"][step][n]
             if n == "unused":
-                assert a is None and b is None
+                assert not a.any() and not b.any()
                 continue
             assert torch.equal(a, b), (step, n)          # every rank holds the same reduced gradient
             assert torch.allclose(a, p.grad, rtol=1e-5, atol=1e-6), (step, n)
+
+
+def _worker_late_parameter(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sizes, xs = _data()
+    mine = shard_by_edges(sizes, world)[rank]
+    m = _TwoBlock()
+    gb = GradientBuckets(m.named_parameters(), average=False)
+    steps = []
+    for step in range(4):          # ``side`` is used by nobody in steps 0-1 and wakes up on rank 1 only in step 2
+        gb.zero_grad()
+        sum(m(xs[i], use_side=(rank == 1 and step >= 2)) for i in mine).backward()
+        gb.finish()
+        steps.append({n: p.grad.clone() for n, p in m.named_parameters()})
+    # gradient accumulation: two backward passes in one step need overlap=False; with overlap on the second one raises
+    gb.zero_grad()
+    sum(m(xs[i], False) for i in mine).backward()
+    try:
+        sum(m(xs[i], False) for i in mine).backward()
+        raised = False
+    except RuntimeError as e:
+        raised = "overlap=False" in str(e)
+    gb.finish()
+    for h in gb._hooks:
+        h.remove()
+    for p in m.parameters():
+        p.grad = None
+    gb2 = GradientBuckets(m.named_parameters(), average=False, overlap=False)
+    acc = []
+    for step in range(2):
+        gb2.zero_grad()
+        for _ in range(2):
+            sum(m(xs[i], rank == 1) for i in mine).backward()
+        gb2.finish()
+        acc.append({n: p.grad.clone() for n, p in m.named_parameters()})
+    torch.save(dict(steps=steps, idle=gb.idle, raised=raised, acc=acc), out + f".{rank}")
+    dist.destroy_process_group()
+
+
+def test_parameter_that_wakes_up_after_the_first_step_is_still_reduced(tmp_path):
+    """a parameter with no gradient anywhere in step 0 used to be dropped for good; when it later got a
+    gradient on one rank it was never all-reduced and the ranks diverged.  It now lives in the ``idle`` bucket, which
+    is reduced from finish() every step.  Also: a second backward() in a step raises under overlap, and
+    overlap=False sums both passes."""
+    out = str(tmp_path / "late.pt")
+    mp.spawn(_worker_late_parameter, args=(2, _free_port(), out), nprocs=2, join=True)
+    r0, r1 = torch.load(out + ".0"), torch.load(out + ".1")
+    assert sorted(r0["idle"]) == ["side.bias", "side.weight", "unused"] == sorted(r1["idle"])
+    assert r0["raised"] and r1["raised"]
+    sizes, xs = _data()
+    shards = shard_by_edges(sizes, 2)
+    for step in range(4):
+        m = _TwoBlock()
+        (sum(m(xs[i], False) for i in shards[0]) + sum(m(xs[i], step >= 2) for i in shards[1])).backward()
+        for n, p in m.named_parameters():
+            a, b = r0["steps"][step][n], r1["steps"][step][n]
+            assert torch.equal(a, b), (step, n)
+            want = torch.zeros_like(p) if p.grad is None else p.grad
+            assert torch.allclose(a, want, rtol=1e-5, atol=1e-6), (step, n)
+    assert bool(r0["steps"][2]["side.weight"].any())
+    m = _TwoBlock()
+    (2 * sum(m(xs[i], False) for i in shards[0]) + 2 * sum(m(xs[i], True) for i in shards[1])).backward()
+    for step in range(2):
+        for n, p in m.named_parameters():
+            a, b = r0["acc"][step][n], r1["acc"][step][n]
+            assert torch.equal(a, b), (step, n)
+            want = torch.zeros_like(p) if p.grad is None else p.grad
+            assert torch.allclose(a, want, rtol=1e-5, atol=1e-6), (step, n)
 
 
 def _settle_worker(rank, world, port, out):
