@@ -380,7 +380,9 @@ def config3(args):
                        "complexes_per_gpu": gb // world, "complexes_per_s": gb / (ms * 1e-3), "loss": float(loss),
                        "dense_transformer": "PyTorch library ops (out of scope for kernels, SURVEY.md 2 #5)",
                        "parameters": sum(p.numel() for p in model.parameters()),
-                       "edge_count": "EF_layers edges (edge-layers computed / 3) of the global batch"},
+                       "edge_count": "EF_layers edges (edge-layers computed / 3) of the global batch",
+                       "sharding": "equal complexes per rank, edges balanced within that (parallel.shard_by_edges "
+                                   "equal_counts=True); unshuffled, so every step is the same global batch"},
             "e2e": {"value": tot / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": hb.nbytes, "d2h_bytes_per_step": 0,
                     "note": "the timed step itself copies its pinned host batch (one buffer) to the device"},
             "gpu_launches": launches, "clocks": clocks,
@@ -590,7 +592,7 @@ def main():
         step_tflops = 36.0e6 * tot_edges * LAYERS / world / (ms_dev * 1e-3) / 1e12
         line = {
             "metric": METRIC, "value": tot_edges / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": warm_done, "ms_per_step": ms_dev, "higher_is_better": True, "scaling": args.scaling,
+            "warmup": args.warmup, "warmup_done": warm_done, "ms_per_step": ms_dev, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": {"bf16": "bf16", "bf16x3": "bf16x3 (error-compensated bf16 operands, fp32 storage)"}.get(
                 args.precision, "f32"), "data": "synthetic",
             "config": {"workload": WORKLOAD if args.scaling == "weak" else

@@ -218,30 +218,42 @@ def to_dense_batch(x, batch, batch_size: int, max_nodes: int):
     return dense.view(batch_size, max_nodes, -1), mask.view(batch_size, max_nodes)
 
 
-def laplacian_pe(edge_index: np.ndarray, num_nodes: int, k: int, rng: Optional[np.random.RandomState] = None):
-    """``dgl.lap_pe(g, k)`` (dgl 1.1, un-vendored; reference CProMG.py:562-571): the k eigenvectors after the first of
-    the symmetric normalised Laplacian I - D^-1/2 A D^-1/2 (A = adjacency of the given directed edge list, D = in-degree
-    clipped at 1), ascending eigenvalue, each multiplied by a random sign; zero-padded when the graph has <= k nodes.
+def laplacian_pe(edge_index: np.ndarray, num_nodes: int, k: int, rng: Optional[np.random.RandomState] = None,
+                 random_sign: bool = True):
+    """``dgl.lap_pe(g, k)`` (dgl 1.1, un-vendored: parity unpinned; reference CProMG.py:562-571): the k eigenvectors
+    after the first of I - D^-1/2 A D^-1/2, ascending eigenvalue, each multiplied by a random sign; zero-padded when the
+    graph has <= k nodes.  As in dgl, A is ``adj_external()``: rows = SOURCE, columns = destination of the directed
+    edge list, and D = in-degree clipped at 1 (column sums of A).  On a symmetric edge list the orientation does not
+    matter; on a neighbour-capped radius graph it does (round 2 had A transposed: same spectrum, other eigenvectors).
+    ``random_sign=False`` returns the eigenvectors as LAPACK orients them (what ``LapPECache`` stores).
     Host code on purpose: an O(n^3) eigendecomposition of a ~450-node graph does not belong on the step."""
     A = np.zeros((num_nodes, num_nodes), dtype=np.float64)
-    A[edge_index[1], edge_index[0]] = 1.0                      # dgl adjacency: A[dst, src]
-    deg = np.clip(A.sum(axis=1), 1.0, None) ** -0.5
+    A[edge_index[0], edge_index[1]] = 1.0                      # dgl adj_external: A[src, dst]
+    deg = np.clip(A.sum(axis=0), 1.0, None) ** -0.5            # in-degrees
     L = np.eye(num_nodes) - deg[:, None] * A * deg[None, :]
     val, vec = np.linalg.eig(L)
     order = np.argsort(val.real, kind="stable")
     take = order[1:k + 1]
     pe = np.real(vec[:, take])
-    rng = rng or np.random
-    pe = pe * (2.0 * (rng.rand(pe.shape[1]) > 0.5) - 1.0)
+    if random_sign:
+        pe = pe * random_signs(pe.shape[1], rng)
     if pe.shape[1] < k:
         pe = np.concatenate((pe, np.zeros((num_nodes, k - pe.shape[1]))), axis=1)
     return pe.astype(np.float32)
 
 
+def random_signs(k: int, rng=None) -> np.ndarray:
+    """dgl's draw: ``2 * (np.random.rand(k) > 0.5) - 1`` -- one sign per eigenvector column."""
+    rng = rng or np.random
+    return (2.0 * (rng.rand(k) > 0.5) - 1.0).astype(np.float32)
+
+
 class LapPECache:
-    """Laplacian positional encodings, computed once per complex (keyed by the caller's complex id) instead of on
-    every forward.  ``get`` returns the cached [n, k] array; ``singa_b200.dataset`` stores it in the
-    on-disk record so that even the first epoch pays nothing."""
+    """Laplacian eigenvectors, computed once per complex (keyed by the caller's complex id) instead of on every
+    forward.  The cache (and the on-disk record of ``singa_b200.dataset``) holds them WITHOUT the
+    random signs: the reference draws fresh signs on every forward (dgl.lap_pe inside GAN.py:70,77 -- a
+    sign-invariance augmentation), so the signs are applied per step by whoever hands the encodings to the model
+    (``dataset.collate_records(..., lap_sign_rng=...)``, ``lap_pe`` below), not frozen with the eigenvectors."""
 
     def __init__(self, k: int = 8, seed: int = 0):
         self.k, self.seed, self._store = k, seed, {}
@@ -253,9 +265,7 @@ class LapPECache:
             self.hits += 1
             return hit
         self.misses += 1
-        import zlib
-        rng = np.random.RandomState((self.seed * 1000003 + zlib.crc32(repr(key).encode())) % (2 ** 32))
-        pe = laplacian_pe(edge_index, num_nodes, self.k, rng)
+        pe = laplacian_pe(edge_index, num_nodes, self.k, random_sign=False)
         self._store[key] = pe
         return pe
 
@@ -267,7 +277,8 @@ def lap_pe(data, node_type: str):
     """Signature of the reference's ``lap_pe(data, node_type)`` (CProMG.py:562-571), for ``GAN.py`` running on this
     module: the encodings carried by the batch (``data[node_type]['lap']``, dataset format) when present; otherwise
     computed per complex on the host from ``ptr`` and the ``linked_to`` edges and cached on the complexes' positions
-    (the reference decomposes the whole batched graph on every call: DESIGN.md section 8, f-3)."""
+    (the reference decomposes the whole batched graph on every call: DESIGN.md section 8, f-3).  Every call draws fresh
+    random signs per complex and column from ``np.random``, as dgl does per call."""
     assert node_type in ('protein_atoms', 'ligand_atoms'), "Node type not accepted"
     store = data[node_type]
     have = store.get('lap') if hasattr(store, 'get') else None
@@ -282,7 +293,7 @@ def lap_pe(data, node_type: str):
     for a, b in zip(bounds[:-1], bounds[1:]):
         m = (ei[1] >= a) & (ei[1] < b)
         key = (node_type, b - a, pos_h[a:b].tobytes())
-        out.append(_LAP_CACHE.get(key, ei[:, m] - a, b - a))
+        out.append(_LAP_CACHE.get(key, ei[:, m] - a, b - a) * random_signs(_LAP_CACHE.k))
     return torch.from_numpy(np.concatenate(out, axis=0)).to(pos.device)
 
 
@@ -436,14 +447,21 @@ class PrebuiltGraph:
     CSR of the undirected part (row degrees) and the centre-sorted CSR of the whole list (registered for the
     attention layers).  No search, sort or host read on the step."""
 
-    def __init__(self, edge_index, num_und: int, und_csr, lap_csr):
+    def __init__(self, edge_index, num_und: int, und_csr, lap_csr, k: Optional[int] = None):
         self.edge_index, self.num_und, self.und_csr, self.lap_csr = edge_index, num_und, und_csr, lap_csr
+        self.k = k    # the k of the kNN search the graph was built with (None: unknown, trusted)
         _csr_cache_put((id(edge_index), edge_index._version, lap_csr.num_dst), edge_index, lap_csr)
 
 
 class _GraphEncoderBase(nn.Module):
     def _graph(self, pos, batch, k, prebuilt: Optional[PrebuiltGraph] = None):
         n = pos.size(0)
+        if prebuilt is not None and prebuilt.k is not None and prebuilt.k != k:
+            # the record's graph was searched with another k than this encoder is configured for: do not train on it
+            import warnings
+            warnings.warn(f"prebuilt encoder graph has k={prebuilt.k}, the encoder wants k={k}: "
+                          "building the graph on the device instead", stacklevel=2)
+            prebuilt = None
         if prebuilt is not None:
             ei = prebuilt.edge_index
             row, col = ei[0, :prebuilt.num_und], ei[1, :prebuilt.num_und]

@@ -101,6 +101,9 @@ def pack_complex(g: Dict[str, torch.Tensor], ligand_data: Optional[Dict] = None,
         s, d = _NODE_OF[k]
         for name, arr in _csr_fields(npy["ei_" + k], n[s], n[d], k in SORTED_KEYS).items():
             rec[f"{k}_{name}"] = arr
+    if lap_cache is not None and key is None:
+        raise ValueError("pack_complex: a shared lap_cache needs a per-complex key (key=None would return the first "
+                         "complex's encodings for every complex)")
     cache = lap_cache or LapPECache(lap_k)
     rec["lap_p"] = cache.get((key, "p"), npy["ei_pp"], n["p"])
     rec["lap_l"] = cache.get((key, "l"), npy["ei_ll"], n["l"])
@@ -108,6 +111,7 @@ def pack_complex(g: Dict[str, torch.Tensor], ligand_data: Optional[Dict] = None,
         for prefix, side, k in ENCODER_GRAPHS:
             for name, arr in _encoder_graph_fields(rec["pos_" + side], k).items():
                 rec[f"{prefix}_{name}"] = arr
+            rec[f"{prefix}_k"] = np.int32(k)   # checked against the encoder's knn when the graph is used
     if ligand_data is not None:
         for name in LIGAND_SCALARS:
             rec[name] = np.float32(ligand_data[name])
@@ -244,19 +248,29 @@ class DeviceBatch:
                 ident = torch.arange(E, dtype=torch.int32, device=ei.device)
                 und = ops.EdgeCSR(N, N, E, ident, t[f"{prefix}_und_rowptr"], ei32[1, :E].contiguous(),
                                   ei32[0, :E].contiguous(), ei32[0, :E].contiguous(), t[f"{prefix}_und_rowptr"], ident)
+                und.dst_only = True    # src_ptr / src_idx above are placeholders: segment_sum never reads them
                 lap = ops.EdgeCSR(N, N, E + N, t[f"{prefix}_perm"], t[f"{prefix}_rowptr"], t[f"{prefix}_ssrc"],
                                   t[f"{prefix}_sdst"], ei32[0].contiguous(), t[f"{prefix}_srcptr"], t[f"{prefix}_srcidx"])
-                enc[role] = PrebuiltGraph(ei, E, und, lap)
+                enc[role] = PrebuiltGraph(ei, E, und, lap, k=m.get(f"{prefix}_k"))
             g["enc_graphs"] = enc
             self._graph = g
         return self._graph
 
 
-def collate_records(recs: List[Dict[str, np.ndarray]], pin: bool = True) -> HostBatch:
+def collate_records(recs: List[Dict[str, np.ndarray]], pin: bool = True, lap_sign_rng=None) -> HostBatch:
+    """``lap_sign_rng`` (a numpy RandomState): multiply every complex's stored Laplacian eigenvectors by a fresh random
+    sign per column, the draw dgl.lap_pe makes on each forward of the reference (GAN.py:70,77; cpromg.random_signs).
+    None leaves the stored orientation (deterministic tests and benches)."""
     a = _Arena()
     cat = lambda name: np.concatenate([r[name] for r in recs])
-    for name in ("z_p", "z_l", "bits_p", "bits_l", "pos_p", "pos_l", "lap_p", "lap_l"):
+    for name in ("z_p", "z_l", "bits_p", "bits_l", "pos_p", "pos_l"):
         a.add(name, cat(name))
+    for name in ("lap_p", "lap_l"):
+        if lap_sign_rng is None:
+            a.add(name, cat(name))
+        else:
+            from .cpromg import random_signs
+            a.add(name, np.concatenate([r[name] * random_signs(r[name].shape[1], lap_sign_rng) for r in recs]))
     n = {"p": np.array([len(r["z_p"]) for r in recs]), "l": np.array([len(r["z_l"]) for r in recs])}
     off = {s: np.concatenate(([0], np.cumsum(v))) for s, v in n.items()}
     a.add("ptr_p", off["p"].astype(np.int32))
@@ -304,6 +318,9 @@ def collate_records(recs: List[Dict[str, np.ndarray]], pin: bool = True) -> Host
         for name in ("ssrc", "sdst"):
             a.add(f"{prefix}_{name}", np.concatenate([r[f"{prefix}_{name}"] + off[side][i] for i, r in enumerate(recs)]).astype(np.int32))
         meta[f"{prefix}_und_edges"] = E
+        ks = {int(r.get(f"{prefix}_k", _k)) for r in recs}   # records written before the field existed used the default
+        assert len(ks) == 1, f"records of one batch carry encoder graphs built with different k: {sorted(ks)}"
+        meta[f"{prefix}_k"] = ks.pop()
     if "smi_in" in recs[0]:
         for name in LIGAND_SCALARS:
             a.add(name, np.array([r[name] for r in recs], dtype=np.float32))
@@ -317,8 +334,10 @@ class BatchLoader:
     iterator (and its state) lives as long as the loader.  ``indices`` = this rank's shard (parallel.shard_by_edges)."""
 
     def __init__(self, dataset: ComplexDataset, batch_size: int, indices: Optional[Iterable[int]] = None,
-                 shuffle: bool = True, seed: int = 0, pin: bool = True, prefetch: int = 0):
+                 shuffle: bool = True, seed: int = 0, pin: bool = True, prefetch: int = 0, lap_sign: bool = True):
         self.ds, self.bs, self.shuffle, self.pin = dataset, batch_size, shuffle, pin
+        # fresh Laplacian-eigenvector signs per batch (the reference's per-forward dgl draw), from a seeded stream
+        self.sign_rng = np.random.RandomState((seed + 0x5151) % (2 ** 32)) if lap_sign else None
         self.indices = list(range(len(dataset))) if indices is None else list(indices)
         self.rng = np.random.RandomState(seed)
         self._order, self._pos = [], 0
@@ -347,7 +366,7 @@ class BatchLoader:
                 self._pos = 0
             take.append(self._order[self._pos])
             self._pos += 1
-        return collate_records([self.ds[i] for i in take], self.pin)
+        return collate_records([self.ds[i] for i in take], self.pin, self.sign_rng)
 
 
 def synthetic_records(seeds: Iterable[int], tgt_len: int = 200, vocab: int = 116, pad: int = 110, n_protein=None):

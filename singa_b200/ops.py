@@ -163,6 +163,7 @@ class EdgeCSR:
     src_idx: torch.Tensor     # int32 [E]  sorted positions grouped by source (stable)
     chunks: list = field(default_factory=list)  # (n0, n1, e0, e1), edges of whole destinations
     aux: dict = field(default_factory=dict)     # lazily derived index vectors (int64 copies, composite groupings)
+    dst_only: bool = False    # True: src_ptr / src_idx are placeholders (segment sums over destinations only)
 
     def index(self, name: str) -> torch.Tensor:
         """int64 index vectors for torch gathers: 'perm', 'dst_orig', 'src_orig' (original edge order) and
@@ -177,6 +178,8 @@ class EdgeCSR:
                 hit = torch.empty_like(self.index("perm"))
                 hit[self.index("perm")] = self.src_sorted.long()
             elif name == "src_group":
+                if self.dst_only:
+                    raise ValueError("this EdgeCSR carries no source-side grouping (built for segment sums only)")
                 hit = self.perm.index_select(0, self.src_idx.long()).contiguous()   # int32
             else:
                 raise KeyError(name)

@@ -21,14 +21,18 @@ import torch
 import torch.distributed as dist
 
 
-def shard_by_edges(edge_counts: Sequence[int], world_size: int) -> List[List[int]]:
+def shard_by_edges(edge_counts: Sequence[int], world_size: int, equal_counts: bool = False) -> List[List[int]]:
     """Greedy longest-processing-time assignment of complexes to ranks, balancing EDGE counts
-    (per-complex cost is proportional to edges, not atoms).  Deterministic; returns index lists."""
+    (per-complex cost is proportional to edges, not atoms).  Deterministic; returns index lists.
+    ``equal_counts``: no rank takes more than ceil(n / world_size) complexes (edges balanced within that), so a
+    loader that draws a fixed number of complexes per rank and step walks every shard at the same pace and one
+    step is one global batch."""
     order = sorted(range(len(edge_counts)), key=lambda i: (-edge_counts[i], i))
     loads = [0] * world_size
     shards: List[List[int]] = [[] for _ in range(world_size)]
+    cap = -(-len(edge_counts) // world_size) if equal_counts else len(edge_counts)
     for i in order:
-        r = min(range(world_size), key=lambda k: (loads[k], k))
+        r = min((k for k in range(world_size) if len(shards[k]) < cap), key=lambda k: (loads[k], k))
         shards[r].append(i)
         loads[r] += edge_counts[i]
     return [sorted(s) for s in shards]

@@ -27,7 +27,10 @@ class Trainer:
         self.device = device or next(model.parameters()).device
         world = dist.get_world_size() if dist.is_initialized() else 1
         rank = dist.get_rank() if dist.is_initialized() else 0
-        shard = shard_by_edges(dataset.edge_counts(), world)[rank] if world > 1 else list(range(len(dataset)))
+        # equal complex counts per rank: every rank draws batch_size_per_rank per step, so shards of unequal length
+        # would wrap around at different steps and a step would not be one global batch
+        shard = (shard_by_edges(dataset.edge_counts(), world, equal_counts=True)[rank] if world > 1
+                 else list(range(len(dataset))))
         self.loader = BatchLoader(dataset, batch_size_per_rank, indices=shard, seed=seed + rank, shuffle=shuffle,
                                   prefetch=prefetch)
         self.criterion = torch.nn.CrossEntropyLoss()

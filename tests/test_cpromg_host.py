@@ -120,8 +120,9 @@ def test_laplacian_pe_is_an_eigenbasis_and_is_cached():
     pe = cache.get(("c", 3), ei, n)
     assert pe.shape == (n, 8) and cache.misses == 1
     assert cache.get(("c", 3), ei, n) is pe and cache.hits == 1
-    A = np.zeros((n, n)); A[ei[1], ei[0]] = 1
-    d = np.clip(A.sum(1), 1, None) ** -0.5
+    A = np.zeros((n, n)); A[ei[0], ei[1]] = 1          # dgl adj_external: rows = source
+    assert np.array_equal(A, A.T)                      # this radius graph is symmetric: orientation-free check
+    d = np.clip(A.sum(0), 1, None) ** -0.5
     L = np.eye(n) - d[:, None] * A * d[None, :]
     val = np.sort(np.linalg.eigvalsh(L))
     for j in range(8):
@@ -131,6 +132,47 @@ def test_laplacian_pe_is_an_eigenbasis_and_is_cached():
     assert np.allclose(pe.T @ pe, np.eye(8), atol=1e-4)
     small = cp.laplacian_pe(np.array([[0, 1], [1, 0]]), 2, 8)       # fewer nodes than k: zero padded
     assert small.shape == (2, 8) and np.all(small[:, 1:] == 0)
+    # the cache holds the eigenvectors WITHOUT the random signs; a signed draw only flips whole columns
+    signed = cp.laplacian_pe(ei, n, 8, np.random.RandomState(5))
+    flips = (signed * pe).sum(0)
+    assert np.allclose(np.abs(signed), np.abs(pe), atol=1e-6) and np.allclose(np.abs(flips), 1.0, atol=1e-4)
+    assert (flips < 0).any() and (flips > 0).any()
+
+
+def test_laplacian_pe_orientation_follows_dgl_on_an_asymmetric_graph():
+    """dgl.lap_pe builds L from adj_external() (rows = source) and in-degrees.  On a directed 4-node graph the
+    columns must be right eigenvectors of THAT matrix, not of its transpose (round-2 advisor finding)."""
+    ei = np.array([[0, 0, 1, 2, 3, 3], [1, 2, 2, 3, 0, 1]])
+    n = 4
+    A = np.zeros((n, n)); A[ei[0], ei[1]] = 1
+    d = np.clip(A.sum(0), 1, None) ** -0.5
+    L = np.eye(n) - d[:, None] * A * d[None, :]
+    val, vec = np.linalg.eig(L)
+    order = np.argsort(val.real, kind="stable")
+    pe = cp.laplacian_pe(ei, n, 2, random_sign=False)
+    assert np.allclose(pe, np.real(vec[:, order[1:3]]).astype(np.float32), atol=1e-6)
+    assert not np.allclose(np.abs(pe), np.abs(np.real(np.linalg.eig(L.T)[1][:, np.argsort(np.linalg.eig(L.T)[0].real, kind="stable")[1:3]])), atol=1e-3)
+
+
+def test_collation_draws_fresh_eigenvector_signs_per_batch_when_asked():
+    from singa_b200 import dataset as ds
+    recs = ds.synthetic_records([1, 2], n_protein=30)
+    plain = ds.collate_records(recs, pin=False)
+    assert np.array_equal(plain.arena.views(plain.host)["lap_p"].numpy(), np.concatenate([r["lap_p"] for r in recs]))
+    rng = np.random.RandomState(3)
+    seen = set()
+    for _ in range(6):
+        b = ds.collate_records(recs, pin=False, lap_sign_rng=rng)
+        lap = b.arena.views(b.host)["lap_p"].numpy()
+        n0 = len(recs[0]["lap_p"])
+        for part, rec in ((lap[:n0], recs[0]), (lap[n0:], recs[1])):
+            assert np.array_equal(np.abs(part), np.abs(rec["lap_p"]))
+            col = np.argmax(np.abs(rec["lap_p"]), axis=0)
+            seen.add(tuple(np.sign(part[col, range(8)] * rec["lap_p"][col, range(8)]).astype(int)))
+    assert len(seen) > 3      # signs differ between complexes and between batches
+    import pytest
+    with pytest.raises(ValueError):
+        ds.pack_complex(syn.make_complex(1, n_protein=20, n_ligand=6), lap_cache=cp.LapPECache(8))
 
 
 def test_lap_pe_reference_signature_uses_batch_encodings_or_caches_per_complex():
@@ -143,7 +185,8 @@ def test_lap_pe_reference_signature_uses_batch_encodings_or_caches_per_complex()
     # per complex (not the batched graph), up to the cached random signs
     assert np.allclose(np.abs(pe[30:].numpy()), np.abs(one), atol=1e-5)
     misses = cp._LAP_CACHE.misses
-    assert torch.equal(cp.lap_pe(view, "protein_atoms"), pe) and cp._LAP_CACHE.misses == misses
+    again = cp.lap_pe(view, "protein_atoms")     # same cached eigenvectors, fresh random signs (as dgl per call)
+    assert torch.equal(again.abs(), pe.abs()) and cp._LAP_CACHE.misses == misses
     carried = dict(b, lap_p=torch.zeros(55, 8))
     assert cp.lap_pe(syn.GraphView(carried), "protein_atoms") is carried["lap_p"]
 

@@ -94,9 +94,33 @@ def test_encoder_graphs_in_the_record_equal_the_on_the_fly_construction():
         lap_ei, _ = co.get_laplacian(ei, attr.unsqueeze(1), num_nodes=n)
         assert torch.equal(t[prefix + "_ei"].long(), lap_ei), prefix
         assert hb.meta[prefix + "_und_edges"] == ei.shape[1]
+        assert hb.meta[prefix + "_k"] == k and int(recs[0][prefix + "_k"]) == k   # checked by the encoder on use
         ref = eo.csr_from_edge_index(lap_ei.flip(0), n, n)
         for a, b in (("perm", "perm"), ("rowptr", "rowptr"), ("ssrc", "src_sorted"), ("sdst", "dst_sorted"),
                      ("srcptr", "src_ptr"), ("srcidx", "src_idx")):
             assert np.array_equal(t[f"{prefix}_{a}"].numpy(), ref[b]), (prefix, a)
         und_rowptr = np.concatenate(([0], np.cumsum(np.bincount(ei[0].numpy(), minlength=n))))
         assert np.array_equal(t[prefix + "_und_rowptr"].numpy(), und_rowptr)
+
+
+def test_prebuilt_encoder_graph_declares_its_k_and_its_destination_only_csr(tmp_path):
+    """the record's encoder graphs are built with a fixed k; the batch carries that k so an encoder
+    configured with another knn falls back to the device search instead of silently training on the record's graph,
+    and a record round-trips the field through np.savez.  The undirected-part CSR is marked destination-only."""
+    import pytest
+    from singa_b200 import ops
+    recs = [ds.pack_complex(syn.make_complex(s, n_protein=30, n_ligand=8), key=s) for s in range(2)]
+    ds.save_record(str(tmp_path / "r.npz"), recs[0])
+    back = ds.load_record(str(tmp_path / "r.npz"))
+    assert int(back["ga_k"]) == 48 and int(back["gl_k"]) == 30
+    old = [{k: v for k, v in r.items() if not k.endswith("_k")} for r in recs]      # records from before the field
+    assert ds.collate_records(old, pin=False).meta["ga_k"] == 48
+    mixed = [dict(recs[0]), dict(recs[1], ga_k=np.int32(16))]
+    with pytest.raises(AssertionError):
+        ds.collate_records(mixed, pin=False)
+    i32 = lambda *v: torch.tensor(v, dtype=torch.int32)
+    csr = ops.EdgeCSR(2, 2, 2, i32(0, 1), i32(0, 1, 2), i32(1, 0), i32(0, 1), i32(0, 1), i32(0, 1, 2), i32(0, 1),
+                      dst_only=True)
+    assert csr.index("dst_orig").dtype == torch.int64
+    with pytest.raises(ValueError):
+        csr.index("src_group")

@@ -53,6 +53,12 @@ def test_shards_are_balanced_and_complete():
     loads = [sum(sizes[i] for i in s) for s in shards]
     assert max(loads) - min(loads) <= max(sizes)
     assert shard_by_edges(sizes, 3) == shards  # deterministic
+    # equal counts per rank (what the Trainer uses): 8 complexes over 4 ranks = 2 each, whatever the edge counts
+    sizes = [100, 1, 1, 1, 1, 1, 1, 50]
+    assert sorted(len(s) for s in shard_by_edges(sizes, 4)) != [2, 2, 2, 2]
+    eq = shard_by_edges(sizes, 4, equal_counts=True)
+    assert [len(s) for s in eq] == [2, 2, 2, 2] and sorted(i for s in eq for i in s) == list(range(8))
+    assert [len(s) for s in shard_by_edges([3, 2, 1], 2, equal_counts=True)] == [1, 2]   # cap = ceil(3 / 2)
 
 
 def test_two_rank_allreduce_matches_single_process(tmp_path):
