@@ -240,27 +240,82 @@ def parity_against_port(model, graph, outs_ref, grads_ref, dev):
             "against": "oracle/ef_oracle.py (CPU port, fp32) on the cpu_baseline sample, same parameters/frames/loss"}
 
 
+def run_cpu_reference(graph, steps: int, warmup: int, state=None, keep=False):
+    """fwd+bwd of the UNMODIFIED reference ``EquivariantEmbedding`` (model/Embedding.py:205-480 over model/EF_layers.py,
+    loaded by oracle/ref_loader.py from /root/reference or the build-time copy in oracle/_ref) on all host threads: the
+    reference's stock path, every block of every pass included.  Same parameters (portable seed 0), edge frames
+    (the rand_like draws of init_edge_rot_mat are fed from synthetic.frame_randoms seed 1) and loss as run_cpu_port."""
+    from oracle import ref_loader as rl
+    from singa_b200 import synthetic as syn
+    ef, emb = rl.load_reference()
+    torch.set_num_threads(os.cpu_count() or 1)
+    torch.manual_seed(0)
+    ref = emb.EquivariantEmbedding(rl.EasyDict(rl.DEFAULT_EMBEDDING_CONFIG), device="cpu")
+    if state is None:
+        syn.load_portable_parameters(ref, 0)
+    else:   # the B200 modules keep the reference's state_dict surface: strict load
+        ref.load_state_dict({k: v.detach().cpu() for k, v in state.items()}, strict=True)
+    rnd = syn.frame_randoms(graph, 1)
+    Rp, Rl = loss_weights(graph)
+    times, out = [], None
+    orig = torch.rand_like
+    try:
+        for it in range(warmup + steps):
+            ref.zero_grad(set_to_none=True)
+            draws = iter([rnd["pp"], rnd["ll"], rnd["lp"]])
+            torch.rand_like = lambda x, **k: next(draws)
+            t0 = time.perf_counter()
+            out = ref(syn.GraphView(graph))
+            loss = (out[syn.PROTEIN].embedding * Rp).sum() + (out[syn.LIGAND].embedding * Rl).sum()
+            loss.backward()
+            dt = time.perf_counter() - t0
+            if it >= warmup:
+                times.append(dt)
+    finally:
+        torch.rand_like = orig
+    sec = float(np.mean(times))
+    if keep:
+        return (sec, {k: v.embedding.detach() for k, v in out.items()},
+                {n: p.grad for n, p in ref.named_parameters() if p.grad is not None})
+    return sec
+
+
+def reference_kind() -> str:
+    """"reference": the unmodified reference files are on this machine (/root/reference or oracle/_ref); else "port"."""
+    from oracle import ref_loader as rl
+    return "reference" if rl.reference_available() else "port"
+
+
 def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     graph, n = cpu_sample_graph(REF_SAMPLE_ATOMS)
     edges = metric_edges(graph)
-    sec = run_cpu_port(graph, args.steps, args.warmup)
-    val = edges / sec
+    kind = reference_kind()
     cores = os.cpu_count() or 1
+    what = ("UNMODIFIED reference EquivariantEmbedding (model/Embedding.py + model/EF_layers.py via oracle/ref_loader.py, "
+            "e3nn / torch_geometric symbols from the loader's shims; all blocks of all passes, the stock path)"
+            if kind == "reference" else "CPU port of the reference (oracle/ef_oracle.py; reference files not on this machine)")
+    sec = run_cpu_reference(graph, args.steps, args.warmup) if kind == "reference" else run_cpu_port(graph, args.steps, args.warmup)
+    val = edges / sec
     sample = (f"FIXED sample: synthetic complex seed 0 cut to {n} protein + 24 ligand atoms, {count_edges(graph)} edges "
-              f"({count_edge_layers(graph)} edge-layers), 8 A radius graph; CPU port of the reference (oracle/ef_oracle.py), "
-              f"fp32, {cores} threads")
-    emit({
+              f"({count_edge_layers(graph)} edge-layers), 8 A radius graph; {what}, fp32, {cores} threads")
+    line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "sample": sample},
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-    })
+    }
+    if kind == "reference":   # once, beside it: the port on the same sample, to show the two agree
+        psec = run_cpu_port(graph, 1, 1)
+        line["cpu_baseline"]["port_value"] = edges / psec
+        line["cpu_baseline"]["port_note"] = ("oracle/ef_oracle.py on the same sample (skips the hetero passes' dead blocks, "
+                                             "so it does less work than the stock reference path)")
+    emit(line)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -401,6 +456,13 @@ def config5(args):
     import stress_bench
     a = types.SimpleNamespace(atoms=args.atoms or 8000, complexes=1, lmax=8, steps=args.steps,
                               warmup=max(args.warmup, 2), precision=args.precision, profile=True)
+    # clocks and throttle reasons DURING the timed region, on rank 0's GPU (round 2's config-5 lines had none)
+    rank0 = int(os.environ.get("RANK", "0")) == 0
+    sampler = ClockSampler(int(os.environ.get("LOCAL_RANK", "0")))
+    clocks = {}
+    if rank0:
+        sampler.start()
+        a.timed_region_hooks = (sampler.mark, lambda: clocks.update(sampler.stop()))
     r = stress_bench.run(a)
     if r is None:
         return
@@ -414,7 +476,8 @@ def config5(args):
                      "edge_count": "all four edge sets, as given (hetero edges counted once)"},
           "e2e": {"value": r["edges_total"] / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                   "note": "graph built on the device by the radius-graph kernel outside the timed region; inputs resident"},
-          "gpu_launches": r["gpu_launches_per_step"] * args.steps, "kernel_ms_per_step": r["kernel_ms_per_step"]})
+          "gpu_launches": r["gpu_launches_per_step"] * args.steps, "clocks": clocks or None,
+          "kernel_ms_per_step": r["kernel_ms_per_step"]})
 
 
 def main():
@@ -618,14 +681,19 @@ def main():
             # CPU port on ONE full config-2-sized complex, with the model's current parameters; the same complex then
             # goes through the CUDA path in the benchmarked precision: measured parity at config-2 size in every run
             graph, n = cpu_sample_graph(PARITY_SAMPLE_ATOMS)
-            sec, outs_ref, grads_ref = run_cpu_port(graph, 1, 0, state=model.state_dict(), keep=True)
+            kind = reference_kind()
+            run = run_cpu_reference if kind == "reference" else run_cpu_port
+            sec, outs_ref, grads_ref = run(graph, 1, 0, state=model.state_dict(), keep=True)
             e = metric_edges(graph)
             line["cpu_baseline"] = {
-                "value": e / sec, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
+                "value": e / sec, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": kind,
                 "sample": f"one synthetic complex (seed 0) with {n} protein + 24 ligand atoms, {count_edges(graph)} "
                           f"edges ({count_edge_layers(graph)} edge-layers), fwd+bwd once, {sec:.1f} s"}
             line["parity"] = parity_against_port(model, graph, outs_ref, grads_ref, dev)
             line["parity"]["precision"] = args.precision
+            if kind == "reference":
+                line["parity"]["against"] = ("the UNMODIFIED reference EquivariantEmbedding on the host (oracle/ref_loader.py), "
+                                             "fp32, on the cpu_baseline sample, same parameters/frames/loss")
         emit(line)
     if world > 1:
         dist.destroy_process_group()

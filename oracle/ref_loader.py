@@ -1,7 +1,8 @@
 """TEST INFRASTRUCTURE ONLY -- loads the UNMODIFIED reference model/EF_layers.py
 and model/Embedding.py from /root/reference on CPU.
 
-Only usable where /root/reference exists (the build container).  Used by
+Usable where /root/reference exists (the build container) or where oracle/_ref/ holds the build-time copy of the
+path's three files (the GPU box; see REFERENCE_ROOT below).  Used by bench.py's reference arm / cpu_baseline, by
 oracle/make_golden.py to generate tests/golden/*.pt and by the not-gpu tests to
 pin oracle/ef_oracle.py (the travelling restatement) against the real code.
 Nothing in singa_b200/ may import this file.
@@ -35,7 +36,24 @@ import types
 import numpy as np
 import torch
 
-REFERENCE_ROOT = os.environ.get("SINGA_REFERENCE_ROOT", "/root/reference")
+# Where the unmodified reference files are read from: /root/reference in the build container; on the GPU box, which
+# has no /root/reference, the three files of the path that __graft_entry__.build_oracle_ref() copied (unchanged, at
+# build time, never committed) into the git-ignored oracle/_ref/ -- they travel with the snapshot like libefl.so does.
+_SHIPPED_ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+REFERENCE_FILES = ("model/EF_layers.py", "model/Embedding.py", "model/Jd.pt")
+
+
+def _pick_root() -> str:
+    env = os.environ.get("SINGA_REFERENCE_ROOT")
+    if env:
+        return env
+    for root in ("/root/reference", _SHIPPED_ROOT):
+        if os.path.isfile(os.path.join(root, "model", "EF_layers.py")):
+            return root
+    return "/root/reference"
+
+
+REFERENCE_ROOT = _pick_root()
 
 
 def reference_available() -> bool:

@@ -69,7 +69,8 @@ class GradientBuckets:
     is exactly zero, as in the reference where the optimiser skips it; with weight decay it would decay.
 
     One ``backward()`` per step is assumed when ``overlap`` is on: a bucket is reduced the moment its last gradient
-    arrives, and a gradient arriving for a bucket that was already reduced raises.  For gradient accumulation (several
+    arrives, and a gradient arriving for a bucket that was already reduced in the same step raises (a backward after
+    ``finish()`` and before the next ``zero_grad()`` is outside the cycle and left alone).  For gradient accumulation (several
     backward passes per step) build with ``overlap=False``: everything is then reduced in ``finish()``.
     """
 
@@ -79,6 +80,7 @@ class GradientBuckets:
         self.average = average
         self.overlap = overlap
         self.idle: List[str] = []
+        self._open = True     # inside a zero_grad() ... finish() cycle (hooks outside one are ignored)
         self._bucket_of = bucket_of
         self._named = [(n, p) for n, p in named_params if p.requires_grad]
         self._touched: Dict[int, bool] = {id(p): False for _, p in self._named}
@@ -127,6 +129,7 @@ class GradientBuckets:
 
     # -- per step ------------------------------------------------------------------------------
     def zero_grad(self) -> None:
+        self._open = True
         for b in self.buckets:
             b.flat.zero_()
             b.ready, b.handle, b.launched = 0, None, False
@@ -140,8 +143,8 @@ class GradientBuckets:
     def _on_grad(self, p) -> None:
         self._touched[id(p)] = True
         b = self._owner.get(id(p))
-        if b is None:
-            return
+        if b is None or not self._open:
+            return   # a backward outside zero_grad() ... finish() (an evaluation pass, a parity probe) is not reduced
         if b.launched:
             raise RuntimeError(
                 f"GradientBuckets: a gradient arrived for bucket '{b.key}' after its all-reduce was launched (a second "
@@ -175,6 +178,7 @@ class GradientBuckets:
                 b.flat.div_(dist.get_world_size(self.group))
         if not self._settled:
             self._settle()
+        self._open = False
 
     def _settle(self) -> None:
         flags = torch.tensor([1.0 if self._touched[id(p)] else 0.0 for _, p in self._named],

@@ -160,6 +160,7 @@ def _worker_late_parameter(rank, world, port, out):
     except RuntimeError as e:
         raised = "overlap=False" in str(e)
     gb.finish()
+    sum(m(xs[i], False) for i in mine).backward()      # after finish(): outside the cycle, neither reduced nor an error
     for h in gb._hooks:
         h.remove()
     for p in m.parameters():

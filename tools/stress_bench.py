@@ -123,11 +123,16 @@ def run(args):
     n0 = _lib.launch_count
     if args.profile:
         _lib.start_profile()
+    hooks = getattr(args, "timed_region_hooks", None)   # (on_start, on_stop): bench.py's nvidia-smi clock sampler
+    if hooks:
+        hooks[0]()
     a.record()
     for _ in range(args.steps):
         loss = step()
     b.record()
     torch.cuda.synchronize()
+    if hooks:
+        hooks[1]()
     prof = _lib.stop_profile() if args.profile else {}
     ms = torch.tensor([a.elapsed_time(b) / args.steps], device=dev)
     tot = torch.tensor([float(edges)], device=dev)
